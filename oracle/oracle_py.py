@@ -1,0 +1,268 @@
+"""ctypes binding of the CPU ORACLE (oracle/liborb_oracle.so).
+
+TEST INFRASTRUCTURE, NOT PRODUCT: only tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py may import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build(force=False):
+    if force or not os.path.exists(_LIB_PATH):
+        subprocess.check_call(["make", "-C", _HERE, "liborb_oracle.so"] + (["-B"] if force else []))
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB_PATH)
+        vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+        L.orbo_create.restype = vp
+        L.orbo_create.argtypes = [i, f, i, i, i]
+        L.orbo_destroy.argtypes = [vp]
+        L.orbo_set_modes.argtypes = [vp, i, i]
+        L.orbo_extract.restype = i
+        L.orbo_extract.argtypes = [vp, vp, i, i, sz, vp, vp, i]
+        L.orbo_scale_tables.argtypes = [vp, vp, vp, vp, vp]
+        L.orbo_features_per_level.argtypes = [vp, vp]
+        L.orbo_umax.argtypes = [vp, vp]
+        L.orbo_level_size.argtypes = [vp, i, vp, vp]
+        L.orbo_level_padded.argtypes = [vp, i, vp]
+        L.orbo_level_blurred.argtypes = [vp, i, vp]
+        L.orbo_level_candidates.restype = i
+        L.orbo_level_candidates.argtypes = [vp, i, vp, i]
+        L.orbo_level_nkeys.restype = i
+        L.orbo_level_nkeys.argtypes = [vp, i]
+        L.orbo_stage_seconds.argtypes = [vp, vp]
+        L.orbo_resize_linear_u8.argtypes = [vp, i, i, sz, vp, i, i, sz]
+        L.orbo_border_reflect101.argtypes = [vp, i, i, sz, vp, i, sz]
+        L.orbo_gauss7.argtypes = [vp, i, i, sz, vp, sz]
+        L.orbo_fast.restype = i
+        L.orbo_fast.argtypes = [vp, i, i, sz, i, i, vp, i]
+        L.orbo_fast_atan2.restype = f
+        L.orbo_fast_atan2.argtypes = [f, f]
+        L.orbo_distribute.restype = i
+        L.orbo_distribute.argtypes = [vp, i, i, i, i, i, i, i, vp, i]
+        L.orbo_descriptor_distance.restype = i
+        L.orbo_descriptor_distance.argtypes = [vp, vp]
+        L.orbo_match_bruteforce.argtypes = [vp, i, vp, i, vp, vp, vp]
+        L.orbo_match_candidates.argtypes = [vp, i, vp, i, vp, vp, vp, vp, vp, vp]
+        L.orbo_grid_build.restype = vp
+        L.orbo_grid_build.argtypes = [vp, i, f, f, f, f]
+        L.orbo_grid_destroy.argtypes = [vp]
+        L.orbo_grid_query.restype = i
+        L.orbo_grid_query.argtypes = [vp, vp, f, f, f, i, i, vp, i]
+        L.orbo_search_for_initialization.restype = i
+        L.orbo_search_for_initialization.argtypes = [vp, vp, i, vp, vp, i, f, f, f, f, vp, vp, i, f, i]
+        L.orbo_stereo_matches.restype = i
+        L.orbo_stereo_matches.argtypes = [vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, f, f, f, vp, vp]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+class OracleExtractor:
+    """Mirror of ORB_SLAM2::ORBextractor (include/ORBextractor.h:45-111) over the CPU oracle."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, tie_mode=0, fma_mode=0):
+        self.L = lib()
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self.h = self.L.orbo_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+        self.L.orbo_set_modes(self.h, tie_mode, fma_mode)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orbo_destroy(self.h)
+            self.h = None
+
+    def set_modes(self, tie_mode=0, fma_mode=0):
+        self.L.orbo_set_modes(self.h, tie_mode, fma_mode)
+
+    def __call__(self, img):
+        img = _u8(img)
+        hh, ww = img.shape
+        cap = max(4 * self.nfeatures + 64 * self.nlevels, 1024)
+        kps = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        n = self.L.orbo_extract(self.h, _p(img), ww, hh, img.strides[0], _p(kps), _p(desc), cap)
+        assert n <= cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def scale_tables(self):
+        out = [np.zeros(self.nlevels, dtype=np.float32) for _ in range(4)]
+        self.L.orbo_scale_tables(self.h, *[_p(o) for o in out])
+        return out
+
+    def features_per_level(self):
+        o = np.zeros(self.nlevels, dtype=np.int32)
+        self.L.orbo_features_per_level(self.h, _p(o))
+        return o
+
+    def umax(self):
+        o = np.zeros(16, dtype=np.int32)
+        self.L.orbo_umax(self.h, _p(o))
+        return o
+
+    def level_size(self, l):
+        w, h = C.c_int(), C.c_int()
+        self.L.orbo_level_size(self.h, l, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level_padded(self, l):
+        w, h = self.level_size(l)
+        o = np.zeros((h + 38, w + 38), dtype=np.uint8)
+        self.L.orbo_level_padded(self.h, l, _p(o))
+        return o
+
+    def level_blurred(self, l):
+        w, h = self.level_size(l)
+        o = np.zeros((h, w), dtype=np.uint8)
+        self.L.orbo_level_blurred(self.h, l, _p(o))
+        return o
+
+    def level_candidates(self, l):
+        n = self.L.orbo_level_candidates(self.h, l, None, 0)
+        o = np.zeros((max(n, 1), 3), dtype=np.int32)
+        self.L.orbo_level_candidates(self.h, l, _p(o), n)
+        return o[:n]
+
+    def level_nkeys(self, l):
+        return self.L.orbo_level_nkeys(self.h, l)
+
+    def stage_seconds(self):
+        o = np.zeros(6, dtype=np.float64)
+        self.L.orbo_stage_seconds(self.h, _p(o))
+        return o
+
+
+def resize_linear(src, dw, dh):
+    src = _u8(src)
+    dst = np.zeros((dh, dw), dtype=np.uint8)
+    lib().orbo_resize_linear_u8(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def border_reflect101(src, b):
+    src = _u8(src)
+    h, w = src.shape
+    dst = np.zeros((h + 2 * b, w + 2 * b), dtype=np.uint8)
+    lib().orbo_border_reflect101(_p(src), w, h, src.strides[0], _p(dst), b, w + 2 * b)
+    return dst
+
+
+def gauss7(src):
+    src = _u8(src)
+    h, w = src.shape
+    dst = np.zeros((h, w), dtype=np.uint8)
+    lib().orbo_gauss7(_p(src), w, h, src.strides[0], _p(dst), w)
+    return dst
+
+
+def fast(roi, threshold, nms=True):
+    """roi may be a non-contiguous 2-D view (row stride honoured)."""
+    assert roi.dtype == np.uint8 and roi.strides[1] == 1
+    h, w = roi.shape
+    cap = w * h
+    o = np.zeros((max(cap, 1), 3), dtype=np.int32)
+    n = lib().orbo_fast(_p(roi), w, h, roi.strides[0], threshold, int(nms), _p(o), cap)
+    return o[:n]
+
+
+def fast_atan2(y, x):
+    return lib().orbo_fast_atan2(float(y), float(x))
+
+
+def distribute(xyr, minX, maxX, minY, maxY, N, tie_mode=0):
+    xyr = np.ascontiguousarray(xyr, dtype=np.int32)
+    n = len(xyr)
+    out = np.zeros(max(n, 1), dtype=np.int32)
+    m = lib().orbo_distribute(_p(xyr), n, minX, maxX, minY, maxY, N, tie_mode, _p(out), n)
+    return out[:m]
+
+
+def descriptor_distance(a, b):
+    a, b = _u8(a), _u8(b)
+    return lib().orbo_descriptor_distance(_p(a), _p(b))
+
+
+def match_bruteforce(q, t):
+    q, t = _u8(q), _u8(t)
+    nq, nt = len(q), len(t)
+    bi = np.zeros(nq, np.int32); bd = np.zeros(nq, np.int32); sd = np.zeros(nq, np.int32)
+    lib().orbo_match_bruteforce(_p(q), nq, _p(t), nt, _p(bi), _p(bd), _p(sd))
+    return bi, bd, sd
+
+
+def match_candidates(q, t, off, idx):
+    q, t = _u8(q), _u8(t)
+    off = np.ascontiguousarray(off, np.int32); idx = np.ascontiguousarray(idx, np.int32)
+    nq = len(q)
+    bi = np.zeros(nq, np.int32); bd = np.zeros(nq, np.int32); si = np.zeros(nq, np.int32); sd = np.zeros(nq, np.int32)
+    lib().orbo_match_candidates(_p(q), nq, _p(t), len(t), _p(off), _p(idx), _p(bi), _p(bd), _p(si), _p(sd))
+    return bi, bd, si, sd
+
+
+def grid_query_all(kps, queries, r, minLevel, maxLevel, bounds):
+    """GetFeaturesInArea for every (x, y) in queries -> CSR (off, idx)."""
+    kps = np.ascontiguousarray(kps)
+    G = lib().orbo_grid_build(_p(kps), len(kps), *[float(b) for b in bounds])
+    off = [0]
+    idx = []
+    buf = np.zeros(max(len(kps), 1), np.int32)
+    for (x, y) in queries:
+        n = lib().orbo_grid_query(G, _p(kps), float(x), float(y), float(r), minLevel, maxLevel, _p(buf), len(buf))
+        idx.append(buf[:n].copy())
+        off.append(off[-1] + n)
+    lib().orbo_grid_destroy(G)
+    return np.asarray(off, np.int32), (np.concatenate(idx) if idx else np.zeros(0, np.int32)).astype(np.int32)
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_matched, windowSize=100, nnratio=0.9, checkOri=True):
+    k1 = np.ascontiguousarray(k1); k2 = np.ascontiguousarray(k2)
+    d1, d2 = _u8(d1), _u8(d2)
+    prev = np.ascontiguousarray(prev_matched, dtype=np.float32).copy()
+    m12 = np.zeros(len(k1), np.int32)
+    n = lib().orbo_search_for_initialization(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2),
+                                             *[float(b) for b in bounds], _p(prev), _p(m12), windowSize, nnratio, int(checkOri))
+    return n, m12, prev
+
+
+def stereo_matches(kl, dl, kr, dr, pyrL, pyrR, sf, isf, bf, maxD, minD=0.0):
+    """pyrL/pyrR: lists of 2-D uint8 arrays (level interiors, any row stride)."""
+    kl = np.ascontiguousarray(kl); kr = np.ascontiguousarray(kr)
+    dl, dr = _u8(dl), _u8(dr)
+    nl = len(pyrL)
+    PL = (C.c_void_p * nl)(*[p.ctypes.data for p in pyrL])
+    PR = (C.c_void_p * nl)(*[p.ctypes.data for p in pyrR])
+    lw = np.array([p.shape[1] for p in pyrL], np.int32)
+    lh = np.array([p.shape[0] for p in pyrL], np.int32)
+    sL = np.array([p.strides[0] for p in pyrL], np.uint64)
+    sR = np.array([p.strides[0] for p in pyrR], np.uint64)
+    sf = np.ascontiguousarray(sf, np.float32); isf = np.ascontiguousarray(isf, np.float32)
+    uR = np.zeros(len(kl), np.float32); dep = np.zeros(len(kl), np.float32)
+    n = lib().orbo_stereo_matches(_p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), PL, PR, _p(lw), _p(lh), _p(sL), _p(sR),
+                                  _p(sf), _p(isf), nl, bf, minD, maxD, _p(uR), _p(dep))
+    return n, uR, dep

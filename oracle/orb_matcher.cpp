@@ -1,0 +1,288 @@
+// orb_matcher.cpp -- CPU ORACLE (test infrastructure, not product).
+// Restatement of ORBmatcher::DescriptorDistance (ORBmatcher.cc:1649-1665), the best/second-best inner
+// loop shared by the SearchBy* routines (e.g. ORBmatcher.cc:205-230, 84-110), the Frame grid
+// (Frame.cc:230-245, 342-407), ORBmatcher::SearchForInitialization (ORBmatcher.cc:405-520) with
+// ComputeThreeMaxima (:1603-1644), and Frame::ComputeStereoMatches (Frame.cc:481-655).
+#include "orb_oracle.h"
+#include "orb_internal.h"
+#include <climits>
+#include <cstring>
+#include <algorithm>
+#include <utility>
+
+namespace orbo {
+
+// 8 x (xor + SWAR popcount) on 32-bit words.
+int descriptor_distance(const uint8_t* a, const uint8_t* b)
+{
+    int dist = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t wa, wb;
+        std::memcpy(&wa, a + 4 * i, 4);
+        std::memcpy(&wb, b + 4 * i, 4);
+        uint32_t v = wa ^ wb;
+        v = v - ((v >> 1) & 0x55555555u);
+        v = (v & 0x33333333u) + ((v >> 2) & 0x33333333u);
+        dist += (int)((((v + (v >> 4)) & 0x0F0F0F0Fu) * 0x01010101u) >> 24);
+    }
+    return dist;
+}
+
+static const int GRID_COLS = 64, GRID_ROWS = 48;   // Frame.h:37-38
+static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // ORBmatcher.cc:37-39
+
+struct Grid {
+    float minX, minY, invW, invH;
+    std::vector<int> cell[GRID_COLS][GRID_ROWS];
+};
+
+static void three_maxima(std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+} // namespace orbo
+
+struct orbo_grid { orbo::Grid g; };
+
+extern "C" {
+
+int orbo_descriptor_distance(const uint8_t* a, const uint8_t* b) { return orbo::descriptor_distance(a, b); }
+
+void orbo_match_bruteforce(const uint8_t* q, int nq, const uint8_t* t, int nt, int* best_idx, int* best_dist, int* second_dist)
+{
+    for (int i = 0; i < nq; i++) {
+        int b1 = 256, b2 = 256, bi = -1;
+        for (int j = 0; j < nt; j++) {
+            int d = orbo::descriptor_distance(q + 32 * (size_t)i, t + 32 * (size_t)j);
+            if (d < b1) { b2 = b1; b1 = d; bi = j; }
+            else if (d < b2) { b2 = d; }
+        }
+        best_idx[i] = bi; best_dist[i] = b1; second_dist[i] = b2;
+    }
+}
+
+void orbo_match_candidates(const uint8_t* q, int nq, const uint8_t* t, int nt, const int* off, const int* idx,
+                           int* best_idx, int* best_dist, int* second_idx, int* second_dist)
+{
+    (void)nt;
+    for (int i = 0; i < nq; i++) {
+        int b1 = 256, b2 = 256, bi = -1, si = -1;
+        for (int c = off[i]; c < off[i + 1]; c++) {
+            int j = idx[c];
+            int d = orbo::descriptor_distance(q + 32 * (size_t)i, t + 32 * (size_t)j);
+            if (d < b1) { b2 = b1; si = bi; b1 = d; bi = j; }
+            else if (d < b2) { b2 = d; si = j; }
+        }
+        best_idx[i] = bi; best_dist[i] = b1; second_idx[i] = si; second_dist[i] = b2;
+    }
+}
+
+orbo_grid* orbo_grid_build(const orbo_kp* kps, int n, float minX, float maxX, float minY, float maxY)
+{
+    orbo_grid* G = new orbo_grid;
+    G->g.minX = minX; G->g.minY = minY;
+    G->g.invW = static_cast<float>(orbo::GRID_COLS) / static_cast<float>(maxX - minX);   // Frame.cc ctor
+    G->g.invH = static_cast<float>(orbo::GRID_ROWS) / static_cast<float>(maxY - minY);
+    for (int i = 0; i < n; i++) {
+        int px = (int)std::round((kps[i].x - minX) * G->g.invW);     // PosInGrid, Frame.cc:397-407
+        int py = (int)std::round((kps[i].y - minY) * G->g.invH);
+        if (px < 0 || px >= orbo::GRID_COLS || py < 0 || py >= orbo::GRID_ROWS) continue;
+        G->g.cell[px][py].push_back(i);
+    }
+    return G;
+}
+void orbo_grid_destroy(orbo_grid* g) { delete g; }
+
+static void grid_query(const orbo::Grid& g, const orbo_kp* kps, float x, float y, float r, int minLevel, int maxLevel, std::vector<int>& out)
+{
+    using namespace orbo;
+    out.clear();
+    const int nMinCellX = std::max(0, (int)std::floor((x - g.minX - r) * g.invW));
+    if (nMinCellX >= GRID_COLS) return;
+    const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - g.minX + r) * g.invW));
+    if (nMaxCellX < 0) return;
+    const int nMinCellY = std::max(0, (int)std::floor((y - g.minY - r) * g.invH));
+    if (nMinCellY >= GRID_ROWS) return;
+    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - g.minY + r) * g.invH));
+    if (nMaxCellY < 0) return;
+    const bool checkLevels = (minLevel > 0) || (maxLevel >= 0);
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+            for (int id : g.cell[ix][iy]) {
+                const orbo_kp& kp = kps[id];
+                if (checkLevels) {
+                    if (kp.octave < minLevel) continue;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                }
+                const float dx = kp.x - x, dy = kp.y - y;
+                if (std::fabs(dx) < r && std::fabs(dy) < r) out.push_back(id);
+            }
+}
+
+int orbo_grid_query(const orbo_grid* G, const orbo_kp* kps, float x, float y, float r, int minLevel, int maxLevel, int* out, int cap)
+{
+    std::vector<int> v;
+    grid_query(G->g, kps, x, y, r, minLevel, maxLevel, v);
+    for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];
+    return (int)v.size();
+}
+
+int orbo_search_for_initialization(const orbo_kp* k1, const uint8_t* d1, int n1, const orbo_kp* k2, const uint8_t* d2, int n2,
+                                   float minX, float maxX, float minY, float maxY,
+                                   float* prev, int* m12, int windowSize, float nnratio, int checkOri)
+{
+    using namespace orbo;
+    int nmatches = 0;
+    for (int i = 0; i < n1; i++) m12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> matchedDist(n2, INT_MAX), m21(n2, -1);
+    orbo_grid* G = orbo_grid_build(k2, n2, minX, maxX, minY, maxY);
+    std::vector<int> cand;
+    for (int i1 = 0; i1 < n1; i1++) {
+        const int level1 = k1[i1].octave;
+        if (level1 > 0) continue;
+        grid_query(G->g, k2, prev[2 * i1], prev[2 * i1 + 1], (float)windowSize, level1, level1, cand);
+        if (cand.empty()) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : cand) {
+            int dist = descriptor_distance(d1 + 32 * (size_t)i1, d2 + 32 * (size_t)i2);
+            if (matchedDist[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (m21[bestIdx2] >= 0) { m12[m21[bestIdx2]] = -1; nmatches--; }
+                m12[i1] = bestIdx2; m21[bestIdx2] = i1; matchedDist[bestIdx2] = bestDist; nmatches++;
+                if (checkOri) {
+                    float rot = k1[i1].angle - k2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    orbo_grid_destroy(G);
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i]) if (m12[idx1] >= 0) { m12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)
+        if (m12[i1] >= 0) { prev[2 * i1] = k2[m12[i1]].x; prev[2 * i1 + 1] = k2[m12[i1]].y; }
+    return nmatches;
+}
+
+int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl, const orbo_kp* kr, const uint8_t* dr, int nr,
+                        const uint8_t* const* pyrL, const uint8_t* const* pyrR, const int* lw, const int* lh,
+                        const size_t* strideL, const size_t* strideR,
+                        const float* sf, const float* isf, int nlevels, float bf, float minD, float maxD,
+                        float* uRight, float* depth)
+{
+    using namespace orbo;
+    (void)nlevels; (void)lh;
+    for (int i = 0; i < nl; i++) { uRight[i] = -1.0f; depth[i] = -1.0f; }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const int nRows = lh[0];
+    std::vector<std::vector<int>> rows(nRows);
+    for (int iR = 0; iR < nr; iR++) {
+        const float kpY = kr[iR].y;
+        const float r = 2.0f * sf[kr[iR].octave];
+        const int maxr = (int)std::ceil(kpY + r), minr = (int)std::floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < nRows) rows[yi].push_back(iR);     // the reference indexes unchecked; in range for real keypoints
+    }
+    std::vector<std::pair<int, int>> distIdx;
+    for (int iL = 0; iL < nl; iL++) {
+        const orbo_kp& kpL = kl[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y, uL = kpL.x;
+        const int row = (int)vL;
+        if (row < 0 || row >= nRows) continue;
+        const std::vector<int>& cand = rows[row];
+        if (cand.empty()) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        int bestIdxR = 0;
+        for (int iR : cand) {
+            const orbo_kp& kpR = kr[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = descriptor_distance(dl + 32 * (size_t)iL, dr + 32 * (size_t)iR);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            const float uR0 = kr[bestIdxR].x;
+            const float scaleFactor = isf[kpL.octave];
+            const float scaleduL = std::round(kpL.x * scaleFactor);
+            const float scaledvL = std::round(kpL.y * scaleFactor);
+            const float scaleduR0 = std::round(uR0 * scaleFactor);
+            const int w = 5, L = 5;
+            const int lev = kpL.octave;
+            const uint8_t* IL = pyrL[lev];
+            const uint8_t* IR = pyrR[lev];
+            const int cu = (int)scaleduL, cv = (int)scaledvL, cr = (int)scaleduR0;
+            int bestSad = INT_MAX, bestincR = 0;
+            float vDists[2 * 5 + 1];
+            const float iniu = scaleduR0 + L - w;
+            const float endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= lw[lev]) continue;
+            const float cL = (float)IL[(size_t)cv * strideL[lev] + cu];
+            for (int incR = -L; incR <= +L; incR++) {
+                const float cR = (float)IR[(size_t)cv * strideR[lev] + cr + incR];
+                double acc = 0;
+                for (int dy = -w; dy <= w; dy++)
+                    for (int dx = -w; dx <= w; dx++) {
+                        float a = (float)IL[(size_t)(cv + dy) * strideL[lev] + cu + dx] - cL;
+                        float b = (float)IR[(size_t)(cv + dy) * strideR[lev] + cr + incR + dx] - cR;
+                        acc += std::fabs(a - b);
+                    }
+                float dist = (float)acc;
+                if (dist < bestSad) { bestSad = (int)dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = sf[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+                depth[iL] = bf / disparity;
+                uRight[iL] = bestuR;
+                distIdx.push_back(std::make_pair(bestSad, iL));
+            }
+        }
+    }
+    if (distIdx.empty()) return 0;        // the reference reads vDistIdx[0] of an empty vector here (Frame.cc:642)
+    std::sort(distIdx.begin(), distIdx.end());
+    const float median = (float)distIdx[distIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    int kept = (int)distIdx.size();
+    for (int i = (int)distIdx.size() - 1; i >= 0; i--) {
+        if (distIdx[i].first < thDist) break;
+        uRight[distIdx[i].second] = -1; depth[distIdx[i].second] = -1; kept--;
+    }
+    return kept;
+}
+
+} // extern "C"
