@@ -1,0 +1,191 @@
+/* orbx.h -- C ABI of liborbx.so: the sm_100a CUDA implementation of ORB-SLAM2's data-parallel front end.
+ *
+ * This is the drop-in boundary.  Everything above it (include/ORBextractor.h,
+ * include/ORBmatcher.h, the Python ctypes mirror in orb_slam2v2-1_b200/orbx) only forwards to these entry
+ * points; everything below it is hand-written CUDA.  There is NO CPU fallback: every compute entry point
+ * returns ORBX_ERR_CUDA when no device is usable.
+ *
+ * Conventions: plain C types only; every function returns an int status (0 = ORBX_OK) unless stated;
+ * no exception crosses the ABI; the text of the last failure of the calling thread is orbx_last_error().
+ * One extractor handle owns one CUDA stream and one device workspace: calls on DIFFERENT handles may run
+ * concurrently from different host threads (the reference extracts left/right images on two std::threads,
+ * reference src/Frame.cc:78-81); one handle must not be used from two threads at once (the reference's
+ * ORBextractor is not re-entrant either: it mutates mvImagePyramid, src/ORBextractor.cc:1107-1132).
+ *
+ * Reference citations are relative to kimwin2/ORB_SLAM2v2-1.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    ORBX_OK = 0,
+    ORBX_ERR_ARG = 1,      /* bad argument (null pointer, non-positive size, unsupported shape) */
+    ORBX_ERR_CUDA = 2,     /* CUDA runtime failure, including "no device" */
+    ORBX_ERR_CAPACITY = 3, /* caller's output buffer too small; *n still receives the true count */
+    ORBX_ERR_STATE = 4     /* call order violated (e.g. fetch before extract) */
+};
+
+/* Same field order and size (28 bytes) as cv::KeyPoint {pt.x, pt.y, size, angle, response, octave, class_id}. */
+typedef struct orbx_kp {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbx_kp;
+
+typedef struct orbx_extractor orbx_extractor;
+
+/* ---------------------------------------------------------------------------------------------------------
+ * ORBextractor  (reference include/ORBextractor.h:45-111, src/ORBextractor.cc)
+ * ------------------------------------------------------------------------------------------------------- */
+
+/* Replaces ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * (src/ORBextractor.cc:410-470).  device = CUDA ordinal.  max_batch = largest number of frames one call will
+ * carry (workspace is sized for it at the first call of each image shape). */
+int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                int device, int max_batch, orbx_extractor** out);
+void orbx_destroy(orbx_extractor* ex);
+
+/* descriptor rotation arithmetic of computeOrbDescriptor (src/ORBextractor.cc:119-120):
+ * 0 = each product and sum rounded separately (portable definition, default),
+ * 1 = FMA-contracted the way g++ -O3 -march=native compiles the reference on an FMA host. */
+int orbx_set_fma_mode(orbx_extractor* ex, int fma_mode);
+
+/* Replaces the by-value accessors GetLevels / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares (include/ORBextractor.h:63-83).  Each non-null pointer receives nlevels floats. */
+int orbx_levels(const orbx_extractor* ex);
+int orbx_scale_tables(const orbx_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2);
+/* mnFeaturesPerLevel (src/ORBextractor.cc:435-446) and umax[0..15] (:454-469); protected members of the reference
+ * class, exported for the parity tests. */
+int orbx_features_per_level(const orbx_extractor* ex, int* out_nlevels);
+int orbx_umax(const orbx_extractor* ex, int* out16);
+/* Upper bound on the keypoints one frame can produce (a quadtree pass may overshoot the per-level quota,
+ * src/ORBextractor.cc:669-737): callers size kps/desc with it. */
+int orbx_max_keypoints(const orbx_extractor* ex);
+
+/* Replaces ORBextractor::operator()(image, mask, keypoints, descriptors) (src/ORBextractor.cc:1043-1105) for one
+ * 8-bit single-channel HOST image (row stride in bytes).  Synchronous.  kps receives *n keypoints (level-0 pixel
+ * units, level-ascending, quadtree list order inside a level), desc receives *n rows of 32 bytes.  cap = capacity of
+ * kps/desc in keypoints.  w<=0 or h<=0 or img==NULL -> *n = 0, ORBX_OK (the reference returns silently on an empty
+ * image, :1046-1047).  The mask argument of the reference is ignored there (:1043 "Mask is ignored") and absent here. */
+int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t stride,
+                 orbx_kp* kps, uint8_t* desc, int cap, int* n);
+
+/* Throughput path: B frames of one shape per call (independent frames).
+ * imgs[b] = HOST pointer of frame b.  kps/desc are HOST arrays of B*cap entries (frame b at offset b*cap);
+ * n receives B counts.  Synchronous: returns when the results are in the caller's buffers. */
+int orbx_extract_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, int w, int h, size_t stride,
+                       orbx_kp* kps, uint8_t* desc, int cap, int* n);
+
+/* Device-resident variant: d_imgs = DEVICE pointer to B frames (frame b at d_imgs + b*frame_stride, rows pitch bytes
+ * apart; pitch must be a multiple of 4).  Enqueues the whole extraction on the handle's stream and returns without
+ * synchronising; results stay in the handle's device workspace until orbx_fetch / the next extract call. */
+int orbx_extract_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w, int h, size_t pitch, size_t frame_stride);
+/* Waits for the handle's stream and copies the results of the last orbx_extract_device call to HOST buffers laid out
+ * as in orbx_extract_batch. */
+int orbx_fetch(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, int* n);
+/* Device pointers of the last results: kps = B*stride_kp orbx_kp, desc = B*stride_kp*32 bytes, counts = B ints
+ * (valid until the next extract call on this handle; read them on orbx_stream()). */
+int orbx_results_device(orbx_extractor* ex, const orbx_kp** d_kps, const uint8_t** d_desc, const int** d_counts, int* stride_kp);
+int orbx_sync(orbx_extractor* ex);
+/* The handle's cudaStream_t (as void*), so that callers can record CUDA events around the launches. */
+void* orbx_stream(orbx_extractor* ex);
+/* Number of kernels the last extract call launched (for bench.py's gpu_launches). */
+int orbx_last_launches(const orbx_extractor* ex);
+
+/* Replaces reads of the public member ORBextractor::mvImagePyramid (include/ORBextractor.h:85; read by
+ * Frame::ComputeStereoMatches, src/Frame.cc:488,578,590,595).  Level size of the last call: */
+int orbx_level_size(const orbx_extractor* ex, int level, int* w, int* h);
+/* Copies level `level` of frame `frame` of the last call to HOST memory.  border = 19 reproduces the reference's padded
+ * (w+38)x(h+38) buffer (BORDER_REFLECT_101 of the level itself, src/ORBextractor.cc:1113-1128); border = 0 gives the
+ * w x h interior that mvImagePyramid[level] views.  dst_stride in bytes. */
+int orbx_pyramid_level(orbx_extractor* ex, int frame, int level, int border, uint8_t* dst, size_t dst_stride);
+/* Zero-copy device view of the same interior (for the device stereo matcher). */
+int orbx_pyramid_device(orbx_extractor* ex, int frame, int level, const uint8_t** d_ptr, size_t* pitch);
+
+/* Stage dumps of the last call (parity tests only): blurred level (w x h) and the FAST candidates handed to
+ * DistributeOctTree in reference order as (x, y, response) int triples relative to minBorder = 16. */
+int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* dst, size_t dst_stride);
+int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, int* xyr, int cap, int* n);
+int orbx_debug_level_count(orbx_extractor* ex, int frame, int level, int* n);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * ORBmatcher  (reference include/ORBmatcher.h:37-102, src/ORBmatcher.cc; Frame::ComputeStereoMatches)
+ * Descriptors are rows of 32 bytes (CV_8U N x 32, continuous), as ORBmatcher::DescriptorDistance requires
+ * (src/ORBmatcher.cc:1649-1665).
+ * ------------------------------------------------------------------------------------------------------- */
+
+typedef struct orbx_matcher orbx_matcher;
+/* A matcher context = one CUDA stream + growable device scratch.  ORBmatcher itself is stateless apart from
+ * (nnratio, checkOri) (src/ORBmatcher.cc:41-43); those stay arguments. */
+int orbm_create(int device, orbx_matcher** out);
+void orbm_destroy(orbx_matcher* m);
+void* orbm_stream(orbx_matcher* m);
+/* Number of kernels the last matcher call launched. */
+int orbm_last_launches(const orbx_matcher* m);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1649-1665) for n independent row pairs (a[i], b[i]) -> dist[i]. */
+int orbm_descriptor_distance(orbx_matcher* m, const uint8_t* a, const uint8_t* b, int n, int* dist);
+
+/* Best / second-best scan shared by the SearchBy* routines (inner loop src/ORBmatcher.cc:205-226): for every query
+ * row scan ALL train rows in index order; strict '<' for best, else-if '<' for second, both start at 256.
+ * best_idx = -1 when nt == 0.  HOST buffers. */
+int orbm_match_bruteforce(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                          int* best_idx, int* best_dist, int* second_dist);
+/* The same scan followed by the acceptance test of src/ORBmatcher.cc:228-230: accepted[i] = best <= th_low &&
+ * (float)best < nnratio * (float)second. */
+int orbm_match_ratio(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int th_low, float nnratio,
+                     int* best_idx, int* best_dist, int* second_dist, uint8_t* accepted);
+/* Device-resident variant (all pointers DEVICE memory; enqueued on orbm_stream(), not synchronised). */
+int orbm_match_bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
+                                 int* d_best_idx, int* d_best_dist, int* d_second_dist);
+
+/* Candidate-list scan (the windowed / BoW-bucketed searches): query i scans train rows
+ * cand_idx[cand_off[i] .. cand_off[i+1]) in that order.  second_idx = -1 when there is none.  HOST buffers. */
+int orbm_match_candidates(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                          const int* cand_off, const int* cand_idx,
+                          int* best_idx, int* best_dist, int* second_idx, int* second_dist);
+/* All candidate distances, for the order-dependent replays (SearchForInitialization's vMatchedDistance skip,
+ * src/ORBmatcher.cc:444): dist[c] = distance(query owning slot c, train cand_idx[c]). */
+int orbm_candidate_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                             const int* cand_off, const int* cand_idx, int* dist);
+
+/* Frame grid (src/Frame.cc:230-245 AssignFeaturesToGrid, :397-407 PosInGrid) and Frame::GetFeaturesInArea
+ * (:342-395) for a batch of queries, on the device.  Produces the CSR candidate lists in the reference's order
+ * (cell column outer, cell row inner, insertion order inside a cell).  cand_idx receives at most cap entries;
+ * cand_off has nq+1 entries and always holds the true totals (ORBX_ERR_CAPACITY if cand_off[nq] > cap). */
+int orbm_grid_candidates(orbx_matcher* m, const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY,
+                         const float* qxy, int nq, const float* qr, int minLevel, int maxLevel, const int* q_level,
+                         int* cand_off, int* cand_idx, int cap);
+
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520).  prev_matched: in/out n1 x 2 floats
+ * (vbPrevMatched); matches12: n1 ints (-1 = none).  *nmatches receives the return value of the reference routine. */
+int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1, const uint8_t* d1, int n1,
+                                   const orbx_kp* k2, const uint8_t* d2, int n2,
+                                   float minX, float maxX, float minY, float maxY,
+                                   float* prev_matched, int* matches12, int windowSize, float nnratio, int checkOri,
+                                   int* nmatches);
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:481-655).  left/right = extractor handles whose LAST call processed the
+ * two images (their device pyramids are read in place; frame = index inside that batch).  Keypoints/descriptors are
+ * HOST arrays as returned by orbx_extract.  maxD is explicit (the reference reads an uninitialised mb, src/Frame.cc:511
+ * vs :114; the intended value is fx).  uRight/depth receive nl floats (-1 = no match); *nmatched the survivors. */
+int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, int frame,
+                        const orbx_kp* kl, const uint8_t* dl, int nl,
+                        const orbx_kp* kr, const uint8_t* dr, int nr,
+                        float bf, float minD, float maxD, float* uRight, float* depth, int* nmatched);
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char* orbx_last_error(void);
+/* Library/build identification, e.g. "orbx 0.1 sm_100a". */
+const char* orbx_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

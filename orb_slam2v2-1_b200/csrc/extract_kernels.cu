@@ -1,0 +1,704 @@
+// extract_kernels.cu -- sm_100a kernels of the ORB extractor (reference src/ORBextractor.cc).
+//
+// Data layout in HBM (per handle, frame-major slabs, see FrameBufs): every pyramid level is a border-less u8 plane with a
+// 32-byte-aligned pitch; the reference's 19-px REFLECT_101 border (ORBextractor.cc:1113-1128) is never read by any
+// extraction stage, so it is produced on demand by k_reflect_copy when a caller asks for mvImagePyramid.
+// All arithmetic that decides a keypoint or a descriptor bit is integer or individually-rounded float
+// (__fmul_rn/__fadd_rn/__fdiv_rn): nvcc must not contract anything here.
+#include "extract_kernels.cuh"
+#include "sincosf_glibc.h"
+#include <float.h>
+
+namespace orbx {
+
+__device__ __forceinline__ const uint8_t* level_plane(const Plan& P, const FrameBufs& F, int f, int l, int& pitch)
+{
+    if (l == 0) { pitch = (int)F.lv0Pitch; return F.lv0 + (size_t)f * F.lv0Frame; }
+    pitch = P.lv[l].pitch;
+    return F.pyr + (size_t)f * P.pyrSlab + P.lv[l].planeOff;
+}
+
+__device__ __forceinline__ int level_of_cell(const Plan& P, int cell)
+{
+    int l = 0;
+    while (l + 1 < P.nlevels && cell >= P.lv[l + 1].cellBase) ++l;
+    return l;
+}
+
+// ------------------------------------------------------------------------------------------------ pyramid
+// cv::resize INTER_LINEAR, 8-bit: 11-bit coefficients (host tables), horizontal pass in int32, vertical pass
+// (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.  One thread = 4 horizontally adjacent output pixels.
+__global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, int spitch, size_t sframe,
+                                                uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dframe,
+                                                const int2* __restrict__ xtab, const int4* __restrict__ ytab)
+{
+    const int f = blockIdx.z;
+    const int dy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (dy >= dh || x4 >= dw) return;
+    const int4 yy = __ldg(&ytab[dy]);
+    const uint8_t* S0 = src + (size_t)f * sframe + (size_t)yy.x * spitch;
+    const uint8_t* S1 = src + (size_t)f * sframe + (size_t)yy.y * spitch;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int dx = x4 + k;
+        if (dx < dw) {
+            const int2 t = __ldg(&xtab[dx]);
+            const int sx = t.x & 0xFFFF, sx1 = t.x >> 16;
+            const int a0 = t.y & 0xFFFF, a1 = t.y >> 16;
+            const int H0 = (int)__ldg(S0 + sx) * a0 + (int)__ldg(S0 + sx1) * a1;
+            const int H1 = (int)__ldg(S1 + sx) * a0 + (int)__ldg(S1 + sx1) * a1;
+            int v = (((yy.z * (H0 >> 4)) >> 16) + ((yy.w * (H1 >> 4)) >> 16) + 2) >> 2;
+            v = min(max(v, 0), 255);
+            out |= (uint32_t)v << (8 * k);
+        }
+    }
+    *reinterpret_cast<uint32_t*>(dst + (size_t)f * dframe + (size_t)dy * dpitch + x4) = out;   // pitch is a multiple of 32
+}
+
+void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
+                   size_t dframe, const int2* xtab, const int4* ytab, int B)
+{
+    dim3 blk(32, 8);
+    dim3 grd((dw + 127) / 128, (dh + 7) / 8, B);
+    k_resize<<<grd, blk, 0, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, xtab, ytab);
+}
+
+// ------------------------------------------------------------------------------------------------ FAST per cell
+constexpr int FAST_THREADS = 128;
+
+// raw = max over the 16 arcs of 9 contiguous ring pixels of min(ring - centre) resp. min(centre - ring)
+// (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  Circular window minima via
+// prefix/suffix minima of the two ring halves: window k covers d[k..7] + d[8..8+k], window 8+k covers d[8+k..15] + d[0..k].
+__device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch)
+{
+    const int v = c[0];
+    int d[16];
+    d[0] = c[3 * pitch] - v;       d[1] = c[3 * pitch + 1] - v;   d[2] = c[2 * pitch + 2] - v;   d[3] = c[pitch + 3] - v;
+    d[4] = c[3] - v;               d[5] = c[-pitch + 3] - v;      d[6] = c[-2 * pitch + 2] - v;  d[7] = c[-3 * pitch + 1] - v;
+    d[8] = c[-3 * pitch] - v;      d[9] = c[-3 * pitch - 1] - v;  d[10] = c[-2 * pitch - 2] - v; d[11] = c[-pitch - 3] - v;
+    d[12] = c[-3] - v;             d[13] = c[pitch - 3] - v;      d[14] = c[2 * pitch - 2] - v;  d[15] = c[3 * pitch - 1] - v;
+    int sufA[8], preA[8], sufB[8], preB[8];
+    int SufA[8], PreA[8], SufB[8], PreB[8];
+    sufA[7] = SufA[7] = d[7];  sufB[7] = SufB[7] = d[15];
+    preA[0] = PreA[0] = d[0];  preB[0] = PreB[0] = d[8];
+#pragma unroll
+    for (int k = 6; k >= 0; k--) {
+        sufA[k] = min(sufA[k + 1], d[k]);      SufA[k] = max(SufA[k + 1], d[k]);
+        sufB[k] = min(sufB[k + 1], d[8 + k]);  SufB[k] = max(SufB[k + 1], d[8 + k]);
+    }
+#pragma unroll
+    for (int k = 1; k < 8; k++) {
+        preA[k] = min(preA[k - 1], d[k]);      PreA[k] = max(PreA[k - 1], d[k]);
+        preB[k] = min(preB[k - 1], d[8 + k]);  PreB[k] = max(PreB[k - 1], d[8 + k]);
+    }
+    int bright = -255, dark = 255;   // dark holds the minimum over arcs of the arc maximum
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        bright = max(bright, max(min(sufA[k], preB[k]), min(sufB[k], preA[k])));
+        dark = min(dark, min(max(SufA[k], PreB[k]), max(SufB[k], PreA[k])));
+    }
+    return max(bright, -dark);
+}
+
+size_t fast_smem_bytes(const Plan& P)
+{
+    int mw = 0, mh = 0;
+    for (int l = 0; l < P.nlevels; l++) { mw = max(mw, P.lv[l].wCell); mh = max(mh, P.lv[l].hCell); }
+    const size_t tile = (size_t)(mh + 6) * (size_t)((mw + 6 + 3 + 3) & ~3);
+    const size_t sc = ((size_t)(mh + 2) * (mw + 2) + 3) & ~(size_t)3;
+    const size_t list = (size_t)mw * mh * 2;
+    return tile + sc + list + 16;
+}
+
+__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const Plan P, const FrameBufs F)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int s_nlist;
+    __shared__ int s_wsum[FAST_THREADS / 32 + 1];
+    const int cell = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int l = level_of_cell(P, cell);
+    const LevelGeom& G = P.lv[l];
+    const int ci = cell - G.cellBase;
+    const int ci_i = ci / G.nCols, ci_j = ci - ci_i * G.nCols;
+    int* cntOut = F.cellCount + (size_t)f * P.totalCells + cell;
+
+    // cell ROI (ORBextractor.cc:791-806): [iniX, maxX) x [iniY, maxY), overlap of 6 px with the next cell
+    const int iniX = MIN_BORDER + ci_j * G.wCell, iniY = MIN_BORDER + ci_i * G.hCell;
+    const int maxX = min(iniX + G.wCell + 6, G.maxBX), maxY = min(iniY + G.hCell + 6, G.maxBY);
+    const int tw = maxX - iniX, th = maxY - iniY;
+    if (iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7) {     // skipped cell / ROI too small for cv::FAST
+        if (tid == 0) *cntOut = 0;
+        return;
+    }
+    const int iw = tw - 6, ih = th - 6, npx = iw * ih;    // detection zone: no corner within 3 px of the ROI edge
+    const int ax = iniX & ~3;                             // word-aligned tile origin
+    const int dx0 = iniX - ax;
+    const int nwords = (maxX - ax + 3) >> 2;
+    const int tp = nwords * 4;                            // tile pitch (bytes)
+    const int scp = iw + 2;                               // score-map pitch: 1-px zero frame
+    uint8_t* tile = smem;
+    uint8_t* sc = tile + (size_t)th * tp;
+    uint16_t* list = reinterpret_cast<uint16_t*>(sc + ((((size_t)(ih + 2) * scp) + 3) & ~(size_t)3));
+
+    int pitch;
+    const uint8_t* img = level_plane(P, F, f, l, pitch);
+    for (int i = tid; i < th * nwords; i += FAST_THREADS) {
+        const int r = i / nwords, c = i - r * nwords;
+        reinterpret_cast<uint32_t*>(tile)[r * nwords + c] =
+            __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(iniY + r) * pitch + ax) + c);
+    }
+    for (int i = tid; i < ((ih + 2) * scp + 3) / 4; i += FAST_THREADS) reinterpret_cast<uint32_t*>(sc)[i] = 0;
+    if (tid == 0) s_nlist = 0;
+    __syncthreads();
+
+    // phase A: compass pre-test at the lower threshold (a 9-arc always contains two adjacent compass pixels)
+    const int tlow = min(P.iniTh, P.minTh);
+    const int npxR = (npx + 31) & ~31;
+    for (int p = tid; p < npxR; p += FAST_THREADS) {
+        bool pass = false;
+        if (p < npx) {
+            const int y = p / iw, x = p - y * iw;
+            const uint8_t* c = tile + (y + 3) * tp + (x + 3 + dx0);
+            const int v = c[0];
+            const int hi = v + tlow, lo = v - tlow;
+            const int p0 = c[3 * tp], p4 = c[3], p8 = c[-3 * tp], p12 = c[-3];
+            const bool b = ((p0 > hi) | (p8 > hi)) & ((p4 > hi) | (p12 > hi));
+            const bool dk = ((p0 < lo) | (p8 < lo)) & ((p4 < lo) | (p12 < lo));
+            pass = b | dk;
+        }
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
+        int base = 0;
+        if (lane == 0 && m) base = atomicAdd(&s_nlist, __popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        if (pass) list[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)p;
+    }
+    __syncthreads();
+
+    // phase C: exact score of the survivors
+    const int nlist = s_nlist;
+    for (int k = tid; k < nlist; k += FAST_THREADS) {
+        const int p = list[k];
+        const int y = p / iw, x = p - y * iw;
+        const int raw = fast_raw_score(tile + (y + 3) * tp + (x + 3 + dx0), tp);
+        if (raw > tlow) sc[(y + 1) * scp + x + 1] = (uint8_t)raw;
+    }
+    __syncthreads();
+
+    // NMS (strict >, neighbours outside the detection zone or below threshold count as 0) + ordered emission.
+    // kept at threshold t  <=>  raw > t and raw > all 8 neighbours' raw: independent of t, so the minThFAST retry
+    // (ORBextractor.cc:812-816) is a re-threshold of the same local maxima.
+    const int K = (npx + FAST_THREADS - 1) / FAST_THREADS;     // <= 32 (cells are < 62 x 62)
+    unsigned keepMask = 0;
+    int cIni = 0, cMin = 0;
+    for (int k = 0; k < K; k++) {
+        const int p = tid * K + k;
+        if (p >= npx) break;
+        const int y = p / iw, x = p - y * iw;
+        const uint8_t* s = sc + (y + 1) * scp + x + 1;
+        const int v = s[0];
+        if (v == 0) continue;
+        const bool keep = v > s[-1] && v > s[1] && v > s[-scp - 1] && v > s[-scp] && v > s[-scp + 1] &&
+                          v > s[scp - 1] && v > s[scp] && v > s[scp + 1];
+        if (keep) {
+            keepMask |= 1u << k;
+            cIni += (v > P.iniTh);
+            cMin += (v > P.minTh);
+        }
+    }
+    const int packed = (cIni << 16) | cMin;
+    int inc = packed;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_wsum[wid] = inc;
+    __syncthreads();
+    int woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < FAST_THREADS / 32; w++) {
+        const int v = s_wsum[w];
+        if (w < wid) woff += v;
+        total += v;
+    }
+    const bool useIni = (total >> 16) > 0;
+    const int excl = woff + inc - packed;
+    int off = useIni ? (excl >> 16) : (excl & 0xFFFF);
+    const int th_ = useIni ? P.iniTh : P.minTh;
+    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)ci * G.slotCap;
+    for (int k = 0; k < K; k++) {
+        if (!(keepMask >> k & 1u)) continue;
+        const int p = tid * K + k;
+        const int y = p / iw, x = p - y * iw;
+        const int v = sc[(y + 1) * scp + x + 1];
+        if (v > th_) {
+            // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
+            out[off++] = pack_key(x + 3 + ci_j * G.wCell, y + 3 + ci_i * G.hCell, v - 1);
+        }
+    }
+    if (tid == 0) *cntOut = useIni ? (total >> 16) : (total & 0xFFFF);
+}
+
+void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
+{
+    dim3 grd(P.totalCells, B);
+    k_fast_cells<<<grd, FAST_THREADS, smemBytes, s>>>(P, F);
+}
+
+// ------------------------------------------------------------------------------------------------ quadtree
+constexpr int OCT_THREADS = 1024;
+
+// in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
+__device__ int block_exclusive_scan(int* a, int n, int* wsum)
+{
+    const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (n + T - 1) / T;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    int s = 0;
+    for (int i = b; i < e; i++) s += a[i];
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const int v = lane < (T >> 5) ? wsum[lane] : 0;
+        int vi = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
+            if (lane >= o) vi += t;
+        }
+        wsum[lane] = vi - v;
+        if (lane == 31) wsum[32] = vi;
+    }
+    __syncthreads();
+    int off = wsum[wid] + inc - s;
+    for (int i = b; i < e; i++) { const int t = a[i]; a[i] = off; off += t; }
+    const int total = wsum[32];
+    __syncthreads();
+    return total;
+}
+
+size_t octree_smem_bytes(int capS, int sortCap)
+{
+    // rectA, rectB (short4) | cntA, cntB | cc[4] | chBeg | tmp | skey[sortCap] | rankOf, mapS (u16) | childPos[4] (u16)
+    return (size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 8) + (size_t)sortCap * 4 + 64;
+}
+
+// DistributeOctTree.  The reference keeps nodes in a std::list built with push_front; a pass over the list splits
+// nodes and the new list is  reverse(children in creation order) ++ (unsplit nodes in their old order).  Here the list
+// is an array in list order, rebuilt every pass with prefix sums; every candidate carries the position of its node.
+// Tie-break of the "largest first" phase (ORBextractor.cc:684 sorts by (size, heap address)): creation order, later
+// first == smaller list position first (the portable definition of the oracle, tie_mode 0).
+__global__ void __launch_bounds__(OCT_THREADS, 1) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
+{
+    extern __shared__ __align__(16) uint8_t smraw[];
+    __shared__ int wsum[33];
+    __shared__ int s_k, s_nexp, s_m;
+    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, T = OCT_THREADS, lane = tid & 31, wid = tid >> 5;
+    const LevelGeom& G = P.lv[l];
+
+    short4* rA = reinterpret_cast<short4*>(smraw);
+    short4* rB = rA + capS;
+    int* cA = reinterpret_cast<int*>(rB + capS);
+    int* cB = cA + capS;
+    int* cc = cB + capS;                   // child counts of the nodes being split, by processing rank
+    int* chBeg = cc + 4 * capS;            // creation index of a rank's first child
+    int* tmp = chBeg + capS;
+    uint32_t* skey = reinterpret_cast<uint32_t*>(tmp + capS);   // processing order (positions) / sort keys
+    uint16_t* rankOf = reinterpret_cast<uint16_t*>(skey + sortCap);
+    uint16_t* mapS = rankOf + capS;
+    uint16_t* childPos = mapS + capS;
+
+    const int ncell = G.nCols * G.nRows;
+    const int* cellCount = F.cellCount + (size_t)f * P.totalCells + G.cellBase;
+    int* cellOff = F.cellOff + (size_t)f * P.totalCells + G.cellBase;
+    const uint32_t* slots = F.slots + (size_t)f * P.slotSlab + G.slotOff;
+    uint32_t* keys = F.keys + (size_t)f * P.keySlab + G.keyOff;
+    uint16_t* knode = F.knode + (size_t)f * P.keySlab + G.keyOff;
+    uint32_t* outKeys = F.levelKeys + (size_t)f * P.totalNodes + G.nodeBase;
+    int* outCount = F.levelCount + (size_t)f * MAX_LEVELS + l;
+
+    // candidate order of the reference: cell row, cell column, then cv::FAST's row-major order inside the cell
+    for (int i = tid; i < ncell; i += T) cellOff[i] = cellCount[i];
+    __syncthreads();
+    const int n = block_exclusive_scan(cellOff, ncell, wsum);
+    if (n == 0) {
+        if (tid == 0) *outCount = 0;
+        return;
+    }
+    const int nIni = G.nIni;
+    int* rootCnt = cc;          // scratch: nIni <= capS
+    for (int i = tid; i < nIni; i += T) rootCnt[i] = 0;
+    __syncthreads();
+    for (int c = wid; c < ncell; c += T / 32) {
+        const int cnt = cellCount[c], off = cellOff[c];
+        const uint32_t* src = slots + (size_t)c * G.slotCap;
+        for (int e = lane; e < cnt; e += 32) {
+            const uint32_t key = src[e];
+            int root = (int)__fdiv_rn((float)key_x(key), G.hX);      // vpIniNodes[kp.pt.x/hX] (:569)
+            root = min(root, nIni - 1);
+            keys[off + e] = key;
+            knode[off + e] = (uint16_t)root;
+            atomicAdd(&rootCnt[root], 1);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int m0 = 0;
+        for (int i = 0; i < nIni; i++) {
+            if (rootCnt[i] > 0) {           // empty roots are erased (:574-585)
+                rA[m0] = make_short4((short)(int)__fmul_rn(G.hX, (float)i), (short)(int)__fmul_rn(G.hX, (float)(i + 1)),
+                                     (short)0, (short)(G.maxBY - MIN_BORDER));
+                cA[m0] = rootCnt[i];
+                tmp[i] = m0++;
+            }
+        }
+        s_m = m0;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += T) knode[i] = (uint16_t)tmp[knode[i]];
+    int m = s_m;
+    const int N = G.quota;
+    bool lf = false;
+    __syncthreads();
+
+    for (;;) {
+        // ---- processing order P: all expandable nodes (more than one key)
+        for (int p = tid; p < m; p += T) { tmp[p] = cA[p] > 1; rankOf[p] = 0xFFFF; }
+        if (tid == 0) { s_k = 0x7FFFFFFF; s_nexp = 0; }
+        __syncthreads();
+        const int np = block_exclusive_scan(tmp, m, wsum);
+        if (np == 0) break;                                   // nothing to split: list size cannot change
+        if (!lf) {
+            for (int p = tid; p < m; p += T) if (cA[p] > 1) skey[tmp[p]] = (uint32_t)p;      // list order (:606)
+            __syncthreads();
+        } else {
+            int sp = 1;
+            while (sp < np) sp <<= 1;
+            for (int p = tid; p < m; p += T) if (cA[p] > 1) skey[tmp[p]] = ((uint32_t)cA[p] << 12) | (uint32_t)(4095 - p);
+            for (int r = np + tid; r < sp; r += T) skey[r] = 0;
+            for (int size = 2; size <= sp; size <<= 1)
+                for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                    __syncthreads();
+                    for (int i = tid; i < sp; i += T) {
+                        const int j = i ^ stride;
+                        if (j > i) {
+                            const uint32_t a = skey[i], b = skey[j];
+                            const bool desc = (i & size) == 0;
+                            if ((a < b) == desc) { skey[i] = b; skey[j] = a; }
+                        }
+                    }
+                }
+            __syncthreads();
+            for (int r = tid; r < np; r += T) skey[r] = 4095u - (skey[r] & 4095u);
+            __syncthreads();
+        }
+        for (int r = tid; r < np; r += T) rankOf[skey[r]] = (uint16_t)r;
+        for (int i = tid; i < 4 * np; i += T) cc[i] = 0;
+        __syncthreads();
+
+        // ---- quadrant of every key of an expandable node (DivideNode :481-537), child counts
+        for (int i0 = 0; i0 < n; i0 += T) {
+            const int i = i0 + tid;
+            int code = -1;
+            if (i < n) {
+                const int pos = knode[i] & 0xFFF;
+                const int r = rankOf[pos];
+                if (r != 0xFFFF) {
+                    const uint32_t key = keys[i];
+                    const short4 rc = rA[pos];
+                    const int midX = rc.x + ((rc.y - rc.x + 1) >> 1), midY = rc.z + ((rc.w - rc.z + 1) >> 1);
+                    const int q = (key_x(key) < midX ? 0 : 1) + (key_y(key) < midY ? 0 : 2);
+                    knode[i] = (uint16_t)(pos | (q << 12));
+                    code = 4 * r + q;
+                }
+            }
+            const unsigned peers = __match_any_sync(0xFFFFFFFFu, code);
+            if (code >= 0 && lane == __ffs(peers) - 1) atomicAdd(&cc[code], __popc(peers));
+        }
+        __syncthreads();
+
+        // ---- children per rank, creation indices, early stop of the largest-first phase (:730-731)
+        for (int r = tid; r < np; r += T)
+            chBeg[r] = (cc[4 * r] > 0) + (cc[4 * r + 1] > 0) + (cc[4 * r + 2] > 0) + (cc[4 * r + 3] > 0);
+        __syncthreads();
+        const int totalCh = block_exclusive_scan(chBeg, np, wsum);
+        int k = np;
+        if (lf) {
+            for (int r = tid; r < np; r += T) {
+                const int end = (r + 1 < np) ? chBeg[r + 1] : totalCh;
+                if (m + end - (r + 1) >= N) atomicMin(&s_k, r);
+            }
+            __syncthreads();
+            if (s_k != 0x7FFFFFFF) k = s_k + 1;
+        }
+        const int C = (k == np) ? totalCh : chBeg[k];
+
+        // ---- new list = reverse(children) ++ unsplit nodes
+        for (int p = tid; p < m; p += T) tmp[p] = (int)rankOf[p] >= k;
+        __syncthreads();
+        block_exclusive_scan(tmp, m, wsum);
+        for (int p = tid; p < m; p += T)
+            if ((int)rankOf[p] >= k) {
+                const int q = C + tmp[p];
+                mapS[p] = (uint16_t)q;
+                rB[q] = rA[p];
+                cB[q] = cA[p];
+            }
+        int nexp = 0;
+        for (int r = tid; r < k; r += T) {
+            const int pos = skey[r];
+            const short4 rc = rA[pos];
+            const int midX = rc.x + ((rc.y - rc.x + 1) >> 1), midY = rc.z + ((rc.w - rc.z + 1) >> 1);
+            int c = chBeg[r];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int cq = cc[4 * r + q];
+                if (cq > 0) {
+                    const int at = C - 1 - c;
+                    c++;
+                    rB[at] = make_short4((q & 1) ? (short)midX : rc.x, (q & 1) ? rc.y : (short)midX,
+                                         (q & 2) ? (short)midY : rc.z, (q & 2) ? rc.w : (short)midY);
+                    cB[at] = cq;
+                    childPos[4 * r + q] = (uint16_t)at;
+                    nexp += cq > 1;
+                }
+            }
+        }
+        if (nexp) atomicAdd(&s_nexp, nexp);
+        __syncthreads();
+        for (int i = tid; i < n; i += T) {
+            const int kn = knode[i];
+            const int pos = kn & 0xFFF, q = kn >> 12;
+            const int r = rankOf[pos];
+            knode[i] = (r < k) ? childPos[4 * r + q] : mapS[pos];
+        }
+        const int m2 = C + (m - k);
+        const bool done = (m2 >= N) || (m2 == m);
+        if (!done && !lf && m2 + 3 * s_nexp > N) lf = true;
+        { short4* t = rA; rA = rB; rB = t; }
+        { int* t = cA; cA = cB; cB = t; }
+        m = m2;
+        __syncthreads();
+        if (done) break;
+    }
+
+    // ---- best key of every node: highest response, first in candidate order (:742-760)
+    unsigned* best = reinterpret_cast<unsigned*>(tmp);
+    for (int p = tid; p < m; p += T) best[p] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += T)
+        atomicMax(&best[knode[i] & 0xFFF], ((unsigned)key_r(keys[i]) << 20) | (unsigned)(0xFFFFF - i));
+    __syncthreads();
+    for (int p = tid; p < m; p += T) outKeys[p] = keys[0xFFFFF - (best[p] & 0xFFFFF)];
+    if (tid == 0) *outCount = m;
+}
+
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, size_t smemBytes)
+{
+    static thread_local size_t configured = 0;
+    if (smemBytes > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        if (e != cudaSuccess) return e;
+        configured = smemBytes;
+    }
+    dim3 grd(P.nlevels, B);
+    k_octree<<<grd, OCT_THREADS, smemBytes, s>>>(P, F, capS, sortCap);
+    return cudaSuccess;
+}
+
+// ------------------------------------------------------------------------------------------------ Gaussian blur
+// cv::GaussianBlur(7x7, sigma 2) on u8, OpenCV 4.x fixed-point path: taps 18,34,48,56,48,34,18 / 256; the horizontal pass
+// is exact 8.8, the vertical pass 8.16, out = (acc + 32768) >> 16; BORDER_REFLECT_101 of the level itself (the reference
+// blurs a border-less clone, ORBextractor.cc:1085).
+constexpr int BT_W = 64, BT_H = 32, BLUR_THREADS = 256;
+constexpr int BIN_P = BT_W + 8;      // input tile pitch
+
+__device__ __forceinline__ int reflect101(int p, int len)
+{
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}
+
+__global__ void __launch_bounds__(BLUR_THREADS) k_blur(const Plan P, const FrameBufs F)
+{
+    __shared__ uint8_t in[(BT_H + 6) * BIN_P];
+    __shared__ uint16_t hs[(BT_H + 6) * BT_W];
+    const int f = blockIdx.y, tid = threadIdx.x;
+    int l = 0;
+    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].blurTileBase) ++l;
+    const LevelGeom& G = P.lv[l];
+    const int t = blockIdx.x - G.blurTileBase;
+    const int ty = t / G.blurTilesX, tx = t - ty * G.blurTilesX;
+    const int x0 = tx * BT_W, y0 = ty * BT_H;
+    int pitch;
+    const uint8_t* img = level_plane(P, F, f, l, pitch);
+    for (int i = tid; i < (BT_H + 6) * (BT_W + 6); i += BLUR_THREADS) {
+        const int r = i / (BT_W + 6), c = i - r * (BT_W + 6);
+        const int yy = reflect101(y0 + r - 3, G.h), xx = reflect101(x0 + c - 3, G.w);
+        in[r * BIN_P + c] = __ldg(img + (size_t)yy * pitch + xx);
+    }
+    __syncthreads();
+    for (int i = tid; i < (BT_H + 6) * BT_W; i += BLUR_THREADS) {
+        const int r = i / BT_W, c = i - r * BT_W;
+        const uint8_t* s = in + r * BIN_P + c;
+        hs[i] = (uint16_t)(18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3]);
+    }
+    __syncthreads();
+    uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff;
+    for (int i = tid; i < BT_H * BT_W; i += BLUR_THREADS) {
+        const int r = i / BT_W, c = i - r * BT_W;
+        if (x0 + c < G.w && y0 + r < G.h) {
+            const uint16_t* s = hs + r * BT_W + c;
+            const unsigned acc = 18u * (s[0] + s[6 * BT_W]) + 34u * (s[BT_W] + s[5 * BT_W]) + 48u * (s[2 * BT_W] + s[4 * BT_W]) +
+                                 56u * s[3 * BT_W];
+            dst[(size_t)(y0 + r) * G.pitch + x0 + c] = (uint8_t)((acc + 32768u) >> 16);
+        }
+    }
+}
+
+void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
+{
+    dim3 grd(P.totalBlurTiles, B);
+    k_blur<<<grd, BLUR_THREADS, 0, s>>>(P, F);
+}
+
+// ------------------------------------------------------------------------------------------------ orientation + rBRIEF
+// cv::fastAtan2 (degrees): float32 odd polynomial, every operation individually rounded.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x)
+{
+    const float scale = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * scale;
+    const float p3 = -0.3258083974640975f * scale;
+    const float p5 = 0.1555786518463281f * scale;
+    const float p7 = -0.04432655554792128f * scale;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+constexpr int DESC_WARPS = 8;
+
+__global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const UMaxTable um,
+                                                                    const uint32_t* __restrict__ patT)
+{
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);      // keypoint index inside the frame
+    const int* lc = F.levelCount + (size_t)f * MAX_LEVELS;
+    int l = -1, idx = 0, total = 0;
+    for (int i = 0; i < P.nlevels; i++) {                             // levels are concatenated in ascending order (:1103)
+        const int c = lc[i];
+        if (l < 0 && g < total + c) { l = i; idx = g - total; }
+        total += c;
+    }
+    if (g == 0 && lane == 0) F.counts[f] = total;
+    if (l < 0) return;
+    const LevelGeom& G = P.lv[l];
+    const uint32_t key = F.levelKeys[(size_t)f * P.totalNodes + G.nodeBase + idx];
+    const int cx = key_x(key) + MIN_BORDER, cy = key_y(key) + MIN_BORDER;      // level coordinates (:841-842)
+
+    // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level
+    int pitch;
+    const uint8_t* img = level_plane(P, F, f, l, pitch);
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int u = lane - HALF_PATCH, au = abs(u);
+        const uint8_t* c = img + (size_t)cy * pitch + cx + u;
+#pragma unroll
+        for (int v = -HALF_PATCH; v <= HALF_PATCH; v++) {
+            if (au <= um.v[v < 0 ? -v : v]) {
+                const int val = __ldg(c + v * pitch);
+                m10 += u * val;
+                m01 += v * val;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
+        m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // rBRIEF on the blurred level: lane = descriptor byte, 8 test pairs each
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float a, b;
+    orbx_sc::sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);       // a = cos, b = sin (:112-113)
+    const uint8_t* ctr = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)cy * G.pitch + cx;
+    const int bp = G.pitch;
+    unsigned val = 0;
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+        const uint32_t w = __ldg(&patT[bit * 32 + lane]);
+        const float x0 = (float)(int8_t)(w & 0xFF), y0 = (float)(int8_t)((w >> 8) & 0xFF);
+        const float x1 = (float)(int8_t)((w >> 16) & 0xFF), y1 = (float)(int8_t)(w >> 24);
+        int r0, c0, r1, c1;
+        if (P.fmaMode) {     // contracted form g++ -O3 -march=native emits for x*b + y*a and x*a - y*b
+            r0 = __float2int_rn(__fmaf_rn(x0, b, __fmul_rn(y0, a)));
+            c0 = __float2int_rn(__fmaf_rn(x0, a, -__fmul_rn(y0, b)));
+            r1 = __float2int_rn(__fmaf_rn(x1, b, __fmul_rn(y1, a)));
+            c1 = __float2int_rn(__fmaf_rn(x1, a, -__fmul_rn(y1, b)));
+        } else {
+            r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+            c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+            r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+            c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        }
+        const int t0 = __ldg(ctr + r0 * bp + c0), t1 = __ldg(ctr + r1 * bp + c1);
+        val |= (unsigned)(t0 < t1) << bit;
+    }
+    const size_t o = (size_t)f * P.totalNodes + g;
+    F.desc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orbx_kp kp;
+        kp.x = l ? __fmul_rn((float)cx, G.scale) : (float)cx;       // pt *= mvScaleFactor[level] for level != 0 (:1095-1101)
+        kp.y = l ? __fmul_rn((float)cy, G.scale) : (float)cy;
+        kp.size = (float)G.scaledPatch;
+        kp.angle = angle;
+        kp.response = (float)key_r(key);
+        kp.octave = l;
+        kp.class_id = -1;
+        F.kps[o] = kp;
+    }
+}
+
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const uint32_t* patT, int B)
+{
+    dim3 grd((P.totalNodes + DESC_WARPS - 1) / DESC_WARPS, B);
+    k_orient_describe<<<grd, DESC_WARPS * 32, 0, s>>>(P, F, um, patT);
+}
+
+// ------------------------------------------------------------------------------------------------ padded copy-out
+__global__ void k_reflect_copy(const uint8_t* __restrict__ src, int w, int h, int spitch, uint8_t* __restrict__ dst, int border, int dpitch)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= w + 2 * border || y >= h + 2 * border) return;
+    dst[(size_t)y * dpitch + x] = src[(size_t)reflect101(y - border, h) * spitch + reflect101(x - border, w)];
+}
+
+void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch)
+{
+    dim3 blk(32, 8), grd((w + 2 * border + 31) / 32, (h + 2 * border + 7) / 8);
+    k_reflect_copy<<<grd, blk, 0, s>>>(src, w, h, spitch, dst, border, dpitch);
+}
+
+}  // namespace orbx

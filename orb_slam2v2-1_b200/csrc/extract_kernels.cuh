@@ -1,0 +1,44 @@
+// extract_kernels.cuh -- launch interface of the ORB extraction kernels (extract_kernels.cu).
+#pragma once
+#include "orbx_common.cuh"
+
+namespace orbx {
+
+// Device buffers of one extractor handle for a batch of B frames (frame-major slabs).
+struct FrameBufs {
+    const uint8_t* lv0;            // level-0 planes (H2D staging or the caller's device images)
+    unsigned long long lv0Pitch, lv0Frame;
+    uint8_t* pyr;                  // B x Plan::pyrSlab      levels 1..L-1, unblurred (mvImagePyramid interiors)
+    uint8_t* blur;                 // B x Plan::blurSlab     7x7 Gaussian of every level
+    int* cellCount;                // B x totalCells         FAST candidates kept per cell
+    int* cellOff;                  // B x totalCells         exclusive scan of cellCount inside a level
+    uint32_t* slots;               // B x slotSlab           per-cell candidate slots (packed keys, row-major inside a cell)
+    uint32_t* keys;                // B x keySlab            per-level compacted candidates in reference order
+    uint16_t* knode;               // B x keySlab            node position (12 bits) | quadrant << 12 of every candidate
+    uint32_t* levelKeys;           // B x totalNodes         quadtree output per level, list order
+    int* levelCount;               // B x MAX_LEVELS
+    orbx_kp* kps;                  // B x totalNodes
+    uint8_t* desc;                 // B x totalNodes x 32
+    int* counts;                   // B
+};
+
+struct UMaxTable { int v[16]; };
+
+// cv::resize(INTER_LINEAR) of one level from the previous one for all frames (ComputePyramid, ORBextractor.cc:1120).
+void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
+                   size_t dframe, const int2* xtab, const int4* ytab, int B);
+// per-cell FAST-9/16 + NMS + ini/min retry, all levels and frames (ComputeKeyPointsOctTree cell loop, :789-829)
+void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);
+// DistributeOctTree (:539-763), one CTA per (level, frame)
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, size_t smemBytes);
+// GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
+void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
+// IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const uint32_t* patT, int B);
+// padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
+void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch);
+
+size_t fast_smem_bytes(const Plan& P);
+size_t octree_smem_bytes(int capS, int sortCap);
+
+}  // namespace orbx

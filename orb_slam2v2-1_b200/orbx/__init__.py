@@ -1,0 +1,386 @@
+"""orbx -- Python mirror of the reference's front-end interface over the C ABI of liborbx.so (include/orbx.h).
+
+`ORBextractor` / `ORBmatcher` keep the reference's names, argument meaning and error behaviour
+(include/ORBextractor.h:45-111, include/ORBmatcher.h:37-102 of kimwin2/ORB_SLAM2v2-1); every compute call goes
+through ctypes into hand-written sm_100a CUDA.  There is no CPU fallback: importing works anywhere (so that the
+ABI can be inspected), but creating an extractor or matcher without the library or without a CUDA device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liborbx.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+OK, ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_STATE = range(5)
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("orbx error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Load liborbx.so (built in-tree by __graft_entry__.build() / make -C csrc).  Fails loudly when absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OrbxError(ERR_STATE, "liborbx.so is not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                        "there is no CPU fallback" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    sig = {
+        "orbx_create": (i, [i, f, i, i, i, i, i, vp]),
+        "orbx_destroy": (None, [vp]),
+        "orbx_set_fma_mode": (i, [vp, i]),
+        "orbx_levels": (i, [vp]),
+        "orbx_scale_tables": (i, [vp, vp, vp, vp, vp]),
+        "orbx_features_per_level": (i, [vp, vp]),
+        "orbx_umax": (i, [vp, vp]),
+        "orbx_max_keypoints": (i, [vp]),
+        "orbx_extract": (i, [vp, vp, i, i, sz, vp, vp, i, vp]),
+        "orbx_extract_batch": (i, [vp, vp, i, i, i, sz, vp, vp, i, vp]),
+        "orbx_extract_device": (i, [vp, vp, i, i, i, sz, sz]),
+        "orbx_fetch": (i, [vp, vp, vp, i, vp]),
+        "orbx_results_device": (i, [vp, vp, vp, vp, vp]),
+        "orbx_sync": (i, [vp]),
+        "orbx_stream": (vp, [vp]),
+        "orbx_last_launches": (i, [vp]),
+        "orbx_level_size": (i, [vp, i, vp, vp]),
+        "orbx_pyramid_level": (i, [vp, i, i, i, vp, sz]),
+        "orbx_pyramid_device": (i, [vp, i, i, vp, vp]),
+        "orbx_debug_blurred_level": (i, [vp, i, i, vp, sz]),
+        "orbx_debug_candidates": (i, [vp, i, i, vp, i, vp]),
+        "orbx_debug_level_count": (i, [vp, i, i, vp]),
+        "orbm_create": (i, [i, vp]),
+        "orbm_destroy": (None, [vp]),
+        "orbm_stream": (vp, [vp]),
+        "orbm_last_launches": (i, [vp]),
+        "orbm_descriptor_distance": (i, [vp, vp, vp, i, vp]),
+        "orbm_match_bruteforce": (i, [vp, vp, i, vp, i, vp, vp, vp]),
+        "orbm_match_ratio": (i, [vp, vp, i, vp, i, i, f, vp, vp, vp, vp]),
+        "orbm_match_bruteforce_device": (i, [vp, vp, i, vp, i, vp, vp, vp]),
+        "orbm_match_candidates": (i, [vp, vp, i, vp, i, vp, vp, vp, vp, vp, vp]),
+        "orbm_candidate_distances": (i, [vp, vp, i, vp, i, vp, vp, vp]),
+        "orbm_grid_candidates": (i, [vp, vp, i, f, f, f, f, vp, i, vp, i, i, vp, vp, vp, i]),
+        "orbm_search_for_initialization": (i, [vp, vp, vp, i, vp, vp, i, f, f, f, f, vp, vp, i, f, i, vp]),
+        "orbm_stereo_matches": (i, [vp, vp, vp, i, vp, vp, i, vp, vp, i, f, f, f, vp, vp, vp]),
+        "orbx_last_error": (C.c_char_p, []),
+        "orbx_version": (C.c_char_p, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+ABI_SYMBOLS = None  # filled lazily by abi_symbols()
+
+
+def _check(rc, allow=()):
+    if rc != OK and rc not in allow:
+        raise OrbxError(rc, lib().orbx_last_error().decode())
+    return rc
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a):
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+class ORBextractor:
+    """ORB_SLAM2::ORBextractor (include/ORBextractor.h:45-111).
+
+    ex = ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST); kps, desc = ex(image).
+    `mask` is accepted and ignored like the reference ("Mask is ignored in the current implementation").
+    An empty image returns (empty, empty) like the reference's silent return (src/ORBextractor.cc:1046-1047).
+    """
+
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, device=0, max_batch=1):
+        self._L = lib()
+        h = C.c_void_p()
+        _check(self._L.orbx_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device, max_batch, C.byref(h)))
+        self._h = h
+        self.nfeatures, self.nlevels, self.device = nfeatures, nlevels, device
+        self.last_batch = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # --- accessors (ORBextractor.h:63-83)
+    def GetLevels(self):
+        return self._L.orbx_levels(self._h)
+
+    def _tables(self):
+        out = [np.zeros(self.nlevels, np.float32) for _ in range(4)]
+        _check(self._L.orbx_scale_tables(self._h, *[_p(o) for o in out]))
+        return out
+
+    def GetScaleFactor(self):
+        return float(self._tables()[0][1]) if self.nlevels > 1 else 1.0
+
+    def GetScaleFactors(self):
+        return self._tables()[0]
+
+    def GetInverseScaleFactors(self):
+        return self._tables()[1]
+
+    def GetScaleSigmaSquares(self):
+        return self._tables()[2]
+
+    def GetInverseScaleSigmaSquares(self):
+        return self._tables()[3]
+
+    def features_per_level(self):
+        o = np.zeros(self.nlevels, np.int32)
+        _check(self._L.orbx_features_per_level(self._h, _p(o)))
+        return o
+
+    def umax(self):
+        o = np.zeros(16, np.int32)
+        _check(self._L.orbx_umax(self._h, _p(o)))
+        return o
+
+    def set_fma_mode(self, mode):
+        _check(self._L.orbx_set_fma_mode(self._h, int(mode)))
+
+    def max_keypoints(self):
+        return self._L.orbx_max_keypoints(self._h)
+
+    # --- operator()
+    def __call__(self, image, mask=None):
+        if image is None or image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 expected"
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        hh, ww = image.shape
+        cap = max(self.max_keypoints(), 64)
+        for _ in range(2):
+            kps = np.zeros(cap, KP_DTYPE)
+            desc = np.zeros((cap, 32), np.uint8)
+            n = C.c_int(0)
+            rc = _check(self._L.orbx_extract(self._h, _p(image), ww, hh, image.strides[0], _p(kps), _p(desc), cap, C.byref(n)),
+                        allow=(ERR_CAPACITY,))
+            self.last_batch = 1
+            if rc == OK:
+                break
+            cap = n.value
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, images):
+        """images: sequence of equally-shaped 2-D uint8 arrays -> list of (kps, desc)."""
+        imgs = [_u8(im) for im in images]
+        B = len(imgs)
+        hh, ww = imgs[0].shape
+        assert all(im.shape == (hh, ww) for im in imgs)
+        ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
+        # the capacity depends on the shape: probe with a first call that may report ORBX_ERR_CAPACITY
+        cap = max(self.max_keypoints(), 64)
+        for _ in range(2):
+            kps = np.zeros((B, cap), KP_DTYPE)
+            desc = np.zeros((B, cap, 32), np.uint8)
+            n = np.zeros(B, np.int32)
+            rc = _check(self._L.orbx_extract_batch(self._h, ptrs, B, ww, hh, ww, _p(kps), _p(desc), cap, _p(n)), allow=(ERR_CAPACITY,))
+            self.last_batch = B
+            if rc == OK:
+                break
+            cap = int(n.max())
+        return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
+
+    def extract_device(self, d_ptr, B, w, h, pitch, frame_stride):
+        """Enqueue extraction of B device-resident frames on the handle's stream (no synchronisation)."""
+        _check(self._L.orbx_extract_device(self._h, C.c_void_p(d_ptr), B, w, h, pitch, frame_stride))
+        self.last_batch = B
+
+    def fetch(self):
+        B = self.last_batch
+        cap = max(self.max_keypoints(), 64)
+        kps = np.zeros((B, cap), KP_DTYPE)
+        desc = np.zeros((B, cap, 32), np.uint8)
+        n = np.zeros(B, np.int32)
+        _check(self._L.orbx_fetch(self._h, _p(kps), _p(desc), cap, _p(n)))
+        return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
+
+    def sync(self):
+        _check(self._L.orbx_sync(self._h))
+
+    def stream(self):
+        return self._L.orbx_stream(self._h)
+
+    def last_launches(self):
+        return self._L.orbx_last_launches(self._h)
+
+    # --- mvImagePyramid (ORBextractor.h:85)
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        _check(self._L.orbx_level_size(self._h, level, C.byref(w), C.byref(h)))
+        return w.value, h.value
+
+    def pyramid_level(self, level, frame=0, border=0):
+        w, h = self.level_size(level)
+        o = np.zeros((h + 2 * border, w + 2 * border), np.uint8)
+        _check(self._L.orbx_pyramid_level(self._h, frame, level, border, _p(o), o.strides[0]))
+        return o
+
+    @property
+    def mvImagePyramid(self):
+        return [self.pyramid_level(l) for l in range(self.nlevels)]
+
+    # --- stage dumps (parity tests)
+    def blurred_level(self, level, frame=0):
+        w, h = self.level_size(level)
+        o = np.zeros((h, w), np.uint8)
+        _check(self._L.orbx_debug_blurred_level(self._h, frame, level, _p(o), o.strides[0]))
+        return o
+
+    def level_candidates(self, level, frame=0):
+        n = C.c_int(0)
+        _check(self._L.orbx_debug_candidates(self._h, frame, level, None, 0, C.byref(n)))
+        o = np.zeros((max(n.value, 1), 3), np.int32)
+        _check(self._L.orbx_debug_candidates(self._h, frame, level, _p(o), n.value, C.byref(n)))
+        return o[:n.value]
+
+    def level_count(self, level, frame=0):
+        n = C.c_int(0)
+        _check(self._L.orbx_debug_level_count(self._h, frame, level, C.byref(n)))
+        return n.value
+
+
+class ORBmatcher:
+    """ORB_SLAM2::ORBmatcher (include/ORBmatcher.h:37-102): the descriptor-level searches."""
+
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30        # src/ORBmatcher.cc:37-39
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self._L = lib()
+        h = C.c_void_p()
+        _check(self._L.orbm_create(device, C.byref(h)))
+        self._h = h
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def stream(self):
+        return self._L.orbm_stream(self._h)
+
+    def DescriptorDistance(self, a, b):
+        """ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1649-1665); a, b: 32-byte rows or [n, 32] arrays."""
+        a, b = _u8(a).reshape(-1, 32), _u8(b).reshape(-1, 32)
+        assert a.shape == b.shape
+        d = np.zeros(len(a), np.int32)
+        _check(self._L.orbm_descriptor_distance(self._h, _p(a), _p(b), len(a), _p(d)))
+        return int(d[0]) if len(d) == 1 else d
+
+    def match_bruteforce(self, q, t):
+        q, t = _u8(q).reshape(-1, 32), _u8(t).reshape(-1, 32)
+        nq = len(q)
+        bi, bd, sd = (np.zeros(nq, np.int32) for _ in range(3))
+        _check(self._L.orbm_match_bruteforce(self._h, _p(q), nq, _p(t), len(t), _p(bi), _p(bd), _p(sd)))
+        return bi, bd, sd
+
+    def match_ratio(self, q, t, th_low=None, nnratio=None):
+        q, t = _u8(q).reshape(-1, 32), _u8(t).reshape(-1, 32)
+        nq = len(q)
+        bi, bd, sd = (np.zeros(nq, np.int32) for _ in range(3))
+        acc = np.zeros(nq, np.uint8)
+        _check(self._L.orbm_match_ratio(self._h, _p(q), nq, _p(t), len(t), self.TH_LOW if th_low is None else th_low,
+                                        self.mfNNratio if nnratio is None else nnratio, _p(bi), _p(bd), _p(sd), _p(acc)))
+        return bi, bd, sd, acc.astype(bool)
+
+    def match_bruteforce_device(self, d_q, nq, d_t, nt, d_bi, d_bd, d_sd):
+        _check(self._L.orbm_match_bruteforce_device(self._h, C.c_void_p(d_q), nq, C.c_void_p(d_t), nt,
+                                                    C.c_void_p(d_bi), C.c_void_p(d_bd), C.c_void_p(d_sd)))
+
+    def match_candidates(self, q, t, off, idx):
+        q, t = _u8(q).reshape(-1, 32), _u8(t).reshape(-1, 32)
+        off = np.ascontiguousarray(off, np.int32)
+        idx = np.ascontiguousarray(idx, np.int32)
+        nq = len(q)
+        bi, bd, si, sd = (np.zeros(nq, np.int32) for _ in range(4))
+        _check(self._L.orbm_match_candidates(self._h, _p(q), nq, _p(t), len(t), _p(off), _p(idx), _p(bi), _p(bd), _p(si), _p(sd)))
+        return bi, bd, si, sd
+
+    def candidate_distances(self, q, t, off, idx):
+        q, t = _u8(q).reshape(-1, 32), _u8(t).reshape(-1, 32)
+        off = np.ascontiguousarray(off, np.int32)
+        idx = np.ascontiguousarray(idx, np.int32)
+        d = np.zeros(max(len(idx), 1), np.int32)
+        _check(self._L.orbm_candidate_distances(self._h, _p(q), len(q), _p(t), len(t), _p(off), _p(idx), _p(d)))
+        return d[:len(idx)]
+
+    def grid_candidates(self, kps, bounds, qxy, r, minLevel=-1, maxLevel=-1, q_level=None):
+        """Frame::GetFeaturesInArea (src/Frame.cc:342-395) for all queries -> CSR (off, idx).
+        r: scalar or per-query radii; q_level: optional per-query level (minLevel = maxLevel = q_level[i])."""
+        kps = np.ascontiguousarray(kps, KP_DTYPE)
+        qxy = np.ascontiguousarray(qxy, np.float32).reshape(-1, 2)
+        nq = len(qxy)
+        qr = np.ascontiguousarray(np.broadcast_to(np.asarray(r, np.float32), (nq,)))
+        ql = None if q_level is None else np.ascontiguousarray(q_level, np.int32)
+        off = np.zeros(nq + 1, np.int32)
+        cap = max(64 * nq, 1024)
+        for _ in range(2):
+            idx = np.zeros(cap, np.int32)
+            rc = _check(self._L.orbm_grid_candidates(self._h, _p(kps), len(kps), *[float(b) for b in bounds], _p(qxy), nq, _p(qr),
+                                                     minLevel, maxLevel, _p(ql), _p(off), _p(idx), cap), allow=(ERR_CAPACITY,))
+            if rc == OK:
+                break
+            cap = int(off[nq])
+        return off, idx[:off[nq]].copy()
+
+    def SearchForInitialization(self, k1, d1, k2, d2, bounds, vbPrevMatched, windowSize=10):
+        """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520).
+        Returns (nmatches, vnMatches12, updated vbPrevMatched)."""
+        k1 = np.ascontiguousarray(k1, KP_DTYPE)
+        k2 = np.ascontiguousarray(k2, KP_DTYPE)
+        d1, d2 = _u8(d1).reshape(-1, 32), _u8(d2).reshape(-1, 32)
+        prev = np.ascontiguousarray(vbPrevMatched, np.float32).copy()
+        m12 = np.zeros(len(k1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_for_initialization(self._h, _p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2),
+                                                      *[float(b) for b in bounds], _p(prev), _p(m12), windowSize,
+                                                      self.mfNNratio, int(self.mbCheckOrientation), C.byref(nm)))
+        return nm.value, m12, prev
+
+    def ComputeStereoMatches(self, left, right, kl, dl, kr, dr, bf, maxD, minD=0.0, frame=0):
+        """Frame::ComputeStereoMatches (src/Frame.cc:481-655) on the device pyramids of two extractor handles.
+        Returns (n surviving matches, mvuRight, mvDepth)."""
+        kl = np.ascontiguousarray(kl, KP_DTYPE)
+        kr = np.ascontiguousarray(kr, KP_DTYPE)
+        dl, dr = _u8(dl).reshape(-1, 32), _u8(dr).reshape(-1, 32)
+        uR = np.zeros(len(kl), np.float32)
+        dep = np.zeros(len(kl), np.float32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_stereo_matches(self._h, left._h, right._h, frame, _p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr),
+                                           bf, minD, maxD, _p(uR), _p(dep), C.byref(nm)))
+        return nm.value, uR, dep
+
+
+def version():
+    return lib().orbx_version().decode()

@@ -1,0 +1,148 @@
+"""Parity of the CUDA extractor (liborbx.so through the C ABI) with the CPU oracle, stage by stage and end to end.
+Bit-exact everywhere: pyramid bytes, FAST candidates (order included), per-level keypoint counts, blurred levels,
+keypoint fields (angles included: the device fastAtan2 is op-for-op) and descriptor bytes."""
+import numpy as np
+import pytest
+
+import oracle_py as O
+import orbx
+from orbx import synth
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [  # (w, h, nfeatures)  BASELINE.json configs 1, 2, 3, 5 + the mono-init extractor (Tracking.cc:125)
+    (640, 480, 1000), (640, 480, 2000), (752, 480, 1200), (1241, 376, 2000), (1920, 1080, 4000)]
+
+
+def _compare_frame(ex, oe, img, stages=True, frame=0, result=None):
+    okps, odesc = oe(img)
+    if result is None:
+        kps, desc = ex(img)
+    else:
+        kps, desc = result
+    msgs = []
+    if stages:
+        for l in range(ex.nlevels):
+            assert ex.level_size(l) == oe.level_size(l)
+            if not np.array_equal(ex.pyramid_level(l, frame, border=19), oe.level_padded(l)):
+                msgs.append("pyramid level %d differs" % l)
+            gc, oc = ex.level_candidates(l, frame), oe.level_candidates(l)
+            if not np.array_equal(gc, oc):
+                msgs.append("FAST candidates level %d differ (%d vs %d)" % (l, len(gc), len(oc)))
+            if ex.level_count(l, frame) != oe.level_nkeys(l):
+                msgs.append("quadtree count level %d: %d vs %d" % (l, ex.level_count(l, frame), oe.level_nkeys(l)))
+            if not np.array_equal(ex.blurred_level(l, frame), oe.level_blurred(l)):
+                msgs.append("blurred level %d differs" % l)
+    if len(kps) != len(okps):
+        msgs.append("keypoint count %d vs %d" % (len(kps), len(okps)))
+    else:
+        for fld in KPF:
+            if not np.array_equal(kps[fld], okps[fld]):
+                bad = np.flatnonzero(kps[fld] != okps[fld])
+                msgs.append("field %s differs at %d keypoints (first %d: %r vs %r)" % (fld, len(bad), bad[0], kps[fld][bad[0]], okps[fld][bad[0]]))
+        if not np.array_equal(desc, odesc):
+            bits = int(np.unpackbits(desc ^ odesc).sum())
+            msgs.append("descriptors differ: %d bits in %d rows" % (bits, int((desc != odesc).any(axis=1).sum())))
+    assert not msgs, "; ".join(msgs)
+    return len(kps)
+
+
+KPF = ["x", "y", "size", "angle", "response", "octave", "class_id"]
+
+
+def test_tables_match_oracle():
+    for nf, sf, nl in [(1000, 1.2, 8), (2000, 1.2, 8), (1200, 1.2, 8), (4000, 1.2, 8), (500, 1.5, 4), (777, 1.1, 10)]:
+        ex = orbx.ORBextractor(nf, sf, nl, 20, 7)
+        oe = O.OracleExtractor(nf, sf, nl, 20, 7)
+        for a, b in zip(ex._tables(), oe.scale_tables()):
+            assert a.tobytes() == b.tobytes()
+        assert list(ex.features_per_level()) == list(oe.features_per_level())
+        assert list(ex.umax()) == list(oe.umax())
+        assert ex.GetLevels() == nl
+
+
+@pytest.mark.parametrize("w,h,nf", CONFIGS)
+def test_rects_frame_stage_by_stage(w, h, nf):
+    ex = orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
+    seed = {640: 1000, 752: 2000, 1241: 3000, 1920: 5000}[w]
+    n = _compare_frame(ex, oe, synth.rects(w, h, seed))
+    assert n > nf // 2
+
+
+@pytest.mark.parametrize("kind", ["texture", "lowcontrast", "flat"])
+def test_other_kinds_640x480(kind):
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    n = _compare_frame(ex, oe, synth.frame(kind, 640, 480, 1100))
+    if kind == "flat":
+        assert n == 0
+
+
+def test_many_frames_end_to_end():
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    for i in range(12):
+        _compare_frame(ex, oe, synth.rects(640, 480, 1000 + i), stages=False)
+
+
+def test_batch_equals_single_and_oracle():
+    B = 6
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    kinds = ["rects", "texture", "rects", "lowcontrast", "flat", "rects"]
+    imgs = [synth.frame(k, 640, 480, 1200 + i) for i, k in enumerate(kinds)]
+    res = ex.extract_batch(imgs)
+    for b in range(B):
+        _compare_frame(ex, oe, imgs[b], stages=(b in (1, 3)), frame=b, result=res[b])
+
+
+def test_strided_input_and_shape_change():
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    big = synth.rects(800, 600, 77)
+    view = big[40:40 + 480, 60:60 + 640]          # a sub-view, like a cv::Mat ROI
+    kps, desc = ex(view)
+    _compare_frame(ex, oe, np.ascontiguousarray(view), stages=False, result=(kps, desc))
+    _compare_frame(ex, oe, synth.rects(752, 480, 5), stages=False)     # re-plans for the new shape
+    _compare_frame(ex, oe, synth.rects(320, 240, 6), stages=True)
+
+
+def test_small_and_odd_parameters():
+    for (w, h, nf, sf, nl, ini, mn) in [(320, 240, 500, 1.2, 8, 20, 7), (401, 301, 300, 1.5, 4, 30, 10), (960, 540, 1500, 1.1, 10, 15, 5),
+                                        (640, 480, 50, 1.2, 8, 20, 7), (200, 640, 400, 1.2, 4, 20, 7)]:
+        ex = orbx.ORBextractor(nf, sf, nl, ini, mn)
+        oe = O.OracleExtractor(nf, sf, nl, ini, mn)
+        _compare_frame(ex, oe, synth.rects(w, h, w + h))
+        _compare_frame(ex, oe, synth.texture(w, h, w), stages=False)
+
+
+def test_empty_image_and_errors():
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    kps, desc = ex(np.zeros((0, 0), np.uint8))
+    assert len(kps) == 0 and desc.shape == (0, 32)
+    with pytest.raises(orbx.OrbxError):      # smaller than one FAST cell at the top level: the reference divides by zero
+        ex(np.zeros((64, 64), np.uint8))
+    with pytest.raises(orbx.OrbxError):
+        orbx.ORBextractor(1000, 1.2, 99, 20, 7)
+
+
+def test_fma_mode_matches_contracted_oracle():
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7)
+    ex.set_fma_mode(1)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7, fma_mode=1)
+    _compare_frame(ex, oe, synth.rects(640, 480, 1003), stages=False)
+
+
+def test_device_resident_input():
+    import torch
+    B = 4
+    imgs = np.stack([synth.rects(640, 480, 1300 + i) for i in range(B)])
+    d = torch.from_numpy(imgs).cuda()
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    torch.cuda.synchronize()
+    ex.extract_device(d.data_ptr(), B, 640, 480, 640, 640 * 480)
+    res = ex.fetch()
+    for b in range(B):
+        _compare_frame(ex, oe, imgs[b], stages=False, result=res[b])
