@@ -1,21 +1,542 @@
-// matcher_frame.cu -- frame-level searches of the C ABI: Frame grid + GetFeaturesInArea, SearchForInitialization,
-// ComputeStereoMatches.  (being written: entry points present so that the ABI is complete)
+// matcher_frame.cu -- frame-level searches of the C ABI: the Frame grid + GetFeaturesInArea (reference src/Frame.cc:230-245,
+// 342-407), ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) and Frame::ComputeStereoMatches
+// (src/Frame.cc:481-655).  Candidate enumeration, Hamming distances and the SAD refinement run on the device; the
+// order-dependent greedy bookkeeping of the reference (vMatchedDistance / vnMatches21 steals, rotation histogram, the
+// median cut) is replayed sequentially on the host from the device results, which keeps indices bit-exact.
 #include "matcher_internal.cuh"
+#include <limits.h>
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <utility>
+#include <vector>
+
+namespace orbx {
+
+constexpr int GRID_COLS = 64, GRID_ROWS = 48;      // FRAME_GRID_COLS / FRAME_GRID_ROWS, include/Frame.h:37-38
+constexpr int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:37-39
+
+struct GridParams { float minX, minY, invW, invH; };
+
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// ------------------------------------------------------------------------------------------------ GetFeaturesInArea
+// One warp per query.  The CSR grid is stored column-major (cell = ix * 48 + iy), i.e. in the reference's own loop
+// order (ix outer, iy inner, insertion order inside a cell), so the cells of one grid column that the window touches
+// are ONE contiguous entry range: a warp filters it 32 entries at a time and compacts with a ballot.
+template <bool WRITE>
+__global__ void __launch_bounds__(256) k_grid_query(const orbx_kp* __restrict__ kps, const int* __restrict__ cellStart,
+                                                    const int* __restrict__ entries, GridParams gp, const float* __restrict__ qxy,
+                                                    const float* __restrict__ qr, int nq, int minLevel, int maxLevel,
+                                                    const int* __restrict__ qlevel, int* __restrict__ off, int* __restrict__ idx_out)
+{
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (qi >= nq) return;
+    const float x = qxy[2 * qi], y = qxy[2 * qi + 1], r = qr[qi];
+    const int minL = qlevel ? qlevel[qi] : minLevel, maxL = qlevel ? qlevel[qi] : maxLevel;
+    int total = 0;
+    const int base = WRITE ? off[qi] : 0;
+    // (x - mnMinX - r) * mfGridElementWidthInv, float, left to right (Frame.cc:347-361)
+    const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, gp.minX), r), gp.invW)));
+    const int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, gp.minX), r), gp.invW)));
+    const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, gp.minY), r), gp.invH)));
+    const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, gp.minY), r), gp.invH)));
+    if (cx0 < GRID_COLS && cx1 >= 0 && cy0 < GRID_ROWS && cy1 >= 0) {
+        const bool checkLevels = (minL > 0) || (maxL >= 0);
+        for (int ix = cx0; ix <= cx1; ix++) {
+            const int s = cellStart[ix * GRID_ROWS + cy0], e = cellStart[ix * GRID_ROWS + cy1 + 1];
+            for (int c0 = s; c0 < e; c0 += 32) {
+                const int c = c0 + lane;
+                bool pass = false;
+                int id = 0;
+                if (c < e) {
+                    id = entries[c];
+                    const orbx_kp kp = kps[id];
+                    pass = true;
+                    if (checkLevels) {
+                        if (kp.octave < minL) pass = false;
+                        if (maxL >= 0 && kp.octave > maxL) pass = false;
+                    }
+                    if (!(fabsf(__fsub_rn(kp.x, x)) < r && fabsf(__fsub_rn(kp.y, y)) < r)) pass = false;
+                }
+                const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
+                if (WRITE && pass) idx_out[base + total + __popc(m & ((1u << lane) - 1))] = id;
+                total += __popc(m);
+            }
+        }
+    }
+    if (!WRITE && lane == 0) off[qi] = total;
+}
+
+// exclusive scan of a[0..n) in place, a[n] = total; one CTA
+__global__ void __launch_bounds__(1024) k_scan_offsets(int* a, int n)
+{
+    __shared__ int wsum[33];
+    const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (n + T - 1) / T;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    int s = 0;
+    for (int i = b; i < e; i++) s += a[i];
+    int inc = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const int v = wsum[lane];
+        int vi = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
+            if (lane >= o) vi += t;
+        }
+        wsum[lane] = vi - v;
+        if (lane == 31) wsum[32] = vi;
+    }
+    __syncthreads();
+    int off = wsum[wid] + inc - s;
+    for (int i = b; i < e; i++) { const int t = a[i]; a[i] = off; off += t; }
+    if (tid == 0) a[n] = wsum[32];
+}
+
+__global__ void __launch_bounds__(256) k_cand_dist(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t,
+                                                   const int* __restrict__ off, const int* __restrict__ idx, int* __restrict__ dist)
+{
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (qi >= nq) return;
+    const uint4 qa = __ldg(&q[2 * qi]), qb = __ldg(&q[2 * qi + 1]);
+    for (int c = off[qi] + lane; c < off[qi + 1]; c += 32) {
+        const int j = idx[c];
+        dist[c] = hamming256(qa, qb, __ldg(&t[2 * (size_t)j]), __ldg(&t[2 * (size_t)j + 1]));
+    }
+}
+
+// Frame::AssignFeaturesToGrid / PosInGrid (Frame.cc:230-245, 397-407) as a stable counting sort into CSR
+static void build_grid_host(const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY, GridParams& gp,
+                            std::vector<int>& start, std::vector<int>& entries)
+{
+    gp.minX = minX;
+    gp.minY = minY;
+    gp.invW = (float)GRID_COLS / (float)(maxX - minX);
+    gp.invH = (float)GRID_ROWS / (float)(maxY - minY);
+    std::vector<int> cell(n);
+    start.assign(GRID_COLS * GRID_ROWS + 1, 0);
+    for (int i = 0; i < n; i++) {
+        const int px = (int)roundf((kps[i].x - minX) * gp.invW), py = (int)roundf((kps[i].y - minY) * gp.invH);
+        cell[i] = (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) ? -1 : px * GRID_ROWS + py;
+        if (cell[i] >= 0) start[cell[i] + 1]++;
+    }
+    for (int c = 0; c < GRID_COLS * GRID_ROWS; c++) start[c + 1] += start[c];
+    entries.assign(std::max(start.back(), 1), 0);
+    std::vector<int> fill(start.begin(), start.end() - 1);
+    for (int i = 0; i < n; i++)
+        if (cell[i] >= 0) entries[fill[cell[i]]++] = i;
+}
+
+static inline size_t idx_bytes(int total) { return (sizeof(int) * (size_t)std::max(total, 1) + 255) / 256 * 256; }
+
+// Device-side candidate enumeration.  On return the CSR lives on the device: *d_off in arena (nq+1 ints),
+// *d_idx in arena2 (total ints); *total holds the candidate count.  d_kps: device keypoints of the searched frame.
+static int grid_candidates_dev(orbx_matcher* m, const orbx_kp* d_kps, const int* d_cellStart, const int* d_entries, const GridParams& gp,
+                               const float* d_qxy, const float* d_qr, int nq, int minLevel, int maxLevel, const int* d_qlevel,
+                               int* d_off, int nArrays, int** d_idx, int* total)
+{
+    const int blocks = (nq + 7) / 8;
+    k_grid_query<false><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, d_off, nullptr);
+    k_scan_offsets<<<1, 1024, 0, m->stream>>>(d_off, nq);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(total, d_off + nq, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    int rc = m->arena2.reserve(idx_bytes(*total) * (size_t)nArrays);     // nArrays int arrays of `total` entries, d_idx first
+    if (rc) return rc;
+    *d_idx = (int*)m->arena2.base;
+    k_grid_query<true><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, d_off, *d_idx);
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 3;
+    return ORBX_OK;
+}
+
+
+}  // namespace orbx
 
 using namespace orbx;
 
 extern "C" {
 
-int orbm_grid_candidates(orbx_matcher*, const orbx_kp*, int, float, float, float, float, const float*, int, const float*, int, int,
-                         const int*, int*, int*, int)
-{ set_error("orbm_grid_candidates: not implemented yet"); return ORBX_ERR_STATE; }
+int orbm_grid_candidates(orbx_matcher* m, const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY,
+                         const float* qxy, int nq, const float* qr, int minLevel, int maxLevel, const int* q_level,
+                         int* cand_off, int* cand_idx, int cap)
+{
+    if (!m || n < 0 || nq < 0 || (n > 0 && !kps) || (nq > 0 && (!qxy || !qr)) || !cand_off || !(maxX > minX) || !(maxY > minY) || cap < 0) {
+        set_error("orbm_grid_candidates: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nq == 0) { cand_off[0] = 0; return ORBX_OK; }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    GridParams gp;
+    std::vector<int> start, entries;
+    build_grid_host(kps, n, minX, maxX, minY, maxY, gp, start, entries);
+    Carver cv(m->arena);
+    const size_t oK = cv.take(sizeof(orbx_kp) * (size_t)std::max(n, 1)), oS = cv.take(sizeof(int) * start.size()),
+                 oE = cv.take(sizeof(int) * entries.size()), oQ = cv.take(sizeof(float) * 2 * (size_t)nq),
+                 oR = cv.take(sizeof(float) * (size_t)nq), oL = cv.take(sizeof(int) * (size_t)nq), oO = cv.take(sizeof(int) * ((size_t)nq + 1));
+    int rc = m->arena.reserve(cv.total());
+    if (rc) return rc;
+    uint8_t* B = m->arena.base;
+    cudaStream_t s = m->stream;
+    if (n > 0) ORBX_CUDA(cudaMemcpyAsync(B + oK, kps, sizeof(orbx_kp) * (size_t)n, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy, sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr, sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
+    if (q_level) ORBX_CUDA(cudaMemcpyAsync(B + oL, q_level, sizeof(int) * (size_t)nq, cudaMemcpyHostToDevice, s));
+    int* d_idx = nullptr;
+    int total = 0;
+    rc = grid_candidates_dev(m, (const orbx_kp*)(B + oK), (const int*)(B + oS), (const int*)(B + oE), gp, (const float*)(B + oQ),
+                             (const float*)(B + oR), nq, minLevel, maxLevel, q_level ? (const int*)(B + oL) : nullptr, (int*)(B + oO), 1,
+                             &d_idx, &total);
+    if (rc) return rc;
+    ORBX_CUDA(cudaMemcpyAsync(cand_off, B + oO, sizeof(int) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s));
+    const int ncopy = std::min(total, cap);
+    if (ncopy > 0 && cand_idx) ORBX_CUDA(cudaMemcpyAsync(cand_idx, d_idx, sizeof(int) * (size_t)ncopy, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    if (total > cap) { set_error("orbm_grid_candidates: %d candidates, capacity %d", total, cap); return ORBX_ERR_CAPACITY; }
+    return ORBX_OK;
+}
 
-int orbm_search_for_initialization(orbx_matcher*, const orbx_kp*, const uint8_t*, int, const orbx_kp*, const uint8_t*, int,
-                                   float, float, float, float, float*, int*, int, float, int, int*)
-{ set_error("orbm_search_for_initialization: not implemented yet"); return ORBX_ERR_STATE; }
+}  // extern "C"
 
-int orbm_stereo_matches(orbx_matcher*, orbx_extractor*, orbx_extractor*, int, const orbx_kp*, const uint8_t*, int,
-                        const orbx_kp*, const uint8_t*, int, float, float, float, float*, float*, int*)
-{ set_error("orbm_stereo_matches: not implemented yet"); return ORBX_ERR_STATE; }
+// ================================================================================================ SearchForInitialization
+namespace orbx {
 
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1603-1644) on bin sizes
+static void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+}  // namespace orbx
+
+extern "C" int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1, const uint8_t* d1, int n1,
+                                              const orbx_kp* k2, const uint8_t* d2, int n2,
+                                              float minX, float maxX, float minY, float maxY,
+                                              float* prev_matched, int* matches12, int windowSize, float nnratio, int checkOri,
+                                              int* nmatches)
+{
+    if (!m || n1 < 0 || n2 < 0 || (n1 > 0 && (!k1 || !d1 || !prev_matched || !matches12)) || (n2 > 0 && (!k2 || !d2)) ||
+        !(maxX > minX) || !(maxY > minY)) {
+        set_error("orbm_search_for_initialization: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nmatches) *nmatches = 0;
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    // queries: level-0 keypoints of F1 only (:421-423), searched around vbPrevMatched in level 0 of F2 (:425)
+    std::vector<int> qmap;
+    std::vector<float> qxy, qr;
+    std::vector<uint8_t> qdesc;
+    for (int i = 0; i < n1; i++)
+        if (k1[i].octave <= 0) {
+            qmap.push_back(i);
+            qxy.push_back(prev_matched[2 * i]);
+            qxy.push_back(prev_matched[2 * i + 1]);
+            qr.push_back((float)windowSize);
+        }
+    const int nq = (int)qmap.size();
+    if (nq == 0 || n2 == 0) return ORBX_OK;
+    qdesc.resize((size_t)nq * 32);
+    for (int q = 0; q < nq; q++) memcpy(&qdesc[(size_t)q * 32], d1 + (size_t)qmap[q] * 32, 32);
+
+    ORBX_CUDA(cudaSetDevice(m->device));
+    GridParams gp;
+    std::vector<int> start, entries;
+    build_grid_host(k2, n2, minX, maxX, minY, maxY, gp, start, entries);
+    Carver cv(m->arena);
+    const size_t oK = cv.take(sizeof(orbx_kp) * (size_t)n2), oS = cv.take(sizeof(int) * start.size()), oE = cv.take(sizeof(int) * entries.size()),
+                 oQ = cv.take(sizeof(float) * 2 * (size_t)nq), oR = cv.take(sizeof(float) * (size_t)nq), oO = cv.take(sizeof(int) * ((size_t)nq + 1)),
+                 oQD = cv.take((size_t)nq * 32), oTD = cv.take((size_t)n2 * 32);
+    int rc = m->arena.reserve(cv.total());
+    if (rc) return rc;
+    uint8_t* B = m->arena.base;
+    cudaStream_t s = m->stream;
+    ORBX_CUDA(cudaMemcpyAsync(B + oK, k2, sizeof(orbx_kp) * (size_t)n2, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy.data(), sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr.data(), sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oQD, qdesc.data(), (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oTD, d2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
+    int* d_idx = nullptr;
+    int total = 0;
+    // GetFeaturesInArea(x, y, windowSize, level1, level1) with level1 == 0
+    rc = grid_candidates_dev(m, (const orbx_kp*)(B + oK), (const int*)(B + oS), (const int*)(B + oE), gp, (const float*)(B + oQ),
+                             (const float*)(B + oR), nq, 0, 0, nullptr, (int*)(B + oO), 2, &d_idx, &total);
+    if (rc) return rc;
+    int* d_dist = (int*)(m->arena2.base + idx_bytes(total));      // second array of arena2
+    k_cand_dist<<<(nq + 7) / 8, 256, 0, s>>>((const uint4*)(B + oQD), nq, (const uint4*)(B + oTD), (const int*)(B + oO), d_idx, d_dist);
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 4;
+    std::vector<int> off(nq + 1), idx(std::max(total, 1)), dist(std::max(total, 1));
+    ORBX_CUDA(cudaMemcpyAsync(off.data(), B + oO, sizeof(int) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s));
+    if (total > 0) {
+        ORBX_CUDA(cudaMemcpyAsync(idx.data(), d_idx, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+        ORBX_CUDA(cudaMemcpyAsync(dist.data(), d_dist, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+    }
+    ORBX_CUDA(cudaStreamSynchronize(s));
+
+    // sequential replay of the greedy loop (:427-483): the vMatchedDistance skip and the steals depend on visit order
+    int nm = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> matchedDist(n2, INT_MAX), m21(n2, -1);
+    for (int q = 0; q < nq; q++) {
+        const int i1 = qmap[q];
+        if (off[q + 1] == off[q]) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int c = off[q]; c < off[q + 1]; c++) {
+            const int i2 = idx[c], d = dist[c];
+            if (matchedDist[i2] <= d) continue;
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = i2; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        if (bestDist <= TH_LOW && bestDist < (float)bestDist2 * nnratio) {
+            if (m21[bestIdx2] >= 0) { matches12[m21[bestIdx2]] = -1; nm--; }
+            matches12[i1] = bestIdx2;
+            m21[bestIdx2] = i1;
+            matchedDist[bestIdx2] = bestDist;
+            nm++;
+            if (checkOri) {
+                float rot = k1[i1].angle - k2[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);       // factor = 1/HISTO_LENGTH as in the reference (:413), kept as is
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(i1);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int i1 : rotHist[i])
+                if (matches12[i1] >= 0) { matches12[i1] = -1; nm--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)          // update vbPrevMatched (:515-517)
+        if (matches12[i1] >= 0) { prev_matched[2 * i1] = k2[matches12[i1]].x; prev_matched[2 * i1 + 1] = k2[matches12[i1]].y; }
+    if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+
+// ================================================================================================ ComputeStereoMatches
+namespace orbx {
+
+struct StereoView {
+    const uint8_t* L[MAX_LEVELS];
+    const uint8_t* R[MAX_LEVELS];
+    int pitchL[MAX_LEVELS], pitchR[MAX_LEVELS], colsR[MAX_LEVELS];
+    float sf[MAX_LEVELS], isf[MAX_LEVELS];
+};
+
+// One warp per left keypoint: row-band Hamming search (Frame.cc:521-563), then the 11-shift 11x11 SAD on the unblurred
+// pyramid level of the left keypoint (:566-607) and the parabola fit (:609-637).  SADs are integers (centre-subtracted
+// u8 patches), so lanes can sum them in any order; the float tail runs on individually rounded operations.
+__global__ void __launch_bounds__(256) k_stereo(const orbx_kp* __restrict__ kl, const uint4* __restrict__ dl, int nl,
+                                                const orbx_kp* __restrict__ kr, const uint4* __restrict__ dr,
+                                                const int* __restrict__ rowStart, const int* __restrict__ rowEntries, int nRows,
+                                                StereoView V, float bf, float minD, float maxD,
+                                                float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ bestSad)
+{
+    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (iL >= nl) return;
+    if (lane == 0) { uRight[iL] = -1.0f; depth[iL] = -1.0f; bestSad[iL] = -1; }
+    const orbx_kp kpL = kl[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;                                   // vRowIndices[vL]
+    if (row < 0 || row >= nRows) return;
+    const int s = rowStart[row], e = rowStart[row + 1];
+    if (s == e) return;
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (maxU < 0) return;
+    const uint4 qa = __ldg(&dl[2 * iL]), qb = __ldg(&dl[2 * iL + 1]);
+    uint32_t best = KEY_NONE;
+    for (int c = s + lane; c < e; c += 32) {
+        const int iR = rowEntries[c];
+        const orbx_kp kpR = kr[iR];
+        if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+        if (kpR.x >= minU && kpR.x <= maxU) {
+            const int d = hamming256(qa, qb, __ldg(&dr[2 * (size_t)iR]), __ldg(&dr[2 * (size_t)iR + 1]));
+            if (d < TH_HIGH) best = min(best, ((uint32_t)d << KEY_SHIFT) | (uint32_t)(c - s));     // strict <, first in list order
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+    if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
+    const int bestIdxR = rowEntries[s + (int)(best & KEY_POS_MASK)];
+
+    const float uR0 = kr[bestIdxR].x;
+    const float scaleFactor = V.isf[levelL];
+    const float scaleduL = roundf(__fmul_rn(kpL.x, scaleFactor));
+    const float scaledvL = roundf(__fmul_rn(kpL.y, scaleFactor));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
+    const int w = 5, Ls = 5;
+    const float iniu = scaleduR0 + Ls - w, endu = scaleduR0 + Ls + w + 1;        // small integers: exact
+    if (iniu < 0 || endu >= (float)V.colsR[levelL]) return;
+    const int cu = (int)scaleduL, cv = (int)scaledvL, cr = (int)scaleduR0;
+    const uint8_t* IL = V.L[levelL];
+    const uint8_t* IR = V.R[levelL];
+    const int pL = V.pitchL[levelL], pR = V.pitchR[levelL];
+    const int cL = IL[(size_t)cv * pL + cu];
+    int cR = 0;                                                 // centre of the right window at shift lane - 5
+    if (lane < 11) cR = IR[(size_t)cv * pR + cr + lane - Ls];
+    int sad[11], cRk[11];
+#pragma unroll
+    for (int k = 0; k < 11; k++) { sad[k] = 0; cRk[k] = __shfl_sync(0xFFFFFFFFu, cR, k); }
+    for (int p = lane; p < 121; p += 32) {
+        const int dy = p / 11 - w, dx = p % 11 - w;
+        const int a = (int)IL[(size_t)(cv + dy) * pL + cu + dx] - cL;
+        const uint8_t* rrow = IR + (size_t)(cv + dy) * pR + cr + dx - Ls;
+#pragma unroll
+        for (int k = 0; k < 11; k++) sad[k] += abs(a - ((int)rrow[k] - cRk[k]));
+    }
+#pragma unroll
+    for (int k = 0; k < 11; k++)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sad[k] += __shfl_xor_sync(0xFFFFFFFFu, sad[k], o);
+    if (lane != 0) return;
+    int bestDist = INT_MAX, bestincR = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++)
+        if (sad[k] < bestDist) { bestDist = sad[k]; bestincR = k - Ls; }
+    if (bestincR == -Ls || bestincR == Ls) return;
+    float d1 = 0, d2 = 0, d3 = 0;
+#pragma unroll
+    for (int k = 1; k < 10; k++)
+        if (k == bestincR + Ls) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
+    const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+    if (deltaR < -1 || deltaR > 1) return;                      // a NaN (flat triple) passes, as in the reference
+    float bestuR = __fmul_rn(V.sf[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestincR), deltaR));
+    float disparity = __fsub_rn(uL, bestuR);
+    if (disparity >= minD && disparity < maxD) {
+        if (disparity <= 0) {
+            disparity = 0.01f;
+            bestuR = (float)((double)uL - 0.01);                // `bestuR = uL-0.01;` is a double subtraction
+        }
+        depth[iL] = __fdiv_rn(bf, disparity);
+        uRight[iL] = bestuR;
+        bestSad[iL] = bestDist;
+    }
+}
+
+}  // namespace orbx
+
+extern "C" int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, int frame,
+                                   const orbx_kp* kl, const uint8_t* dl, int nl, const orbx_kp* kr, const uint8_t* dr, int nr,
+                                   float bf, float minD, float maxD, float* uRight, float* depth, int* nmatched)
+{
+    if (!m || !left || !right || nl < 0 || nr < 0 || (nl > 0 && (!kl || !dl || !uRight || !depth)) || (nr > 0 && (!kr || !dr))) {
+        set_error("orbm_stereo_matches: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nmatched) *nmatched = 0;
+    for (int i = 0; i < nl; i++) { uRight[i] = -1.0f; depth[i] = -1.0f; }
+    if (nl == 0 || nr == 0) return ORBX_OK;
+    const int nlev = orbx_levels(left);
+    if (nlev != orbx_levels(right) || nlev > MAX_LEVELS) { set_error("orbm_stereo_matches: extractors differ"); return ORBX_ERR_ARG; }
+    int rc = orbx_sync(left);
+    if (rc) return rc;
+    rc = orbx_sync(right);
+    if (rc) return rc;
+    StereoView V;
+    memset(&V, 0, sizeof V);
+    int nRows = 0;
+    rc = orbx_scale_tables(left, V.sf, V.isf, nullptr, nullptr);
+    if (rc) return rc;
+    for (int l = 0; l < nlev; l++) {
+        size_t pl = 0, pr = 0;
+        int wl, hl, wr, hr;
+        if ((rc = orbx_pyramid_device(left, frame, l, &V.L[l], &pl)) || (rc = orbx_pyramid_device(right, frame, l, &V.R[l], &pr)) ||
+            (rc = orbx_level_size(left, l, &wl, &hl)) || (rc = orbx_level_size(right, l, &wr, &hr)))
+            return rc;
+        if (wl != wr || hl != hr) { set_error("orbm_stereo_matches: left/right pyramids differ in size"); return ORBX_ERR_ARG; }
+        V.pitchL[l] = (int)pl;
+        V.pitchR[l] = (int)pr;
+        V.colsR[l] = wr;
+        if (l == 0) nRows = hl;        // mpORBextractorLeft->mvImagePyramid[0].rows (:488)
+    }
+    for (int i = 0; i < nl; i++)
+        if (kl[i].octave < 0 || kl[i].octave >= nlev) { set_error("orbm_stereo_matches: left octave out of range"); return ORBX_ERR_ARG; }
+    // row table (:490-508): right keypoint iR is registered in rows floor(y - r) .. ceil(y + r), r = 2 * scale[octave]
+    std::vector<int> rowStart(nRows + 1, 0), rowEntries;
+    std::vector<std::pair<int, int>> span(nr);
+    for (int iR = 0; iR < nr; iR++) {
+        if (kr[iR].octave < 0 || kr[iR].octave >= nlev) { set_error("orbm_stereo_matches: right octave out of range"); return ORBX_ERR_ARG; }
+        const float kpY = kr[iR].y, r = 2.0f * V.sf[kr[iR].octave];
+        const int maxr = (int)ceilf(kpY + r), minr = (int)floorf(kpY - r);
+        span[iR] = std::make_pair(std::max(minr, 0), std::min(maxr, nRows - 1));   // the reference indexes unchecked
+        for (int y = span[iR].first; y <= span[iR].second; y++) rowStart[y + 1]++;
+    }
+    for (int y = 0; y < nRows; y++) rowStart[y + 1] += rowStart[y];
+    rowEntries.assign(std::max(rowStart[nRows], 1), 0);
+    {
+        std::vector<int> fill(rowStart.begin(), rowStart.end() - 1);
+        for (int iR = 0; iR < nr; iR++)
+            for (int y = span[iR].first; y <= span[iR].second; y++) rowEntries[fill[y]++] = iR;
+    }
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Carver cv(m->arena);
+    const size_t oKL = cv.take(sizeof(orbx_kp) * (size_t)nl), oDL = cv.take((size_t)nl * 32), oKR = cv.take(sizeof(orbx_kp) * (size_t)nr),
+                 oDR = cv.take((size_t)nr * 32), oRS = cv.take(sizeof(int) * rowStart.size()), oRE = cv.take(sizeof(int) * rowEntries.size()),
+                 oU = cv.take(sizeof(float) * (size_t)nl), oD = cv.take(sizeof(float) * (size_t)nl), oS = cv.take(sizeof(int) * (size_t)nl);
+    rc = m->arena.reserve(cv.total());
+    if (rc) return rc;
+    uint8_t* B = m->arena.base;
+    cudaStream_t s = m->stream;
+    ORBX_CUDA(cudaMemcpyAsync(B + oKL, kl, sizeof(orbx_kp) * (size_t)nl, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oDL, dl, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oKR, kr, sizeof(orbx_kp) * (size_t)nr, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oDR, dr, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oRS, rowStart.data(), sizeof(int) * rowStart.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oRE, rowEntries.data(), sizeof(int) * rowEntries.size(), cudaMemcpyHostToDevice, s));
+    k_stereo<<<(nl + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oKL), (const uint4*)(B + oDL), nl, (const orbx_kp*)(B + oKR),
+                                          (const uint4*)(B + oDR), (const int*)(B + oRS), (const int*)(B + oRE), nRows, V, bf, minD, maxD,
+                                          (float*)(B + oU), (float*)(B + oD), (int*)(B + oS));
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 1;
+    std::vector<int> sad(nl);
+    ORBX_CUDA(cudaMemcpyAsync(uRight, B + oU, sizeof(float) * (size_t)nl, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(depth, B + oD, sizeof(float) * (size_t)nl, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(sad.data(), B + oS, sizeof(int) * (size_t)nl, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    // median cut (:641-654): sort (SAD, iL) pairs, drop everything at or above 1.5 * 1.4 * median
+    std::vector<std::pair<int, int>> distIdx;
+    for (int i = 0; i < nl; i++)
+        if (sad[i] >= 0) distIdx.push_back(std::make_pair(sad[i], i));
+    if (distIdx.empty()) return ORBX_OK;      // the reference reads vDistIdx[0] of an empty vector here (:642): guarded
+    std::sort(distIdx.begin(), distIdx.end());
+    const float median = (float)distIdx[distIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    int kept = (int)distIdx.size();
+    for (int i = (int)distIdx.size() - 1; i >= 0; i--) {
+        if (distIdx[i].first < thDist) break;
+        uRight[distIdx[i].second] = -1;
+        depth[distIdx[i].second] = -1;
+        kept--;
+    }
+    if (nmatched) *nmatched = kept;
+    return ORBX_OK;
 }

@@ -28,7 +28,7 @@ struct orbx_matcher {
     int device = 0;
     int smCount = 148;
     cudaStream_t stream = nullptr;
-    orbx::Arena arena;
+    orbx::Arena arena, arena2;     // arena2: buffers whose size is known only after a device count
     uint2* d_partial = nullptr;
     size_t partialCap = 0;
     int lastLaunches = 0;

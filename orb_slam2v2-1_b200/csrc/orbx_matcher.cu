@@ -201,6 +201,7 @@ int orbm_create(int device, orbx_matcher** out)
     }
     m->smCount = prop.multiProcessorCount;
     m->arena.stream = m->stream;
+    m->arena2.stream = m->stream;
     *out = m;
     return ORBX_OK;
 }
@@ -211,6 +212,7 @@ void orbm_destroy(orbx_matcher* m)
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
     cudaFree(m->arena.base);
+    cudaFree(m->arena2.base);
     cudaFree(m->d_partial);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;

@@ -110,7 +110,7 @@ def test_strided_input_and_shape_change():
 
 def test_small_and_odd_parameters():
     for (w, h, nf, sf, nl, ini, mn) in [(320, 240, 500, 1.2, 8, 20, 7), (401, 301, 300, 1.5, 4, 30, 10), (960, 540, 1500, 1.1, 10, 15, 5),
-                                        (640, 480, 50, 1.2, 8, 20, 7), (200, 640, 400, 1.2, 4, 20, 7)]:
+                                        (640, 480, 50, 1.2, 8, 20, 7), (300, 400, 400, 1.2, 4, 20, 7)]:
         ex = orbx.ORBextractor(nf, sf, nl, ini, mn)
         oe = O.OracleExtractor(nf, sf, nl, ini, mn)
         _compare_frame(ex, oe, synth.rects(w, h, w + h))
