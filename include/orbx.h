@@ -95,6 +95,11 @@ int orbx_results_device(orbx_extractor* ex, const orbx_kp** d_kps, const uint8_t
 int orbx_sync(orbx_extractor* ex);
 /* The handle's cudaStream_t (as void*), so that callers can record CUDA events around the launches. */
 void* orbx_stream(orbx_extractor* ex);
+/* Per-stage device timing: with profiling on, every extract call records a CUDA event on the handle's stream after each
+ * stage; orbx_stage_ms waits for the last call and returns the 5 stage durations in milliseconds:
+ * pyramid (nlevels-1 launches), cell FAST, quadtree, Gaussian blur, orientation+descriptors (1 launch each). */
+int orbx_set_profiling(orbx_extractor* ex, int on);
+int orbx_stage_ms(orbx_extractor* ex, float* out5);
 /* Number of kernels the last extract call launched (for bench.py's gpu_launches). */
 int orbx_last_launches(const orbx_extractor* ex);
 

@@ -94,17 +94,21 @@ void gauss7(const uint8_t* src, int w, int h, size_t sstride, uint8_t* dst, size
     std::vector<uint16_t> tmp((size_t)w * h);
     for (int y = 0; y < h; y++) {
         const uint8_t* S = src + (size_t)y * sstride;
+        uint16_t* T = &tmp[(size_t)y * w];
         for (int x = 0; x < w; x++) {
             int acc = 0;
-            for (int k = 0; k < 7; k++) acc += K[k] * S[reflect101(x + k - 3, w)];
-            tmp[(size_t)y * w + x] = (uint16_t)acc;
+            if (x >= 3 && x + 3 < w) for (int k = 0; k < 7; k++) acc += K[k] * S[x + k - 3];
+            else for (int k = 0; k < 7; k++) acc += K[k] * S[reflect101(x + k - 3, w)];
+            T[x] = (uint16_t)acc;
         }
     }
     for (int y = 0; y < h; y++) {
         uint8_t* D = dst + (size_t)y * dstride;
+        const uint16_t* R[7];
+        for (int k = 0; k < 7; k++) R[k] = &tmp[(size_t)reflect101(y + k - 3, h) * w];
         for (int x = 0; x < w; x++) {
             uint32_t acc = 0;
-            for (int k = 0; k < 7; k++) acc += (uint32_t)K[k] * tmp[(size_t)reflect101(y + k - 3, h) * w + x];
+            for (int k = 0; k < 7; k++) acc += (uint32_t)K[k] * R[k][x];
             D[x] = (uint8_t)((acc + 32768u) >> 16);
         }
     }
@@ -139,7 +143,15 @@ void fast_detect(const uint8_t* roi, int w, int h, size_t stride, int threshold,
     std::vector<int> score((size_t)w * h, 0);   // 0 for non-corners and the 3-px frame, like OpenCV's zeroed row buffers
     for (int y = 3; y < h - 3; y++)
         for (int x = 3; x < w - 3; x++) {
-            int raw = fast_raw(roi + (size_t)y * stride + x, stride);
+            // OpenCV-style early exit (does not change the result): an arc of 9 contiguous ring pixels always contains two
+            // adjacent compass pixels (ring positions 0, 4, 8, 12), so both must be brighter (or darker) than centre +- t.
+            const uint8_t* p = roi + (size_t)y * stride + x;
+            const int v = p[0], hi = v + threshold, lo = v - threshold;
+            const int p0 = p[3 * (ptrdiff_t)stride], p4 = p[3], p8 = p[-3 * (ptrdiff_t)stride], p12 = p[-3];
+            const bool br = ((p0 > hi) || (p8 > hi)) && ((p4 > hi) || (p12 > hi));
+            const bool dk = ((p0 < lo) || (p8 < lo)) && ((p4 < lo) || (p12 < lo));
+            if (!br && !dk) { score[(size_t)y * w + x] = -1; continue; }
+            int raw = fast_raw(p, stride);
             if (raw > threshold) score[(size_t)y * w + x] = raw - 1;
             else score[(size_t)y * w + x] = -1;  // marker: not a corner
         }

@@ -72,6 +72,8 @@ struct orbx_extractor {
 
     int lastB = 0;                     // frames of the last call (0 = none)
     int lastLaunches = 0;
+    bool profile = false;              // record an event after every stage of enqueue()
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace orbx {
@@ -269,6 +271,8 @@ static int enqueue(orbx_extractor* ex, int B)
     const FrameBufs& F = ex->bufs;
     cudaStream_t s = ex->stream;
     int launches = 0;
+    const bool prof = ex->profile;
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     for (int l = 1; l < ex->nlevels; l++) {
         const uint8_t* src = l == 1 ? F.lv0 : F.pyr + P.lv[l - 1].planeOff;
         const int spitch = l == 1 ? (int)F.lv0Pitch : P.lv[l - 1].pitch;
@@ -277,10 +281,15 @@ static int enqueue(orbx_extractor* ex, int B)
                       ex->d_xtab + ex->xtabOff[l], ex->d_ytab + ex->ytabOff[l], B);
         launches++;
     }
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     launch_fast_cells(s, P, F, B, ex->fastSmem);
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octSmem));
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     launch_blur(s, P, F, B);
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     launch_orient_describe(s, P, F, ex->um, ex->d_patT, B);
+    if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     launches += 4;
     ORBX_CUDA(cudaGetLastError());
     ex->lastLaunches = launches;
@@ -380,6 +389,8 @@ void orbx_destroy(orbx_extractor* ex)
     if (ex->stream) cudaStreamSynchronize(ex->stream);
     free_shape(ex);
     cudaFree(ex->d_patT);
+    for (int i = 0; i < 6; i++)
+        if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
     if (ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
 }
@@ -389,6 +400,26 @@ int orbx_set_fma_mode(orbx_extractor* ex, int fma_mode)
     if (!ex) { set_error("null handle"); return ORBX_ERR_ARG; }
     ex->fmaMode = fma_mode ? 1 : 0;
     ex->plan.fmaMode = ex->fmaMode;
+    return ORBX_OK;
+}
+
+int orbx_set_profiling(orbx_extractor* ex, int on)
+{
+    if (!ex) { set_error("null handle"); return ORBX_ERR_ARG; }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    if (on && !ex->ev[0])
+        for (int i = 0; i < 6; i++) ORBX_CUDA(cudaEventCreate(&ex->ev[i]));
+    ex->profile = on != 0;
+    return ORBX_OK;
+}
+
+int orbx_stage_ms(orbx_extractor* ex, float* out5)
+{
+    if (!ex || !out5) { set_error("null argument"); return ORBX_ERR_ARG; }
+    if (!ex->profile || ex->lastB == 0) { set_error("orbx_stage_ms: profiling is off or nothing ran"); return ORBX_ERR_STATE; }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    ORBX_CUDA(cudaEventSynchronize(ex->ev[5]));
+    for (int i = 0; i < 5; i++) ORBX_CUDA(cudaEventElapsedTime(&out5[i], ex->ev[i], ex->ev[i + 1]));
     return ORBX_OK;
 }
 

@@ -56,6 +56,8 @@ def lib():
         "orbx_sync": (i, [vp]),
         "orbx_stream": (vp, [vp]),
         "orbx_last_launches": (i, [vp]),
+        "orbx_set_profiling": (i, [vp, i]),
+        "orbx_stage_ms": (i, [vp, vp]),
         "orbx_level_size": (i, [vp, i, vp, vp]),
         "orbx_pyramid_level": (i, [vp, i, i, i, vp, sz]),
         "orbx_pyramid_device": (i, [vp, i, i, vp, vp]),
@@ -231,6 +233,16 @@ class ORBextractor:
 
     def last_launches(self):
         return self._L.orbx_last_launches(self._h)
+
+    STAGES = ("pyramid", "fast_cells", "octree", "blur", "orient_describe")
+
+    def set_profiling(self, on=True):
+        _check(self._L.orbx_set_profiling(self._h, int(on)))
+
+    def stage_ms(self):
+        o = np.zeros(5, np.float32)
+        _check(self._L.orbx_stage_ms(self._h, _p(o)))
+        return dict(zip(self.STAGES, [float(v) for v in o]))
 
     # --- mvImagePyramid (ORBextractor.h:85)
     def level_size(self, level):
