@@ -26,43 +26,70 @@ __device__ __forceinline__ int level_of_cell(const Plan& P, int cell)
 }
 
 // ------------------------------------------------------------------------------------------------ pyramid
-// cv::resize INTER_LINEAR, 8-bit: 11-bit coefficients (host tables), horizontal pass in int32, vertical pass
-// (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.  One thread = 4 horizontally adjacent output pixels.
+// cv::resize INTER_LINEAR, 8-bit: 11-bit coefficients (host tables), horizontal pass H = S[sx]*a0 + S[sx+1]*a1 in int32,
+// vertical pass (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.
+// One thread = 4 adjacent output columns x RS_ROWS output rows.  The 8 source bytes a row needs lie within 8 contiguous
+// bytes: three aligned word loads + a funnel shift + two PRMTs (selectors precomputed per column group on the host)
+// replace 8 byte loads.  Walking down the rows, the horizontal pass of source row sy+1 is reused as row sy of the next
+// output row whenever the source advances by exactly one row (5 of 6 rows at scale 1.2).
+constexpr int RS_ROWS = 8;
+
+struct ResizeCols { int4 a, b; };   // a = {w0 | w1 << 16, w2 | shift << 16, selL, selR}; b = 4 x (a0 | a1 << 16)
+
+__device__ __forceinline__ void resize_hrow(const uint8_t* row, const ResizeCols& c, int H[4])
+{
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(row);
+    const uint32_t w0 = __ldg(r + (c.a.x & 0xFFFF)), w1 = __ldg(r + (c.a.x >> 16)), w2 = __ldg(r + (c.a.y & 0xFFFF));
+    const int sh = c.a.y >> 16;
+    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+    const uint32_t L = __byte_perm(lo, hi, c.a.z), R = __byte_perm(lo, hi, c.a.w);
+    H[0] = ((int)(L & 0xFF) * (c.b.x & 0xFFFF) + (int)(R & 0xFF) * (c.b.x >> 16)) >> 4;
+    H[1] = ((int)((L >> 8) & 0xFF) * (c.b.y & 0xFFFF) + (int)((R >> 8) & 0xFF) * (c.b.y >> 16)) >> 4;
+    H[2] = ((int)((L >> 16) & 0xFF) * (c.b.z & 0xFFFF) + (int)((R >> 16) & 0xFF) * (c.b.z >> 16)) >> 4;
+    H[3] = ((int)(L >> 24) * (c.b.w & 0xFFFF) + (int)(R >> 24) * (c.b.w >> 16)) >> 4;
+}
+
 __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, int spitch, size_t sframe,
                                                 uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dframe,
-                                                const int2* __restrict__ xtab, const int4* __restrict__ ytab)
+                                                const ResizeCols* __restrict__ xtab, const int4* __restrict__ ytab)
 {
     const int f = blockIdx.z;
-    const int dy = blockIdx.y * blockDim.y + threadIdx.y;
-    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (dy >= dh || x4 >= dw) return;
-    const int4 yy = __ldg(&ytab[dy]);
-    const uint8_t* S0 = src + (size_t)f * sframe + (size_t)yy.x * spitch;
-    const uint8_t* S1 = src + (size_t)f * sframe + (size_t)yy.y * spitch;
-    uint32_t out = 0;
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;          // column group
+    const int y0 = (blockIdx.y * blockDim.y + threadIdx.y) * RS_ROWS;
+    if (g * 4 >= dw || y0 >= dh) return;
+    ResizeCols c;
+    c.a = __ldg(&xtab[g].a);
+    c.b = __ldg(&xtab[g].b);
+    const uint8_t* S = src + (size_t)f * sframe;
+    uint8_t* D = dst + (size_t)f * dframe + (size_t)g * 4;
+    int cached = -1, Hc[4] = {0, 0, 0, 0};
+    const int y1 = min(y0 + RS_ROWS, dh);
+    for (int dy = y0; dy < y1; dy++) {
+        const int4 yy = __ldg(&ytab[dy]);                          // {sy0, sy1 (clamped), b0, b1}
+        int H0[4], H1[4];
+        if (yy.x == cached) { H0[0] = Hc[0]; H0[1] = Hc[1]; H0[2] = Hc[2]; H0[3] = Hc[3]; }
+        else resize_hrow(S + (size_t)yy.x * spitch, c, H0);
+        if (yy.y == yy.x) { H1[0] = H0[0]; H1[1] = H0[1]; H1[2] = H0[2]; H1[3] = H0[3]; }
+        else resize_hrow(S + (size_t)yy.y * spitch, c, H1);
+        uint32_t out = 0;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int dx = x4 + k;
-        if (dx < dw) {
-            const int2 t = __ldg(&xtab[dx]);
-            const int sx = t.x & 0xFFFF, sx1 = t.x >> 16;
-            const int a0 = t.y & 0xFFFF, a1 = t.y >> 16;
-            const int H0 = (int)__ldg(S0 + sx) * a0 + (int)__ldg(S0 + sx1) * a1;
-            const int H1 = (int)__ldg(S1 + sx) * a0 + (int)__ldg(S1 + sx1) * a1;
-            int v = (((yy.z * (H0 >> 4)) >> 16) + ((yy.w * (H1 >> 4)) >> 16) + 2) >> 2;
+        for (int k = 0; k < 4; k++) {
+            int v = (((yy.z * H0[k]) >> 16) + ((yy.w * H1[k]) >> 16) + 2) >> 2;
             v = min(max(v, 0), 255);
             out |= (uint32_t)v << (8 * k);
+            Hc[k] = H1[k];
         }
+        cached = yy.y;
+        *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = out;     // pitch is a multiple of 32: the last word may pad
     }
-    *reinterpret_cast<uint32_t*>(dst + (size_t)f * dframe + (size_t)dy * dpitch + x4) = out;   // pitch is a multiple of 32
 }
 
 void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
-                   size_t dframe, const int2* xtab, const int4* ytab, int B)
+                   size_t dframe, const void* xtab, const int4* ytab, int B)
 {
     dim3 blk(32, 8);
-    dim3 grd((dw + 127) / 128, (dh + 7) / 8, B);
-    k_resize<<<grd, blk, 0, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, xtab, ytab);
+    dim3 grd(((dw + 3) / 4 + 31) / 32, (dh + 8 * RS_ROWS - 1) / (8 * RS_ROWS), B);
+    k_resize<<<grd, blk, 0, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
 }
 
 // ------------------------------------------------------------------------------------------------ FAST per cell
@@ -515,11 +542,16 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 }
 
 // ------------------------------------------------------------------------------------------------ Gaussian blur
-// cv::GaussianBlur(7x7, sigma 2) on u8, OpenCV 4.x fixed-point path: taps 18,34,48,56,48,34,18 / 256; the horizontal pass
-// is exact 8.8, the vertical pass 8.16, out = (acc + 32768) >> 16; BORDER_REFLECT_101 of the level itself (the reference
-// blurs a border-less clone, ORBextractor.cc:1085).
-constexpr int BT_W = 64, BT_H = 32, BLUR_THREADS = 256;
-constexpr int BIN_P = BT_W + 8;      // input tile pitch
+// cv::GaussianBlur(7x7, sigma 2) on u8, OpenCV 4.x fixed-point path: taps 18,34,48,56,48,34,18 / 256; the first pass is
+// exact 8.8 (no rounding), the second 8.16, out = (acc + 32768) >> 16; BORDER_REFLECT_101 of the level itself (the
+// reference blurs a border-less clone, ORBextractor.cc:1085).  Because the first pass is exact, the result equals
+// (sum_ij K_i K_j p_ij + 32768) >> 16 whichever direction runs first.  Here the VERTICAL pass runs first: a lane owns 4
+// adjacent columns (one 32-bit word) and walks down a strip of rows with a 7-row sliding window held in registers as
+// packed u16x2 pairs (every partial sum fits 16 bits, so 32-bit multiply-adds work on two pixels at once); the
+// horizontal pass takes the neighbour columns from the adjacent lanes by shuffle.  Lanes 0 and 31 are halo lanes.
+constexpr int BLUR_COLS = 120;       // output columns per warp: lanes 1..30 x 4
+constexpr int BLUR_ROWS = 64;        // rows per strip
+constexpr int BLUR_WARPS = 8;
 
 __device__ __forceinline__ int reflect101(int p, int len)
 {
@@ -528,47 +560,80 @@ __device__ __forceinline__ int reflect101(int p, int len)
     return p;
 }
 
-__global__ void __launch_bounds__(BLUR_THREADS) k_blur(const Plan P, const FrameBufs F)
+__device__ __forceinline__ void blur_load_row(const uint8_t* img, int pitch, int h, int y, int x, bool fastcol, int c0, int c1, int c2,
+                                              int c3, unsigned& a, unsigned& b)
 {
-    __shared__ uint8_t in[(BT_H + 6) * BIN_P];
-    __shared__ uint16_t hs[(BT_H + 6) * BT_W];
-    const int f = blockIdx.y, tid = threadIdx.x;
+    const uint8_t* row = img + (size_t)reflect101(y, h) * pitch;
+    unsigned v;
+    if (fastcol) v = __ldg(reinterpret_cast<const unsigned*>(row + x));
+    else v = (unsigned)__ldg(row + c0) | ((unsigned)__ldg(row + c1) << 8) | ((unsigned)__ldg(row + c2) << 16) | ((unsigned)__ldg(row + c3) << 24);
+    a = __byte_perm(v, 0, 0x4140);      // (b0, 0, b1, 0)
+    b = __byte_perm(v, 0, 0x4342);      // (b2, 0, b3, 0)
+}
+
+__global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const FrameBufs F)
+{
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);
+    if (tile >= P.totalBlurTiles) return;
     int l = 0;
-    while (l + 1 < P.nlevels && (int)blockIdx.x >= P.lv[l + 1].blurTileBase) ++l;
+    while (l + 1 < P.nlevels && tile >= P.lv[l + 1].blurTileBase) ++l;
     const LevelGeom& G = P.lv[l];
-    const int t = blockIdx.x - G.blurTileBase;
+    const int t = tile - G.blurTileBase;
     const int ty = t / G.blurTilesX, tx = t - ty * G.blurTilesX;
-    const int x0 = tx * BT_W, y0 = ty * BT_H;
+    const int w = G.w, h = G.h;
+    const int x = tx * BLUR_COLS + (lane - 1) * 4;      // first of this lane's 4 columns (may be < 0 or >= w: halo / padding)
+    const int y0 = ty * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    for (int i = tid; i < (BT_H + 6) * (BT_W + 6); i += BLUR_THREADS) {
-        const int r = i / (BT_W + 6), c = i - r * (BT_W + 6);
-        const int yy = reflect101(y0 + r - 3, G.h), xx = reflect101(x0 + c - 3, G.w);
-        in[r * BIN_P + c] = __ldg(img + (size_t)yy * pitch + xx);
+    // source columns: a word load when the 4 columns are inside the image, else 4 reflected byte loads
+    const bool fastcol = x >= 0 && x + 3 < w;
+    const int c0 = reflect101(x, w), c1 = reflect101(x + 1, w), c2 = reflect101(x + 2, w), c3 = reflect101(x + 3, w);
+    const bool active = x < w + 4 && x > -8;            // lanes far outside the image contribute nothing anyone reads
+
+    unsigned wa[7], wb[7];      // window: packed (col x, col x+1) and (col x+2, col x+3) of the last 7 rows
+#define load_row(Y, A, B) blur_load_row(img, pitch, h, (Y), x, fastcol, c0, c1, c2, c3, (A), (B))
+    if (active) {
+#pragma unroll
+        for (int j = 0; j < 6; j++) load_row(y0 - 3 + j, wa[j], wb[j]);
     }
-    __syncthreads();
-    for (int i = tid; i < (BT_H + 6) * BT_W; i += BLUR_THREADS) {
-        const int r = i / BT_W, c = i - r * BT_W;
-        const uint8_t* s = in + r * BIN_P + c;
-        hs[i] = (uint16_t)(18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3]);
-    }
-    __syncthreads();
     uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff;
-    for (int i = tid; i < BT_H * BT_W; i += BLUR_THREADS) {
-        const int r = i / BT_W, c = i - r * BT_W;
-        if (x0 + c < G.w && y0 + r < G.h) {
-            const uint16_t* s = hs + r * BT_W + c;
-            const unsigned acc = 18u * (s[0] + s[6 * BT_W]) + 34u * (s[BT_W] + s[5 * BT_W]) + 48u * (s[2 * BT_W] + s[4 * BT_W]) +
-                                 56u * s[3 * BT_W];
-            dst[(size_t)(y0 + r) * G.pitch + x0 + c] = (uint8_t)((acc + 32768u) >> 16);
+    for (int yb = y0; yb < y1; yb += 7) {
+#pragma unroll
+        for (int j = 0; j < 7; j++) {
+            const int y = yb + j;                        // output row; its window is rows y-3 .. y+3
+            const int s = (j + 6) % 7;                   // slot receiving row y+3
+            unsigned va = 0, vb = 0;
+            if (active) {
+                load_row(y + 3, wa[s], wb[s]);
+                // rows y-3..y+3 sit in slots (s+1)%7 .. s ; the taps are symmetric
+                va = 18u * (wa[(s + 1) % 7] + wa[s]) + 34u * (wa[(s + 2) % 7] + wa[(s + 6) % 7]) +
+                     48u * (wa[(s + 3) % 7] + wa[(s + 5) % 7]) + 56u * wa[(s + 4) % 7];
+                vb = 18u * (wb[(s + 1) % 7] + wb[s]) + 34u * (wb[(s + 2) % 7] + wb[(s + 6) % 7]) +
+                     48u * (wb[(s + 3) % 7] + wb[(s + 5) % 7]) + 56u * wb[(s + 4) % 7];
+            }
+            // horizontal pass: v[-3..6] around this lane's column x
+            const unsigned la = __shfl_up_sync(0xFFFFFFFFu, va, 1), lb = __shfl_up_sync(0xFFFFFFFFu, vb, 1);
+            const unsigned ra = __shfl_down_sync(0xFFFFFFFFu, va, 1), rb = __shfl_down_sync(0xFFFFFFFFu, vb, 1);
+            const unsigned vm3 = la >> 16, vm2 = lb & 0xFFFFu, vm1 = lb >> 16;
+            const unsigned v0 = va & 0xFFFFu, v1 = va >> 16, v2 = vb & 0xFFFFu, v3 = vb >> 16;
+            const unsigned v4 = ra & 0xFFFFu, v5 = ra >> 16, v6 = rb & 0xFFFFu;
+            const unsigned o0 = (18u * (vm3 + v3) + 34u * (vm2 + v2) + 48u * (vm1 + v1) + 56u * v0 + 32768u) >> 16;
+            const unsigned o1 = (18u * (vm2 + v4) + 34u * (vm1 + v3) + 48u * (v0 + v2) + 56u * v1 + 32768u) >> 16;
+            const unsigned o2 = (18u * (vm1 + v5) + 34u * (v0 + v4) + 48u * (v1 + v3) + 56u * v2 + 32768u) >> 16;
+            const unsigned o3 = (18u * (v0 + v6) + 34u * (v1 + v5) + 48u * (v2 + v4) + 56u * v3 + 32768u) >> 16;
+            if (lane >= 1 && lane <= 30 && x < w && y < y1)     // the last word of a row may extend into the pitch padding
+                *reinterpret_cast<unsigned*>(dst + (size_t)y * G.pitch + x) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
         }
     }
 }
 
+#undef load_row
+
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
 {
-    dim3 grd(P.totalBlurTiles, B);
-    k_blur<<<grd, BLUR_THREADS, 0, s>>>(P, F);
+    dim3 grd((P.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, B);
+    k_blur<<<grd, BLUR_WARPS * 32, 0, s>>>(P, F);
 }
 
 // ------------------------------------------------------------------------------------------------ orientation + rBRIEF

@@ -59,7 +59,7 @@ struct orbx_extractor {
     int capS = 0, sortCap = 0;
     size_t fastSmem = 0, octSmem = 0;
     std::vector<int> xtabOff, ytabOff;
-    int2* d_xtab = nullptr;
+    int* d_xtab = nullptr;            // 8 ints per group of 4 output columns, all levels
     int4* d_ytab = nullptr;
     uint8_t* d_lv0 = nullptr;          // own level-0 planes (host-input path)
     size_t lv0Pitch = 0, lv0Frame = 0;
@@ -133,9 +133,9 @@ static int build_plan(orbx_extractor* ex, int w, int h)
         capS = std::max(capS, std::max(G.quota + 4, 4 * G.nIni) + 4);
         G.nodeBase = nodes;
         nodes += G.nodeCap;
-        G.blurTilesX = (G.w + 63) / 64;
+        G.blurTilesX = (G.w + 119) / 120;        // k_blur: 120 output columns x 64 rows per warp
         G.blurTileBase = tiles;
-        tiles += G.blurTilesX * ((G.h + 31) / 32);
+        tiles += G.blurTilesX * ((G.h + 63) / 64);
         G.scaledPatch = (int)(31 * ex->mvScaleFactor[l]);            // PATCH_SIZE*mvScaleFactor[level] (:845)
         G.scale = ex->mvScaleFactor[l];
         G.planeOff = pyr;
@@ -166,21 +166,47 @@ static int build_plan(orbx_extractor* ex, int w, int h)
 }
 
 // cv::resize INTER_LINEAR coefficient tables (8-bit fixed-point path): 11-bit weights from float fx.
-static void build_resize_tables(int sw, int sh, int dw, int dh, std::vector<int2>& xt, std::vector<int4>& yt)
+// Column table: one record of 8 ints per group of 4 output columns (k_resize):
+//   [0] w0 | w1 << 16, [1] w2 | shift << 16 : the three aligned source words covering bytes sx(first) .. +7 and the funnel
+//       shift (bits) that brings byte sx(first) to position 0 (word indices clamped to the last word of the row),
+//   [2] selL, [3] selR : PRMT selectors of the four left (sx) and right (sx+1, clamped) source bytes,
+//   [4..7] a0 | a1 << 16 of the four columns.
+static bool build_resize_tables(int sw, int sh, int dw, int dh, std::vector<int>& xt, std::vector<int4>& yt)
 {
     const double sxs = (double)sw / dw, sys = (double)sh / dh;
-    xt.resize(dw);
-    yt.resize(dh);
-    for (int dx = 0; dx < dw; dx++) {
-        float fx = (float)((dx + 0.5) * sxs - 0.5);
+    const int ngroups = (dw + 3) / 4;
+    std::vector<int> sxv(ngroups * 4), sx1v(ngroups * 4), a0v(ngroups * 4), a1v(ngroups * 4);
+    for (int dx = 0; dx < ngroups * 4; dx++) {
+        const int d = std::min(dx, dw - 1);          // columns past dw (pitch padding) repeat the last one
+        float fx = (float)((d + 0.5) * sxs - 0.5);
         int sx = (int)floorf(fx);
         fx -= sx;
         if (sx < 0) { fx = 0.f; sx = 0; }
         if (sx + 1 >= sw) { fx = 0.f; sx = sw - 1; }
-        const int sx1 = std::min(sx + 1, sw - 1);
-        const int a0 = (short)round_half_even((1.f - fx) * 2048.f), a1 = (short)round_half_even(fx * 2048.f);
-        xt[dx] = make_int2(sx | (sx1 << 16), (a0 & 0xFFFF) | (a1 << 16));
+        sxv[dx] = sx;
+        sx1v[dx] = std::min(sx + 1, sw - 1);
+        a0v[dx] = (short)round_half_even((1.f - fx) * 2048.f);
+        a1v[dx] = (short)round_half_even(fx * 2048.f);
     }
+    xt.assign((size_t)ngroups * 8, 0);
+    const int lastWord = (sw - 1) >> 2;
+    for (int g = 0; g < ngroups; g++) {
+        const int base = sxv[4 * g];
+        const int w0 = base >> 2, w1 = std::min(w0 + 1, lastWord), w2 = std::min(w0 + 2, lastWord);
+        int selL = 0, selR = 0;
+        for (int k = 0; k < 4; k++) {
+            if (sx1v[4 * g + k] - base > 7 || sxv[4 * g + k] < base) return false;     // window wider than 8 bytes: scaleFactor > 2
+            selL |= ((sxv[4 * g + k] - base) & 7) << (4 * k);
+            selR |= ((sx1v[4 * g + k] - base) & 7) << (4 * k);
+        }
+        int* r = &xt[(size_t)g * 8];
+        r[0] = w0 | (w1 << 16);
+        r[1] = w2 | (((base & 3) * 8) << 16);
+        r[2] = selL;
+        r[3] = selR;
+        for (int k = 0; k < 4; k++) r[4 + k] = (a0v[4 * g + k] & 0xFFFF) | (a1v[4 * g + k] << 16);
+    }
+    yt.resize(dh);
     for (int dy = 0; dy < dh; dy++) {
         float fy = (float)((dy + 0.5) * sys - 0.5);
         const int sy = (int)floorf(fy);
@@ -188,6 +214,7 @@ static void build_resize_tables(int sw, int sh, int dw, int dh, std::vector<int2
         const int b0 = (short)round_half_even((1.f - fy) * 2048.f), b1 = (short)round_half_even(fy * 2048.f);
         yt[dy] = make_int4(std::min(std::max(sy, 0), sh - 1), std::min(std::max(sy + 1, 0), sh - 1), b0, b1);
     }
+    return true;
 }
 
 static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
@@ -201,23 +228,26 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     const int cap = std::max(B, ex->maxBatch);
 
     // resize tables
-    std::vector<int2> xall;
+    std::vector<int> xall;
     std::vector<int4> yall;
     ex->xtabOff.assign(ex->nlevels, 0);
     ex->ytabOff.assign(ex->nlevels, 0);
     for (int l = 1; l < ex->nlevels; l++) {
-        std::vector<int2> xt;
+        std::vector<int> xt;
         std::vector<int4> yt;
-        build_resize_tables(P.lv[l - 1].w, P.lv[l - 1].h, P.lv[l].w, P.lv[l].h, xt, yt);
+        if (!build_resize_tables(P.lv[l - 1].w, P.lv[l - 1].h, P.lv[l].w, P.lv[l].h, xt, yt)) {
+            set_error("scaleFactor too large for the resize kernel (level ratio above 2)");
+            return ORBX_ERR_ARG;
+        }
         ex->xtabOff[l] = (int)xall.size();
         ex->ytabOff[l] = (int)yall.size();
         xall.insert(xall.end(), xt.begin(), xt.end());
         yall.insert(yall.end(), yt.begin(), yt.end());
     }
-    ORBX_CUDA(cudaMalloc(&ex->d_xtab, std::max<size_t>(xall.size(), 1) * sizeof(int2)));
+    ORBX_CUDA(cudaMalloc(&ex->d_xtab, std::max<size_t>(xall.size(), 8) * sizeof(int)));
     ORBX_CUDA(cudaMalloc(&ex->d_ytab, std::max<size_t>(yall.size(), 1) * sizeof(int4)));
     if (!xall.empty()) {
-        ORBX_CUDA(cudaMemcpyAsync(ex->d_xtab, xall.data(), xall.size() * sizeof(int2), cudaMemcpyHostToDevice, ex->stream));
+        ORBX_CUDA(cudaMemcpyAsync(ex->d_xtab, xall.data(), xall.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
         ORBX_CUDA(cudaMemcpyAsync(ex->d_ytab, yall.data(), yall.size() * sizeof(int4), cudaMemcpyHostToDevice, ex->stream));
         ORBX_CUDA(cudaStreamSynchronize(ex->stream));
     }
