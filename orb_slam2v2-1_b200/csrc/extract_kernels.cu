@@ -93,58 +93,74 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 }
 
 // ------------------------------------------------------------------------------------------------ FAST per cell
-constexpr int FAST_THREADS = 128;
+// One WARP per cell (four cells per CTA): everything below is warp-synchronous, no block barrier and no shared-memory atomic.
+//   1. the cell ROI is staged in shared memory as aligned 32-bit words;
+//   2. pre-filter on 4 pixels at a time: a 9-arc always contains two adjacent compass pixels (ring positions 0, 4, 8, 12),
+//      so a corner needs |p - centre| > t on such a pair; |.| comes from the native VABSDIFF4.U8 and the threshold test is
+//      SWAR on the four bytes; survivors are appended in row-major order to the warp's private list (ballot ranks);
+//   3. exact score of the survivors (packed s16x2 min/max, VIMNMX) into a u8 score map (0 = not a corner);
+//   4. NMS + emission from the list, which is already in cv::FAST's output order.
+// The cell is processed at iniThFAST first and, only if that yields no keypoint, again at minThFAST
+// (ORBextractor.cc:809-816): kept(t) = raw > t and raw > every neighbour's raw, so each pass is exact on its own.
+constexpr int FAST_WARPS = 4;
 
 // raw = max over the 16 arcs of 9 contiguous ring pixels of min(ring - centre) resp. min(centre - ring)
-// (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  Circular window minima via
-// prefix/suffix minima of the two ring halves: window k covers d[k..7] + d[8..8+k], window 8+k covers d[8+k..15] + d[0..k].
+// (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  min/max commute with the subtraction of the
+// centre, so the arcs are evaluated on the raw ring values.  Register k holds (ring[k], ring[k+8]) as s16x2: window k
+// (lo half) = min(ring[k..7], ring[8..8+k]) and window 8+k (hi half) = min(ring[8+k..15], ring[0..k]), i.e.
+// min(suffix-min of the pairs, half-swapped prefix-min of the pairs).
 __device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch)
 {
     const int v = c[0];
-    int d[16];
-    d[0] = c[3 * pitch] - v;       d[1] = c[3 * pitch + 1] - v;   d[2] = c[2 * pitch + 2] - v;   d[3] = c[pitch + 3] - v;
-    d[4] = c[3] - v;               d[5] = c[-pitch + 3] - v;      d[6] = c[-2 * pitch + 2] - v;  d[7] = c[-3 * pitch + 1] - v;
-    d[8] = c[-3 * pitch] - v;      d[9] = c[-3 * pitch - 1] - v;  d[10] = c[-2 * pitch - 2] - v; d[11] = c[-pitch - 3] - v;
-    d[12] = c[-3] - v;             d[13] = c[pitch - 3] - v;      d[14] = c[2 * pitch - 2] - v;  d[15] = c[3 * pitch - 1] - v;
-    int sufA[8], preA[8], sufB[8], preB[8];
-    int SufA[8], PreA[8], SufB[8], PreB[8];
-    sufA[7] = SufA[7] = d[7];  sufB[7] = SufB[7] = d[15];
-    preA[0] = PreA[0] = d[0];  preB[0] = PreB[0] = d[8];
+    unsigned r0 = c[3 * pitch], r1 = c[3 * pitch + 1], r2 = c[2 * pitch + 2], r3 = c[pitch + 3];
+    unsigned r4 = c[3], r5 = c[-pitch + 3], r6 = c[-2 * pitch + 2], r7 = c[-3 * pitch + 1];
+    unsigned r8 = c[-3 * pitch], r9 = c[-3 * pitch - 1], r10 = c[-2 * pitch - 2], r11 = c[-pitch - 3];
+    unsigned r12 = c[-3], r13 = c[pitch - 3], r14 = c[2 * pitch - 2], r15 = c[3 * pitch - 1];
+    unsigned Pk[8];
+    Pk[0] = __byte_perm(r0, r8, 0x5410);  Pk[1] = __byte_perm(r1, r9, 0x5410);  Pk[2] = __byte_perm(r2, r10, 0x5410);
+    Pk[3] = __byte_perm(r3, r11, 0x5410); Pk[4] = __byte_perm(r4, r12, 0x5410); Pk[5] = __byte_perm(r5, r13, 0x5410);
+    Pk[6] = __byte_perm(r6, r14, 0x5410); Pk[7] = __byte_perm(r7, r15, 0x5410);
+    unsigned sn[8], sx[8], pn[8], px[8];     // suffix / prefix minima and maxima of the pairs
+    sn[7] = sx[7] = Pk[7];
+    pn[0] = px[0] = Pk[0];
 #pragma unroll
-    for (int k = 6; k >= 0; k--) {
-        sufA[k] = min(sufA[k + 1], d[k]);      SufA[k] = max(SufA[k + 1], d[k]);
-        sufB[k] = min(sufB[k + 1], d[8 + k]);  SufB[k] = max(SufB[k + 1], d[8 + k]);
-    }
+    for (int k = 6; k >= 0; k--) { sn[k] = __vmins2(sn[k + 1], Pk[k]); sx[k] = __vmaxs2(sx[k + 1], Pk[k]); }
 #pragma unroll
-    for (int k = 1; k < 8; k++) {
-        preA[k] = min(preA[k - 1], d[k]);      PreA[k] = max(PreA[k - 1], d[k]);
-        preB[k] = min(preB[k - 1], d[8 + k]);  PreB[k] = max(PreB[k - 1], d[8 + k]);
-    }
-    int bright = -255, dark = 255;   // dark holds the minimum over arcs of the arc maximum
+    for (int k = 1; k < 8; k++) { pn[k] = __vmins2(pn[k - 1], Pk[k]); px[k] = __vmaxs2(px[k - 1], Pk[k]); }
+    unsigned bright = 0, dark = 0x7FFF7FFFu;     // bright: max over windows of the window min; dark: min of the window max
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        bright = max(bright, max(min(sufA[k], preB[k]), min(sufB[k], preA[k])));
-        dark = min(dark, min(max(SufA[k], PreB[k]), max(SufB[k], PreA[k])));
+        bright = __vmaxs2(bright, __vmins2(sn[k], __byte_perm(pn[k], 0, 0x1032)));
+        dark = __vmins2(dark, __vmaxs2(sx[k], __byte_perm(px[k], 0, 0x1032)));
     }
-    return max(bright, -dark);
+    const int b = max((int)(bright & 0xFFFF), (int)(bright >> 16)) - v;
+    const int d = v - min((int)(dark & 0xFFFF), (int)(dark >> 16));
+    return max(b, d);
+}
+
+// shared memory of one warp: tile words | score map | survivor list
+__host__ __device__ inline int fast_warp_smem(int wCell, int hCell)
+{
+    const int tile = (hCell + 6) * (((wCell + 6 + 3 + 3) >> 2) << 2);
+    const int sc = (hCell + 2) * ((wCell + 2 + 3) & ~3);
+    const int list = ((wCell * hCell * 2) + 3) & ~3;
+    return (tile + sc + list + 15) & ~15;
 }
 
 size_t fast_smem_bytes(const Plan& P)
 {
-    int mw = 0, mh = 0;
-    for (int l = 0; l < P.nlevels; l++) { mw = max(mw, P.lv[l].wCell); mh = max(mh, P.lv[l].hCell); }
-    const size_t tile = (size_t)(mh + 6) * (size_t)((mw + 6 + 3 + 3) & ~3);
-    const size_t sc = ((size_t)(mh + 2) * (mw + 2) + 3) & ~(size_t)3;
-    const size_t list = (size_t)mw * mh * 2;
-    return tile + sc + list + 16;
+    int m = 0;
+    for (int l = 0; l < P.nlevels; l++) m = max(m, fast_warp_smem(P.lv[l].wCell, P.lv[l].hCell));
+    return (size_t)m * FAST_WARPS;
 }
 
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const Plan P, const FrameBufs F)
+__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int s_nlist;
-    __shared__ int s_wsum[FAST_THREADS / 32 + 1];
-    const int cell = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, f = blockIdx.y;
+    const int cell = blockIdx.x * FAST_WARPS + wid;
+    if (cell >= P.totalCells) return;
+    const unsigned FULL = 0xFFFFFFFFu, ltmask = (1u << lane) - 1;
     const int l = level_of_cell(P, cell);
     const LevelGeom& G = P.lv[l];
     const int ci = cell - G.cellBase;
@@ -156,122 +172,124 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const Plan P, const
     const int maxX = min(iniX + G.wCell + 6, G.maxBX), maxY = min(iniY + G.hCell + 6, G.maxBY);
     const int tw = maxX - iniX, th = maxY - iniY;
     if (iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7) {     // skipped cell / ROI too small for cv::FAST
-        if (tid == 0) *cntOut = 0;
+        if (lane == 0) *cntOut = 0;
         return;
     }
-    const int iw = tw - 6, ih = th - 6, npx = iw * ih;    // detection zone: no corner within 3 px of the ROI edge
+    const int iw = tw - 6, ih = th - 6;                   // detection zone: no corner within 3 px of the ROI edge
     const int ax = iniX & ~3;                             // word-aligned tile origin
     const int dx0 = iniX - ax;
-    const int nwords = (maxX - ax + 3) >> 2;
-    const int tp = nwords * 4;                            // tile pitch (bytes)
-    const int scp = iw + 2;                               // score-map pitch: 1-px zero frame
-    uint8_t* tile = smem;
-    uint8_t* sc = tile + (size_t)th * tp;
-    uint16_t* list = reinterpret_cast<uint16_t*>(sc + ((((size_t)(ih + 2) * scp) + 3) & ~(size_t)3));
+    const int tpw = (maxX - ax + 3) >> 2, tp = tpw * 4;   // tile pitch in words / bytes
+    const int scp = (iw + 2 + 3) & ~3;                    // score-map pitch: 1-px zero frame
+    uint8_t* tile = smem + (size_t)wid * smemPerWarp;
+    uint8_t* sc = tile + th * tp;
+    uint16_t* list = reinterpret_cast<uint16_t*>(sc + (ih + 2) * scp);
+    uint32_t* tileW = reinterpret_cast<uint32_t*>(tile);
 
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    for (int i = tid; i < th * nwords; i += FAST_THREADS) {
-        const int r = i / nwords, c = i - r * nwords;
-        reinterpret_cast<uint32_t*>(tile)[r * nwords + c] =
-            __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(iniY + r) * pitch + ax) + c);
-    }
-    for (int i = tid; i < ((ih + 2) * scp + 3) / 4; i += FAST_THREADS) reinterpret_cast<uint32_t*>(sc)[i] = 0;
-    if (tid == 0) s_nlist = 0;
-    __syncthreads();
-
-    // phase A: compass pre-test at the lower threshold (a 9-arc always contains two adjacent compass pixels)
-    const int tlow = min(P.iniTh, P.minTh);
-    const int npxR = (npx + 31) & ~31;
-    for (int p = tid; p < npxR; p += FAST_THREADS) {
-        bool pass = false;
-        if (p < npx) {
-            const int y = p / iw, x = p - y * iw;
-            const uint8_t* c = tile + (y + 3) * tp + (x + 3 + dx0);
-            const int v = c[0];
-            const int hi = v + tlow, lo = v - tlow;
-            const int p0 = c[3 * tp], p4 = c[3], p8 = c[-3 * tp], p12 = c[-3];
-            const bool b = ((p0 > hi) | (p8 > hi)) & ((p4 > hi) | (p12 > hi));
-            const bool dk = ((p0 < lo) | (p8 < lo)) & ((p4 < lo) | (p12 < lo));
-            pass = b | dk;
-        }
-        const unsigned m = __ballot_sync(0xFFFFFFFFu, pass);
-        int base = 0;
-        if (lane == 0 && m) base = atomicAdd(&s_nlist, __popc(m));
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (pass) list[base + __popc(m & ((1u << lane) - 1))] = (uint16_t)p;
-    }
-    __syncthreads();
-
-    // phase C: exact score of the survivors
-    const int nlist = s_nlist;
-    for (int k = tid; k < nlist; k += FAST_THREADS) {
-        const int p = list[k];
-        const int y = p / iw, x = p - y * iw;
-        const int raw = fast_raw_score(tile + (y + 3) * tp + (x + 3 + dx0), tp);
-        if (raw > tlow) sc[(y + 1) * scp + x + 1] = (uint8_t)raw;
-    }
-    __syncthreads();
-
-    // NMS (strict >, neighbours outside the detection zone or below threshold count as 0) + ordered emission.
-    // kept at threshold t  <=>  raw > t and raw > all 8 neighbours' raw: independent of t, so the minThFAST retry
-    // (ORBextractor.cc:812-816) is a re-threshold of the same local maxima.
-    const int K = (npx + FAST_THREADS - 1) / FAST_THREADS;     // <= 32 (cells are < 62 x 62)
-    unsigned keepMask = 0;
-    int cIni = 0, cMin = 0;
-    for (int k = 0; k < K; k++) {
-        const int p = tid * K + k;
-        if (p >= npx) break;
-        const int y = p / iw, x = p - y * iw;
-        const uint8_t* s = sc + (y + 1) * scp + x + 1;
-        const int v = s[0];
-        if (v == 0) continue;
-        const bool keep = v > s[-1] && v > s[1] && v > s[-scp - 1] && v > s[-scp] && v > s[-scp + 1] &&
-                          v > s[scp - 1] && v > s[scp] && v > s[scp + 1];
-        if (keep) {
-            keepMask |= 1u << k;
-            cIni += (v > P.iniTh);
-            cMin += (v > P.minTh);
+    {
+        const uint8_t* src = img + (size_t)iniY * pitch + ax;
+        const int n = th * tpw;
+        const unsigned inv = 65536u / (unsigned)tpw + 1;          // i / tpw == (i * inv) >> 16 for i < 65536 / tpw * ... (n < 1400)
+        for (int i = lane; i < n; i += 32) {
+            const int r = (int)(((unsigned)i * inv) >> 16), cidx = i - r * tpw;
+            tileW[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch) + cidx);
         }
     }
-    const int packed = (cIni << 16) | cMin;
-    int inc = packed;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
-        if (lane >= o) inc += t;
-    }
-    if (lane == 31) s_wsum[wid] = inc;
-    __syncthreads();
-    int woff = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < FAST_THREADS / 32; w++) {
-        const int v = s_wsum[w];
-        if (w < wid) woff += v;
-        total += v;
-    }
-    const bool useIni = (total >> 16) > 0;
-    const int excl = woff + inc - packed;
-    int off = useIni ? (excl >> 16) : (excl & 0xFFFF);
-    const int th_ = useIni ? P.iniTh : P.minTh;
+    // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih); word items of the zone
+    const int zx0 = dx0 + 3, zx1 = zx0 + iw;
+    const int wFirst = zx0 >> 2, nwz = ((zx1 - 1) >> 2) - wFirst + 1;
+    const int nitems = ih * nwz;
+    const unsigned invz = 65536u / (unsigned)nwz + 1;
     uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)ci * G.slotCap;
-    for (int k = 0; k < K; k++) {
-        if (!(keepMask >> k & 1u)) continue;
-        const int p = tid * K + k;
-        const int y = p / iw, x = p - y * iw;
-        const int v = sc[(y + 1) * scp + x + 1];
-        if (v > th_) {
-            // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
-            out[off++] = pack_key(x + 3 + ci_j * G.wCell, y + 3 + ci_i * G.hCell, v - 1);
+    const int scWords = ((ih + 2) * scp) >> 2;
+    int total = 0;
+
+    for (int pass = 0; pass < 2; pass++) {
+        const int t = pass == 0 ? P.iniTh : P.minTh;
+        if (pass == 1 && (total > 0 || P.minTh == P.iniTh)) break;
+        for (int i = lane; i < scWords; i += 32) reinterpret_cast<uint32_t*>(sc)[i] = 0;
+        __syncwarp();
+        // ---- pre-filter
+        const unsigned K = (unsigned)(127 - min(t, 127)) * 0x01010101u;     // byte > t  <=>  bit 7 of ((byte & 0x7f) + 127 - t) | byte
+        int n = 0;
+        for (int i0 = 0; i0 < nitems; i0 += 32) {
+            const int i = i0 + lane;
+            unsigned comb = 0;
+            int row = 0, wc = 0;
+            if (i < nitems) {
+                const int r = (int)(((unsigned)i * invz) >> 16);
+                wc = wFirst + i - r * nwz;
+                row = r + 3;
+                const uint32_t* w = tileW + row * tpw + wc;
+                const unsigned C = w[0], Lw = w[-1], Rw = w[1], U = w[-3 * tpw], D = w[3 * tpw];
+                const unsigned P12 = __funnelshift_r(Lw, C, 8), P4 = __funnelshift_r(C, Rw, 24);
+                const unsigned a0 = __vabsdiffu4(D, C), a8 = __vabsdiffu4(U, C), a4 = __vabsdiffu4(P4, C), a12 = __vabsdiffu4(P12, C);
+                const unsigned g0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, g8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
+                const unsigned g4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, g12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
+                comb = (g0 | g8) & (g4 | g12) & 0x80808080u;
+                // bytes of this word outside the zone
+                const int lo = max(zx0 - 4 * wc, 0), hi = min(zx1 - 4 * wc, 4);
+                const unsigned m = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
+                comb &= m;
+            }
+            if (__ballot_sync(FULL, comb != 0) == 0) continue;
+            const unsigned b0 = __ballot_sync(FULL, comb & 0x80u), b1 = __ballot_sync(FULL, comb & 0x8000u);
+            const unsigned b2 = __ballot_sync(FULL, comb & 0x800000u), b3 = __ballot_sync(FULL, comb & 0x80000000u);
+            int pos = n + __popc(b0 & ltmask) + __popc(b1 & ltmask) + __popc(b2 & ltmask) + __popc(b3 & ltmask);
+            const int e = (row << 8) | (wc << 2);
+            if (comb & 0x80u) list[pos++] = (uint16_t)e;
+            if (comb & 0x8000u) list[pos++] = (uint16_t)(e + 1);
+            if (comb & 0x800000u) list[pos++] = (uint16_t)(e + 2);
+            if (comb & 0x80000000u) list[pos++] = (uint16_t)(e + 3);
+            n += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
         }
+        __syncwarp();
+        // ---- exact score of the survivors
+        for (int k = lane; k < n; k += 32) {
+            const int e = list[k];
+            const int row = e >> 8, col = e & 0xFF;
+            const int raw = fast_raw_score(tile + row * tp + col, tp);
+            if (raw > t) sc[(row - 2) * scp + (col - zx0 + 1)] = (uint8_t)raw;
+        }
+        __syncwarp();
+        // ---- NMS (strict >, neighbours outside the zone or not corners count as 0) + emission in list order
+        for (int k0 = 0; k0 < n; k0 += 32) {
+            const int k = k0 + lane;
+            bool keep = false;
+            int e = 0, v = 0;
+            if (k < n) {
+                e = list[k];
+                const uint8_t* s = sc + ((e >> 8) - 2) * scp + ((e & 0xFF) - zx0 + 1);
+                v = s[0];
+                if (v) {
+                    const int m1 = max(max((int)s[-1], (int)s[1]), max((int)s[-scp - 1], (int)s[-scp]));
+                    const int m2 = max(max((int)s[-scp + 1], (int)s[scp - 1]), max((int)s[scp], (int)s[scp + 1]));
+                    keep = v > max(m1, m2);
+                }
+            }
+            const unsigned kb = __ballot_sync(FULL, keep);
+            if (keep) {
+                // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
+                const int x = (e & 0xFF) - dx0 + ci_j * G.wCell, y = (e >> 8) + ci_i * G.hCell;
+                out[total + __popc(kb & ltmask)] = pack_key(x, y, v - 1);
+            }
+            total += __popc(kb);
+        }
+        __syncwarp();
     }
-    if (tid == 0) *cntOut = useIni ? (total >> 16) : (total & 0xFFFF);
+    if (lane == 0) *cntOut = total;
 }
 
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
 {
-    dim3 grd(P.totalCells, B);
-    k_fast_cells<<<grd, FAST_THREADS, smemBytes, s>>>(P, F);
+    static thread_local size_t configured = 48 * 1024;
+    if (smemBytes > configured) {      // small levels can have cells of up to 61 x 61 pixels
+        cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        configured = smemBytes;
+    }
+    dim3 grd((P.totalCells + FAST_WARPS - 1) / FAST_WARPS, B);
+    k_fast_cells<<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS));
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree
