@@ -293,7 +293,8 @@ void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B,
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree
-constexpr int OCT_THREADS = 1024;
+constexpr int OCT_THREADS = 256;       // several (level, frame) problems per SM hide each other's barrier and memory latency
+constexpr int OCT_KEYS_SMEM = 4096;    // candidates of a level kept in shared memory when they fit (else the global workspace)
 
 // in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
 __device__ int block_exclusive_scan(int* a, int n, int* wsum)
@@ -333,7 +334,9 @@ __device__ int block_exclusive_scan(int* a, int n, int* wsum)
 size_t octree_smem_bytes(int capS, int sortCap)
 {
     // rectA, rectB (short4) | cntA, cntB | cc[4] | chBeg | tmp | skey[sortCap] | rankOf, mapS (u16) | childPos[4] (u16)
-    return (size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 8) + (size_t)sortCap * 4 + 64;
+    // ... | keys (u32) and node positions (u16) of up to OCT_KEYS_SMEM candidates
+    const size_t nodes = ((size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 8) + (size_t)sortCap * 4 + 15) & ~(size_t)15;
+    return nodes + (size_t)OCT_KEYS_SMEM * 6 + 64;
 }
 
 // DistributeOctTree.  The reference keeps nodes in a std::list built with push_front; a pass over the list splits
@@ -341,7 +344,7 @@ size_t octree_smem_bytes(int capS, int sortCap)
 // is an array in list order, rebuilt every pass with prefix sums; every candidate carries the position of its node.
 // Tie-break of the "largest first" phase (ORBextractor.cc:684 sorts by (size, heap address)): creation order, later
 // first == smaller list position first (the portable definition of the oracle, tie_mode 0).
-__global__ void __launch_bounds__(OCT_THREADS, 1) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
+__global__ void __launch_bounds__(OCT_THREADS, 4) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     __shared__ int wsum[33];
@@ -367,6 +370,8 @@ __global__ void __launch_bounds__(OCT_THREADS, 1) k_octree(const Plan P, const F
     const uint32_t* slots = F.slots + (size_t)f * P.slotSlab + G.slotOff;
     uint32_t* keys = F.keys + (size_t)f * P.keySlab + G.keyOff;
     uint16_t* knode = F.knode + (size_t)f * P.keySlab + G.keyOff;
+    uint32_t* keysS = reinterpret_cast<uint32_t*>(smraw + ((((size_t)capS * 56 + (size_t)sortCap * 4) + 15) & ~(size_t)15));
+    uint16_t* knodeS = reinterpret_cast<uint16_t*>(keysS + OCT_KEYS_SMEM);
     uint32_t* outKeys = F.levelKeys + (size_t)f * P.totalNodes + G.nodeBase;
     int* outCount = F.levelCount + (size_t)f * MAX_LEVELS + l;
 
@@ -378,6 +383,7 @@ __global__ void __launch_bounds__(OCT_THREADS, 1) k_octree(const Plan P, const F
         if (tid == 0) *outCount = 0;
         return;
     }
+    if (n <= OCT_KEYS_SMEM) { keys = keysS; knode = knodeS; }
     const int nIni = G.nIni;
     int* rootCnt = cc;          // scratch: nIni <= capS
     for (int i = tid; i < nIni; i += T) rootCnt[i] = 0;
@@ -578,15 +584,12 @@ __device__ __forceinline__ int reflect101(int p, int len)
     return p;
 }
 
-__device__ __forceinline__ void blur_load_row(const uint8_t* img, int pitch, int h, int y, int x, bool fastcol, int c0, int c1, int c2,
-                                              int c3, unsigned& a, unsigned& b)
+// single reflection + clamp: exact for -len < p < 2*len - 1, which covers every coordinate whose value is actually used
+__device__ __forceinline__ int reflect1(int p, int len)
 {
-    const uint8_t* row = img + (size_t)reflect101(y, h) * pitch;
-    unsigned v;
-    if (fastcol) v = __ldg(reinterpret_cast<const unsigned*>(row + x));
-    else v = (unsigned)__ldg(row + c0) | ((unsigned)__ldg(row + c1) << 8) | ((unsigned)__ldg(row + c2) << 16) | ((unsigned)__ldg(row + c3) << 24);
-    a = __byte_perm(v, 0, 0x4140);      // (b0, 0, b1, 0)
-    b = __byte_perm(v, 0, 0x4342);      // (b2, 0, b3, 0)
+    p = p < 0 ? -p : p;
+    p = p >= len ? 2 * (len - 1) - p : p;
+    return min(max(p, 0), len - 1);
 }
 
 __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const FrameBufs F)
@@ -604,32 +607,38 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const
     const int y0 = ty * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    // source columns: a word load when the 4 columns are inside the image, else 4 reflected byte loads
-    const bool fastcol = x >= 0 && x + 3 < w;
-    const int c0 = reflect101(x, w), c1 = reflect101(x + 1, w), c2 = reflect101(x + 2, w), c3 = reflect101(x + 3, w);
-    const bool active = x < w + 4 && x > -8;            // lanes far outside the image contribute nothing anyone reads
+    // The lane's 4 source columns, reflected at the image borders, always lie within two aligned words: one PRMT with a
+    // per-lane selector puts them in order.  Warps that touch no border load a single word.
+    const int c0 = reflect1(x, w), c1 = reflect1(x + 1, w), c2 = reflect1(x + 2, w), c3 = reflect1(x + 3, w);
+    const int wA = min(min(c0, c1), min(c2, c3)) >> 2, wB = max(max(c0, c1), max(c2, c3)) >> 2;
+    const unsigned offA = (unsigned)wA * 4, offB = (unsigned)wB * 4;
+    auto nib = [&](int c) { return (unsigned)((c >> 2) == wA ? c - 4 * wA : 4 + c - 4 * wB); };
+    const unsigned sel = nib(c0) | (nib(c1) << 4) | (nib(c2) << 8) | (nib(c3) << 12);
+    const bool edgeWarp = __any_sync(0xFFFFFFFFu, sel != 0x3210u);
 
     unsigned wa[7], wb[7];      // window: packed (col x, col x+1) and (col x+2, col x+3) of the last 7 rows
-#define load_row(Y, A, B) blur_load_row(img, pitch, h, (Y), x, fastcol, c0, c1, c2, c3, (A), (B))
-    if (active) {
-#pragma unroll
-        for (int j = 0; j < 6; j++) load_row(y0 - 3 + j, wa[j], wb[j]);
+#define LOAD_ROW(Y, A, B)                                                                                   \
+    {                                                                                                       \
+        const uint8_t* row_ = img + (unsigned)(reflect1((Y), h) * pitch);                                   \
+        unsigned v_ = __ldg(reinterpret_cast<const unsigned*>(row_ + offA));                                \
+        if (edgeWarp) v_ = __byte_perm(v_, __ldg(reinterpret_cast<const unsigned*>(row_ + offB)), sel);     \
+        A = __byte_perm(v_, 0, 0x4140);                                                                     \
+        B = __byte_perm(v_, 0, 0x4342);                                                                     \
     }
-    uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff;
+#pragma unroll
+    for (int j = 0; j < 6; j++) LOAD_ROW(y0 - 3 + j, wa[j], wb[j]);
+    uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + x;
+    const bool writer = lane >= 1 && lane <= 30 && x < w;     // the last word of a row may extend into the pitch padding
     for (int yb = y0; yb < y1; yb += 7) {
 #pragma unroll
         for (int j = 0; j < 7; j++) {
             const int y = yb + j;                        // output row; its window is rows y-3 .. y+3
-            const int s = (j + 6) % 7;                   // slot receiving row y+3
-            unsigned va = 0, vb = 0;
-            if (active) {
-                load_row(y + 3, wa[s], wb[s]);
-                // rows y-3..y+3 sit in slots (s+1)%7 .. s ; the taps are symmetric
-                va = 18u * (wa[(s + 1) % 7] + wa[s]) + 34u * (wa[(s + 2) % 7] + wa[(s + 6) % 7]) +
-                     48u * (wa[(s + 3) % 7] + wa[(s + 5) % 7]) + 56u * wa[(s + 4) % 7];
-                vb = 18u * (wb[(s + 1) % 7] + wb[s]) + 34u * (wb[(s + 2) % 7] + wb[(s + 6) % 7]) +
-                     48u * (wb[(s + 3) % 7] + wb[(s + 5) % 7]) + 56u * wb[(s + 4) % 7];
-            }
+            const int s = (j + 6) % 7;                   // slot receiving row y+3; rows y-3..y+3 sit in slots (s+1)%7 .. s
+            LOAD_ROW(y + 3, wa[s], wb[s]);
+            const unsigned va = 18u * (wa[(s + 1) % 7] + wa[s]) + 34u * (wa[(s + 2) % 7] + wa[(s + 6) % 7]) +
+                                48u * (wa[(s + 3) % 7] + wa[(s + 5) % 7]) + 56u * wa[(s + 4) % 7];
+            const unsigned vb = 18u * (wb[(s + 1) % 7] + wb[s]) + 34u * (wb[(s + 2) % 7] + wb[(s + 6) % 7]) +
+                                48u * (wb[(s + 3) % 7] + wb[(s + 5) % 7]) + 56u * wb[(s + 4) % 7];
             // horizontal pass: v[-3..6] around this lane's column x
             const unsigned la = __shfl_up_sync(0xFFFFFFFFu, va, 1), lb = __shfl_up_sync(0xFFFFFFFFu, vb, 1);
             const unsigned ra = __shfl_down_sync(0xFFFFFFFFu, va, 1), rb = __shfl_down_sync(0xFFFFFFFFu, vb, 1);
@@ -640,10 +649,11 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const
             const unsigned o1 = (18u * (vm2 + v4) + 34u * (vm1 + v3) + 48u * (v0 + v2) + 56u * v1 + 32768u) >> 16;
             const unsigned o2 = (18u * (vm1 + v5) + 34u * (v0 + v4) + 48u * (v1 + v3) + 56u * v2 + 32768u) >> 16;
             const unsigned o3 = (18u * (v0 + v6) + 34u * (v1 + v5) + 48u * (v2 + v4) + 56u * v3 + 32768u) >> 16;
-            if (lane >= 1 && lane <= 30 && x < w && y < y1)     // the last word of a row may extend into the pitch padding
-                *reinterpret_cast<unsigned*>(dst + (size_t)y * G.pitch + x) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+            if (writer && y < y1)
+                *reinterpret_cast<unsigned*>(dst + (unsigned)(y * G.pitch)) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
         }
     }
+#undef LOAD_ROW
 }
 
 #undef load_row
@@ -681,39 +691,56 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 
 constexpr int DESC_WARPS = 8;
 
+// cvRound without the (quarter-rate) F2I: adding 1.5 * 2^23 rounds to nearest-even in the FADD itself and leaves the
+// integer in the low mantissa bits; exact for |v| < 2^22.
+__device__ __forceinline__ int round_magic_bits(float v) { return __float_as_int(__fadd_rn(v, 12582912.f)); }
+constexpr int MAGIC_BITS = 0x4B400000;
+
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const UMaxTable um,
-                                                                    const uint32_t* __restrict__ patT)
+                                                                    const float4* __restrict__ patT)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int g = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);      // keypoint index inside the frame
-    const int* lc = F.levelCount + (size_t)f * MAX_LEVELS;
-    int l = -1, idx = 0, total = 0;
-    for (int i = 0; i < P.nlevels; i++) {                             // levels are concatenated in ascending order (:1103)
-        const int c = lc[i];
-        if (l < 0 && g < total + c) { l = i; idx = g - total; }
-        total += c;
+    // levels are concatenated in ascending order (:1103): lane i holds the count of level i, a warp scan finds the level
+    const int myc = lane < P.nlevels ? F.levelCount[(size_t)f * MAX_LEVELS + lane] : 0;
+    int inc = myc;
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
     }
+    const int total = __shfl_sync(0xFFFFFFFFu, inc, MAX_LEVELS - 1 < 31 ? 15 : 31);
     if (g == 0 && lane == 0) F.counts[f] = total;
-    if (l < 0) return;
+    if (g >= total) return;
+    const unsigned below = __ballot_sync(0xFFFFFFFFu, inc <= g);        // levels that end at or before g
+    const int l = __popc(below & 0xFFFFu);
+    const int idx = g - __shfl_sync(0xFFFFFFFFu, inc - myc, l);
     const LevelGeom& G = P.lv[l];
     const uint32_t key = F.levelKeys[(size_t)f * P.totalNodes + G.nodeBase + idx];
     const int cx = key_x(key) + MIN_BORDER, cy = key_y(key) + MIN_BORDER;      // level coordinates (:841-842)
 
-    // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level
+    // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level; lane = column u, so
+    // m10 = u * (column sum) and m01 = sum of v * pixel with v a compile-time constant per row
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
+    {
         const int u = lane - HALF_PATCH, au = abs(u);
-        const uint8_t* c = img + (size_t)cy * pitch + cx + u;
+        int vmax = -1;                                   // rows |v| <= vmax belong to column u (the disc is convex)
+#pragma unroll
+        for (int v = 0; v <= HALF_PATCH; v++)
+            if (lane < 31 && au <= um.v[v]) vmax = v;
+        const uint8_t* c = img + (unsigned)(cy * pitch + cx + u);
+        int colsum = 0;
 #pragma unroll
         for (int v = -HALF_PATCH; v <= HALF_PATCH; v++) {
-            if (au <= um.v[v < 0 ? -v : v]) {
+            if ((v < 0 ? -v : v) <= vmax) {
                 const int val = __ldg(c + v * pitch);
-                m10 += u * val;
+                colsum += val;
                 m01 += v * val;
             }
         }
+        m10 = u * colsum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -726,45 +753,50 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
     float a, b;
     orbx_sc::sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);       // a = cos, b = sin (:112-113)
-    const uint8_t* ctr = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)cy * G.pitch + cx;
     const int bp = G.pitch;
+    // centre pointer with the column rounding bias folded in: index = (rbits - MAGIC) * bp + cbits, pointer - MAGIC
+    const uint8_t* ctr = F.blur + (size_t)f * P.blurSlab + G.blurOff + (unsigned)(cy * bp + cx);
+    const uint8_t* ctrb = ctr - (long long)MAGIC_BITS;
     unsigned val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; bit++) {
-        const uint32_t w = __ldg(&patT[bit * 32 + lane]);
-        const float x0 = (float)(int8_t)(w & 0xFF), y0 = (float)(int8_t)((w >> 8) & 0xFF);
-        const float x1 = (float)(int8_t)((w >> 16) & 0xFF), y1 = (float)(int8_t)(w >> 24);
+        const float4 pt = __ldg(&patT[bit * 32 + lane]);
         int r0, c0, r1, c1;
         if (P.fmaMode) {     // contracted form g++ -O3 -march=native emits for x*b + y*a and x*a - y*b
-            r0 = __float2int_rn(__fmaf_rn(x0, b, __fmul_rn(y0, a)));
-            c0 = __float2int_rn(__fmaf_rn(x0, a, -__fmul_rn(y0, b)));
-            r1 = __float2int_rn(__fmaf_rn(x1, b, __fmul_rn(y1, a)));
-            c1 = __float2int_rn(__fmaf_rn(x1, a, -__fmul_rn(y1, b)));
+            r0 = round_magic_bits(__fmaf_rn(pt.x, b, __fmul_rn(pt.y, a)));
+            c0 = round_magic_bits(__fmaf_rn(pt.x, a, -__fmul_rn(pt.y, b)));
+            r1 = round_magic_bits(__fmaf_rn(pt.z, b, __fmul_rn(pt.w, a)));
+            c1 = round_magic_bits(__fmaf_rn(pt.z, a, -__fmul_rn(pt.w, b)));
         } else {
-            r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-            c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-            r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-            c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+            r0 = round_magic_bits(__fadd_rn(__fmul_rn(pt.x, b), __fmul_rn(pt.y, a)));
+            c0 = round_magic_bits(__fsub_rn(__fmul_rn(pt.x, a), __fmul_rn(pt.y, b)));
+            r1 = round_magic_bits(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
+            c1 = round_magic_bits(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
         }
-        const int t0 = __ldg(ctr + r0 * bp + c0), t1 = __ldg(ctr + r1 * bp + c1);
+        const int t0 = __ldg(ctrb + ((r0 - MAGIC_BITS) * bp + c0)), t1 = __ldg(ctrb + ((r1 - MAGIC_BITS) * bp + c1));
         val |= (unsigned)(t0 < t1) << bit;
     }
     const size_t o = (size_t)f * P.totalNodes + g;
     F.desc[o * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        orbx_kp kp;
-        kp.x = l ? __fmul_rn((float)cx, G.scale) : (float)cx;       // pt *= mvScaleFactor[level] for level != 0 (:1095-1101)
-        kp.y = l ? __fmul_rn((float)cy, G.scale) : (float)cy;
-        kp.size = (float)G.scaledPatch;
-        kp.angle = angle;
-        kp.response = (float)key_r(key);
-        kp.octave = l;
-        kp.class_id = -1;
-        F.kps[o] = kp;
+    // keypoint record: 7 words written by 7 lanes
+    if (lane < 7) {
+        const float kx = l ? __fmul_rn((float)cx, G.scale) : (float)cx;      // pt *= mvScaleFactor[level] for level != 0 (:1095-1101)
+        const float ky = l ? __fmul_rn((float)cy, G.scale) : (float)cy;
+        unsigned wv;
+        switch (lane) {
+            case 0: wv = __float_as_uint(kx); break;
+            case 1: wv = __float_as_uint(ky); break;
+            case 2: wv = __float_as_uint((float)G.scaledPatch); break;
+            case 3: wv = __float_as_uint(angle); break;
+            case 4: wv = __float_as_uint((float)key_r(key)); break;
+            case 5: wv = (unsigned)l; break;
+            default: wv = 0xFFFFFFFFu; break;                                  // class_id = -1
+        }
+        reinterpret_cast<unsigned*>(F.kps + o)[lane] = wv;
     }
 }
 
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const uint32_t* patT, int B)
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const float4* patT, int B)
 {
     dim3 grd((P.totalNodes + DESC_WARPS - 1) / DESC_WARPS, B);
     k_orient_describe<<<grd, DESC_WARPS * 32, 0, s>>>(P, F, um, patT);

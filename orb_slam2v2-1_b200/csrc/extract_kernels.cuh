@@ -35,7 +35,7 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const uint32_t* patT, int B);
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const float4* patT, int B);
 // padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
 void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch);
 

@@ -49,7 +49,7 @@ struct orbx_extractor {
 
     int device = 0, maxBatch = 1, fmaMode = 0;
     cudaStream_t stream = nullptr;
-    uint32_t* d_patT = nullptr;
+    float4* d_patT = nullptr;          // rBRIEF pattern as floats: patT[bit * 32 + byte] = (x0, y0, x1, y1)
     UMaxTable um{};
 
     // current shape
@@ -398,10 +398,14 @@ int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, in
     for (int i = 0; i < 16; i++) ex->um.v[i] = ex->umax[i];
 
     if (!cuda_ok(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking), "cudaStreamCreate", __FILE__, __LINE__)) { delete ex; return ORBX_ERR_CUDA; }
-    // rBRIEF pattern, transposed so that lane = descriptor byte reads consecutive words: patT[bit*32 + byte]
-    uint32_t patT[256];
+    // rBRIEF pattern, transposed so that lane = descriptor byte reads consecutive entries, coordinates already as floats
+    float4 patT[256];
     for (int byte = 0; byte < 32; byte++)
-        for (int bit = 0; bit < 8; bit++) patT[bit * 32 + byte] = kPatternPacked[byte * 8 + bit];
+        for (int bit = 0; bit < 8; bit++) {
+            const uint32_t w = kPatternPacked[byte * 8 + bit];
+            patT[bit * 32 + byte] = make_float4((float)(int8_t)(w & 0xFF), (float)(int8_t)((w >> 8) & 0xFF),
+                                                (float)(int8_t)((w >> 16) & 0xFF), (float)(int8_t)(w >> 24));
+        }
     if (!cuda_ok(cudaMalloc(&ex->d_patT, sizeof patT), "cudaMalloc(pattern)", __FILE__, __LINE__) ||
         !cuda_ok(cudaMemcpy(ex->d_patT, patT, sizeof patT, cudaMemcpyHostToDevice), "cudaMemcpy(pattern)", __FILE__, __LINE__)) {
         cudaStreamDestroy(ex->stream);
