@@ -1,0 +1,55 @@
+// Exercises the drop-in C++ headers (include/ORBextractor.h, include/ORBmatcher.h) the way Frame.cc uses the reference
+// classes.  usage: dropin_test in.raw w h nfeatures out.bin
+// out.bin: int32 n | n x 28-byte keypoints | n x 32 descriptor bytes | int32 levels | per level int32 w,h + bytes |
+//          int32 nmatch_self | n int32 matches (SearchBruteForce of the descriptors against themselves)
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+int main(int argc, char** argv)
+{
+    if (argc < 6) return 2;
+    const int w = atoi(argv[2]), h = atoi(argv[3]), nf = atoi(argv[4]);
+    std::vector<uint8_t> img((size_t)w * h);
+    FILE* f = fopen(argv[1], "rb");
+    if (!f || fread(img.data(), 1, img.size(), f) != img.size()) return 3;
+    fclose(f);
+    try {
+        ORB_SLAM2::ORBextractor* ex = new ORB_SLAM2::ORBextractor(nf, 1.2f, 8, 20, 7);     // Tracking.cc:113-119
+        cv::Mat im(h, w, cv::CV_8UC1, img.data());
+        std::vector<cv::KeyPoint> keys;
+        cv::Mat desc;
+        (*ex)(im, cv::Mat(), keys, desc);                                                    // Frame.cc:247-253
+        ORB_SLAM2::ORBmatcher matcher(0.9, true);
+        std::vector<int> m;
+        const int nm = keys.empty() ? 0 : matcher.SearchBruteForce(desc, desc, m);
+        const int d01 = keys.size() > 1 ? ORB_SLAM2::ORBmatcher::DescriptorDistance(desc.row(0), desc.row(1)) : -1;
+        FILE* o = fopen(argv[5], "wb");
+        const int n = (int)keys.size();
+        fwrite(&n, 4, 1, o);
+        static_assert(sizeof(cv::KeyPoint) == 28, "cv::KeyPoint layout");
+        fwrite(keys.data(), 28, n, o);
+        for (int i = 0; i < n; i++) fwrite(desc.ptr<uint8_t>(i), 1, 32, o);
+        const int L = ex->GetLevels();
+        fwrite(&L, 4, 1, o);
+        for (int l = 0; l < L; l++) {
+            const cv::Mat& p = ex->mvImagePyramid[l];
+            fwrite(&p.cols, 4, 1, o);
+            fwrite(&p.rows, 4, 1, o);
+            for (int y = 0; y < p.rows; y++) fwrite(p.ptr<uint8_t>(y), 1, p.cols, o);
+        }
+        fwrite(&nm, 4, 1, o);
+        m.resize(n, -1);
+        fwrite(m.data(), 4, n, o);
+        fwrite(&d01, 4, 1, o);
+        fclose(o);
+        printf("ok %d keypoints, %d self matches, scale[1]=%g\n", n, nm, ex->GetScaleFactors()[1]);
+        delete ex;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "error: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

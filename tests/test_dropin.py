@@ -1,0 +1,78 @@
+"""The drop-in C++ headers (include/ORBextractor.h, include/ORBmatcher.h) used the way Frame.cc / Tracking.cc use the
+reference classes (tests/native/dropin_test.cpp).  CPU leg: the program compiles with g++ alone, links against
+liborbx.so, and -- there being no CPU fallback -- fails loudly without a device.  GPU leg: its outputs (keypoints,
+descriptors, mvImagePyramid, a brute-force self match, DescriptorDistance) equal the oracle's."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_py as O
+import orbx
+from orbx import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build(tmp_path):
+    if not os.path.exists(orbx.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    exe = str(tmp_path / "dropin_test")
+    libdir = os.path.dirname(orbx.LIB_PATH)
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), "-o", exe,
+                           os.path.join(ROOT, "tests", "native", "dropin_test.cpp"), "-L", libdir, "-lorbx", "-Wl,-rpath," + libdir])
+    return exe
+
+
+def _has_gpu():
+    import torch
+    return torch.cuda.is_available()
+
+
+def test_dropin_compiles_links_and_has_no_cpu_fallback(tmp_path):
+    exe = _build(tmp_path)
+    if _has_gpu():
+        pytest.skip("GPU present: covered by the gpu leg")
+    img = synth.rects(320, 240, 7)
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(img.tobytes())
+    r = subprocess.run([exe, str(raw), "320", "240", "500", str(tmp_path / "out.bin")], capture_output=True, text=True)
+    assert r.returncode == 1 and "orbx_create" in r.stderr, (r.returncode, r.stderr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,nf,seed", [(640, 480, 1000, 1000), (752, 480, 1200, 2000)])
+def test_dropin_matches_oracle(tmp_path, w, h, nf, seed):
+    exe = _build(tmp_path)
+    img = synth.rects(w, h, seed)
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(img.tobytes())
+    out = tmp_path / "out.bin"
+    subprocess.check_call([exe, str(raw), str(w), str(h), str(nf), str(out)])
+    b = out.read_bytes()
+    n, = struct.unpack_from("<i", b, 0)
+    p = 4
+    kps = np.frombuffer(b, dtype=orbx.KP_DTYPE, count=n, offset=p); p += 28 * n
+    desc = np.frombuffer(b, dtype=np.uint8, count=32 * n, offset=p).reshape(n, 32); p += 32 * n
+    oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
+    okps, odesc = oe(img)
+    assert n == len(okps) and kps.tobytes() == okps.tobytes()
+    assert np.array_equal(desc, odesc)
+    L, = struct.unpack_from("<i", b, p); p += 4
+    assert L == 8
+    for l in range(L):
+        lw, lh = struct.unpack_from("<ii", b, p); p += 8
+        lev = np.frombuffer(b, dtype=np.uint8, count=lw * lh, offset=p).reshape(lh, lw); p += lw * lh
+        assert (lw, lh) == oe.level_size(l)
+        assert np.array_equal(lev, oe.level_padded(l)[19:-19, 19:-19]), "mvImagePyramid[%d]" % l
+    nm, = struct.unpack_from("<i", b, p); p += 4
+    m = np.frombuffer(b, dtype=np.int32, count=n, offset=p); p += 4 * n
+    d01, = struct.unpack_from("<i", b, p)
+    bi, bd, sd = O.match_bruteforce(odesc, odesc)
+    acc = (bd <= 50) & (bd.astype(np.float32) < np.float32(0.9) * sd.astype(np.float32))
+    assert nm == int(acc.sum())
+    assert np.array_equal(m, np.where(acc, bi, -1))
+    assert d01 == O.descriptor_distance(odesc[0], odesc[1])
