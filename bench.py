@@ -241,8 +241,8 @@ def run_ours(args):
     import ctypes as C
     L = orbx.lib()
     pinned = torch.from_numpy(host).pin_memory()
-    chunk = min(64, B)
-    nthreads = 3
+    chunk = min(args.e2e_chunk, B)
+    nthreads = args.e2e_threads
     workers = [orbx.ORBextractor(*PARAMS, device=local, max_batch=chunk) for _ in range(nthreads)]
     for wk in workers:
         wk(host[0])                                                  # plans the shape; max_keypoints is exact afterwards
@@ -366,6 +366,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (= extractor handles) of the e2e leg")
+    ap.add_argument("--e2e-chunk", type=int, default=64, help="frames per orbx_extract_batch call in the e2e leg")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -572,7 +572,10 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, in
     ORBX_CUDA(cudaSetDevice(ex->device));
     int rc = ensure_shape(ex, w, h, B);
     if (rc) return rc;
-    for (int b = 0; b < B; b++) {
+    // frames whose host rows are laid out exactly like the device slab (stride == device pitch) travel as one linear
+    // copy per run of frames that are also contiguous in host memory; anything else as one 2-D copy per frame
+    const bool linear = stride == ex->lv0Pitch;
+    for (int b = 0; b < B;) {
         if (!imgs[b]) { set_error("orbx_extract_batch: imgs[%d] is null", b); return ORBX_ERR_ARG; }
         cudaPointerAttributes attr;
         const bool pinned = cudaPointerGetAttributes(&attr, imgs[b]) == cudaSuccess && attr.type == cudaMemoryTypeHost;
@@ -585,7 +588,18 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, in
             src = st;
             spitch = ex->lv0Pitch;
         }
-        ORBX_CUDA(cudaMemcpy2DAsync(ex->d_lv0 + (size_t)b * ex->lv0Frame, ex->lv0Pitch, src, spitch, w, h, cudaMemcpyHostToDevice, ex->stream));
+        int run = 1;
+        if (pinned && linear) {
+            while (b + run < B && imgs[b + run] == imgs[b] + (size_t)run * ex->lv0Frame &&
+                   cudaPointerGetAttributes(&attr, imgs[b + run]) == cudaSuccess && attr.type == cudaMemoryTypeHost)
+                run++;
+            cudaGetLastError();
+            const size_t bytes = (size_t)(run - 1) * ex->lv0Frame + (size_t)(h - 1) * stride + w;
+            ORBX_CUDA(cudaMemcpyAsync(ex->d_lv0 + (size_t)b * ex->lv0Frame, src, bytes, cudaMemcpyHostToDevice, ex->stream));
+        } else {
+            ORBX_CUDA(cudaMemcpy2DAsync(ex->d_lv0 + (size_t)b * ex->lv0Frame, ex->lv0Pitch, src, spitch, w, h, cudaMemcpyHostToDevice, ex->stream));
+        }
+        b += run;
     }
     ex->bufs.lv0 = ex->d_lv0;
     ex->bufs.lv0Pitch = ex->lv0Pitch;
