@@ -27,69 +27,78 @@ __device__ __forceinline__ int level_of_cell(const Plan& P, int cell)
 
 // ------------------------------------------------------------------------------------------------ pyramid
 // cv::resize INTER_LINEAR, 8-bit: 11-bit coefficients (host tables), horizontal pass H = S[sx]*a0 + S[sx+1]*a1 in int32,
-// vertical pass (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2.
-// One thread = 4 adjacent output columns x RS_ROWS output rows.  The 8 source bytes a row needs lie within 8 contiguous
-// bytes: three aligned word loads + a funnel shift + two PRMTs (selectors precomputed per column group on the host)
-// replace 8 byte loads.  Walking down the rows, the horizontal pass of source row sy+1 is reused as row sy of the next
-// output row whenever the source advances by exactly one row (5 of 6 rows at scale 1.2).
-constexpr int RS_ROWS = 8;
+// vertical pass (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2  (always within 0..255: the weights sum to 2048).
+// One CTA = a tile of 128 output columns x RS_TILE_H output rows, in two phases:
+//   1. horizontal pass of every source row the tile touches, once, into shared memory (H >> 4 as u16, one uint2 per
+//      group of 4 output columns: the kernel is bound by L1/shared-memory wavefronts, so the narrow format wins).  The (left, right) source bytes of two adjacent output columns span at most 4
+//      bytes (level ratio <= 2), i.e. two aligned words: one PRMT (selector precomputed per column group on the host)
+//      builds the word (L0, R0, L1, R1) and one IDP.2A per column (FMA pipe, the 16-bit weight pair a0 | a1 << 16 as the
+//      other operand) finishes it.  Rows are independent, so the loop is unrolled and many loads are in flight per thread
+//      (the level-0 source streams from HBM);
+//   2. vertical pass from shared memory: two LDS.64 per 4 output pixels, products on the FMA pipe (IMAD), shift-adds as
+//      LEA.HI, one 32-bit store.
+constexpr int RS_TILE_H = 64;
 
-struct ResizeCols { int4 a, b; };   // a = {w0 | w1 << 16, w2 | shift << 16, selL, selR}; b = 4 x (a0 | a1 << 16)
-
-__device__ __forceinline__ void resize_hrow(const uint8_t* row, const ResizeCols& c, int H[4])
-{
-    const uint32_t* r = reinterpret_cast<const uint32_t*>(row);
-    const uint32_t w0 = __ldg(r + (c.a.x & 0xFFFF)), w1 = __ldg(r + (c.a.x >> 16)), w2 = __ldg(r + (c.a.y & 0xFFFF));
-    const int sh = c.a.y >> 16;
-    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
-    const uint32_t L = __byte_perm(lo, hi, c.a.z), R = __byte_perm(lo, hi, c.a.w);
-    H[0] = ((int)(L & 0xFF) * (c.b.x & 0xFFFF) + (int)(R & 0xFF) * (c.b.x >> 16)) >> 4;
-    H[1] = ((int)((L >> 8) & 0xFF) * (c.b.y & 0xFFFF) + (int)((R >> 8) & 0xFF) * (c.b.y >> 16)) >> 4;
-    H[2] = ((int)((L >> 16) & 0xFF) * (c.b.z & 0xFFFF) + (int)((R >> 16) & 0xFF) * (c.b.z >> 16)) >> 4;
-    H[3] = ((int)(L >> 24) * (c.b.w & 0xFFFF) + (int)(R >> 24) * (c.b.w >> 16)) >> 4;
-}
+struct ResizeCols { int4 a, b; };   // a = {word of pair 01, word of pair 23, sel01, sel23}; b = 4 x (a0 | a1 << 16)
 
 __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, int spitch, size_t sframe,
                                                 uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dframe,
                                                 const ResizeCols* __restrict__ xtab, const int4* __restrict__ ytab)
 {
-    const int f = blockIdx.z;
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;          // column group
-    const int y0 = (blockIdx.y * blockDim.y + threadIdx.y) * RS_ROWS;
-    if (g * 4 >= dw || y0 >= dh) return;
-    ResizeCols c;
-    c.a = __ldg(&xtab[g].a);
-    c.b = __ldg(&xtab[g].b);
-    const uint8_t* S = src + (size_t)f * sframe;
+    extern __shared__ uint2 Hs[];                                  // [source row of the tile][column group], 4 x u16
+    const int f = blockIdx.z, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int g = min(blockIdx.x * 32 + tx, (dw - 1) >> 2);        // column group (clamped: idle lanes repeat the last one)
+    const int oy0 = blockIdx.y * RS_TILE_H, oy1 = min(oy0 + RS_TILE_H, dh);
+    const int sFirst = __ldg(&ytab[oy0]).x, n = __ldg(&ytab[oy1 - 1]).y - sFirst + 1;
+    const int4 ca = __ldg(&xtab[g].a), cb = __ldg(&xtab[g].b);
+    const uint32_t* S = reinterpret_cast<const uint32_t*>(src + (size_t)f * sframe + (size_t)sFirst * spitch);
+    const int wpitch = spitch >> 2;
+#pragma unroll 4
+    for (int r = ty; r < n; r += 8) {
+        const uint32_t* row = S + (size_t)r * wpitch;
+        const uint32_t wa = __ldg(row + ca.x), wb = __ldg(row + ca.x + 1), wc = __ldg(row + ca.y), wd = __ldg(row + ca.y + 1);
+        const uint32_t W01 = __byte_perm(wa, wb, ca.z), W23 = __byte_perm(wc, wd, ca.w);
+        // H >> 4 <= 32640 fits 16 bits: (H1 >> 4) << 16 | (H0 >> 4) == ((H1 << 12) & 0xFFFF0000) | (H0 >> 4), the merge on the FMA pipe
+        const unsigned H0 = __dp2a_lo((unsigned)cb.x, W01, 0u), H1 = __dp2a_hi((unsigned)cb.y, W01, 0u);
+        const unsigned H2 = __dp2a_lo((unsigned)cb.z, W23, 0u), H3 = __dp2a_hi((unsigned)cb.w, W23, 0u);
+        Hs[r * 32 + tx] = make_uint2((H1 >> 4) * 65536u + (H0 >> 4), (H3 >> 4) * 65536u + (H2 >> 4));
+    }
+    __syncthreads();
+    if (blockIdx.x * 32 + tx > ((dw - 1) >> 2)) return;
     uint8_t* D = dst + (size_t)f * dframe + (size_t)g * 4;
-    int cached = -1, Hc[4] = {0, 0, 0, 0};
-    const int y1 = min(y0 + RS_ROWS, dh);
-    for (int dy = y0; dy < y1; dy++) {
+#pragma unroll 2
+    for (int dy = oy0 + ty; dy < oy1; dy += 8) {
         const int4 yy = __ldg(&ytab[dy]);                          // {sy0, sy1 (clamped), b0, b1}
-        int H0[4], H1[4];
-        if (yy.x == cached) { H0[0] = Hc[0]; H0[1] = Hc[1]; H0[2] = Hc[2]; H0[3] = Hc[3]; }
-        else resize_hrow(S + (size_t)yy.x * spitch, c, H0);
-        if (yy.y == yy.x) { H1[0] = H0[0]; H1[1] = H0[1]; H1[2] = H0[2]; H1[3] = H0[3]; }
-        else resize_hrow(S + (size_t)yy.y * spitch, c, H1);
-        uint32_t out = 0;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            int v = (((yy.z * H0[k]) >> 16) + ((yy.w * H1[k]) >> 16) + 2) >> 2;
-            v = min(max(v, 0), 255);
-            out |= (uint32_t)v << (8 * k);
-            Hc[k] = H1[k];
-        }
-        cached = yy.y;
-        *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = out;     // pitch is a multiple of 32: the last word may pad
+        const uint2 h0 = Hs[(yy.x - sFirst) * 32 + tx], h1 = Hs[(yy.y - sFirst) * 32 + tx];
+        const unsigned b0 = (unsigned)yy.z, b1 = (unsigned)yy.w;
+        const unsigned v0 = ((b0 * (h0.x & 0xFFFFu)) >> 16) + (((b1 * (h1.x & 0xFFFFu)) >> 16) + 2u);      // <= 1022, >> 2 below
+        const unsigned v1 = ((b0 * (h0.x >> 16)) >> 16) + (((b1 * (h1.x >> 16)) >> 16) + 2u);
+        const unsigned v2 = ((b0 * (h0.y & 0xFFFFu)) >> 16) + (((b1 * (h1.y & 0xFFFFu)) >> 16) + 2u);
+        const unsigned v3 = ((b0 * (h0.y >> 16)) >> 16) + (((b1 * (h1.y >> 16)) >> 16) + 2u);
+        // pack: (v0 | v1 << 16) >> 2 has v0 >> 2 in byte 0 and v1 >> 2 in byte 2 (v < 1024)
+        const unsigned p01 = (v1 * 65536u + v0) >> 2, p23 = (v3 * 65536u + v2) >> 2;
+        *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = __byte_perm(p01, p23, 0x6420);     // pitch is a multiple of 32: the last word may pad
     }
 }
 
-void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
-                   size_t dframe, const void* xtab, const int4* ytab, int B)
+// shared memory for a level pair: source rows one tile can touch
+size_t resize_smem_bytes(int sh, int dh)
 {
-    dim3 blk(32, 8);
-    dim3 grd(((dw + 3) / 4 + 31) / 32, (dh + 8 * RS_ROWS - 1) / (8 * RS_ROWS), B);
-    k_resize<<<grd, blk, 0, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
+    const int rows = (int)((double)RS_TILE_H * sh / dh) + 4;
+    return (size_t)rows * 32 * sizeof(uint2);
+}
+
+void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
+                   size_t dframe, const void* xtab, const int4* ytab, int B, int sh)
+{
+    const size_t smem = resize_smem_bytes(sh, dh);
+    static thread_local size_t configured = 48 * 1024;
+    if (smem > configured) {
+        cudaFuncSetAttribute(k_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    dim3 grd(((dw + 3) / 4 + 31) / 32, (dh + RS_TILE_H - 1) / RS_TILE_H, B);
+    k_resize<<<grd, 256, smem, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
 }
 
 // ------------------------------------------------------------------------------------------------ FAST per cell
@@ -568,12 +577,18 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 // ------------------------------------------------------------------------------------------------ Gaussian blur
 // cv::GaussianBlur(7x7, sigma 2) on u8, OpenCV 4.x fixed-point path: taps 18,34,48,56,48,34,18 / 256; the first pass is
 // exact 8.8 (no rounding), the second 8.16, out = (acc + 32768) >> 16; BORDER_REFLECT_101 of the level itself (the
-// reference blurs a border-less clone, ORBextractor.cc:1085).  Because the first pass is exact, the result equals
-// (sum_ij K_i K_j p_ij + 32768) >> 16 whichever direction runs first.  Here the VERTICAL pass runs first: a lane owns 4
-// adjacent columns (one 32-bit word) and walks down a strip of rows with a 7-row sliding window held in registers as
-// packed u16x2 pairs (every partial sum fits 16 bits, so 32-bit multiply-adds work on two pixels at once); the
-// horizontal pass takes the neighbour columns from the adjacent lanes by shuffle.  Lanes 0 and 31 are halo lanes.
-constexpr int BLUR_COLS = 120;       // output columns per warp: lanes 1..30 x 4
+// reference blurs a border-less clone, ORBextractor.cc:1085).
+// Both passes run on the dot-product instructions (IDP.4A / IDP.2A, 64 lanes/clk/SM beside the ALU pipe, see
+// tools/int_pipe_bench.cu) instead of unpack + multiply-add chains.  A lane owns 4 adjacent columns (one 32-bit word) and
+// walks down a strip of rows:
+//   horizontal: the 7 taps of each of the 4 pixels lie in the words L | C | R (left neighbour, own, right neighbour, all
+//               loaded straight from L1): 10 IDP.4A against constant tap words give h0..h3 (<= 65280, exact);
+//   pairing:    P(r) = h(r-1) | h(r) << 16 per column (one IMAD each): a sliding window of the last 6 pairs per column
+//               lives in registers;
+//   vertical:   out(y) = 18 h(y-3) + 34 h(y-2) + 48 h(y-1) + 56 h(y) + 48 h(y+1) + 34 h(y+2) + 18 h(y+3) + 32768
+//                      = IDP.2A(P(y-2),(18,34)) + IDP.2A(P(y),(48,56)) + IDP.2A(P(y+2),(48,34)) + IDP.2A(P(y+3),(0,18)),
+//               and the result byte is bits 16..23 of the accumulator (one PRMT tree packs the 4 pixels).
+constexpr int BLUR_COLS = 128;       // output columns per warp: 32 lanes x 4
 constexpr int BLUR_ROWS = 64;        // rows per strip
 constexpr int BLUR_WARPS = 8;
 
@@ -592,6 +607,23 @@ __device__ __forceinline__ int reflect1(int p, int len)
     return min(max(p, 0), len - 1);
 }
 
+// The 4 pixels at columns xb .. xb+3 reflected into [0, w) always lie within two aligned words: byte offsets of the two
+// words and the PRMT selector that puts them in order (0x3210 with offB unused when no border is involved).
+struct BlurWord { unsigned offA, offB, sel; };
+__device__ __forceinline__ BlurWord blur_word(int xb, int w)
+{
+    const int c0 = reflect1(xb, w), c1 = reflect1(xb + 1, w), c2 = reflect1(xb + 2, w), c3 = reflect1(xb + 3, w);
+    const int wA = min(min(c0, c1), min(c2, c3)) >> 2, wB = max(max(c0, c1), max(c2, c3)) >> 2;
+    auto nib = [&](int c) { return (unsigned)((c >> 2) == wA ? c - 4 * wA : 4 + c - 4 * wB); };
+    BlurWord r;
+    r.offA = (unsigned)wA * 4;
+    r.offB = (unsigned)wB * 4;
+    r.sel = nib(c0) | (nib(c1) << 4) | (nib(c2) << 8) | (nib(c3) << 12);
+    return r;
+}
+
+#define TAPS4(a, b, c, d) ((unsigned)(a) | ((unsigned)(b) << 8) | ((unsigned)(c) << 16) | ((unsigned)(d) << 24))
+
 __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const FrameBufs F)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
@@ -603,60 +635,65 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const
     const int t = tile - G.blurTileBase;
     const int ty = t / G.blurTilesX, tx = t - ty * G.blurTilesX;
     const int w = G.w, h = G.h;
-    const int x = tx * BLUR_COLS + (lane - 1) * 4;      // first of this lane's 4 columns (may be < 0 or >= w: halo / padding)
+    const int x = tx * BLUR_COLS + lane * 4;            // first of this lane's 4 columns
+    if (x >= w) return;                                 // no warp-wide operation below: idle lanes leave
     const int y0 = ty * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    // The lane's 4 source columns, reflected at the image borders, always lie within two aligned words: one PRMT with a
-    // per-lane selector puts them in order.  Warps that touch no border load a single word.
-    const int c0 = reflect1(x, w), c1 = reflect1(x + 1, w), c2 = reflect1(x + 2, w), c3 = reflect1(x + 3, w);
-    const int wA = min(min(c0, c1), min(c2, c3)) >> 2, wB = max(max(c0, c1), max(c2, c3)) >> 2;
-    const unsigned offA = (unsigned)wA * 4, offB = (unsigned)wB * 4;
-    auto nib = [&](int c) { return (unsigned)((c >> 2) == wA ? c - 4 * wA : 4 + c - 4 * wB); };
-    const unsigned sel = nib(c0) | (nib(c1) << 4) | (nib(c2) << 8) | (nib(c3) << 12);
-    const bool edgeWarp = __any_sync(0xFFFFFFFFu, sel != 0x3210u);
+    const BlurWord wl = blur_word(x - 4, w), wc = blur_word(x, w), wr = blur_word(x + 4, w);
+    const bool edge = (wl.sel != 0x3210u) | (wc.sel != 0x3210u) | (wr.sel != 0x3210u);
 
-    unsigned wa[7], wb[7];      // window: packed (col x, col x+1) and (col x+2, col x+3) of the last 7 rows
-#define LOAD_ROW(Y, A, B)                                                                                   \
-    {                                                                                                       \
-        const uint8_t* row_ = img + (unsigned)(reflect1((Y), h) * pitch);                                   \
-        unsigned v_ = __ldg(reinterpret_cast<const unsigned*>(row_ + offA));                                \
-        if (edgeWarp) v_ = __byte_perm(v_, __ldg(reinterpret_cast<const unsigned*>(row_ + offB)), sel);     \
-        A = __byte_perm(v_, 0, 0x4140);                                                                     \
-        B = __byte_perm(v_, 0, 0x4342);                                                                     \
-    }
+    unsigned hp[4] = {0, 0, 0, 0};      // h of the previous row
+    unsigned Pw[6][4];                  // pairs P(r-5) .. P(r), slot = r mod 6 (statically indexed: the loop is unrolled by 6)
 #pragma unroll
-    for (int j = 0; j < 6; j++) LOAD_ROW(y0 - 3 + j, wa[j], wb[j]);
+    for (int j = 0; j < 6; j++) Pw[j][0] = Pw[j][1] = Pw[j][2] = Pw[j][3] = 0;
     uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + x;
-    const bool writer = lane >= 1 && lane <= 30 && x < w;     // the last word of a row may extend into the pitch padding
-    for (int yb = y0; yb < y1; yb += 7) {
+    // iteration i handles source row r = y0 - 3 + i and, from i = 6 on, emits output row y = r - 3
+    const int niter = (y1 - y0) + 6;
+    for (int ib = 0; ib < niter; ib += 6) {
 #pragma unroll
-        for (int j = 0; j < 7; j++) {
-            const int y = yb + j;                        // output row; its window is rows y-3 .. y+3
-            const int s = (j + 6) % 7;                   // slot receiving row y+3; rows y-3..y+3 sit in slots (s+1)%7 .. s
-            LOAD_ROW(y + 3, wa[s], wb[s]);
-            const unsigned va = 18u * (wa[(s + 1) % 7] + wa[s]) + 34u * (wa[(s + 2) % 7] + wa[(s + 6) % 7]) +
-                                48u * (wa[(s + 3) % 7] + wa[(s + 5) % 7]) + 56u * wa[(s + 4) % 7];
-            const unsigned vb = 18u * (wb[(s + 1) % 7] + wb[s]) + 34u * (wb[(s + 2) % 7] + wb[(s + 6) % 7]) +
-                                48u * (wb[(s + 3) % 7] + wb[(s + 5) % 7]) + 56u * wb[(s + 4) % 7];
-            // horizontal pass: v[-3..6] around this lane's column x
-            const unsigned la = __shfl_up_sync(0xFFFFFFFFu, va, 1), lb = __shfl_up_sync(0xFFFFFFFFu, vb, 1);
-            const unsigned ra = __shfl_down_sync(0xFFFFFFFFu, va, 1), rb = __shfl_down_sync(0xFFFFFFFFu, vb, 1);
-            const unsigned vm3 = la >> 16, vm2 = lb & 0xFFFFu, vm1 = lb >> 16;
-            const unsigned v0 = va & 0xFFFFu, v1 = va >> 16, v2 = vb & 0xFFFFu, v3 = vb >> 16;
-            const unsigned v4 = ra & 0xFFFFu, v5 = ra >> 16, v6 = rb & 0xFFFFu;
-            const unsigned o0 = (18u * (vm3 + v3) + 34u * (vm2 + v2) + 48u * (vm1 + v1) + 56u * v0 + 32768u) >> 16;
-            const unsigned o1 = (18u * (vm2 + v4) + 34u * (vm1 + v3) + 48u * (v0 + v2) + 56u * v1 + 32768u) >> 16;
-            const unsigned o2 = (18u * (vm1 + v5) + 34u * (v0 + v4) + 48u * (v1 + v3) + 56u * v2 + 32768u) >> 16;
-            const unsigned o3 = (18u * (v0 + v6) + 34u * (v1 + v5) + 48u * (v2 + v4) + 56u * v3 + 32768u) >> 16;
-            if (writer && y < y1)
-                *reinterpret_cast<unsigned*>(dst + (unsigned)(y * G.pitch)) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+        for (int j = 0; j < 6; j++) {
+            const int i = ib + j;
+            const int r = y0 - 3 + i;
+            const uint8_t* row = img + (unsigned)(reflect1(r, h) * pitch);
+            unsigned L = __ldg(reinterpret_cast<const unsigned*>(row + wl.offA));
+            unsigned C = __ldg(reinterpret_cast<const unsigned*>(row + wc.offA));
+            unsigned R = __ldg(reinterpret_cast<const unsigned*>(row + wr.offA));
+            if (edge) {
+                L = __byte_perm(L, __ldg(reinterpret_cast<const unsigned*>(row + wl.offB)), wl.sel);
+                C = __byte_perm(C, __ldg(reinterpret_cast<const unsigned*>(row + wc.offB)), wc.sel);
+                R = __byte_perm(R, __ldg(reinterpret_cast<const unsigned*>(row + wr.offB)), wr.sel);
+            }
+            const unsigned h0 = __dp4a(C, TAPS4(56, 48, 34, 18), __dp4a(L, TAPS4(0, 18, 34, 48), 0u));
+            const unsigned h1 = __dp4a(R, TAPS4(18, 0, 0, 0), __dp4a(C, TAPS4(48, 56, 48, 34), __dp4a(L, TAPS4(0, 0, 18, 34), 0u)));
+            const unsigned h2 = __dp4a(R, TAPS4(34, 18, 0, 0), __dp4a(C, TAPS4(34, 48, 56, 48), __dp4a(L, TAPS4(0, 0, 0, 18), 0u)));
+            const unsigned h3 = __dp4a(R, TAPS4(48, 34, 18, 0), __dp4a(C, TAPS4(18, 34, 48, 56), 0u));
+            // slot j receives P(r) = (h(r-1), h(r)); P(r-1) sits in slot j-1, ... (mod 6)
+            Pw[j][0] = h0 * 65536u + hp[0];
+            Pw[j][1] = h1 * 65536u + hp[1];
+            Pw[j][2] = h2 * 65536u + hp[2];
+            Pw[j][3] = h3 * 65536u + hp[3];
+            hp[0] = h0; hp[1] = h1; hp[2] = h2; hp[3] = h3;
+            const int y = r - 3;
+            if (i >= 6 && y < y1) {
+                unsigned o[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    // P(y+3) = P(r) slot j, P(y+2) = P(r-1) slot j-1, P(y) = P(r-3) slot j-3, P(y-2) = P(r-5) slot j-5
+                    unsigned acc = __dp2a_lo(Pw[(j + 1) % 6][k], TAPS4(18, 34, 0, 0), 32768u);
+                    acc = __dp2a_lo(Pw[(j + 3) % 6][k], TAPS4(48, 56, 0, 0), acc);
+                    acc = __dp2a_lo(Pw[(j + 5) % 6][k], TAPS4(48, 34, 0, 0), acc);
+                    o[k] = __dp2a_lo(Pw[j][k], TAPS4(0, 18, 0, 0), acc);
+                }
+                // byte 2 of each accumulator
+                *reinterpret_cast<unsigned*>(dst + (unsigned)(y * G.pitch)) =
+                    __byte_perm(__byte_perm(o[0], o[1], 0x0062), __byte_perm(o[2], o[3], 0x0062), 0x5410);
+            }
         }
     }
-#undef LOAD_ROW
 }
 
-#undef load_row
+#undef TAPS4
 
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
 {

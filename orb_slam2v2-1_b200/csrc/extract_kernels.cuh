@@ -26,7 +26,7 @@ struct UMaxTable { int v[16]; };
 
 // cv::resize(INTER_LINEAR) of one level from the previous one for all frames (ComputePyramid, ORBextractor.cc:1120).
 void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
-                   size_t dframe, const void* xtab, const int4* ytab, int B);
+                   size_t dframe, const void* xtab, const int4* ytab, int B, int sh);
 // xtab: one 32-byte record per group of 4 output columns (see build_resize_tables)
 // per-cell FAST-9/16 + NMS + ini/min retry, all levels and frames (ComputeKeyPointsOctTree cell loop, :789-829)
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);

@@ -133,7 +133,7 @@ static int build_plan(orbx_extractor* ex, int w, int h)
         capS = std::max(capS, std::max(G.quota + 4, 4 * G.nIni) + 4);
         G.nodeBase = nodes;
         nodes += G.nodeCap;
-        G.blurTilesX = (G.w + 119) / 120;        // k_blur: 120 output columns x 64 rows per warp
+        G.blurTilesX = (G.w + 127) / 128;        // k_blur: 128 output columns x 64 rows per warp
         G.blurTileBase = tiles;
         tiles += G.blurTilesX * ((G.h + 63) / 64);
         G.scaledPatch = (int)(31 * ex->mvScaleFactor[l]);            // PATCH_SIZE*mvScaleFactor[level] (:845)
@@ -167,9 +167,9 @@ static int build_plan(orbx_extractor* ex, int w, int h)
 
 // cv::resize INTER_LINEAR coefficient tables (8-bit fixed-point path): 11-bit weights from float fx.
 // Column table: one record of 8 ints per group of 4 output columns (k_resize):
-//   [0] w0 | w1 << 16, [1] w2 | shift << 16 : the three aligned source words covering bytes sx(first) .. +7 and the funnel
-//       shift (bits) that brings byte sx(first) to position 0 (word indices clamped to the last word of the row),
-//   [2] selL, [3] selR : PRMT selectors of the four left (sx) and right (sx+1, clamped) source bytes,
+//   [0] word index of the aligned word pair holding the bytes (sx, sx+1) of columns 0 and 1, [1] same for columns 2, 3,
+//   [2] sel01, [3] sel23 : PRMT selectors that build (L0, R0, L1, R1) resp. (L2, R2, L3, R3) from that word pair
+//       (R = sx+1 clamped to the last column),
 //   [4..7] a0 | a1 << 16 of the four columns.
 static bool build_resize_tables(int sw, int sh, int dw, int dh, std::vector<int>& xt, std::vector<int4>& yt)
 {
@@ -190,20 +190,21 @@ static bool build_resize_tables(int sw, int sh, int dw, int dh, std::vector<int>
     }
     xt.assign((size_t)ngroups * 8, 0);
     const int lastWord = (sw - 1) >> 2;
+    if (lastWord < 1) return false;
     for (int g = 0; g < ngroups; g++) {
-        const int base = sxv[4 * g];
-        const int w0 = base >> 2, w1 = std::min(w0 + 1, lastWord), w2 = std::min(w0 + 2, lastWord);
-        int selL = 0, selR = 0;
-        for (int k = 0; k < 4; k++) {
-            if (sx1v[4 * g + k] - base > 7 || sxv[4 * g + k] < base) return false;     // window wider than 8 bytes: scaleFactor > 2
-            selL |= ((sxv[4 * g + k] - base) & 7) << (4 * k);
-            selR |= ((sx1v[4 * g + k] - base) & 7) << (4 * k);
-        }
         int* r = &xt[(size_t)g * 8];
-        r[0] = w0 | (w1 << 16);
-        r[1] = w2 | (((base & 3) * 8) << 16);
-        r[2] = selL;
-        r[3] = selR;
+        for (int pr = 0; pr < 2; pr++) {
+            const int k0 = 4 * g + 2 * pr;
+            const int word = std::min(sxv[k0] >> 2, lastWord - 1);       // the pair (word, word + 1) stays inside the row
+            const int off[4] = {sxv[k0] - 4 * word, sx1v[k0] - 4 * word, sxv[k0 + 1] - 4 * word, sx1v[k0 + 1] - 4 * word};
+            int sel = 0;
+            for (int k = 0; k < 4; k++) {
+                if (off[k] < 0 || off[k] > 7) return false;             // span wider than two words: level ratio above 2
+                sel |= off[k] << (4 * k);
+            }
+            r[pr] = word;
+            r[2 + pr] = sel;
+        }
         for (int k = 0; k < 4; k++) r[4 + k] = (a0v[4 * g + k] & 0xFFFF) | (a1v[4 * g + k] << 16);
     }
     yt.resize(dh);
@@ -308,7 +309,7 @@ static int enqueue(orbx_extractor* ex, int B)
         const int spitch = l == 1 ? (int)F.lv0Pitch : P.lv[l - 1].pitch;
         const size_t sframe = l == 1 ? (size_t)F.lv0Frame : (size_t)P.pyrSlab;
         launch_resize(s, src, spitch, sframe, F.pyr + P.lv[l].planeOff, P.lv[l].w, P.lv[l].h, P.lv[l].pitch, P.pyrSlab,
-                      ex->d_xtab + ex->xtabOff[l], ex->d_ytab + ex->ytabOff[l], B);
+                      ex->d_xtab + ex->xtabOff[l], ex->d_ytab + ex->ytabOff[l], B, P.lv[l - 1].h);
         launches++;
     }
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
