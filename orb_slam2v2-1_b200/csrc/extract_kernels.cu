@@ -591,6 +591,9 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 constexpr int BLUR_COLS = 128;       // output columns per warp: 32 lanes x 4
 constexpr int BLUR_ROWS = 64;        // rows per strip
 constexpr int BLUR_WARPS = 8;
+#ifndef BLUR_MINB
+#define BLUR_MINB 2
+#endif
 
 __device__ __forceinline__ int reflect101(int p, int len)
 {
@@ -624,7 +627,7 @@ __device__ __forceinline__ BlurWord blur_word(int xb, int w)
 
 #define TAPS4(a, b, c, d) ((unsigned)(a) | ((unsigned)(b) << 8) | ((unsigned)(c) << 16) | ((unsigned)(d) << 24))
 
-__global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const FrameBufs F)
+__global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan P, const FrameBufs F)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);
@@ -643,54 +646,63 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, 2) k_blur(const Plan P, const
     const BlurWord wl = blur_word(x - 4, w), wc = blur_word(x, w), wr = blur_word(x + 4, w);
     const bool edge = (wl.sel != 0x3210u) | (wc.sel != 0x3210u) | (wr.sel != 0x3210u);
 
+    const bool interiorY = y0 >= 3 && y1 + 3 <= h;     // warp-uniform: no vertical reflection in this strip
+    const uint8_t* base = img + wc.offA;
+    const int dLA = (int)wl.offA - (int)wc.offA, dLB = (int)wl.offB - (int)wc.offA, dCB = (int)wc.offB - (int)wc.offA;
+    const int dRA = (int)wr.offA - (int)wc.offA, dRB = (int)wr.offB - (int)wc.offA;
+
     unsigned hp[4] = {0, 0, 0, 0};      // h of the previous row
     unsigned Pw[6][4];                  // pairs P(r-5) .. P(r), slot = r mod 6 (statically indexed: the loop is unrolled by 6)
-#pragma unroll
-    for (int j = 0; j < 6; j++) Pw[j][0] = Pw[j][1] = Pw[j][2] = Pw[j][3] = 0;
     uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + x;
     // iteration i handles source row r = y0 - 3 + i and, from i = 6 on, emits output row y = r - 3
-    const int niter = (y1 - y0) + 6;
-    for (int ib = 0; ib < niter; ib += 6) {
-#pragma unroll
-        for (int j = 0; j < 6; j++) {
-            const int i = ib + j;
-            const int r = y0 - 3 + i;
-            const uint8_t* row = img + (unsigned)(reflect1(r, h) * pitch);
-            unsigned L = __ldg(reinterpret_cast<const unsigned*>(row + wl.offA));
-            unsigned C = __ldg(reinterpret_cast<const unsigned*>(row + wc.offA));
-            unsigned R = __ldg(reinterpret_cast<const unsigned*>(row + wr.offA));
-            if (edge) {
-                L = __byte_perm(L, __ldg(reinterpret_cast<const unsigned*>(row + wl.offB)), wl.sel);
-                C = __byte_perm(C, __ldg(reinterpret_cast<const unsigned*>(row + wc.offB)), wc.sel);
-                R = __byte_perm(R, __ldg(reinterpret_cast<const unsigned*>(row + wr.offB)), wr.sel);
-            }
-            const unsigned h0 = __dp4a(C, TAPS4(56, 48, 34, 18), __dp4a(L, TAPS4(0, 18, 34, 48), 0u));
-            const unsigned h1 = __dp4a(R, TAPS4(18, 0, 0, 0), __dp4a(C, TAPS4(48, 56, 48, 34), __dp4a(L, TAPS4(0, 0, 18, 34), 0u)));
-            const unsigned h2 = __dp4a(R, TAPS4(34, 18, 0, 0), __dp4a(C, TAPS4(34, 48, 56, 48), __dp4a(L, TAPS4(0, 0, 0, 18), 0u)));
-            const unsigned h3 = __dp4a(R, TAPS4(48, 34, 18, 0), __dp4a(C, TAPS4(18, 34, 48, 56), 0u));
-            // slot j receives P(r) = (h(r-1), h(r)); P(r-1) sits in slot j-1, ... (mod 6)
-            Pw[j][0] = h0 * 65536u + hp[0];
-            Pw[j][1] = h1 * 65536u + hp[1];
-            Pw[j][2] = h2 * 65536u + hp[2];
-            Pw[j][3] = h3 * 65536u + hp[3];
-            hp[0] = h0; hp[1] = h1; hp[2] = h2; hp[3] = h3;
-            const int y = r - 3;
-            if (i >= 6 && y < y1) {
-                unsigned o[4];
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    // P(y+3) = P(r) slot j, P(y+2) = P(r-1) slot j-1, P(y) = P(r-3) slot j-3, P(y-2) = P(r-5) slot j-5
-                    unsigned acc = __dp2a_lo(Pw[(j + 1) % 6][k], TAPS4(18, 34, 0, 0), 32768u);
-                    acc = __dp2a_lo(Pw[(j + 3) % 6][k], TAPS4(48, 56, 0, 0), acc);
-                    acc = __dp2a_lo(Pw[(j + 5) % 6][k], TAPS4(48, 34, 0, 0), acc);
-                    o[k] = __dp2a_lo(Pw[j][k], TAPS4(0, 18, 0, 0), acc);
-                }
-                // byte 2 of each accumulator
-                *reinterpret_cast<unsigned*>(dst + (unsigned)(y * G.pitch)) =
-                    __byte_perm(__byte_perm(o[0], o[1], 0x0062), __byte_perm(o[2], o[3], 0x0062), 0x5410);
-            }
-        }
+#ifndef BLUR_PF
+#define BLUR_PF 12
+#endif
+#define BLUR_ROW(J, EMIT)                                                                                             \
+    {                                                                                                                 \
+        const int r = rbase + (J);                                                                                    \
+        const int rr = interiorY ? r : reflect1(r, h);                                                                \
+        const uint8_t* pc = base + (size_t)(unsigned)rr * (unsigned)pitch;                                            \
+        if (BLUR_PF > 0 && r + BLUR_PF < h)   /* pull the line of a later row into L1 without holding registers */    \
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(pc + (size_t)BLUR_PF * (unsigned)pitch));                   \
+        unsigned L = __ldg(reinterpret_cast<const unsigned*>(pc + dLA));                                              \
+        unsigned C = __ldg(reinterpret_cast<const unsigned*>(pc));                                                    \
+        unsigned R = __ldg(reinterpret_cast<const unsigned*>(pc + dRA));                                              \
+        if (edge) {                                                                                                   \
+            L = __byte_perm(L, __ldg(reinterpret_cast<const unsigned*>(pc + dLB)), wl.sel);                           \
+            C = __byte_perm(C, __ldg(reinterpret_cast<const unsigned*>(pc + dCB)), wc.sel);                           \
+            R = __byte_perm(R, __ldg(reinterpret_cast<const unsigned*>(pc + dRB)), wr.sel);                           \
+        }                                                                                                             \
+        const unsigned h0 = __dp4a(C, TAPS4(56, 48, 34, 18), __dp4a(L, TAPS4(0, 18, 34, 48), 0u));                    \
+        const unsigned h1 = __dp4a(R, TAPS4(18, 0, 0, 0), __dp4a(C, TAPS4(48, 56, 48, 34), __dp4a(L, TAPS4(0, 0, 18, 34), 0u))); \
+        const unsigned h2 = __dp4a(R, TAPS4(34, 18, 0, 0), __dp4a(C, TAPS4(34, 48, 56, 48), __dp4a(L, TAPS4(0, 0, 0, 18), 0u))); \
+        const unsigned h3 = __dp4a(R, TAPS4(48, 34, 18, 0), __dp4a(C, TAPS4(18, 34, 48, 56), 0u));                    \
+        /* slot J receives P(r) = (h(r-1), h(r)); P(r-1) sits in slot J-1, ... (mod 6) */                             \
+        Pw[J][0] = h0 * 65536u + hp[0];                                                                               \
+        Pw[J][1] = h1 * 65536u + hp[1];                                                                               \
+        Pw[J][2] = h2 * 65536u + hp[2];                                                                               \
+        Pw[J][3] = h3 * 65536u + hp[3];                                                                               \
+        hp[0] = h0; hp[1] = h1; hp[2] = h2; hp[3] = h3;                                                               \
+        if ((EMIT) && r - 3 < y1) {                                                                                   \
+            unsigned o[4];                                                                                            \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                           \
+                /* P(y+3) = P(r) slot J, P(y+2) = P(r-1) slot J-1, P(y) = P(r-3) slot J-3, P(y-2) = P(r-5) slot J-5 */ \
+                unsigned acc = __dp2a_lo(Pw[((J) + 1) % 6][k], TAPS4(18, 34, 0, 0), 32768u);                          \
+                acc = __dp2a_lo(Pw[((J) + 3) % 6][k], TAPS4(48, 56, 0, 0), acc);                                      \
+                acc = __dp2a_lo(Pw[((J) + 5) % 6][k], TAPS4(48, 34, 0, 0), acc);                                      \
+                o[k] = __dp2a_lo(Pw[J][k], TAPS4(0, 18, 0, 0), acc);                                                  \
+            }                                                                                                         \
+            /* byte 2 of each accumulator */                                                                          \
+            *reinterpret_cast<unsigned*>(dst + (size_t)(unsigned)(r - 3) * (unsigned)G.pitch) =                       \
+                __byte_perm(__byte_perm(o[0], o[1], 0x0062), __byte_perm(o[2], o[3], 0x0062), 0x5410);                \
+        }                                                                                                             \
     }
+    int rbase = y0 - 3;
+    BLUR_ROW(0, false) BLUR_ROW(1, false) BLUR_ROW(2, false) BLUR_ROW(3, false) BLUR_ROW(4, false) BLUR_ROW(5, false)
+    for (rbase += 6; rbase - 3 < y1; rbase += 6) {
+        BLUR_ROW(0, true) BLUR_ROW(1, true) BLUR_ROW(2, true) BLUR_ROW(3, true) BLUR_ROW(4, true) BLUR_ROW(5, true)
+    }
+#undef BLUR_ROW
 }
 
 #undef TAPS4
@@ -733,7 +745,7 @@ constexpr int DESC_WARPS = 8;
 __device__ __forceinline__ int round_magic_bits(float v) { return __float_as_int(__fadd_rn(v, 12582912.f)); }
 constexpr int MAGIC_BITS = 0x4B400000;
 
-__global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const UMaxTable um,
+__global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const uint2* __restrict__ icTab,
                                                                     const float4* __restrict__ patT)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
@@ -756,28 +768,27 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     const uint32_t key = F.levelKeys[(size_t)f * P.totalNodes + G.nodeBase + idx];
     const int cx = key_x(key) + MIN_BORDER, cy = key_y(key) + MIN_BORDER;      // level coordinates (:841-842)
 
-    // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level; lane = column u, so
-    // m10 = u * (column sum) and m01 = sum of v * pixel with v a compile-time constant per row
+    // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level.  The 31 x 31 patch is read as aligned
+    // 32-bit words (9 per row whatever the alignment of cx - 15): 279 (row, word) items spread over the 32 lanes, and every
+    // item is two IDP.4A against host-built weight words (u resp. v inside the disc, 0 outside) selected by the alignment.
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     int m10 = 0, m01 = 0;
     {
-        const int u = lane - HALF_PATCH, au = abs(u);
-        int vmax = -1;                                   // rows |v| <= vmax belong to column u (the disc is convex)
+        const int x0 = cx - HALF_PATCH, al = x0 & 3;
+        const uint8_t* org = img + (size_t)(unsigned)((cy - HALF_PATCH) * pitch + (x0 - al));
+        const uint2* tab = icTab + al * IC_ITEMS_PAD;
 #pragma unroll
-        for (int v = 0; v <= HALF_PATCH; v++)
-            if (lane < 31 && au <= um.v[v]) vmax = v;
-        const uint8_t* c = img + (unsigned)(cy * pitch + cx + u);
-        int colsum = 0;
-#pragma unroll
-        for (int v = -HALF_PATCH; v <= HALF_PATCH; v++) {
-            if ((v < 0 ? -v : v) <= vmax) {
-                const int val = __ldg(c + v * pitch);
-                colsum += val;
-                m01 += v * val;
+        for (int k = 0; k < 9; k++) {
+            const int i = lane + 32 * k;
+            if (k < 8 || i < IC_ITEMS) {
+                const int row = (i * 57) >> 9, word = i - 9 * row;         // i / 9 for i < 288
+                const uint2 wt = __ldg(&tab[i]);
+                const unsigned px = __ldg(reinterpret_cast<const unsigned*>(org + (unsigned)(row * pitch + 4 * word)));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(px), "r"(wt.x));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(px), "r"(wt.y));
             }
         }
-        m10 = u * colsum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -833,10 +844,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     }
 }
 
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const float4* patT, int B)
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B)
 {
     dim3 grd((P.totalNodes + DESC_WARPS - 1) / DESC_WARPS, B);
-    k_orient_describe<<<grd, DESC_WARPS * 32, 0, s>>>(P, F, um, patT);
+    k_orient_describe<<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT);
 }
 
 // ------------------------------------------------------------------------------------------------ padded copy-out

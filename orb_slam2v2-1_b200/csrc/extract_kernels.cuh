@@ -23,6 +23,8 @@ struct FrameBufs {
 };
 
 struct UMaxTable { int v[16]; };
+// IC_Angle weight table: [alignment 0..3][item] -> (u weights, v weights) as 4 signed bytes each; item = row * 9 + word
+constexpr int IC_ITEMS = 31 * 9, IC_ITEMS_PAD = 288;
 
 // cv::resize(INTER_LINEAR) of one level from the previous one for all frames (ComputePyramid, ORBextractor.cc:1120).
 void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
@@ -35,7 +37,7 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const UMaxTable& um, const float4* patT, int B);
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B);
 // padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
 void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch);
 

@@ -50,6 +50,7 @@ struct orbx_extractor {
     int device = 0, maxBatch = 1, fmaMode = 0;
     cudaStream_t stream = nullptr;
     float4* d_patT = nullptr;          // rBRIEF pattern as floats: patT[bit * 32 + byte] = (x0, y0, x1, y1)
+    uint2* d_icTab = nullptr;          // IC_Angle weight words (see extract_kernels.cuh)
     UMaxTable um{};
 
     // current shape
@@ -319,7 +320,7 @@ static int enqueue(orbx_extractor* ex, int B)
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
-    launch_orient_describe(s, P, F, ex->um, ex->d_patT, B);
+    launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     launches += 4;
     ORBX_CUDA(cudaGetLastError());
@@ -407,8 +408,29 @@ int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, in
             patT[bit * 32 + byte] = make_float4((float)(int8_t)(w & 0xFF), (float)(int8_t)((w >> 8) & 0xFF),
                                                 (float)(int8_t)((w >> 16) & 0xFF), (float)(int8_t)(w >> 24));
         }
+    // IC_Angle weights (:77-104): pixel (u, v) of the patch counts iff |u| <= umax[|v|]; for the word `word` of row v + 15 and
+    // alignment al, byte b is column u = 4 * word + b - al - 15
+    std::vector<uint2> icTab(4 * IC_ITEMS_PAD, make_uint2(0u, 0u));
+    for (int al = 0; al < 4; al++)
+        for (int row = 0; row < 31; row++)
+            for (int word = 0; word < 9; word++) {
+                const int v = row - HALF_PATCH;
+                uint32_t wu = 0, wv = 0;
+                for (int b = 0; b < 4; b++) {
+                    const int u = 4 * word + b - al - HALF_PATCH;
+                    if (abs(u) <= ex->umax[abs(v)]) {
+                        wu |= (uint32_t)(uint8_t)(int8_t)u << (8 * b);
+                        wv |= (uint32_t)(uint8_t)(int8_t)v << (8 * b);
+                    }
+                }
+                icTab[(size_t)al * IC_ITEMS_PAD + row * 9 + word] = make_uint2(wu, wv);
+            }
     if (!cuda_ok(cudaMalloc(&ex->d_patT, sizeof patT), "cudaMalloc(pattern)", __FILE__, __LINE__) ||
-        !cuda_ok(cudaMemcpy(ex->d_patT, patT, sizeof patT, cudaMemcpyHostToDevice), "cudaMemcpy(pattern)", __FILE__, __LINE__)) {
+        !cuda_ok(cudaMemcpy(ex->d_patT, patT, sizeof patT, cudaMemcpyHostToDevice), "cudaMemcpy(pattern)", __FILE__, __LINE__) ||
+        !cuda_ok(cudaMalloc(&ex->d_icTab, icTab.size() * sizeof(uint2)), "cudaMalloc(icTab)", __FILE__, __LINE__) ||
+        !cuda_ok(cudaMemcpy(ex->d_icTab, icTab.data(), icTab.size() * sizeof(uint2), cudaMemcpyHostToDevice), "cudaMemcpy(icTab)", __FILE__, __LINE__)) {
+        cudaFree(ex->d_patT);
+        cudaFree(ex->d_icTab);
         cudaStreamDestroy(ex->stream);
         delete ex;
         return ORBX_ERR_CUDA;
@@ -424,6 +446,7 @@ void orbx_destroy(orbx_extractor* ex)
     if (ex->stream) cudaStreamSynchronize(ex->stream);
     free_shape(ex);
     cudaFree(ex->d_patT);
+    cudaFree(ex->d_icTab);
     for (int i = 0; i < 6; i++)
         if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
     if (ex->stream) cudaStreamDestroy(ex->stream);
