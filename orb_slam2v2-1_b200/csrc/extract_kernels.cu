@@ -589,7 +589,7 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 //                      = IDP.2A(P(y-2),(18,34)) + IDP.2A(P(y),(48,56)) + IDP.2A(P(y+2),(48,34)) + IDP.2A(P(y+3),(0,18)),
 //               and the result byte is bits 16..23 of the accumulator (one PRMT tree packs the 4 pixels).
 constexpr int BLUR_COLS = 128;       // output columns per warp: 32 lanes x 4
-constexpr int BLUR_ROWS = 64;        // rows per strip
+constexpr int BLUR_ROWS = 60;        // rows per strip (+ 6 halo rows = 11 blocks of 6)
 constexpr int BLUR_WARPS = 8;
 #ifndef BLUR_MINB
 #define BLUR_MINB 2
@@ -610,22 +610,107 @@ __device__ __forceinline__ int reflect1(int p, int len)
     return min(max(p, 0), len - 1);
 }
 
-// The 4 pixels at columns xb .. xb+3 reflected into [0, w) always lie within two aligned words: byte offsets of the two
-// words and the PRMT selector that puts them in order (0x3210 with offB unused when no border is involved).
-struct BlurWord { unsigned offA, offB, sel; };
-__device__ __forceinline__ BlurWord blur_word(int xb, int w)
+#define TAPS4(a, b, c, d) ((unsigned)(a) | ((unsigned)(b) << 8) | ((unsigned)(c) << 16) | ((unsigned)(d) << 24))
+
+// Border lanes (BORDER_REFLECT_101 in x).  Only bytes 1..3 of L (columns x-3..x-1) and bytes 0..2 of R (x+4..x+6) carry
+// non-zero taps.  A lane loads L at pc-4 (not when x == 0), C at pc, and a third word at pc+4 -- or, for the last lane of a
+// row whose width is 1 mod 4, at pc-8 (two of its reflected columns live there).  Border lanes then rebuild the three
+// words with four PRMTs whose selectors are derived here, per lane, once:
+//   FL = prmt(L, C, sL), FC = prmt(C, L, sC), X = prmt(L, C, s1), FR = prmt(X, R, s2).
+struct BlurEdge { unsigned sL, sC, s1, s2; int dR; bool loadL, loadR, edge; };
+__device__ __forceinline__ BlurEdge blur_edge(int x, int w)
 {
-    const int c0 = reflect1(xb, w), c1 = reflect1(xb + 1, w), c2 = reflect1(xb + 2, w), c3 = reflect1(xb + 3, w);
-    const int wA = min(min(c0, c1), min(c2, c3)) >> 2, wB = max(max(c0, c1), max(c2, c3)) >> 2;
-    auto nib = [&](int c) { return (unsigned)((c >> 2) == wA ? c - 4 * wA : 4 + c - 4 * wB); };
-    BlurWord r;
-    r.offA = (unsigned)wA * 4;
-    r.offB = (unsigned)wB * 4;
-    r.sel = nib(c0) | (nib(c1) << 4) | (nib(c2) << 8) | (nib(c3) << 12);
-    return r;
+    BlurEdge e;
+    e.loadL = x > 0;
+    e.dR = 4;
+    e.loadR = x + 4 < w;
+    e.sL = 0x3210u; e.sC = 0x3210u; e.s1 = 0x3210u; e.s2 = 0x7654u;     // identity: FL = L, FC = C, FR = R
+    e.edge = false;
+    if (x == 0) { e.sL = 0x5670u; e.edge = true; }                        // columns -3..-1 = pixels 3, 2, 1 = C bytes 3, 2, 1
+    if (x + 8 > w) {                                                      // some of columns x .. x+6 lie beyond the row
+        e.edge = true;
+        if (x + 4 >= w && (w & 3) == 1) { e.dR = -8; e.loadR = true; }    // last lane, one valid pixel: third word = columns x-8..x-5
+        unsigned sC = 0, s1 = 0, s2 = 0;
+        for (int k = 0; k < 7; k++) {                                     // column x + k
+            int c = x + k;
+            const bool valid = c < w;
+            if (!valid) c = 2 * (w - 1) - c;
+            const int rel = c - x;                                        // byte position relative to the own word
+            if (k < 4) {                                                  // FC byte k from C (rel 0..3) or L (rel -4..-1): prmt(C, L)
+                sC |= (unsigned)(rel >= 0 ? rel : 8 + rel) << (4 * k);
+            } else {                                                      // FR byte k-4
+                const int b = k - 4;
+                if (rel >= 4) s2 |= (unsigned)(4 + rel - 4) << (4 * b);                      // from the third word (= R) directly
+                else if (rel >= -4) { s1 |= (unsigned)(rel >= 0 ? 4 + rel : 4 + rel) << (4 * b); s2 |= (unsigned)b << (4 * b); }
+                else { s2 |= (unsigned)(4 + rel + 8) << (4 * b); }                           // columns x-8..x-5: third word loaded at pc-8
+            }
+        }
+        // s1 gathers from prmt(L, C): L bytes are 0..3 (rel -4..-1 -> 4 + rel), C bytes are 4..7 (rel 0..3 -> 4 + rel)
+        e.sC = sC; e.s1 = s1; e.s2 = s2 | 0x7000u;
+    }
+    return e;
 }
 
-#define TAPS4(a, b, c, d) ((unsigned)(a) | ((unsigned)(b) << 8) | ((unsigned)(c) << 16) | ((unsigned)(d) << 24))
+// One strip of rows [y0, y1) of one lane's 4 columns.  INTERIOR: the strip needs no vertical reflection (rows y0-3 ..
+// y1+2 all exist), so the source pointers simply advance by one pitch per row.
+template <bool INTERIOR>
+__device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ img, int pitch, int h, int x, int y0, int y1, const BlurEdge E,
+                                           uint8_t* __restrict__ dst, int dpitch)
+{
+    unsigned Pw[6][4];                  // pairs P(r-5) .. P(r), slot = r mod 6 (statically indexed: the loop is unrolled by 6)
+#pragma unroll
+    for (int k = 0; k < 4; k++) Pw[5][k] = 0;
+    int rr = INTERIOR ? y0 - 3 : reflect1(y0 - 3, h);
+    const uint8_t* pc = img + (size_t)(unsigned)rr * (unsigned)pitch + x;
+    const uint8_t* pr = pc + E.dR;
+    // iteration i handles source row r = y0 - 3 + i and, from i = 6 on, emits output row y = r - 3
+#define BLUR_ROW(J, EMIT)                                                                                             \
+    {                                                                                                                 \
+        unsigned L = 0, C, R = 0;                                                                                     \
+        if (E.loadL) L = __ldg(reinterpret_cast<const unsigned*>(pc - 4));                                            \
+        C = __ldg(reinterpret_cast<const unsigned*>(pc));                                                             \
+        if (E.loadR) R = __ldg(reinterpret_cast<const unsigned*>(pr));                                                \
+        if (E.edge) {                                                                                                 \
+            const unsigned X = __byte_perm(L, C, E.s1), FL = __byte_perm(L, C, E.sL), FC = __byte_perm(C, L, E.sC);   \
+            R = __byte_perm(X, R, E.s2); L = FL; C = FC;                                                              \
+        }                                                                                                             \
+        if (INTERIOR) { pc += pitch; pr += pitch; }                                                                   \
+        else {                                                                                                        \
+            const int nr = reflect1(rbase + (J) + 1, h);                                                              \
+            pc += (long long)(nr - rr) * pitch; pr += (long long)(nr - rr) * pitch; rr = nr;                          \
+        }                                                                                                             \
+        const unsigned h0 = __dp4a(C, TAPS4(56, 48, 34, 18), __dp4a(L, TAPS4(0, 18, 34, 48), 0u));                    \
+        const unsigned h1 = __dp4a(R, TAPS4(18, 0, 0, 0), __dp4a(C, TAPS4(48, 56, 48, 34), __dp4a(L, TAPS4(0, 0, 18, 34), 0u))); \
+        const unsigned h2 = __dp4a(R, TAPS4(34, 18, 0, 0), __dp4a(C, TAPS4(34, 48, 56, 48), __dp4a(L, TAPS4(0, 0, 0, 18), 0u))); \
+        const unsigned h3 = __dp4a(R, TAPS4(48, 34, 18, 0), __dp4a(C, TAPS4(18, 34, 48, 56), 0u));                    \
+        /* slot J receives P(r) = (h(r-1), h(r)): low half = high half of P(r-1) (slot J-1), high half = h(r) */      \
+        Pw[J][0] = __byte_perm(h0, Pw[((J) + 5) % 6][0], 0x1076);                                                     \
+        Pw[J][1] = __byte_perm(h1, Pw[((J) + 5) % 6][1], 0x1076);                                                     \
+        Pw[J][2] = __byte_perm(h2, Pw[((J) + 5) % 6][2], 0x1076);                                                     \
+        Pw[J][3] = __byte_perm(h3, Pw[((J) + 5) % 6][3], 0x1076);                                                     \
+        if (EMIT) {                                                                                                   \
+            unsigned o[4];                                                                                            \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                           \
+                /* P(y+3) = P(r) slot J, P(y+2) = P(r-1) slot J-1, P(y) = P(r-3) slot J-3, P(y-2) = P(r-5) slot J-5 */ \
+                unsigned acc = __dp2a_lo(Pw[((J) + 1) % 6][k], TAPS4(18, 34, 0, 0), 32768u);                          \
+                acc = __dp2a_lo(Pw[((J) + 3) % 6][k], TAPS4(48, 56, 0, 0), acc);                                      \
+                acc = __dp2a_lo(Pw[((J) + 5) % 6][k], TAPS4(48, 34, 0, 0), acc);                                      \
+                o[k] = __dp2a_lo(Pw[J][k], TAPS4(0, 18, 0, 0), acc);                                                  \
+            }                                                                                                         \
+            /* byte 2 of each accumulator */                                                                          \
+            if (rbase + (J) - 3 < y1)                                                                                 \
+                *reinterpret_cast<unsigned*>(dst) =                                                                   \
+                    __byte_perm(__byte_perm(o[0], o[1], 0x0062), __byte_perm(o[2], o[3], 0x0062), 0x5410);            \
+            dst += dpitch;                                                                                            \
+        }                                                                                                             \
+    }
+    int rbase = y0 - 3;
+    BLUR_ROW(0, false) BLUR_ROW(1, false) BLUR_ROW(2, false) BLUR_ROW(3, false) BLUR_ROW(4, false) BLUR_ROW(5, false)
+    for (rbase += 6; rbase - 3 < y1; rbase += 6) {
+        BLUR_ROW(0, true) BLUR_ROW(1, true) BLUR_ROW(2, true) BLUR_ROW(3, true) BLUR_ROW(4, true) BLUR_ROW(5, true)
+    }
+#undef BLUR_ROW
+}
 
 __global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan P, const FrameBufs F)
 {
@@ -643,66 +728,10 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan 
     const int y0 = ty * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    const BlurWord wl = blur_word(x - 4, w), wc = blur_word(x, w), wr = blur_word(x + 4, w);
-    const bool edge = (wl.sel != 0x3210u) | (wc.sel != 0x3210u) | (wr.sel != 0x3210u);
-
-    const bool interiorY = y0 >= 3 && y1 + 3 <= h;     // warp-uniform: no vertical reflection in this strip
-    const uint8_t* base = img + wc.offA;
-    const int dLA = (int)wl.offA - (int)wc.offA, dLB = (int)wl.offB - (int)wc.offA, dCB = (int)wc.offB - (int)wc.offA;
-    const int dRA = (int)wr.offA - (int)wc.offA, dRB = (int)wr.offB - (int)wc.offA;
-
-    unsigned hp[4] = {0, 0, 0, 0};      // h of the previous row
-    unsigned Pw[6][4];                  // pairs P(r-5) .. P(r), slot = r mod 6 (statically indexed: the loop is unrolled by 6)
-    uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + x;
-    // iteration i handles source row r = y0 - 3 + i and, from i = 6 on, emits output row y = r - 3
-#ifndef BLUR_PF
-#define BLUR_PF 12
-#endif
-#define BLUR_ROW(J, EMIT)                                                                                             \
-    {                                                                                                                 \
-        const int r = rbase + (J);                                                                                    \
-        const int rr = interiorY ? r : reflect1(r, h);                                                                \
-        const uint8_t* pc = base + (size_t)(unsigned)rr * (unsigned)pitch;                                            \
-        if (BLUR_PF > 0 && r + BLUR_PF < h)   /* pull the line of a later row into L1 without holding registers */    \
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(pc + (size_t)BLUR_PF * (unsigned)pitch));                   \
-        unsigned L = __ldg(reinterpret_cast<const unsigned*>(pc + dLA));                                              \
-        unsigned C = __ldg(reinterpret_cast<const unsigned*>(pc));                                                    \
-        unsigned R = __ldg(reinterpret_cast<const unsigned*>(pc + dRA));                                              \
-        if (edge) {                                                                                                   \
-            L = __byte_perm(L, __ldg(reinterpret_cast<const unsigned*>(pc + dLB)), wl.sel);                           \
-            C = __byte_perm(C, __ldg(reinterpret_cast<const unsigned*>(pc + dCB)), wc.sel);                           \
-            R = __byte_perm(R, __ldg(reinterpret_cast<const unsigned*>(pc + dRB)), wr.sel);                           \
-        }                                                                                                             \
-        const unsigned h0 = __dp4a(C, TAPS4(56, 48, 34, 18), __dp4a(L, TAPS4(0, 18, 34, 48), 0u));                    \
-        const unsigned h1 = __dp4a(R, TAPS4(18, 0, 0, 0), __dp4a(C, TAPS4(48, 56, 48, 34), __dp4a(L, TAPS4(0, 0, 18, 34), 0u))); \
-        const unsigned h2 = __dp4a(R, TAPS4(34, 18, 0, 0), __dp4a(C, TAPS4(34, 48, 56, 48), __dp4a(L, TAPS4(0, 0, 0, 18), 0u))); \
-        const unsigned h3 = __dp4a(R, TAPS4(48, 34, 18, 0), __dp4a(C, TAPS4(18, 34, 48, 56), 0u));                    \
-        /* slot J receives P(r) = (h(r-1), h(r)); P(r-1) sits in slot J-1, ... (mod 6) */                             \
-        Pw[J][0] = h0 * 65536u + hp[0];                                                                               \
-        Pw[J][1] = h1 * 65536u + hp[1];                                                                               \
-        Pw[J][2] = h2 * 65536u + hp[2];                                                                               \
-        Pw[J][3] = h3 * 65536u + hp[3];                                                                               \
-        hp[0] = h0; hp[1] = h1; hp[2] = h2; hp[3] = h3;                                                               \
-        if ((EMIT) && r - 3 < y1) {                                                                                   \
-            unsigned o[4];                                                                                            \
-            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                                           \
-                /* P(y+3) = P(r) slot J, P(y+2) = P(r-1) slot J-1, P(y) = P(r-3) slot J-3, P(y-2) = P(r-5) slot J-5 */ \
-                unsigned acc = __dp2a_lo(Pw[((J) + 1) % 6][k], TAPS4(18, 34, 0, 0), 32768u);                          \
-                acc = __dp2a_lo(Pw[((J) + 3) % 6][k], TAPS4(48, 56, 0, 0), acc);                                      \
-                acc = __dp2a_lo(Pw[((J) + 5) % 6][k], TAPS4(48, 34, 0, 0), acc);                                      \
-                o[k] = __dp2a_lo(Pw[J][k], TAPS4(0, 18, 0, 0), acc);                                                  \
-            }                                                                                                         \
-            /* byte 2 of each accumulator */                                                                          \
-            *reinterpret_cast<unsigned*>(dst + (size_t)(unsigned)(r - 3) * (unsigned)G.pitch) =                       \
-                __byte_perm(__byte_perm(o[0], o[1], 0x0062), __byte_perm(o[2], o[3], 0x0062), 0x5410);                \
-        }                                                                                                             \
-    }
-    int rbase = y0 - 3;
-    BLUR_ROW(0, false) BLUR_ROW(1, false) BLUR_ROW(2, false) BLUR_ROW(3, false) BLUR_ROW(4, false) BLUR_ROW(5, false)
-    for (rbase += 6; rbase - 3 < y1; rbase += 6) {
-        BLUR_ROW(0, true) BLUR_ROW(1, true) BLUR_ROW(2, true) BLUR_ROW(3, true) BLUR_ROW(4, true) BLUR_ROW(5, true)
-    }
-#undef BLUR_ROW
+    const BlurEdge E = blur_edge(x, w);
+    uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)(unsigned)y0 * (unsigned)G.pitch + x;
+    if (y0 >= 3 && y1 + 3 <= h) blur_strip<true>(img, pitch, h, x, y0, y1, E, dst, G.pitch);      // warp-uniform
+    else blur_strip<false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
 }
 
 #undef TAPS4

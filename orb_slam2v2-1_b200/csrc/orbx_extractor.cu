@@ -134,9 +134,9 @@ static int build_plan(orbx_extractor* ex, int w, int h)
         capS = std::max(capS, std::max(G.quota + 4, 4 * G.nIni) + 4);
         G.nodeBase = nodes;
         nodes += G.nodeCap;
-        G.blurTilesX = (G.w + 127) / 128;        // k_blur: 128 output columns x 64 rows per warp
+        G.blurTilesX = (G.w + 127) / 128;        // k_blur: 128 output columns x 60 rows per warp
         G.blurTileBase = tiles;
-        tiles += G.blurTilesX * ((G.h + 63) / 64);
+        tiles += G.blurTilesX * ((G.h + 59) / 60);
         G.scaledPatch = (int)(31 * ex->mvScaleFactor[l]);            // PATCH_SIZE*mvScaleFactor[level] (:845)
         G.scale = ex->mvScaleFactor[l];
         G.planeOff = pyr;
