@@ -100,6 +100,102 @@ public:
             fail("orbm_match_candidates");
     }
 
+    // What the projection searches read from a Frame besides FrameView: mvuRight, which features already hold a MapPoint with
+    // Observations() > 0, and mvScaleFactors.
+    struct FrameState {
+        const std::vector<float>* uRight;          // Frame::mvuRight
+        const std::vector<uint8_t>* occupied;      // F.mvpMapPoints[j] && F.mvpMapPoints[j]->Observations() > 0
+        const std::vector<float>* scaleFactors;    // Frame::mvScaleFactors
+    };
+    // The MapPoint fields the routine reads, one entry per point that passed the reference's own skip tests, in visit order.
+    struct ProjectedPoints {
+        std::vector<float> xy;                      // (mTrackProjX, mTrackProjY) resp. the projection (u, v)
+        std::vector<float> xr;                      // mTrackProjXR resp. u - mbf * invzc
+        std::vector<int> level;                     // mnTrackScaleLevel resp. LastFrame.mvKeys[i].octave
+        std::vector<float> viewCosOrAngle;          // mTrackViewCos resp. LastFrame.mvKeysUn[i].angle
+        std::vector<uint8_t> descriptors;           // GetDescriptor(), 32 bytes per point
+        std::vector<uint8_t> hasObservations;       // Observations() > 0
+    };
+
+    // Search matches between Frame keypoints and projected MapPoints, used to track the local map (ORBmatcher.cc:45-129).
+    // vnMatch[j] = index (into P) of the point the reference would store in F.mvpMapPoints[j], -1 = untouched.
+    int SearchByProjection(const FrameView& F, const FrameState& S, const ProjectedPoints& P, std::vector<int>& vnMatch, const float th = 3)
+    {
+        std::vector<orbx_kp> k = pack(*F.keys);
+        vnMatch.assign(k.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection(m_, k.data(), F.descriptors->ptr<uint8_t>(0), S.uRight->data(), S.occupied->data(), (int)k.size(), F.minX,
+                                      F.maxX, F.minY, F.maxY, S.scaleFactors->data(), (int)S.scaleFactors->size(), P.xy.data(), P.xr.data(),
+                                      P.level.data(), P.viewCosOrAngle.data(), P.descriptors.data(), P.hasObservations.data(),
+                                      (int)P.level.size(), th, mfNNratio, vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection");
+        return n;
+    }
+
+    // Project MapPoints tracked in the last frame into the current frame and search matches, used to track from the previous
+    // frame (ORBmatcher.cc:1330-1472).  mode: 0 = neither, 1 = bForward, 2 = bBackward (:1351-1352).
+    int SearchByProjection(const FrameView& CurrentFrame, const FrameState& S, const ProjectedPoints& P, std::vector<int>& vnMatch, const float th,
+                           const int mode)
+    {
+        std::vector<orbx_kp> k = pack(*CurrentFrame.keys);
+        vnMatch.assign(k.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection_frame(m_, k.data(), CurrentFrame.descriptors->ptr<uint8_t>(0), S.uRight->data(), S.occupied->data(),
+                                            (int)k.size(), CurrentFrame.minX, CurrentFrame.maxX, CurrentFrame.minY, CurrentFrame.maxY,
+                                            S.scaleFactors->data(), (int)S.scaleFactors->size(), P.xy.data(), P.xr.data(), P.level.data(),
+                                            P.viewCosOrAngle.data(), P.descriptors.data(), P.hasObservations.data(), (int)P.level.size(), th, mode,
+                                            mbCheckOrientation, vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection_frame");
+        return n;
+    }
+
+    // A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned int>>) flattened to CSR, in map order.
+    struct FeatureVectorCSR {
+        std::vector<int> node, off, idx;
+        template <class Map> static FeatureVectorCSR from(const Map& fv)
+        {
+            FeatureVectorCSR c;
+            c.off.push_back(0);
+            for (typename Map::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+                c.node.push_back((int)it->first);
+                for (size_t i = 0; i < it->second.size(); i++) c.idx.push_back((int)it->second[i]);
+                c.off.push_back((int)c.idx.size());
+            }
+            return c;
+        }
+    };
+
+    // Search matches between MapPoints in a KeyFrame and ORB in a Frame, brute force constrained to ORB of the same vocabulary
+    // node (ORBmatcher.cc:159-288).  vbValidKF[i]: feature i of the key frame has a MapPoint that is not bad.
+    // vnMatchF[j] = key-frame feature whose MapPoint goes to frame feature j, -1 = none.
+    int SearchByBoW(const FrameView& KF, const std::vector<uint8_t>& vbValidKF, const FeatureVectorCSR& fvKF, const FrameView& F,
+                    const FeatureVectorCSR& fvF, std::vector<int>& vnMatchF)
+    {
+        std::vector<orbx_kp> k1 = pack(*KF.keys), k2 = pack(*F.keys);
+        vnMatchF.assign(k2.size(), -1);
+        int n = 0;
+        if (orbm_search_by_bow(m_, 0, k1.data(), KF.descriptors->ptr<uint8_t>(0), (int)k1.size(), vbValidKF.data(), fvKF.node.data(),
+                               fvKF.off.data(), fvKF.idx.data(), (int)fvKF.node.size(), k2.data(), F.descriptors->ptr<uint8_t>(0), (int)k2.size(),
+                               nullptr, fvF.node.data(), fvF.off.data(), fvF.idx.data(), (int)fvF.node.size(), mfNNratio, mbCheckOrientation,
+                               vnMatchF.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_bow");
+        return n;
+    }
+    // Key frame against key frame (loop closing, ORBmatcher.cc:522-655).  vnMatches12[i] = matched feature of the second key frame.
+    int SearchByBoW(const FrameView& KF1, const std::vector<uint8_t>& vbValid1, const FeatureVectorCSR& fv1, const FrameView& KF2,
+                    const std::vector<uint8_t>& vbValid2, const FeatureVectorCSR& fv2, std::vector<int>& vnMatches12)
+    {
+        std::vector<orbx_kp> k1 = pack(*KF1.keys), k2 = pack(*KF2.keys);
+        vnMatches12.assign(k1.size(), -1);
+        int n = 0;
+        if (orbm_search_by_bow(m_, 1, k1.data(), KF1.descriptors->ptr<uint8_t>(0), (int)k1.size(), vbValid1.data(), fv1.node.data(),
+                               fv1.off.data(), fv1.idx.data(), (int)fv1.node.size(), k2.data(), KF2.descriptors->ptr<uint8_t>(0), (int)k2.size(),
+                               vbValid2.data(), fv2.node.data(), fv2.off.data(), fv2.idx.data(), (int)fv2.node.size(), mfNNratio,
+                               mbCheckOrientation, vnMatches12.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_bow");
+        return n;
+    }
+
     // Frame::ComputeStereoMatches (Frame.cc:481-655): fills mvuRight / mvDepth, returns the surviving matches.  maxD is
     // explicit: the reference reads an uninitialised mb there (Frame.cc:511 vs :114); the intended value is fx.
     int ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<cv::KeyPoint>& keysLeft, const cv::Mat& descLeft,

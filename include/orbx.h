@@ -176,6 +176,46 @@ int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1, const uin
                                    float* prev_matched, int* matches12, int windowSize, float nnratio, int checkOri,
                                    int* nmatches);
 
+/* ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th) (src/ORBmatcher.cc:45-129),
+ * the TrackLocalMap search.  SLAM objects are passed as the plain arrays the routine reads from them:
+ *   frame F: kps = mvKeysUn, desc = mDescriptors, u_right = mvuRight, occupied[j] = (F.mvpMapPoints[j] && Observations() > 0)
+ *            on entry, bounds mnMinX..mnMaxY, sf = mvScaleFactors (nlevels floats);
+ *   map points that passed mbTrackInView && !isBad() (:52-56), in vpMapPoints order: proj_xy = (mTrackProjX, mTrackProjY),
+ *            proj_xr = mTrackProjXR, level = mnTrackScaleLevel, view_cos = mTrackViewCos, mp_desc = GetDescriptor() rows,
+ *            mp_has_obs[i] = Observations() > 0 (a feature taken by such a point is skipped by later points, :88-90).
+ * feature_match[j] (n ints) = index of the point this call stored into F.mvpMapPoints[j], -1 = untouched.
+ * Candidate windows and Hamming distances run on the device; the order-dependent bookkeeping is replayed on the host. */
+int orbm_search_by_projection(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied,
+                              int n, float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                              const float* proj_xy, const float* proj_xr, const int* level, const float* view_cos,
+                              const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, float nnratio,
+                              int* feature_match, int* nmatches);
+
+/* ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)
+ * (src/ORBmatcher.cc:1330-1472), the TrackWithMotionModel search.  Points of the last frame that passed the pMP /
+ * mvbOutlier / invzc / image-bounds filters (:1354-1378), in LastFrame order: proj_xy = (u, v), proj_ur = u - mbf*invzc (:1411),
+ * last_octave / last_angle = LastFrame.mvKeys[i].octave / mvKeysUn[i].angle, descriptor, has_obs.  mode: 0 = neither,
+ * 1 = bForward, 2 = bBackward (:1351-1352).  Outputs as above (after the rotation-consistency pass :1448-1468). */
+int orbm_search_by_projection_frame(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right,
+                                    const uint8_t* occupied, int n, float minX, float maxX, float minY, float maxY,
+                                    const float* sf, int nlevels, const float* proj_xy, const float* proj_ur,
+                                    const int* last_octave, const float* last_angle, const uint8_t* mp_desc,
+                                    const uint8_t* mp_has_obs, int nmp, float th, int mode, int checkOri,
+                                    int* feature_match, int* nmatches);
+
+/* ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:159-288; variant 0) and
+ * SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (:522-655; variant 1).  A DBoW2::FeatureVector is passed as CSR
+ * (node = ascending node ids, off = nn+1 offsets, idx = feature indices in stored order).  valid1[i] = feature i of the
+ * first key frame has a MapPoint that is not bad (:190-196); valid2 likewise for variant 1 (:571-577; may be NULL for
+ * variant 0).  variant 0: matches has n2 entries, matches[j] = feature of the key frame whose MapPoint went to feature j
+ * of the frame (accept best <= TH_LOW); variant 1: n1 entries, matches[i] = matched feature of the second key frame
+ * (accept best < TH_LOW).  -1 = none. */
+int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k1, const uint8_t* d1, int n1, const uint8_t* valid1,
+                       const int* node1, const int* off1, const int* idx1, int nn1,
+                       const orbx_kp* k2, const uint8_t* d2, int n2, const uint8_t* valid2,
+                       const int* node2, const int* off2, const int* idx2, int nn2,
+                       float nnratio, int checkOri, int* matches, int* nmatches);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:481-655).  left/right = extractor handles whose LAST call processed the
  * two images (their device pyramids are read in place; frame = index inside that batch).  Keypoints/descriptors are
  * HOST arrays as returned by orbx_extract.  maxD is explicit (the reference reads an uninitialised mb, src/Frame.cc:511

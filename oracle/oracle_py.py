@@ -68,6 +68,12 @@ def lib():
         L.orbo_grid_query.argtypes = [vp, vp, f, f, f, i, i, vp, i]
         L.orbo_search_for_initialization.restype = i
         L.orbo_search_for_initialization.argtypes = [vp, vp, i, vp, vp, i, f, f, f, f, vp, vp, i, f, i]
+        L.orbo_search_by_projection.restype = i
+        L.orbo_search_by_projection.argtypes = [vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp]
+        L.orbo_search_by_projection_frame.restype = i
+        L.orbo_search_by_projection_frame.argtypes = [vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp]
+        L.orbo_search_by_bow.restype = i
+        L.orbo_search_by_bow.argtypes = [i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp]
         L.orbo_stereo_matches.restype = i
         L.orbo_stereo_matches.argtypes = [vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, f, f, f, vp, vp]
         _lib = L
@@ -248,6 +254,58 @@ def search_for_initialization(k1, d1, k2, d2, bounds, prev_matched, windowSize=1
     n = lib().orbo_search_for_initialization(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2),
                                              *[float(b) for b in bounds], _p(prev), _p(m12), windowSize, nnratio, int(checkOri))
     return n, m12, prev
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def _pn(a):
+    return None if a is None else _p(a)
+
+
+def search_by_projection(kps, desc, u_right, occupied, bounds, sf, proj_xy, proj_xr, level, view_cos, mp_desc, mp_has_obs, th=1.0, nnratio=0.8):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) (ORBmatcher.cc:45-129) -> (nmatches, feature_match)."""
+    kps = np.ascontiguousarray(kps)
+    desc, mp_desc = _u8(desc), _u8(mp_desc)
+    u_right, sf, proj_xy, proj_xr, view_cos = _f32(u_right), _f32(sf), _f32(proj_xy), _f32(proj_xr), _f32(view_cos)
+    occupied, mp_has_obs, level = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(level, np.int32)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orbo_search_by_projection(_p(kps), _p(desc), _p(u_right), _p(occupied), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                        _p(proj_xy), _p(proj_xr), _p(level), _p(view_cos), _p(mp_desc), _p(mp_has_obs), len(level),
+                                        float(th), float(nnratio), _p(fm))
+    return n, fm[:len(kps)]
+
+
+def search_by_projection_frame(kps, desc, u_right, occupied, bounds, sf, proj_xy, proj_ur, last_octave, last_angle, mp_desc, mp_has_obs,
+                               th, mode=0, checkOri=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (ORBmatcher.cc:1330-1472) -> (nmatches, feature_match)."""
+    kps = np.ascontiguousarray(kps)
+    desc, mp_desc = _u8(desc), _u8(mp_desc)
+    u_right, sf, proj_xy, proj_ur, last_angle = _f32(u_right), _f32(sf), _f32(proj_xy), _f32(proj_ur), _f32(last_angle)
+    occupied, mp_has_obs, last_octave = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(last_octave, np.int32)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orbo_search_by_projection_frame(_p(kps), _p(desc), _p(u_right), _p(occupied), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                              _p(proj_xy), _p(proj_ur), _p(last_octave), _p(last_angle), _p(mp_desc), _p(mp_has_obs),
+                                              len(last_octave), float(th), int(mode), int(checkOri), _p(fm))
+    return n, fm[:len(kps)]
+
+
+def search_by_bow(k1, d1, valid1, fv1, k2, d2, fv2, valid2=None, nnratio=0.7, checkOri=True):
+    """ORBmatcher::SearchByBoW, key frame -> frame (ORBmatcher.cc:159-288) when valid2 is None, else key frame -> key frame
+    (:522-655).  fv = (node ids, offsets, feature indices) -> (nmatches, matches)."""
+    k1, k2 = np.ascontiguousarray(k1), np.ascontiguousarray(k2)
+    d1, d2 = _u8(d1), _u8(d2)
+    n1_, o1_, i1_ = [np.ascontiguousarray(a, np.int32) for a in fv1]
+    n2_, o2_, i2_ = [np.ascontiguousarray(a, np.int32) for a in fv2]
+    variant = 0 if valid2 is None else 1
+    valid1 = _u8(valid1)
+    v2 = None if valid2 is None else _u8(valid2)
+    nout = len(k2) if variant == 0 else len(k1)
+    out = np.zeros(max(nout, 1), np.int32)
+    n = lib().orbo_search_by_bow(variant, _p(k1), _p(d1), len(k1), _p(valid1), _p(n1_), _p(o1_), _p(i1_), len(n1_), _p(k2), _p(d2), len(k2),
+                                 _pn(v2), _p(n2_), _p(o2_), _p(i2_), len(n2_), float(nnratio), int(checkOri), _p(out))
+    return n, out[:nout]
 
 
 def stereo_matches(kl, dl, kr, dr, pyrL, pyrR, sf, isf, bf, maxD, minD=0.0):

@@ -2,7 +2,10 @@
 // Restatement of ORBmatcher::DescriptorDistance (ORBmatcher.cc:1649-1665), the best/second-best inner
 // loop shared by the SearchBy* routines (e.g. ORBmatcher.cc:205-230, 84-110), the Frame grid
 // (Frame.cc:230-245, 342-407), ORBmatcher::SearchForInitialization (ORBmatcher.cc:405-520) with
-// ComputeThreeMaxima (:1603-1644), and Frame::ComputeStereoMatches (Frame.cc:481-655).
+// ComputeThreeMaxima (:1603-1644), Frame::ComputeStereoMatches (Frame.cc:481-655), SearchByProjection(Frame, MapPoints)
+// (ORBmatcher.cc:45-129), SearchByProjection(CurrentFrame, LastFrame) (:1330-1472) and both SearchByBoW (:159-288, :522-655).
+// The last four read SLAM objects (MapPoint, KeyFrame, DBoW2::FeatureVector) in the reference; here those reads are the
+// plain arrays documented at each function, computed by the caller exactly as the reference computes them.
 #include "orb_oracle.h"
 #include "orb_internal.h"
 #include <climits>
@@ -185,6 +188,181 @@ int orbo_search_for_initialization(const orbo_kp* k1, const uint8_t* d1, int n1,
     }
     for (int i1 = 0; i1 < n1; i1++)
         if (m12[i1] >= 0) { prev[2 * i1] = k2[m12[i1]].x; prev[2 * i1 + 1] = k2[m12[i1]].y; }
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, const float th)   (ORBmatcher.cc:45-129)
+// Map points are passed after the mbTrackInView / isBad filters (:52-56).  Per point: proj_xy = (mTrackProjX, mTrackProjY),
+// proj_xr = mTrackProjXR, level = mnTrackScaleLevel, view_cos = mTrackViewCos, its descriptor, has_obs = Observations() > 0.
+// Frame: mvKeysUn, mDescriptors, mvuRight, occupied[j] = F.mvpMapPoints[j] && Observations() > 0 on entry, mvScaleFactors.
+// feature_match[j] = index of the point stored into F.mvpMapPoints[j] by this call (-1: untouched).
+int orbo_search_by_projection(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied_in, int n,
+                              float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                              const float* proj_xy, const float* proj_xr, const int* level, const float* view_cos,
+                              const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, float nnratio, int* feature_match)
+{
+    using namespace orbo;
+    (void)nlevels;
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> vIndices;
+    for (int iMP = 0; iMP < nmp; iMP++) {
+        const int nPredictedLevel = level[iMP];
+        float r = view_cos[iMP] > 0.998 ? 2.5f : 4.0f;                    // RadiusByViewingCos (:131-137)
+        if (bFactor) r *= th;
+        grid_query(G->g, kps, proj_xy[2 * iMP], proj_xy[2 * iMP + 1], r * sf[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel, vIndices);
+        if (vIndices.empty()) continue;
+        const uint8_t* MPdescriptor = mp_desc + 32 * (size_t)iMP;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (occupied[idx]) continue;                                   // :88-90
+            if (u_right[idx] > 0) {
+                const float er = std::fabs(proj_xr[iMP] - u_right[idx]);
+                if (er > r * sf[nPredictedLevel]) continue;
+            }
+            const int dist = descriptor_distance(MPdescriptor, desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = kps[idx].octave; bestIdx = idx; }
+            else if (dist < bestDist2) { bestLevel2 = kps[idx].octave; bestDist2 = dist; }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            feature_match[bestIdx] = iMP;                                  // F.mvpMapPoints[bestIdx]=pMP
+            occupied[bestIdx] = mp_has_obs[iMP];
+            nmatches++;
+        }
+    }
+    orbo_grid_destroy(G);
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)  (:1330-1472)
+// Points of the last frame are passed after the pMP / mvbOutlier / invzc / image-bounds filters (:1354-1378), with the
+// projection (u, v), ur = u - mbf*invzc (:1411), their octave and angle in the last frame, descriptor and has_obs.
+// mode: 0 = neither, 1 = bForward, 2 = bBackward (:1351-1352).
+int orbo_search_by_projection_frame(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied_in, int n,
+                                    float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                    const float* proj_xy, const float* proj_ur, const int* last_octave, const float* last_angle,
+                                    const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, int mode, int checkOri,
+                                    int* feature_match)
+{
+    using namespace orbo;
+    (void)nlevels;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> vIndices2;
+    for (int i = 0; i < nmp; i++) {
+        const float u = proj_xy[2 * i], v = proj_xy[2 * i + 1];
+        const int nLastOctave = last_octave[i];
+        const float radius = th * sf[nLastOctave];
+        if (mode == 1) grid_query(G->g, kps, u, v, radius, nLastOctave, -1, vIndices2);
+        else if (mode == 2) grid_query(G->g, kps, u, v, radius, 0, nLastOctave, vIndices2);
+        else grid_query(G->g, kps, u, v, radius, nLastOctave - 1, nLastOctave + 1, vIndices2);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = mp_desc + 32 * (size_t)i;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            if (occupied[i2]) continue;
+            if (u_right[i2] > 0) {
+                const float er = std::fabs(proj_ur[i] - u_right[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = descriptor_distance(dMP, desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            feature_match[bestIdx2] = i;
+            occupied[bestIdx2] = mp_has_obs[i];
+            nmatches++;
+            if (checkOri) {
+                float rot = last_angle[i] - kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    orbo_grid_destroy(G);
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int j : rotHist[i]) { feature_match[j] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (:159-288, variant 0) and SearchByBoW(KeyFrame*, KeyFrame*, ...)
+// (:522-655, variant 1).  A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) is passed as CSR: ascending
+// node ids, offsets, feature indices.  valid1[i]: feature i of the first key frame has a MapPoint that is not bad;
+// valid2[j] (variant 1): same for the second key frame.  variant 0 writes matches[j] (n2 entries) = index of the first
+// key frame's feature whose MapPoint went to feature j of the frame; variant 1 writes matches[i] (n1 entries) = matched
+// feature of the second key frame.
+int orbo_search_by_bow(int variant, const orbo_kp* k1, const uint8_t* d1, int n1, const uint8_t* valid1,
+                       const int* node1, const int* off1, const int* idx1, int nn1,
+                       const orbo_kp* k2, const uint8_t* d2, int n2, const uint8_t* valid2,
+                       const int* node2, const int* off2, const int* idx2, int nn2,
+                       float nnratio, int checkOri, int* matches)
+{
+    using namespace orbo;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    const int nout = variant == 0 ? n2 : n1;
+    for (int i = 0; i < nout; i++) matches[i] = -1;
+    std::vector<uint8_t> taken2(n2, 0);                 // vpMapPointMatches[realIdxF] != NULL (variant 0) / vbMatched2 (variant 1)
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (node1[a] == node2[b]) {
+            for (int p1 = off1[a]; p1 < off1[a + 1]; p1++) {
+                const int realIdx1 = idx1[p1];
+                if (!valid1[realIdx1]) continue;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (int p2 = off2[b]; p2 < off2[b + 1]; p2++) {
+                    const int realIdx2 = idx2[p2];
+                    if (taken2[realIdx2]) continue;
+                    if (variant == 1 && !valid2[realIdx2]) continue;
+                    const int dist = descriptor_distance(d1 + 32 * (size_t)realIdx1, d2 + 32 * (size_t)realIdx2);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = realIdx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                const bool low = variant == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;      // :228 vs :598
+                if (low && (float)bestDist1 < nnratio * (float)bestDist2) {
+                    taken2[bestIdx2] = 1;
+                    if (variant == 0) matches[bestIdx2] = realIdx1; else matches[realIdx1] = bestIdx2;
+                    if (checkOri) {
+                        float rot = k1[realIdx1].angle - k2[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back(variant == 0 ? bestIdx2 : realIdx1);
+                    }
+                    nmatches++;
+                }
+            }
+            a++; b++;
+        } else if (node1[a] < node2[b]) {
+            a = (int)(std::lower_bound(node1, node1 + nn1, node2[b]) - node1);
+        } else {
+            b = (int)(std::lower_bound(node2, node2 + nn2, node1[a]) - node2);
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int j : rotHist[i]) { matches[j] = -1; nmatches--; }
+        }
+    }
     return nmatches;
 }
 

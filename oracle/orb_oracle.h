@@ -89,6 +89,23 @@ int orbo_search_for_initialization(const orbo_kp* k1, const uint8_t* d1, int n1,
 
 // Frame::ComputeStereoMatches (Frame.cc:481-655) with maxD explicit (the reference reads an uninitialised mb).
 // Pyramids are given as per-level interior pointers (unblurred), sizes and strides.
+/* plain-array restatements of ORBmatcher::SearchByProjection(Frame, MapPoints) (ORBmatcher.cc:45-129),
+ * SearchByProjection(CurrentFrame, LastFrame) (:1330-1472) and both SearchByBoW (:159-288, :522-655); see orb_matcher.cpp */
+int orbo_search_by_projection(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied, int n,
+                              float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                              const float* proj_xy, const float* proj_xr, const int* level, const float* view_cos,
+                              const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, float nnratio, int* feature_match);
+int orbo_search_by_projection_frame(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied, int n,
+                                    float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                    const float* proj_xy, const float* proj_ur, const int* last_octave, const float* last_angle,
+                                    const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, int mode, int checkOri,
+                                    int* feature_match);
+int orbo_search_by_bow(int variant, const orbo_kp* k1, const uint8_t* d1, int n1, const uint8_t* valid1,
+                       const int* node1, const int* off1, const int* idx1, int nn1,
+                       const orbo_kp* k2, const uint8_t* d2, int n2, const uint8_t* valid2,
+                       const int* node2, const int* off2, const int* idx2, int nn2,
+                       float nnratio, int checkOri, int* matches);
+
 int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl,
                         const orbo_kp* kr, const uint8_t* dr, int nr,
                         const uint8_t* const* pyrL, const uint8_t* const* pyrR,

@@ -32,12 +32,13 @@ template <bool WRITE>
 __global__ void __launch_bounds__(256) k_grid_query(const orbx_kp* __restrict__ kps, const int* __restrict__ cellStart,
                                                     const int* __restrict__ entries, GridParams gp, const float* __restrict__ qxy,
                                                     const float* __restrict__ qr, int nq, int minLevel, int maxLevel,
-                                                    const int* __restrict__ qlevel, int* __restrict__ off, int* __restrict__ idx_out)
+                                                    const int* __restrict__ qlevel, int qlevelStride, int* __restrict__ off, int* __restrict__ idx_out)
 {
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (qi >= nq) return;
     const float x = qxy[2 * qi], y = qxy[2 * qi + 1], r = qr[qi];
-    const int minL = qlevel ? qlevel[qi] : minLevel, maxL = qlevel ? qlevel[qi] : maxLevel;
+    // qlevel: per-query levels; qlevelStride 1 = (l, l), 2 = (minLevel, maxLevel) pairs; null = the scalar arguments
+    const int minL = qlevel ? qlevel[qlevelStride * qi] : minLevel, maxL = qlevel ? qlevel[qlevelStride * qi + qlevelStride - 1] : maxLevel;
     int total = 0;
     const int base = WRITE ? off[qi] : 0;
     // (x - mnMinX - r) * mfGridElementWidthInv, float, left to right (Frame.cc:347-361)
@@ -144,10 +145,10 @@ static inline size_t idx_bytes(int total) { return (sizeof(int) * (size_t)std::m
 // *d_idx in arena2 (total ints); *total holds the candidate count.  d_kps: device keypoints of the searched frame.
 static int grid_candidates_dev(orbx_matcher* m, const orbx_kp* d_kps, const int* d_cellStart, const int* d_entries, const GridParams& gp,
                                const float* d_qxy, const float* d_qr, int nq, int minLevel, int maxLevel, const int* d_qlevel,
-                               int* d_off, int nArrays, int** d_idx, int* total)
+                               int* d_off, int nArrays, int** d_idx, int* total, int qlevelStride = 1)
 {
     const int blocks = (nq + 7) / 8;
-    k_grid_query<false><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, d_off, nullptr);
+    k_grid_query<false><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, qlevelStride, d_off, nullptr);
     k_scan_offsets<<<1, 1024, 0, m->stream>>>(d_off, nq);
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(total, d_off + nq, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
@@ -155,7 +156,7 @@ static int grid_candidates_dev(orbx_matcher* m, const orbx_kp* d_kps, const int*
     int rc = m->arena2.reserve(idx_bytes(*total) * (size_t)nArrays);     // nArrays int arrays of `total` entries, d_idx first
     if (rc) return rc;
     *d_idx = (int*)m->arena2.base;
-    k_grid_query<true><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, d_off, *d_idx);
+    k_grid_query<true><<<blocks, 256, 0, m->stream>>>(d_kps, d_cellStart, d_entries, gp, d_qxy, d_qr, nq, minLevel, maxLevel, d_qlevel, qlevelStride, d_off, *d_idx);
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 3;
     return ORBX_OK;
@@ -337,6 +338,300 @@ extern "C" int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1
     }
     for (int i1 = 0; i1 < n1; i1++)          // update vbPrevMatched (:515-517)
         if (matches12[i1] >= 0) { prev_matched[2 * i1] = k2[matches12[i1]].x; prev_matched[2 * i1 + 1] = k2[matches12[i1]].y; }
+    if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+
+// ================================================================================================ windowed searches
+namespace orbx {
+
+// Candidates (GetFeaturesInArea with a per-query level range) and their Hamming distances for nq queries against one
+// frame, on the device; the CSR comes back to the host for the sequential replay of the reference's greedy loops.
+static int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
+                              const float* qxy, const float* qr, const int* qlev2, const uint8_t* qdesc, int nq,
+                              std::vector<int>& off, std::vector<int>& idx, std::vector<int>& dist)
+{
+    off.assign((size_t)nq + 1, 0);
+    idx.clear();
+    dist.clear();
+    if (nq == 0 || n == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    GridParams gp;
+    std::vector<int> start, entries;
+    build_grid_host(kps, n, minX, maxX, minY, maxY, gp, start, entries);
+    Carver cv(m->arena);
+    const size_t oK = cv.take(sizeof(orbx_kp) * (size_t)n), oS = cv.take(sizeof(int) * start.size()), oE = cv.take(sizeof(int) * entries.size()),
+                 oQ = cv.take(sizeof(float) * 2 * (size_t)nq), oR = cv.take(sizeof(float) * (size_t)nq), oL = cv.take(sizeof(int) * 2 * (size_t)nq),
+                 oO = cv.take(sizeof(int) * ((size_t)nq + 1)), oQD = cv.take((size_t)nq * 32), oTD = cv.take((size_t)n * 32);
+    int rc = m->arena.reserve(cv.total());
+    if (rc) return rc;
+    uint8_t* B = m->arena.base;
+    cudaStream_t s = m->stream;
+    ORBX_CUDA(cudaMemcpyAsync(B + oK, kps, sizeof(orbx_kp) * (size_t)n, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy, sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr, sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oL, qlev2, sizeof(int) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oQD, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oTD, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+    int* d_idx = nullptr;
+    int total = 0;
+    rc = grid_candidates_dev(m, (const orbx_kp*)(B + oK), (const int*)(B + oS), (const int*)(B + oE), gp, (const float*)(B + oQ),
+                             (const float*)(B + oR), nq, 0, 0, (const int*)(B + oL), (int*)(B + oO), 2, &d_idx, &total, 2);
+    if (rc) return rc;
+    int* d_dist = (int*)(m->arena2.base + idx_bytes(total));      // second array of arena2
+    k_cand_dist<<<(nq + 7) / 8, 256, 0, s>>>((const uint4*)(B + oQD), nq, (const uint4*)(B + oTD), (const int*)(B + oO), d_idx, d_dist);
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 4;
+    idx.resize(std::max(total, 1));
+    dist.resize(std::max(total, 1));
+    ORBX_CUDA(cudaMemcpyAsync(off.data(), B + oO, sizeof(int) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s));
+    if (total > 0) {
+        ORBX_CUDA(cudaMemcpyAsync(idx.data(), d_idx, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+        ORBX_CUDA(cudaMemcpyAsync(dist.data(), d_dist, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+    }
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+// distances of host CSR candidate lists (queries q against rows of t) on the device
+static int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, const std::vector<int>& off,
+                         const std::vector<int>& idx, std::vector<int>& dist)
+{
+    const int total = off[nq];
+    dist.assign(std::max(total, 1), 0);
+    if (total == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Carver cv(m->arena);
+    const size_t oQ = cv.take((size_t)nq * 32), oT = cv.take((size_t)nt * 32), oO = cv.take(sizeof(int) * ((size_t)nq + 1)),
+                 oI = cv.take(sizeof(int) * (size_t)total), oD = cv.take(sizeof(int) * (size_t)total);
+    int rc = m->arena.reserve(cv.total());
+    if (rc) return rc;
+    uint8_t* B = m->arena.base;
+    cudaStream_t s = m->stream;
+    ORBX_CUDA(cudaMemcpyAsync(B + oQ, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oT, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oO, off.data(), sizeof(int) * ((size_t)nq + 1), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaMemcpyAsync(B + oI, idx.data(), sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, s));
+    k_cand_dist<<<(nq + 7) / 8, 256, 0, s>>>((const uint4*)(B + oQ), nq, (const uint4*)(B + oT), (const int*)(B + oO), (const int*)(B + oI), (int*)(B + oD));
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 1;
+    ORBX_CUDA(cudaMemcpyAsync(dist.data(), B + oD, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+}  // namespace orbx
+
+extern "C" int orbm_search_by_projection(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* occupied_in,
+                                         int n, float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                         const float* proj_xy, const float* proj_xr, const int* level, const float* view_cos,
+                                         const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, float nnratio,
+                                         int* feature_match, int* nmatches)
+{
+    if (!m || n < 0 || nmp < 0 || (n > 0 && (!kps || !desc || !u_right || !occupied_in || !feature_match)) || !sf || nlevels < 1 ||
+        (nmp > 0 && (!proj_xy || !proj_xr || !level || !view_cos || !mp_desc || !mp_has_obs)) || !(maxX > minX) || !(maxY > minY)) {
+        set_error("orbm_search_by_projection: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nmatches) *nmatches = 0;
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    const bool bFactor = th != 1.0;
+    std::vector<float> qr(nmp), rr(nmp);
+    std::vector<int> qlev(2 * (size_t)nmp);
+    for (int i = 0; i < nmp; i++) {
+        if (level[i] < 0 || level[i] >= nlevels) { set_error("orbm_search_by_projection: level[%d] = %d out of range", i, level[i]); return ORBX_ERR_ARG; }
+        float r = view_cos[i] > 0.998 ? 2.5f : 4.0f;          // RadiusByViewingCos (:131-137)
+        if (bFactor) r *= th;
+        rr[i] = r;
+        qr[i] = r * sf[level[i]];                              // :68
+        qlev[2 * i] = level[i] - 1;
+        qlev[2 * i + 1] = level[i];
+    }
+    std::vector<int> off, idx, dist;
+    int rc = windowed_distances(m, kps, desc, n, minX, maxX, minY, maxY, proj_xy, qr.data(), qlev.data(), mp_desc, nmp, off, idx, dist);
+    if (rc) return rc;
+    // sequential replay (:50-126): occupancy changes as points are assigned
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    int nm = 0;
+    for (int i = 0; i < nmp; i++) {
+        if (off[i + 1] == off[i]) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int c = off[i]; c < off[i + 1]; c++) {
+            const int j = idx[c];
+            if (occupied[j]) continue;
+            if (u_right[j] > 0) {
+                const float er = fabsf(proj_xr[i] - u_right[j]);
+                if (er > rr[i] * sf[level[i]]) continue;
+            }
+            const int d = dist[c];
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = kps[j].octave; bestIdx = j; }
+            else if (d < bestDist2) { bestLevel2 = kps[j].octave; bestDist2 = d; }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            feature_match[bestIdx] = i;
+            occupied[bestIdx] = mp_has_obs[i];
+            nm++;
+        }
+    }
+    if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_projection_frame(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right,
+                                               const uint8_t* occupied_in, int n, float minX, float maxX, float minY, float maxY,
+                                               const float* sf, int nlevels, const float* proj_xy, const float* proj_ur,
+                                               const int* last_octave, const float* last_angle, const uint8_t* mp_desc,
+                                               const uint8_t* mp_has_obs, int nmp, float th, int mode, int checkOri,
+                                               int* feature_match, int* nmatches)
+{
+    if (!m || n < 0 || nmp < 0 || (n > 0 && (!kps || !desc || !u_right || !occupied_in || !feature_match)) || !sf || nlevels < 1 ||
+        (nmp > 0 && (!proj_xy || !proj_ur || !last_octave || !last_angle || !mp_desc || !mp_has_obs)) || !(maxX > minX) || !(maxY > minY) ||
+        mode < 0 || mode > 2) {
+        set_error("orbm_search_by_projection_frame: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nmatches) *nmatches = 0;
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    std::vector<float> qr(nmp);
+    std::vector<int> qlev(2 * (size_t)nmp);
+    for (int i = 0; i < nmp; i++) {
+        const int o = last_octave[i];
+        if (o < 0 || o >= nlevels) { set_error("orbm_search_by_projection_frame: last_octave[%d] = %d out of range", i, o); return ORBX_ERR_ARG; }
+        qr[i] = th * sf[o];                                                        // :1383
+        if (mode == 1) { qlev[2 * i] = o; qlev[2 * i + 1] = -1; }                   // bForward: GetFeaturesInArea(u, v, radius, nLastOctave)
+        else if (mode == 2) { qlev[2 * i] = 0; qlev[2 * i + 1] = o; }               // bBackward
+        else { qlev[2 * i] = o - 1; qlev[2 * i + 1] = o + 1; }
+    }
+    std::vector<int> off, idx, dist;
+    int rc = windowed_distances(m, kps, desc, n, minX, maxX, minY, maxY, proj_xy, qr.data(), qlev.data(), mp_desc, nmp, off, idx, dist);
+    if (rc) return rc;
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nm = 0;
+    for (int i = 0; i < nmp; i++) {
+        if (off[i + 1] == off[i]) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int c = off[i]; c < off[i + 1]; c++) {
+            const int i2 = idx[c];
+            if (occupied[i2]) continue;
+            if (u_right[i2] > 0) {
+                const float er = fabsf(proj_ur[i] - u_right[i2]);
+                if (er > qr[i]) continue;
+            }
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            feature_match[bestIdx2] = i;
+            occupied[bestIdx2] = mp_has_obs[i];
+            nm++;
+            if (checkOri) {
+                float rot = last_angle[i] - kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int j : rotHist[i]) { feature_match[j] = -1; nm--; }
+    }
+    if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k1, const uint8_t* d1, int n1, const uint8_t* valid1,
+                                  const int* node1, const int* off1, const int* idx1, int nn1,
+                                  const orbx_kp* k2, const uint8_t* d2, int n2, const uint8_t* valid2,
+                                  const int* node2, const int* off2, const int* idx2, int nn2,
+                                  float nnratio, int checkOri, int* matches, int* nmatches)
+{
+    if (!m || (variant != 0 && variant != 1) || n1 < 0 || n2 < 0 || nn1 < 0 || nn2 < 0 || !matches ||
+        (n1 > 0 && (!k1 || !d1 || !valid1)) || (n2 > 0 && (!k2 || !d2)) || (variant == 1 && n2 > 0 && !valid2) ||
+        (nn1 > 0 && (!node1 || !off1 || !idx1)) || (nn2 > 0 && (!node2 || !off2 || !idx2))) {
+        set_error("orbm_search_by_bow: bad argument");
+        return ORBX_ERR_ARG;
+    }
+    if (nmatches) *nmatches = 0;
+    const int nout = variant == 0 ? n2 : n1;
+    for (int i = 0; i < nout; i++) matches[i] = -1;
+    // merge-join of the two feature vectors on the node id (:180-264): every valid feature of a common node of the first
+    // key frame becomes a query whose candidates are the features of the same node in the second, in stored order
+    std::vector<int> qfeat, off(1, 0), idx;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (node1[a] == node2[b]) {
+            for (int p1 = off1[a]; p1 < off1[a + 1]; p1++) {
+                const int f1 = idx1[p1];
+                if (f1 < 0 || f1 >= n1) { set_error("orbm_search_by_bow: feature index out of range"); return ORBX_ERR_ARG; }
+                if (!valid1[f1]) continue;
+                qfeat.push_back(f1);
+                for (int p2 = off2[b]; p2 < off2[b + 1]; p2++) {
+                    if (idx2[p2] < 0 || idx2[p2] >= n2) { set_error("orbm_search_by_bow: feature index out of range"); return ORBX_ERR_ARG; }
+                    idx.push_back(idx2[p2]);
+                }
+                off.push_back((int)idx.size());
+            }
+            a++; b++;
+        } else if (node1[a] < node2[b]) {
+            a = (int)(std::lower_bound(node1, node1 + nn1, node2[b]) - node1);
+        } else {
+            b = (int)(std::lower_bound(node2, node2 + nn2, node1[a]) - node2);
+        }
+    }
+    const int nq = (int)qfeat.size();
+    if (nq == 0) return ORBX_OK;
+    std::vector<uint8_t> qdesc((size_t)nq * 32);
+    for (int q = 0; q < nq; q++) memcpy(&qdesc[(size_t)q * 32], d1 + (size_t)qfeat[q] * 32, 32);
+    std::vector<int> dist;
+    int rc = csr_distances(m, qdesc.data(), nq, d2, n2, off, idx, dist);
+    if (rc) return rc;
+    // sequential replay: features of the second frame taken by earlier queries are skipped (:209, :576)
+    std::vector<uint8_t> taken2(n2, 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nm = 0;
+    for (int q = 0; q < nq; q++) {
+        const int f1 = qfeat[q];
+        int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+        for (int c = off[q]; c < off[q + 1]; c++) {
+            const int f2 = idx[c];
+            if (taken2[f2]) continue;
+            if (variant == 1 && !valid2[f2]) continue;
+            const int d = dist[c];
+            if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdx2 = f2; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        const bool low = variant == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;      // :228 vs :598
+        if (low && (float)bestDist1 < nnratio * (float)bestDist2) {
+            taken2[bestIdx2] = 1;
+            if (variant == 0) matches[bestIdx2] = f1; else matches[f1] = bestIdx2;
+            if (checkOri) {
+                float rot = k1[f1].angle - k2[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(variant == 0 ? bestIdx2 : f1);
+            }
+            nm++;
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int j : rotHist[i]) { matches[j] = -1; nm--; }
+        }
+    }
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
 }

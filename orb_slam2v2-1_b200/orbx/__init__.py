@@ -77,6 +77,9 @@ def lib():
         "orbm_grid_candidates": (i, [vp, vp, i, f, f, f, f, vp, i, vp, i, i, vp, vp, vp, i]),
         "orbm_search_for_initialization": (i, [vp, vp, vp, i, vp, vp, i, f, f, f, f, vp, vp, i, f, i, vp]),
         "orbm_stereo_matches": (i, [vp, vp, vp, i, vp, vp, i, vp, vp, i, f, f, f, vp, vp, vp]),
+        "orbm_search_by_projection": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp]),
+        "orbm_search_by_projection_frame": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp, vp]),
+        "orbm_search_by_bow": (i, [vp, i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp, vp]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
     }
@@ -379,6 +382,58 @@ class ORBmatcher:
                                                       *[float(b) for b in bounds], _p(prev), _p(m12), windowSize,
                                                       self.mfNNratio, int(self.mbCheckOrientation), C.byref(nm)))
         return nm.value, m12, prev
+
+    def SearchByProjection(self, kps, desc, u_right, occupied, bounds, scale_factors, proj_xy, proj_xr, level, view_cos,
+                           mp_desc, mp_has_obs, th=1.0):
+        """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th) (src/ORBmatcher.cc:45-129) on plain arrays (see
+        include/orbx.h).  Returns (nmatches, feature_match)."""
+        kps = np.ascontiguousarray(kps, KP_DTYPE)
+        desc, mp_desc = _u8(desc).reshape(-1, 32), _u8(mp_desc).reshape(-1, 32)
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        u_right, sf, proj_xy, proj_xr, view_cos = f32(u_right), f32(scale_factors), f32(proj_xy).reshape(-1, 2), f32(proj_xr), f32(view_cos)
+        occupied, mp_has_obs, level = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(level, np.int32)
+        fm = np.zeros(max(len(kps), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_by_projection(self._h, _p(kps), _p(desc), _p(u_right), _p(occupied), len(kps), *[float(b) for b in bounds],
+                                                 _p(sf), len(sf), _p(proj_xy), _p(proj_xr), _p(level), _p(view_cos), _p(mp_desc),
+                                                 _p(mp_has_obs), len(level), float(th), self.mfNNratio, _p(fm), C.byref(nm)))
+        return nm.value, fm[:len(kps)]
+
+    def SearchByProjectionFrame(self, kps, desc, u_right, occupied, bounds, scale_factors, proj_xy, proj_ur, last_octave, last_angle,
+                                mp_desc, mp_has_obs, th, mode=0):
+        """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1330-1472) on plain arrays.
+        mode: 0 neither, 1 forward, 2 backward.  Returns (nmatches, feature_match)."""
+        kps = np.ascontiguousarray(kps, KP_DTYPE)
+        desc, mp_desc = _u8(desc).reshape(-1, 32), _u8(mp_desc).reshape(-1, 32)
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        u_right, sf, proj_xy, proj_ur, last_angle = f32(u_right), f32(scale_factors), f32(proj_xy).reshape(-1, 2), f32(proj_ur), f32(last_angle)
+        occupied, mp_has_obs, last_octave = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(last_octave, np.int32)
+        fm = np.zeros(max(len(kps), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_by_projection_frame(self._h, _p(kps), _p(desc), _p(u_right), _p(occupied), len(kps),
+                                                       *[float(b) for b in bounds], _p(sf), len(sf), _p(proj_xy), _p(proj_ur), _p(last_octave),
+                                                       _p(last_angle), _p(mp_desc), _p(mp_has_obs), len(last_octave), float(th), int(mode),
+                                                       int(self.mbCheckOrientation), _p(fm), C.byref(nm)))
+        return nm.value, fm[:len(kps)]
+
+    def SearchByBoW(self, k1, d1, valid1, fv1, k2, d2, fv2, valid2=None):
+        """ORBmatcher::SearchByBoW (src/ORBmatcher.cc:159-288 when valid2 is None: key frame -> frame; :522-655 otherwise:
+        key frame -> key frame).  fv = (node ids ascending, offsets, feature indices) CSR of a DBoW2::FeatureVector.
+        Returns (nmatches, matches)."""
+        k1, k2 = np.ascontiguousarray(k1, KP_DTYPE), np.ascontiguousarray(k2, KP_DTYPE)
+        d1, d2 = _u8(d1).reshape(-1, 32), _u8(d2).reshape(-1, 32)
+        i32 = lambda a: np.ascontiguousarray(a, np.int32)
+        n1_, o1_, i1_ = [i32(a) for a in fv1]
+        n2_, o2_, i2_ = [i32(a) for a in fv2]
+        variant = 0 if valid2 is None else 1
+        valid1 = _u8(valid1)
+        v2 = None if valid2 is None else _u8(valid2)
+        out = np.zeros(max(len(k2) if variant == 0 else len(k1), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_by_bow(self._h, variant, _p(k1), _p(d1), len(k1), _p(valid1), _p(n1_), _p(o1_), _p(i1_), len(n1_),
+                                          _p(k2), _p(d2), len(k2), _p(v2), _p(n2_), _p(o2_), _p(i2_), len(n2_),
+                                          self.mfNNratio, int(self.mbCheckOrientation), _p(out), C.byref(nm)))
+        return nm.value, out[:(len(k2) if variant == 0 else len(k1))]
 
     def ComputeStereoMatches(self, left, right, kl, dl, kr, dr, bf, maxD, minD=0.0, frame=0):
         """Frame::ComputeStereoMatches (src/Frame.cc:481-655) on the device pyramids of two extractor handles.
