@@ -112,36 +112,37 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 // The cell is processed at iniThFAST first and, only if that yields no keypoint, again at minThFAST
 // (ORBextractor.cc:809-816): kept(t) = raw > t and raw > every neighbour's raw, so each pass is exact on its own.
 constexpr int FAST_WARPS = 4;
+constexpr int FAST_ZMASK_WORDS = 24;     // zone masks of up to 24 word columns (cells up to 90 px wide)
 
 // raw = max over the 16 arcs of 9 contiguous ring pixels of min(ring - centre) resp. min(centre - ring)
 // (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  min/max commute with the subtraction of the
-// centre, so the arcs are evaluated on the raw ring values.  Register k holds (ring[k], ring[k+8]) as s16x2: window k
-// (lo half) = min(ring[k..7], ring[8..8+k]) and window 8+k (hi half) = min(ring[8+k..15], ring[0..k]), i.e.
-// min(suffix-min of the pairs, half-swapped prefix-min of the pairs).
+// centre, so the arcs are evaluated on the raw ring values.  E[j] = (ring[j], ring[j+8]) as s16x2 for j = 0..15 (indices
+// mod 16; built with IMADs, i.e. on the FMA pipe): the arc starting at k is the low half of min(E[k..k+8]) and the arc
+// starting at k+8 its high half.  Nine-element minima from shared triples T[j] = min3(E[j..j+2]) and
+// W[k] = min3(T[k], T[k+3], T[k+6]), all 3-input VIMNMX3.
+__device__ __forceinline__ unsigned vmin3s2(unsigned a, unsigned b, unsigned c) { return __vmins2(__vmins2(a, b), c); }
+__device__ __forceinline__ unsigned vmax3s2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
+
 __device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch)
 {
     const int v = c[0];
-    unsigned r0 = c[3 * pitch], r1 = c[3 * pitch + 1], r2 = c[2 * pitch + 2], r3 = c[pitch + 3];
-    unsigned r4 = c[3], r5 = c[-pitch + 3], r6 = c[-2 * pitch + 2], r7 = c[-3 * pitch + 1];
-    unsigned r8 = c[-3 * pitch], r9 = c[-3 * pitch - 1], r10 = c[-2 * pitch - 2], r11 = c[-pitch - 3];
-    unsigned r12 = c[-3], r13 = c[pitch - 3], r14 = c[2 * pitch - 2], r15 = c[3 * pitch - 1];
-    unsigned Pk[8];
-    Pk[0] = __byte_perm(r0, r8, 0x5410);  Pk[1] = __byte_perm(r1, r9, 0x5410);  Pk[2] = __byte_perm(r2, r10, 0x5410);
-    Pk[3] = __byte_perm(r3, r11, 0x5410); Pk[4] = __byte_perm(r4, r12, 0x5410); Pk[5] = __byte_perm(r5, r13, 0x5410);
-    Pk[6] = __byte_perm(r6, r14, 0x5410); Pk[7] = __byte_perm(r7, r15, 0x5410);
-    unsigned sn[8], sx[8], pn[8], px[8];     // suffix / prefix minima and maxima of the pairs
-    sn[7] = sx[7] = Pk[7];
-    pn[0] = px[0] = Pk[0];
+    unsigned r[16];
+    r[0] = c[3 * pitch]; r[1] = c[3 * pitch + 1]; r[2] = c[2 * pitch + 2]; r[3] = c[pitch + 3];
+    r[4] = c[3]; r[5] = c[-pitch + 3]; r[6] = c[-2 * pitch + 2]; r[7] = c[-3 * pitch + 1];
+    r[8] = c[-3 * pitch]; r[9] = c[-3 * pitch - 1]; r[10] = c[-2 * pitch - 2]; r[11] = c[-pitch - 3];
+    r[12] = c[-3]; r[13] = c[pitch - 3]; r[14] = c[2 * pitch - 2]; r[15] = c[3 * pitch - 1];
+    unsigned E[16];
 #pragma unroll
-    for (int k = 6; k >= 0; k--) { sn[k] = __vmins2(sn[k + 1], Pk[k]); sx[k] = __vmaxs2(sx[k + 1], Pk[k]); }
+    for (int j = 0; j < 16; j++) E[j] = r[(j + 8) & 15] * 65536u + r[j];
+    unsigned Tn[14], Tx[14];
 #pragma unroll
-    for (int k = 1; k < 8; k++) { pn[k] = __vmins2(pn[k - 1], Pk[k]); px[k] = __vmaxs2(px[k - 1], Pk[k]); }
-    unsigned bright = 0, dark = 0x7FFF7FFFu;     // bright: max over windows of the window min; dark: min of the window max
+    for (int j = 0; j < 14; j++) { Tn[j] = vmin3s2(E[j], E[j + 1], E[j + 2]); Tx[j] = vmax3s2(E[j], E[j + 1], E[j + 2]); }
+    unsigned Wn[8], Wx[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        bright = __vmaxs2(bright, __vmins2(sn[k], __byte_perm(pn[k], 0, 0x1032)));
-        dark = __vmins2(dark, __vmaxs2(sx[k], __byte_perm(px[k], 0, 0x1032)));
-    }
+    for (int k = 0; k < 8; k++) { Wn[k] = vmin3s2(Tn[k], Tn[k + 3], Tn[k + 6]); Wx[k] = vmax3s2(Tx[k], Tx[k + 3], Tx[k + 6]); }
+    // bright: max over arcs of the arc minimum; dark: min over arcs of the arc maximum
+    const unsigned bright = vmax3s2(vmax3s2(Wn[0], Wn[1], Wn[2]), vmax3s2(Wn[3], Wn[4], Wn[5]), __vmaxs2(Wn[6], Wn[7]));
+    const unsigned dark = vmin3s2(vmin3s2(Wx[0], Wx[1], Wx[2]), vmin3s2(Wx[3], Wx[4], Wx[5]), __vmins2(Wx[6], Wx[7]));
     const int b = max((int)(bright & 0xFFFF), (int)(bright >> 16)) - v;
     const int d = v - min((int)(dark & 0xFFFF), (int)(dark >> 16));
     return max(b, d);
@@ -153,7 +154,7 @@ __host__ __device__ inline int fast_warp_smem(int wCell, int hCell)
     const int tile = (hCell + 6) * (((wCell + 6 + 3 + 3) >> 2) << 2);
     const int sc = (hCell + 2) * ((wCell + 2 + 3) & ~3);
     const int list = ((wCell * hCell * 2) + 3) & ~3;
-    return (tile + sc + list + 15) & ~15;
+    return (FAST_ZMASK_WORDS * 4 + tile + sc + list + 15) & ~15;
 }
 
 size_t fast_smem_bytes(const Plan& P)
@@ -163,46 +164,44 @@ size_t fast_smem_bytes(const Plan& P)
     return (size_t)m * FAST_WARPS;
 }
 
-__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
+__device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F, int smemPerWarp, int f, int cell, uint8_t* smem)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, f = blockIdx.y;
-    const int cell = blockIdx.x * FAST_WARPS + wid;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (cell >= P.totalCells) return;
     const unsigned FULL = 0xFFFFFFFFu, ltmask = (1u << lane) - 1;
-    const int l = level_of_cell(P, cell);
-    const LevelGeom& G = P.lv[l];
-    const int ci = cell - G.cellBase;
-    const int ci_i = ci / G.nCols, ci_j = ci - ci_i * G.nCols;
+    // cell ROI (ORBextractor.cc:791-806): [iniX, maxX) x [iniY, maxY), overlap of 6 px with the next cell -- from the per-shape
+    // cell table: {iniX | iniY << 16, tw | th << 16 (0 = skipped cell), level | xoff << 4 | yoff << 16, cell index in the level}
+    const uint4 ct = __ldg(&F.cellTab[cell]);
     int* cntOut = F.cellCount + (size_t)f * P.totalCells + cell;
-
-    // cell ROI (ORBextractor.cc:791-806): [iniX, maxX) x [iniY, maxY), overlap of 6 px with the next cell
-    const int iniX = MIN_BORDER + ci_j * G.wCell, iniY = MIN_BORDER + ci_i * G.hCell;
-    const int maxX = min(iniX + G.wCell + 6, G.maxBX), maxY = min(iniY + G.hCell + 6, G.maxBY);
-    const int tw = maxX - iniX, th = maxY - iniY;
-    if (iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7) {     // skipped cell / ROI too small for cv::FAST
+    if (ct.y == 0) {                                      // skipped cell / ROI too small for cv::FAST
         if (lane == 0) *cntOut = 0;
         return;
     }
+    const int iniX = ct.x & 0xFFFF, iniY = ct.x >> 16, tw = ct.y & 0xFFFF, th = ct.y >> 16;
+    const int l = ct.z & 15, xoff = (ct.z >> 4) & 0xFFF, yoff = ct.z >> 16;
+    const LevelGeom& G = P.lv[l];
+    const int maxX = iniX + tw;
     const int iw = tw - 6, ih = th - 6;                   // detection zone: no corner within 3 px of the ROI edge
     const int ax = iniX & ~3;                             // word-aligned tile origin
     const int dx0 = iniX - ax;
     const int tpw = (maxX - ax + 3) >> 2, tp = tpw * 4;   // tile pitch in words / bytes
     const int scp = (iw + 2 + 3) & ~3;                    // score-map pitch: 1-px zero frame
-    uint8_t* tile = smem + (size_t)wid * smemPerWarp;
+    uint32_t* zmask = reinterpret_cast<uint32_t*>(smem + (size_t)wid * smemPerWarp);      // zone mask per word column
+    uint8_t* tile = reinterpret_cast<uint8_t*>(zmask + FAST_ZMASK_WORDS);
     uint8_t* sc = tile + th * tp;
     uint16_t* list = reinterpret_cast<uint16_t*>(sc + (ih + 2) * scp);
     uint32_t* tileW = reinterpret_cast<uint32_t*>(tile);
 
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    {
+    {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below
         const uint8_t* src = img + (size_t)iniY * pitch + ax;
         const int n = th * tpw;
-        const unsigned inv = 65536u / (unsigned)tpw + 1;          // i / tpw == (i * inv) >> 16 for i < 65536 / tpw * ... (n < 1400)
+        const unsigned inv = 65536u / (unsigned)tpw + 1;          // i / tpw == (i * inv) >> 16 (n < 1400)
+        const unsigned sbase = (unsigned)__cvta_generic_to_shared(tileW);
         for (int i = lane; i < n; i += 32) {
             const int r = (int)(((unsigned)i * inv) >> 16), cidx = i - r * tpw;
-            tileW[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r * pitch) + cidx);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + 4u * (unsigned)i), "l"(src + (size_t)r * pitch + 4 * cidx));
         }
     }
     // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih); word items of the zone
@@ -210,9 +209,15 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, co
     const int wFirst = zx0 >> 2, nwz = ((zx1 - 1) >> 2) - wFirst + 1;
     const int nitems = ih * nwz;
     const unsigned invz = 65536u / (unsigned)nwz + 1;
-    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)ci * G.slotCap;
+    if (lane < nwz) {                                     // bytes of word column wFirst + lane that lie inside the zone
+        const int wc = wFirst + lane;
+        const int lo = max(zx0 - 4 * wc, 0), hi = min(zx1 - 4 * wc, 4);
+        zmask[lane] = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
+    }
+    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)ct.w * G.slotCap;
     const int scWords = ((ih + 2) * scp) >> 2;
     int total = 0;
+    asm volatile("cp.async.wait_all;" ::: "memory");
 
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? P.iniTh : P.minTh;
@@ -228,7 +233,8 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, co
             int row = 0, wc = 0;
             if (i < nitems) {
                 const int r = (int)(((unsigned)i * invz) >> 16);
-                wc = wFirst + i - r * nwz;
+                const int zc = i - r * nwz;
+                wc = wFirst + zc;
                 row = r + 3;
                 const uint32_t* w = tileW + row * tpw + wc;
                 const unsigned C = w[0], Lw = w[-1], Rw = w[1], U = w[-3 * tpw], D = w[3 * tpw];
@@ -237,10 +243,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, co
                 const unsigned g0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, g8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
                 const unsigned g4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, g12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
                 comb = (g0 | g8) & (g4 | g12) & 0x80808080u;
-                // bytes of this word outside the zone
-                const int lo = max(zx0 - 4 * wc, 0), hi = min(zx1 - 4 * wc, 4);
-                const unsigned m = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
-                comb &= m;
+                comb &= zmask[zc];                       // bytes of this word outside the zone
             }
             if (__ballot_sync(FULL, comb != 0) == 0) continue;
             const unsigned b0 = __ballot_sync(FULL, comb & 0x80u), b1 = __ballot_sync(FULL, comb & 0x8000u);
@@ -280,7 +283,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, co
             const unsigned kb = __ballot_sync(FULL, keep);
             if (keep) {
                 // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
-                const int x = (e & 0xFF) - dx0 + ci_j * G.wCell, y = (e >> 8) + ci_i * G.hCell;
+                const int x = (e & 0xFF) - dx0 + xoff, y = (e >> 8) + yoff;
                 out[total + __popc(kb & ltmask)] = pack_key(x, y, v - 1);
             }
             total += __popc(kb);
@@ -288,6 +291,12 @@ __global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, co
         __syncwarp();
     }
     if (lane == 0) *cntOut = total;
+}
+
+__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    fast_cell_body(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem);
 }
 
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
@@ -712,10 +721,9 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ img, int 
 #undef BLUR_ROW
 }
 
-__global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan P, const FrameBufs F)
+__device__ __forceinline__ void blur_tile_body(const Plan& P, const FrameBufs& F, int f, int tile)
 {
-    const int f = blockIdx.y, lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
     if (tile >= P.totalBlurTiles) return;
     int l = 0;
     while (l + 1 < P.nlevels && tile >= P.lv[l + 1].blurTileBase) ++l;
@@ -736,10 +744,44 @@ __global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan 
 
 #undef TAPS4
 
+__global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan P, const FrameBufs F)
+{
+    blur_tile_body(P, F, blockIdx.y, blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5));
+}
+
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
 {
     dim3 grd((P.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, B);
     k_blur<<<grd, BLUR_WARPS * 32, 0, s>>>(P, F);
+}
+
+// Horizontal fusion of the two independent stages that follow the pyramid: cell FAST keeps the ALU pipe busy (min / max /
+// SWAR compares), the blur lives on the dot-product (IDP) pipe.  One launch whose blocks are FAST blocks and blur blocks
+// interleaved in index order, so that every SM holds warps of both kinds and the two pipes overlap; the quadtree (which
+// needs the FAST output) and the descriptors (which need both) follow as before.
+#ifndef FB_MINB
+#define FB_MINB 6
+#endif
+__global__ void __launch_bounds__(FAST_WARPS * 32, FB_MINB) k_fast_blur(const Plan P, const FrameBufs F, int smemPerWarp, int nF, int nB)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int x = blockIdx.x, T = nF + nB, wid = threadIdx.x >> 5;
+    const int kb = (int)(((long long)x * nB) / T);                       // blur blocks before x
+    const bool isBlur = (int)(((long long)(x + 1) * nB) / T) > kb;
+    if (isBlur) blur_tile_body(P, F, blockIdx.y, kb * FAST_WARPS + wid);
+    else fast_cell_body(P, F, smemPerWarp, blockIdx.y, (x - kb) * FAST_WARPS + wid, smem);
+}
+
+void launch_fast_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
+{
+    static thread_local size_t configured = 48 * 1024;
+    if (smemBytes > configured) {
+        cudaFuncSetAttribute(k_fast_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        configured = smemBytes;
+    }
+    const int nF = (P.totalCells + FAST_WARPS - 1) / FAST_WARPS, nB = (P.totalBlurTiles + FAST_WARPS - 1) / FAST_WARPS;
+    dim3 grd(nF + nB, B);
+    k_fast_blur<<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS), nF, nB);
 }
 
 // ------------------------------------------------------------------------------------------------ orientation + rBRIEF

@@ -3,6 +3,7 @@
 // point fails with ORBX_ERR_CUDA.
 #include "extract_kernels.cuh"
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <vector>
@@ -48,6 +49,7 @@ struct orbx_extractor {
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
 
     int device = 0, maxBatch = 1, fmaMode = 0;
+    bool fuseFastBlur = false;         // FAST and blur in one launch (ORBX_FUSE=1 in the environment; measured slower than two launches)
     cudaStream_t stream = nullptr;
     float4* d_patT = nullptr;          // rBRIEF pattern as floats: patT[bit * 32 + byte] = (x0, y0, x1, y1)
     uint2* d_icTab = nullptr;          // IC_Angle weight words (see extract_kernels.cuh)
@@ -266,6 +268,7 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     const size_t oSlots = take(sizeof(uint32_t) * P.slotSlab * cap), oKeys = take(sizeof(uint32_t) * P.keySlab * cap);
     const size_t oKnode = take(sizeof(uint16_t) * P.keySlab * cap);
     const size_t oLK = take(sizeof(uint32_t) * P.totalNodes * cap), oLC = take(sizeof(int) * MAX_LEVELS * cap);
+    const size_t oCT = take(sizeof(uint4) * P.totalCells);
     // outputs contiguous: counts | kps | desc  (one D2H copy)
     const size_t oOut = off;
     const size_t oCounts = take(sizeof(int) * cap), oKps = take(sizeof(orbx_kp) * P.totalNodes * cap);
@@ -285,6 +288,28 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     F.levelKeys = (uint32_t*)(base + oLK);
     F.levelCount = (int*)(base + oLC);
     F.counts = (int*)(base + oCounts);
+    F.cellTab = (const uint4*)(base + oCT);
+    {   // FAST cell table (ComputeKeyPointsOctTree :789-806)
+        std::vector<uint4> tab(P.totalCells);
+        for (int l = 0; l < ex->nlevels; l++) {
+            const LevelGeom& G = P.lv[l];
+            for (int i = 0; i < G.nRows; i++)
+                for (int j = 0; j < G.nCols; j++) {
+                    const int iniX = MIN_BORDER + j * G.wCell, iniY = MIN_BORDER + i * G.hCell;
+                    const int maxX = std::min(iniX + G.wCell + 6, G.maxBX), maxY = std::min(iniY + G.hCell + 6, G.maxBY);
+                    const int tw = maxX - iniX, th = maxY - iniY;
+                    const bool skip = iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7;
+                    uint4 r;
+                    r.x = (unsigned)iniX | ((unsigned)iniY << 16);
+                    r.y = skip ? 0u : ((unsigned)tw | ((unsigned)th << 16));
+                    r.z = (unsigned)l | ((unsigned)(j * G.wCell) << 4) | ((unsigned)(i * G.hCell) << 16);
+                    r.w = (unsigned)(i * G.nCols + j);
+                    tab[G.cellBase + i * G.nCols + j] = r;
+                }
+        }
+        ORBX_CUDA(cudaMemcpyAsync(base + oCT, tab.data(), sizeof(uint4) * tab.size(), cudaMemcpyHostToDevice, ex->stream));
+        ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+    }
     F.kps = (orbx_kp*)(base + oKps);
     F.desc = base + oDesc;
     ex->h_out_bytes = outBytes;
@@ -314,15 +339,16 @@ static int enqueue(orbx_extractor* ex, int B)
         launches++;
     }
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
-    launch_fast_cells(s, P, F, B, ex->fastSmem);
+    if (ex->fuseFastBlur) launch_fast_blur(s, P, F, B, ex->fastSmem);      // stage 2 = FAST + blur, stage 4 empty
+    else launch_fast_cells(s, P, F, B, ex->fastSmem);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octSmem));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
-    launch_blur(s, P, F, B);
+    if (!ex->fuseFastBlur) launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
-    launches += 4;
+    launches += ex->fuseFastBlur ? 3 : 4;
     ORBX_CUDA(cudaGetLastError());
     ex->lastLaunches = launches;
     ex->lastB = B;
@@ -359,6 +385,7 @@ int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, in
     ex->minThFAST = minThFAST;
     ex->device = device;
     ex->maxBatch = max_batch;
+    if (const char* e = getenv("ORBX_FUSE")) ex->fuseFastBlur = atoi(e) != 0;
 
     // scale tables: float chain, the member scaleFactor is a double (ORBextractor.cc:415-431)
     ex->mvScaleFactor.resize(nlevels);
