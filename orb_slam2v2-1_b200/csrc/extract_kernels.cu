@@ -112,7 +112,6 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 // The cell is processed at iniThFAST first and, only if that yields no keypoint, again at minThFAST
 // (ORBextractor.cc:809-816): kept(t) = raw > t and raw > every neighbour's raw, so each pass is exact on its own.
 constexpr int FAST_WARPS = 4;
-constexpr int FAST_ZMASK_WORDS = 24;     // zone masks of up to 24 word columns (cells up to 90 px wide)
 
 // raw = max over the 16 arcs of 9 contiguous ring pixels of min(ring - centre) resp. min(centre - ring)
 // (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  min/max commute with the subtraction of the
@@ -154,7 +153,7 @@ __host__ __device__ inline int fast_warp_smem(int wCell, int hCell)
     const int tile = (hCell + 6) * (((wCell + 6 + 3 + 3) >> 2) << 2);
     const int sc = (hCell + 2) * ((wCell + 2 + 3) & ~3);
     const int list = ((wCell * hCell * 2) + 3) & ~3;
-    return (FAST_ZMASK_WORDS * 4 + tile + sc + list + 15) & ~15;
+    return (tile + sc + list + 15) & ~15;
 }
 
 size_t fast_smem_bytes(const Plan& P)
@@ -186,35 +185,44 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     const int dx0 = iniX - ax;
     const int tpw = (maxX - ax + 3) >> 2, tp = tpw * 4;   // tile pitch in words / bytes
     const int scp = (iw + 2 + 3) & ~3;                    // score-map pitch: 1-px zero frame
-    uint32_t* zmask = reinterpret_cast<uint32_t*>(smem + (size_t)wid * smemPerWarp);      // zone mask per word column
-    uint8_t* tile = reinterpret_cast<uint8_t*>(zmask + FAST_ZMASK_WORDS);
+    uint8_t* tile = smem + (size_t)wid * smemPerWarp;
     uint8_t* sc = tile + th * tp;
     uint16_t* list = reinterpret_cast<uint16_t*>(sc + (ih + 2) * scp);
     uint32_t* tileW = reinterpret_cast<uint32_t*>(tile);
 
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
-    {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below
-        const uint8_t* src = img + (size_t)iniY * pitch + ax;
-        const int n = th * tpw;
-        const unsigned inv = 65536u / (unsigned)tpw + 1;          // i / tpw == (i * inv) >> 16 (n < 1400)
-        const unsigned sbase = (unsigned)__cvta_generic_to_shared(tileW);
-        for (int i = lane; i < n; i += 32) {
-            const int r = (int)(((unsigned)i * inv) >> 16), cidx = i - r * tpw;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + 4u * (unsigned)i), "l"(src + (size_t)r * pitch + 4 * cidx));
+    {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below.
+        // lane = (row r0, word c0) of a block of rpiS = 32 / tpw whole tile rows: no index arithmetic inside the loop
+        const int rpiS = (ct.w >> 16) & 15;
+        const int r0 = (int)(((unsigned)lane * (65536u / (unsigned)tpw + 1)) >> 16), c0 = lane - r0 * tpw;
+        if (r0 < rpiS) {
+            const uint8_t* p = img + (size_t)(iniY + r0) * pitch + ax + 4 * c0;
+            unsigned sdst = (unsigned)__cvta_generic_to_shared(tileW) + 4u * (unsigned)lane;
+            const size_t pstep = (size_t)rpiS * pitch;
+            const unsigned sstep = 4u * (unsigned)(rpiS * tpw);
+            for (int r = r0; r < th; r += rpiS) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(p));
+                p += pstep;
+                sdst += sstep;
+            }
         }
     }
     // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih); word items of the zone
     const int zx0 = dx0 + 3, zx1 = zx0 + iw;
     const int wFirst = zx0 >> 2, nwz = ((zx1 - 1) >> 2) - wFirst + 1;
-    const int nitems = ih * nwz;
-    const unsigned invz = 65536u / (unsigned)nwz + 1;
-    if (lane < nwz) {                                     // bytes of word column wFirst + lane that lie inside the zone
-        const int wc = wFirst + lane;
+    // pre-filter work items: lane = (row zr0, word column zc) of a block of rpiZ = 32 / nwz zone rows
+    const int rpiZ = (ct.w >> 20) & 15;
+    const int zr0 = (int)(((unsigned)lane * (65536u / (unsigned)nwz + 1)) >> 16), zc = lane - zr0 * nwz;
+    const bool zactive = zr0 < rpiZ;
+    unsigned zm;                                          // bytes of word column wFirst + zc that lie inside the zone
+    {
+        const int wc = wFirst + zc;
         const int lo = max(zx0 - 4 * wc, 0), hi = min(zx1 - 4 * wc, 4);
-        zmask[lane] = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
+        zm = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
+        if (!zactive) zm = 0;
     }
-    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)ct.w * G.slotCap;
+    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)(ct.w & 0xFFFF) * G.slotCap;
     const int scWords = ((ih + 2) * scp) >> 2;
     int total = 0;
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -227,34 +235,28 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         // ---- pre-filter
         const unsigned K = (unsigned)(127 - min(t, 127)) * 0x01010101u;     // byte > t  <=>  bit 7 of ((byte & 0x7f) + 127 - t) | byte
         int n = 0;
-        for (int i0 = 0; i0 < nitems; i0 += 32) {
-            const int i = i0 + lane;
+        const uint32_t* w = tileW + (3 + zr0) * tpw + wFirst + zc;
+        int e = ((3 + zr0) << 8) | ((wFirst + zc) << 2);
+        for (int row0 = zr0; row0 - zr0 < ih; row0 += rpiZ, w += rpiZ * tpw, e += rpiZ << 8) {
             unsigned comb = 0;
-            int row = 0, wc = 0;
-            if (i < nitems) {
-                const int r = (int)(((unsigned)i * invz) >> 16);
-                const int zc = i - r * nwz;
-                wc = wFirst + zc;
-                row = r + 3;
-                const uint32_t* w = tileW + row * tpw + wc;
+            if (zactive && row0 < ih) {
                 const unsigned C = w[0], Lw = w[-1], Rw = w[1], U = w[-3 * tpw], D = w[3 * tpw];
                 const unsigned P12 = __funnelshift_r(Lw, C, 8), P4 = __funnelshift_r(C, Rw, 24);
                 const unsigned a0 = __vabsdiffu4(D, C), a8 = __vabsdiffu4(U, C), a4 = __vabsdiffu4(P4, C), a12 = __vabsdiffu4(P12, C);
                 const unsigned g0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, g8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
                 const unsigned g4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, g12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
-                comb = (g0 | g8) & (g4 | g12) & 0x80808080u;
-                comb &= zmask[zc];                       // bytes of this word outside the zone
+                comb = (g0 | g8) & (g4 | g12) & 0x80808080u & zm;
             }
             if (__ballot_sync(FULL, comb != 0) == 0) continue;
-            const unsigned b0 = __ballot_sync(FULL, comb & 0x80u), b1 = __ballot_sync(FULL, comb & 0x8000u);
-            const unsigned b2 = __ballot_sync(FULL, comb & 0x800000u), b3 = __ballot_sync(FULL, comb & 0x80000000u);
-            int pos = n + __popc(b0 & ltmask) + __popc(b1 & ltmask) + __popc(b2 & ltmask) + __popc(b3 & ltmask);
-            const int e = (row << 8) | (wc << 2);
+            // ordered append: cnt = surviving bytes of this lane (0..4); exclusive prefix over the lanes from three ballots
+            const unsigned cnt = (((comb >> 7) & 0x01010101u) * 0x01010101u) >> 24;
+            const unsigned B0 = __ballot_sync(FULL, cnt & 1u), B1 = __ballot_sync(FULL, cnt & 2u), B2 = __ballot_sync(FULL, cnt & 4u);
+            int pos = n + __popc(B0 & ltmask) + 2 * __popc(B1 & ltmask) + 4 * __popc(B2 & ltmask);
+            n = __shfl_sync(FULL, pos + (int)cnt, 31);
             if (comb & 0x80u) list[pos++] = (uint16_t)e;
             if (comb & 0x8000u) list[pos++] = (uint16_t)(e + 1);
             if (comb & 0x800000u) list[pos++] = (uint16_t)(e + 2);
             if (comb & 0x80000000u) list[pos++] = (uint16_t)(e + 3);
-            n += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
         }
         __syncwarp();
         // ---- exact score of the survivors

@@ -303,7 +303,10 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
                     r.x = (unsigned)iniX | ((unsigned)iniY << 16);
                     r.y = skip ? 0u : ((unsigned)tw | ((unsigned)th << 16));
                     r.z = (unsigned)l | ((unsigned)(j * G.wCell) << 4) | ((unsigned)(i * G.hCell) << 16);
-                    r.w = (unsigned)(i * G.nCols + j);
+                    // rows per warp iteration of the staging loop (32 / tile words per row) and of the pre-filter (32 / zone words per row)
+                    const int ax = iniX & ~3, tpw = (maxX - ax + 3) >> 2;
+                    const int zx0 = iniX - ax + 3, zx1 = zx0 + tw - 6, nwz = skip ? 1 : ((zx1 - 1) >> 2) - (zx0 >> 2) + 1;
+                    r.w = (unsigned)(i * G.nCols + j) | ((unsigned)std::min(std::max(32 / std::max(tpw, 1), 1), 15) << 16) | ((unsigned)std::min(std::max(32 / nwz, 1), 15) << 20);
                     tab[G.cellBase + i * G.nCols + j] = r;
                 }
         }
