@@ -337,8 +337,15 @@ def run_ours(args):
     top_bytes = alg[top] if alg[top] > 0 else alg["fast_cells"]
     achieved = top_bytes * B / (acc[top] / 1e3) / 1e9
     pipeline_gbs = B_ALG * value / world / 1e9
+    traffic, traffic_src = None, None
+    try:      # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same shape), scaled to B frames
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01e_traffic.json")))
+        per_frame = sum(tr["dram_bytes_per_frame"][k] for k in top.split("+"))
+        traffic, traffic_src = per_frame * B, tr["source"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": top_bytes * B,
                 "stage_ms": acc, "stage_alg_bytes_per_frame": alg,
                 "pipeline": {"alg_bytes_per_frame": B_ALG, "achieved": pipeline_gbs, "frac": pipeline_gbs / peak,
