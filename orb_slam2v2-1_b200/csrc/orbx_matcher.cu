@@ -20,6 +20,30 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// Brute-force variant: POPC issues at 16 lanes/clk/SM against 64 for LOP3 (tools/int_pipe_bench.cu), so eight POPCs per pair
+// bind the scan.  Two carry-save adders (sum = a^b^c, carry = majority, one LOP3 each) fold six of the eight xor words into
+// two "ones" and two "twos" words: 6 POPCs + 4 LOP3s give the same integer, and the POPC and ALU pipes end up balanced.
+__device__ __forceinline__ unsigned lop3_xor3(unsigned a, unsigned b, unsigned c)
+{
+    unsigned d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ unsigned lop3_maj(unsigned a, unsigned b, unsigned c)
+{
+    unsigned d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int hamming256_csa(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
+    const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
+    const unsigned s1 = lop3_xor3(x0, x1, x2), c1 = lop3_maj(x0, x1, x2);
+    const unsigned s2 = lop3_xor3(x3, x4, x5), c2 = lop3_maj(x3, x4, x5);
+    return (__popc(s1) + __popc(s2) + __popc(x6) + __popc(x7)) + 2 * (__popc(c1) + __popc(c2));
+}
+
 // a distance of 256 never passes "dist < 256" in the reference scan: map it to the empty key
 __device__ __forceinline__ uint32_t make_key(int d, uint32_t pos) { return d > 255 ? KEY_NONE : ((uint32_t)d << KEY_SHIFT) | pos; }
 
@@ -65,8 +89,9 @@ __global__ void __launch_bounds__(BF_THREADS) k_bf_partial(const uint4* __restri
         __syncthreads();
 #pragma unroll 4
         for (int j = 0; j < cnt; j++) {
-            const int d = hamming256(qa, qb, st[2 * j], st[2 * j + 1]);
-            top2_push(m1, m2, make_key(d, (uint32_t)(base + j)));
+            // distance 256 (complementary rows) yields the key 256 << 22 | pos: above every real key, folded to "none" in the merge
+            const int d = hamming256_csa(qa, qb, st[2 * j], st[2 * j + 1]);
+            top2_push(m1, m2, ((uint32_t)d << KEY_SHIFT) + (uint32_t)(base + j));
         }
     }
     if (qi < nq) partial[(size_t)blockIdx.y * nq + qi] = make_uint2(m1, m2);
@@ -83,6 +108,8 @@ __global__ void k_bf_merge(const uint2* __restrict__ partial, int nq, int nseg, 
         const uint2 p = partial[(size_t)s * nq + qi];
         top2_merge(m1, m2, p.x, p.y);
     }
+    if ((m1 >> KEY_SHIFT) >= 256u) m1 = KEY_NONE;        // "dist < 256" never held (ORBmatcher.cc:217)
+    if ((m2 >> KEY_SHIFT) >= 256u) m2 = KEY_NONE;
     const int b = (int)(m1 >> KEY_SHIFT), sd = (int)(m2 >> KEY_SHIFT);
     best_idx[qi] = m1 == KEY_NONE ? -1 : (int)(m1 & KEY_POS_MASK);
     best_dist[qi] = b;
