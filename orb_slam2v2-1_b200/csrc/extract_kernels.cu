@@ -812,6 +812,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 }
 
 constexpr int DESC_WARPS = 8;
+constexpr int DESC_PATCH_ROWS = 37, DESC_PATCH_WPITCH = 12;      // blurred footprint in shared memory: 37 rows x 12 words (11 used)
 
 // cvRound without the (quarter-rate) F2I: adding 1.5 * 2^23 rounds to nearest-even in the FADD itself and leaves the
 // integer in the low mantissa bits; exact for |v| < 2^22.
@@ -840,6 +841,26 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     const LevelGeom& G = P.lv[l];
     const uint32_t key = F.levelKeys[(size_t)f * P.totalNodes + G.nodeBase + idx];
     const int cx = key_x(key) + MIN_BORDER, cy = key_y(key) + MIN_BORDER;      // level coordinates (:841-842)
+
+    // The 37 x 37 footprint of the descriptor (rotated pattern reach <= 18) on the BLURRED level goes to shared memory as
+    // 11 aligned words per row, copied by LDGSTS while the orientation is computed: the 512 test bytes are then shared-memory
+    // reads instead of scattered global byte loads (which had the kernel bound by L1 wavefronts).
+    __shared__ uint32_t s_patch[DESC_WARPS][DESC_PATCH_ROWS * DESC_PATCH_WPITCH];
+    const int bp = G.pitch;
+    const int px0 = cx - 18, pal = px0 & 3;
+    {
+        const uint8_t* src = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)(unsigned)((cy - 18) * bp + (px0 - pal));
+        const unsigned sbase = (unsigned)__cvta_generic_to_shared(&s_patch[threadIdx.x >> 5][0]);
+#pragma unroll
+        for (int k = 0; k < 13; k++) {
+            const int i = lane + 32 * k;
+            if (k < 12 || i < DESC_PATCH_ROWS * 11) {
+                const int row = (i * 373) >> 12, word = i - 11 * row;          // i / 11 for i < 416
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + 4u * (unsigned)(row * DESC_PATCH_WPITCH + word)),
+                             "l"(src + (size_t)(unsigned)(row * bp + 4 * word)));
+            }
+        }
+    }
 
     // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level.  The 31 x 31 patch is read as aligned
     // 32-bit words (9 per row whatever the alignment of cx - 15): 279 (row, word) items spread over the 32 lanes, and every
@@ -874,10 +895,13 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
     float a, b;
     orbx_sc::sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);       // a = cos, b = sin (:112-113)
-    const int bp = G.pitch;
-    // centre pointer with the column rounding bias folded in: index = (rbits - MAGIC) * bp + cbits, pointer - MAGIC
-    const uint8_t* ctr = F.blur + (size_t)f * P.blurSlab + G.blurOff + (unsigned)(cy * bp + cx);
-    const uint8_t* ctrb = ctr - (long long)MAGIC_BITS;
+    // shared-space byte address of the patch centre with both rounding biases folded in (32-bit arithmetic, wraps):
+    // address = centre + (rbits - MAGIC) * pitch + (cbits - MAGIC)
+    constexpr unsigned PB = DESC_PATCH_WPITCH * 4;
+    const unsigned ctrb = (unsigned)__cvta_generic_to_shared(&s_patch[threadIdx.x >> 5][0]) + 18u * PB + 18u + (unsigned)pal -
+                          (unsigned)MAGIC_BITS * (PB + 1u);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
     unsigned val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; bit++) {
@@ -894,7 +918,9 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
             r1 = round_magic_bits(__fadd_rn(__fmul_rn(pt.z, b), __fmul_rn(pt.w, a)));
             c1 = round_magic_bits(__fsub_rn(__fmul_rn(pt.z, a), __fmul_rn(pt.w, b)));
         }
-        const int t0 = __ldg(ctrb + ((r0 - MAGIC_BITS) * bp + c0)), t1 = __ldg(ctrb + ((r1 - MAGIC_BITS) * bp + c1));
+        unsigned t0, t1;
+        asm("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(ctrb + (unsigned)r0 * PB + (unsigned)c0));
+        asm("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(ctrb + (unsigned)r1 * PB + (unsigned)c1));
         val |= (unsigned)(t0 < t1) << bit;
     }
     const size_t o = (size_t)f * P.totalNodes + g;
