@@ -319,7 +319,8 @@ constexpr int OCT_KEYS_SMEM = 4096;    // candidates of a level kept in shared m
 // in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
 __device__ int block_exclusive_scan(int* a, int n, int* wsum)
 {
-    const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    constexpr int T = OCT_THREADS;      // compile-time: the per-thread chunk is a shift, not an integer division
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + T - 1) / T;
     const int b = min(tid * per, n), e = min(b + per, n);
     int s = 0;
@@ -413,8 +414,8 @@ __global__ void __launch_bounds__(OCT_THREADS, 4) k_octree(const Plan P, const F
         const uint32_t* src = slots + (size_t)c * G.slotCap;
         for (int e = lane; e < cnt; e += 32) {
             const uint32_t key = src[e];
-            int root = (int)__fdiv_rn((float)key_x(key), G.hX);      // vpIniNodes[kp.pt.x/hX] (:569)
-            root = min(root, nIni - 1);
+            int root = 0;                                             // vpIniNodes[kp.pt.x/hX] (:569); one root: no division
+            if (nIni > 1) root = min((int)__fdiv_rn((float)key_x(key), G.hX), nIni - 1);
             keys[off + e] = key;
             knode[off + e] = (uint16_t)root;
             atomicAdd(&rootCnt[root], 1);
