@@ -113,6 +113,11 @@ int orbx_pyramid_level(orbx_extractor* ex, int frame, int level, int border, uin
 /* Zero-copy device view of the same interior (for the device stereo matcher). */
 int orbx_pyramid_device(orbx_extractor* ex, int frame, int level, const uint8_t** d_ptr, size_t* pitch);
 
+/* Layout of that device pyramid for the whole batch: plane of (frame, level) = *d_base + frame * *frame_stride. */
+int orbx_pyramid_layout(orbx_extractor* ex, int level, const uint8_t** d_base, size_t* pitch, size_t* frame_stride);
+/* Frames processed by the last extract call on this handle (0 = none yet). */
+int orbx_last_batch(const orbx_extractor* ex);
+
 /* Stage dumps of the last call (parity tests only): blurred level (w x h) and the FAST candidates handed to
  * DistributeOctTree in reference order as (x, y, response) int triples relative to minBorder = 16. */
 int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* dst, size_t dst_stride);
@@ -224,6 +229,14 @@ int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_extractor* r
                         const orbx_kp* kl, const uint8_t* dl, int nl,
                         const orbx_kp* kr, const uint8_t* dr, int nr,
                         float bf, float minD, float maxD, float* uRight, float* depth, int* nmatched);
+
+/* The same association for every stereo pair of a batch, device-resident end to end: pair b = frame b of the LAST extract
+ * call on `left` and on `right` (equal batch sizes and shapes).  Keypoints and descriptors are read from the handles'
+ * device results, the pyramids in place; candidate search, SAD refinement and the median cut all run on the device.
+ * uRight/depth: HOST arrays of B * cap floats (pair b at offset b * cap, -1 = no match), cap >= the largest left keypoint
+ * count; nmatched: B ints. */
+int orbm_stereo_matches_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float bf, float minD, float maxD,
+                              float* uRight, float* depth, int cap, int* nmatched);
 
 /* Text of the last error raised on the calling thread ("" if none). */
 const char* orbx_last_error(void);

@@ -646,44 +646,12 @@ struct StereoView {
     float sf[MAX_LEVELS], isf[MAX_LEVELS];
 };
 
-// One warp per left keypoint: row-band Hamming search (Frame.cc:521-563), then the 11-shift 11x11 SAD on the unblurred
-// pyramid level of the left keypoint (:566-607) and the parabola fit (:609-637).  SADs are integers (centre-subtracted
-// u8 patches), so lanes can sum them in any order; the float tail runs on individually rounded operations.
-__global__ void __launch_bounds__(256) k_stereo(const orbx_kp* __restrict__ kl, const uint4* __restrict__ dl, int nl,
-                                                const orbx_kp* __restrict__ kr, const uint4* __restrict__ dr,
-                                                const int* __restrict__ rowStart, const int* __restrict__ rowEntries, int nRows,
-                                                StereoView V, float bf, float minD, float maxD,
-                                                float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ bestSad)
+// Sub-pixel refinement of one left keypoint against its best right candidate (Frame.cc:566-637): 11-shift 11x11 SAD on the
+// unblurred level of the left keypoint, parabola fit, disparity test.  Whole warp; lane 0 writes the three outputs
+// (pre-initialised to -1 by the caller).
+__device__ __forceinline__ void stereo_refine(int lane, const orbx_kp& kpL, int levelL, float uL, float uR0, const StereoView& V,
+                                              float bf, float minD, float maxD, float* uRightOut, float* depthOut, int* sadOut)
 {
-    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (iL >= nl) return;
-    if (lane == 0) { uRight[iL] = -1.0f; depth[iL] = -1.0f; bestSad[iL] = -1; }
-    const orbx_kp kpL = kl[iL];
-    const int levelL = kpL.octave;
-    const float vL = kpL.y, uL = kpL.x;
-    const int row = (int)vL;                                   // vRowIndices[vL]
-    if (row < 0 || row >= nRows) return;
-    const int s = rowStart[row], e = rowStart[row + 1];
-    if (s == e) return;
-    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
-    if (maxU < 0) return;
-    const uint4 qa = __ldg(&dl[2 * iL]), qb = __ldg(&dl[2 * iL + 1]);
-    uint32_t best = KEY_NONE;
-    for (int c = s + lane; c < e; c += 32) {
-        const int iR = rowEntries[c];
-        const orbx_kp kpR = kr[iR];
-        if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
-        if (kpR.x >= minU && kpR.x <= maxU) {
-            const int d = hamming256(qa, qb, __ldg(&dr[2 * (size_t)iR]), __ldg(&dr[2 * (size_t)iR + 1]));
-            if (d < TH_HIGH) best = min(best, ((uint32_t)d << KEY_SHIFT) | (uint32_t)(c - s));     // strict <, first in list order
-        }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
-    if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
-    const int bestIdxR = rowEntries[s + (int)(best & KEY_POS_MASK)];
-
-    const float uR0 = kr[bestIdxR].x;
     const float scaleFactor = V.isf[levelL];
     const float scaleduL = roundf(__fmul_rn(kpL.x, scaleFactor));
     const float scaledvL = roundf(__fmul_rn(kpL.y, scaleFactor));
@@ -731,10 +699,50 @@ __global__ void __launch_bounds__(256) k_stereo(const orbx_kp* __restrict__ kl, 
             disparity = 0.01f;
             bestuR = (float)((double)uL - 0.01);                // `bestuR = uL-0.01;` is a double subtraction
         }
-        depth[iL] = __fdiv_rn(bf, disparity);
-        uRight[iL] = bestuR;
-        bestSad[iL] = bestDist;
+        *depthOut = __fdiv_rn(bf, disparity);
+        *uRightOut = bestuR;
+        *sadOut = bestDist;
     }
+}
+
+// One warp per left keypoint: row-band Hamming search (Frame.cc:521-563), then the 11-shift 11x11 SAD on the unblurred
+// pyramid level of the left keypoint (:566-607) and the parabola fit (:609-637).  SADs are integers (centre-subtracted
+// u8 patches), so lanes can sum them in any order; the float tail runs on individually rounded operations.
+__global__ void __launch_bounds__(256) k_stereo(const orbx_kp* __restrict__ kl, const uint4* __restrict__ dl, int nl,
+                                                const orbx_kp* __restrict__ kr, const uint4* __restrict__ dr,
+                                                const int* __restrict__ rowStart, const int* __restrict__ rowEntries, int nRows,
+                                                StereoView V, float bf, float minD, float maxD,
+                                                float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ bestSad)
+{
+    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (iL >= nl) return;
+    if (lane == 0) { uRight[iL] = -1.0f; depth[iL] = -1.0f; bestSad[iL] = -1; }
+    const orbx_kp kpL = kl[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;                                   // vRowIndices[vL]
+    if (row < 0 || row >= nRows) return;
+    const int s = rowStart[row], e = rowStart[row + 1];
+    if (s == e) return;
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (maxU < 0) return;
+    const uint4 qa = __ldg(&dl[2 * iL]), qb = __ldg(&dl[2 * iL + 1]);
+    uint32_t best = KEY_NONE;
+    for (int c = s + lane; c < e; c += 32) {
+        const int iR = rowEntries[c];
+        const orbx_kp kpR = kr[iR];
+        if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+        if (kpR.x >= minU && kpR.x <= maxU) {
+            const int d = hamming256(qa, qb, __ldg(&dr[2 * (size_t)iR]), __ldg(&dr[2 * (size_t)iR + 1]));
+            if (d < TH_HIGH) best = min(best, ((uint32_t)d << KEY_SHIFT) | (uint32_t)(c - s));     // strict <, first in list order
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+    if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
+    const int bestIdxR = rowEntries[s + (int)(best & KEY_POS_MASK)];
+
+    stereo_refine(lane, kpL, levelL, uL, kr[bestIdxR].x, V, bf, minD, maxD, uRight + iL, depth + iL, bestSad + iL);
 }
 
 }  // namespace orbx
@@ -833,5 +841,179 @@ extern "C" int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_e
         kept--;
     }
     if (nmatched) *nmatched = kept;
+    return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ batched stereo
+namespace orbx {
+
+struct StereoBatchView {
+    const uint8_t* L[MAX_LEVELS];
+    const uint8_t* R[MAX_LEVELS];
+    int pitchL[MAX_LEVELS], pitchR[MAX_LEVELS], colsR[MAX_LEVELS];
+    unsigned long long frameL[MAX_LEVELS], frameR[MAX_LEVELS];
+    float sf[MAX_LEVELS], isf[MAX_LEVELS];
+    int nRows, nlev;
+};
+
+// right keypoints as (row band, octave, x): rows floor(y - r) .. ceil(y + r), r = 2 * scale[octave] (Frame.cc:490-508)
+__global__ void k_stereo_prep(const orbx_kp* __restrict__ kr, const int* __restrict__ cntR, int stride, StereoBatchView V, int4* __restrict__ tab)
+{
+    const int f = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cntR[f]) return;
+    const orbx_kp k = kr[(size_t)f * stride + i];
+    const int o = min(max(k.octave, 0), V.nlev - 1);
+    const float r = __fmul_rn(2.0f, V.sf[o]);
+    const int maxr = min((int)ceilf(__fadd_rn(k.y, r)), V.nRows - 1), minr = max((int)floorf(__fsub_rn(k.y, r)), 0);
+    tab[(size_t)f * stride + i] = make_int4(minr, maxr, k.octave, __float_as_int(k.x));
+}
+
+// One warp per (pair, left keypoint).  Candidates = right keypoints whose row band contains the left row, visited in
+// index order like vRowIndices (Frame.cc:521-563); the refinement is stereo_refine.
+__global__ void __launch_bounds__(256) k_stereo_batch(const orbx_kp* __restrict__ kl, const uint4* __restrict__ dl, const int* __restrict__ cntL,
+                                                      int strideL, const orbx_kp* __restrict__ kr, const uint4* __restrict__ dr,
+                                                      const int* __restrict__ cntR, int strideR, const int4* __restrict__ tab,
+                                                      StereoBatchView VB, float bf, float minD, float maxD, int cap,
+                                                      float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ bestSad)
+{
+    const int f = blockIdx.y, iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int nl = cntL[f], nr = cntR[f];
+    if (iL >= nl || iL >= cap) return;
+    const size_t oo = (size_t)f * cap + iL;
+    if (lane == 0) { uRight[oo] = -1.0f; depth[oo] = -1.0f; bestSad[oo] = -1; }
+    const orbx_kp kpL = kl[(size_t)f * strideL + iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;
+    if (row < 0 || row >= VB.nRows) return;
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (maxU < 0) return;
+    const uint4* dlf = dl + 2 * ((size_t)f * strideL + iL);
+    const uint4 qa = __ldg(dlf), qb = __ldg(dlf + 1);
+    const int4* tf = tab + (size_t)f * strideR;
+    const uint4* drf = dr + 2 * (size_t)f * strideR;
+    uint32_t best = KEY_NONE;
+    for (int c = lane; c < nr; c += 32) {
+        const int4 t = __ldg(&tf[c]);
+        if (row < t.x || row > t.y) continue;
+        if (t.z < levelL - 1 || t.z > levelL + 1) continue;
+        const float x = __int_as_float(t.w);
+        if (x >= minU && x <= maxU) {
+            const int d = hamming256(qa, qb, __ldg(&drf[2 * (size_t)c]), __ldg(&drf[2 * (size_t)c + 1]));
+            if (d < TH_HIGH) best = min(best, ((uint32_t)d << KEY_SHIFT) | (uint32_t)c);       // strict <, first in index order
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+    if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
+    const int bestIdxR = (int)(best & KEY_POS_MASK);
+    if (levelL < 0 || levelL >= VB.nlev) return;
+    StereoView V;
+#pragma unroll
+    for (int l = 0; l < MAX_LEVELS; l++) { V.sf[l] = VB.sf[l]; V.isf[l] = VB.isf[l]; V.colsR[l] = VB.colsR[l]; V.pitchL[l] = VB.pitchL[l]; V.pitchR[l] = VB.pitchR[l]; V.L[l] = VB.L[l] + (size_t)f * VB.frameL[l]; V.R[l] = VB.R[l] + (size_t)f * VB.frameR[l]; }
+    stereo_refine(lane, kpL, levelL, uL, __int_as_float(__ldg(&tf[bestIdxR]).w), V, bf, minD, maxD, uRight + oo, depth + oo, bestSad + oo);
+}
+
+// Median cut (Frame.cc:641-654) of one pair per CTA: the reference sorts (SAD, index) pairs and takes the SAD at position
+// size / 2; that value is a rank selection, done here with two 8-bit histogram passes over the 16-bit SADs
+// (SAD <= 121 * 510).  Matches with (float)SAD >= 1.5f * 1.4f * median are removed.
+__global__ void __launch_bounds__(256) k_stereo_median(const int* __restrict__ cntL, int cap, const int* __restrict__ bestSad,
+                                                       float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ nmatched)
+{
+    __shared__ int hist[256];
+    __shared__ int s_bin, s_rank, s_total;
+    const int f = blockIdx.x, tid = threadIdx.x, nl = min(cntL[f], cap);
+    const int* sad = bestSad + (size_t)f * cap;
+    hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < nl; i += 256) if (sad[i] >= 0) atomicAdd(&hist[(sad[i] >> 8) & 255], 1);
+    __syncthreads();
+    if (tid == 0) {
+        int total = 0;
+        for (int b = 0; b < 256; b++) total += hist[b];
+        s_total = total;
+        int k = total / 2, b = 0;                       // vDistIdx[vDistIdx.size() / 2]
+        while (b < 255 && k >= hist[b]) { k -= hist[b]; b++; }
+        s_bin = b;
+        s_rank = k;
+    }
+    __syncthreads();
+    const int total = s_total, hb = s_bin, k = s_rank;
+    if (total == 0) { if (tid == 0) nmatched[f] = 0; return; }     // the reference reads vDistIdx[0] of an empty vector here: guarded
+    __syncthreads();
+    hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < nl; i += 256) if (sad[i] >= 0 && ((sad[i] >> 8) & 255) == hb) atomicAdd(&hist[sad[i] & 255], 1);
+    __syncthreads();
+    if (tid == 0) {
+        int kk = k, b = 0;
+        while (b < 255 && kk >= hist[b]) { kk -= hist[b]; b++; }
+        s_bin = (hb << 8) | b;
+        s_total = 0;
+    }
+    __syncthreads();
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_bin);
+    int kept = 0;
+    for (int i = tid; i < nl; i += 256) {
+        if (sad[i] < 0) continue;
+        if ((float)sad[i] < thDist) kept++;
+        else { uRight[(size_t)f * cap + i] = -1.0f; depth[(size_t)f * cap + i] = -1.0f; }
+    }
+    atomicAdd(&s_total, kept);
+    __syncthreads();
+    if (tid == 0) nmatched[f] = s_total;
+}
+
+}  // namespace orbx
+
+extern "C" int orbm_stereo_matches_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float bf, float minD, float maxD,
+                                         float* uRight, float* depth, int cap, int* nmatched)
+{
+    if (!m || !left || !right || !uRight || !depth || cap < 1) { set_error("orbm_stereo_matches_batch: bad argument"); return ORBX_ERR_ARG; }
+    const int B = orbx_last_batch(left);
+    if (B < 1 || orbx_last_batch(right) != B) { set_error("orbm_stereo_matches_batch: the two handles must hold results of equal batch size"); return ORBX_ERR_STATE; }
+    const int nlev = orbx_levels(left);
+    if (nlev != orbx_levels(right) || nlev > MAX_LEVELS) { set_error("orbm_stereo_matches_batch: extractors differ"); return ORBX_ERR_ARG; }
+    int rc = orbx_sync(left);
+    if (rc) return rc;
+    if ((rc = orbx_sync(right))) return rc;
+    StereoBatchView V;
+    memset(&V, 0, sizeof V);
+    V.nlev = nlev;
+    if ((rc = orbx_scale_tables(left, V.sf, V.isf, nullptr, nullptr))) return rc;
+    for (int l = 0; l < nlev; l++) {
+        size_t pl = 0, pr = 0, fl = 0, fr = 0;
+        int wl, hl, wr, hr;
+        if ((rc = orbx_pyramid_layout(left, l, &V.L[l], &pl, &fl)) || (rc = orbx_pyramid_layout(right, l, &V.R[l], &pr, &fr)) ||
+            (rc = orbx_level_size(left, l, &wl, &hl)) || (rc = orbx_level_size(right, l, &wr, &hr)))
+            return rc;
+        if (wl != wr || hl != hr) { set_error("orbm_stereo_matches_batch: left/right pyramids differ in size"); return ORBX_ERR_ARG; }
+        V.pitchL[l] = (int)pl; V.pitchR[l] = (int)pr; V.frameL[l] = fl; V.frameR[l] = fr; V.colsR[l] = wr;
+        if (l == 0) V.nRows = hl;
+    }
+    const orbx_kp *dkl, *dkr;
+    const uint8_t *ddl, *ddr;
+    const int *dcl, *dcr;
+    int sl = 0, sr = 0;
+    if ((rc = orbx_results_device(left, &dkl, &ddl, &dcl, &sl)) || (rc = orbx_results_device(right, &dkr, &ddr, &dcr, &sr))) return rc;
+    ORBX_CUDA(cudaSetDevice(m->device));
+    Carver cv(m->arena);
+    const size_t oT = cv.take(sizeof(int4) * (size_t)B * sr), oU = cv.take(sizeof(float) * (size_t)B * cap), oD = cv.take(sizeof(float) * (size_t)B * cap),
+                 oS = cv.take(sizeof(int) * (size_t)B * cap), oN = cv.take(sizeof(int) * (size_t)B);
+    if ((rc = m->arena.reserve(cv.total()))) return rc;
+    uint8_t* A = m->arena.base;
+    cudaStream_t s = m->stream;
+    k_stereo_prep<<<dim3((sr + 255) / 256, B), 256, 0, s>>>(dkr, dcr, sr, V, (int4*)(A + oT));
+    // left keypoints beyond cap would be dropped: cap must cover the per-frame keypoint stride of the handle
+    const int nlMax = std::min(sl, cap);
+    k_stereo_batch<<<dim3((nlMax + 7) / 8, B), 256, 0, s>>>(dkl, (const uint4*)ddl, dcl, sl, dkr, (const uint4*)ddr, dcr, sr, (const int4*)(A + oT), V,
+                                                          bf, minD, maxD, cap, (float*)(A + oU), (float*)(A + oD), (int*)(A + oS));
+    k_stereo_median<<<B, 256, 0, s>>>(dcl, cap, (const int*)(A + oS), (float*)(A + oU), (float*)(A + oD), (int*)(A + oN));
+    ORBX_CUDA(cudaGetLastError());
+    m->lastLaunches = 3;
+    ORBX_CUDA(cudaMemcpyAsync(uRight, A + oU, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(depth, A + oD, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
+    if (nmatched) ORBX_CUDA(cudaMemcpyAsync(nmatched, A + oN, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
     return ORBX_OK;
 }

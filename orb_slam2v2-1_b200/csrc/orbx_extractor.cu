@@ -699,6 +699,17 @@ static int plane_of(orbx_extractor* ex, int frame, int level, const uint8_t** p,
     return ORBX_OK;
 }
 
+int orbx_last_batch(const orbx_extractor* ex) { return ex ? ex->lastB : 0; }
+
+int orbx_pyramid_layout(orbx_extractor* ex, int level, const uint8_t** d_base, size_t* pitch, size_t* frame_stride)
+{
+    if (!d_base || !pitch || !frame_stride) { set_error("null argument"); return ORBX_ERR_ARG; }
+    int rc = plane_of(ex, 0, level, d_base, pitch);
+    if (rc) return rc;
+    *frame_stride = level == 0 ? (size_t)ex->bufs.lv0Frame : (size_t)ex->plan.pyrSlab;
+    return ORBX_OK;
+}
+
 int orbx_pyramid_device(orbx_extractor* ex, int frame, int level, const uint8_t** d_ptr, size_t* pitch)
 {
     if (!d_ptr || !pitch) { set_error("null argument"); return ORBX_ERR_ARG; }

@@ -77,6 +77,9 @@ def lib():
         "orbm_grid_candidates": (i, [vp, vp, i, f, f, f, f, vp, i, vp, i, i, vp, vp, vp, i]),
         "orbm_search_for_initialization": (i, [vp, vp, vp, i, vp, vp, i, f, f, f, f, vp, vp, i, f, i, vp]),
         "orbm_stereo_matches": (i, [vp, vp, vp, i, vp, vp, i, vp, vp, i, f, f, f, vp, vp, vp]),
+        "orbm_stereo_matches_batch": (i, [vp, vp, vp, f, f, f, vp, vp, i, vp]),
+        "orbx_pyramid_layout": (i, [vp, i, vp, vp, vp]),
+        "orbx_last_batch": (i, [vp]),
         "orbm_search_by_projection": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp]),
         "orbm_search_by_projection_frame": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp, vp]),
         "orbm_search_by_bow": (i, [vp, i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp, vp]),
@@ -447,6 +450,21 @@ class ORBmatcher:
         _check(self._L.orbm_stereo_matches(self._h, left._h, right._h, frame, _p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr),
                                            bf, minD, maxD, _p(uR), _p(dep), C.byref(nm)))
         return nm.value, uR, dep
+
+
+def _stereo_batch(self, left, right, bf, maxD, minD=0.0):
+    """Frame::ComputeStereoMatches for every pair of the last batch on two extractor handles, device-resident.
+    Returns (nmatched[B], uRight[B, cap], depth[B, cap]); entries beyond a pair's left keypoint count are undefined."""
+    B = left.last_batch
+    cap = max(left.max_keypoints(), 64)
+    uR = np.zeros((B, cap), np.float32)
+    dep = np.zeros((B, cap), np.float32)
+    nm = np.zeros(B, np.int32)
+    _check(self._L.orbm_stereo_matches_batch(self._h, left._h, right._h, bf, minD, maxD, _p(uR), _p(dep), cap, _p(nm)))
+    return nm, uR, dep
+
+
+ORBmatcher.ComputeStereoMatchesBatch = _stereo_batch
 
 
 def version():

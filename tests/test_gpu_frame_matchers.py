@@ -94,3 +94,23 @@ def test_stereo_no_right_keypoints(m):
     exL, exR, kl, dl, kr, dr = _extract_pair(752, 480, 1200, 2002)
     n, uR, dep = m.ComputeStereoMatches(exL, exR, kl, dl, kr[:0], dr[:0], 47.9, 435.2)
     assert n == 0 and (uR == -1).all() and (dep == -1).all()
+
+
+@pytest.mark.parametrize("w,h,nf,fx,bf,seed0", [(752, 480, 1200, 435.2, 47.9, 2000), (1241, 376, 2000, 718.856, 386.1448, 3000)])
+def test_stereo_matches_batch_device_resident(m, w, h, nf, fx, bf, seed0):
+    """orbm_stereo_matches_batch: every pair of a batch, keypoints and pyramids taken from the handles' device results."""
+    B = 3
+    pairs = [synth.stereo_rects(w, h, seed0 + i) for i in range(B)]
+    exL, exR = orbx.ORBextractor(nf, 1.2, 8, 20, 7, max_batch=B), orbx.ORBextractor(nf, 1.2, 8, 20, 7, max_batch=B)
+    resL = exL.extract_batch([p[0] for p in pairs])
+    resR = exR.extract_batch([p[1] for p in pairs])
+    nm, uR, dep = m.ComputeStereoMatchesBatch(exL, exR, bf, fx)
+    for b in range(B):
+        kl, dl = resL[b]
+        kr, dr = resR[b]
+        pyrL = [exL.pyramid_level(l, b) for l in range(8)]
+        pyrR = [exR.pyramid_level(l, b) for l in range(8)]
+        on, ouR, odep = O.stereo_matches(kl, dl, kr, dr, pyrL, pyrR, exL.GetScaleFactors(), exL.GetInverseScaleFactors(), bf, fx)
+        assert nm[b] == on, b
+        assert uR[b, :len(kl)].tobytes() == ouR.tobytes() and dep[b, :len(kl)].tobytes() == odep.tobytes(), b
+        assert on > len(kl) // 10
