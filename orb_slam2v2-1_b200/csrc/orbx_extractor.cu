@@ -578,19 +578,32 @@ int orbx_extract_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w,
 }
 
 // copies the packed output block (counts | kps | desc) of the last call to the pinned buffer and unpacks it
+static bool is_pinned_host(const void* p)
+{
+    cudaPointerAttributes attr;
+    const bool ok = p && cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return ok;
+}
+
 static int fetch_impl(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, int* n)
 {
     const int B = ex->lastB;
     const Plan& P = ex->plan;
-    const size_t capB = ex->capB;
     uint8_t* base = (uint8_t*)ex->bufs.counts;
     const size_t kOff = (uint8_t*)ex->bufs.kps - base, dOff = ex->bufs.desc - base;
-    // counts of all frames are contiguous; kps/desc only for the first B frames
+    // Fast path: the caller's arrays are page-locked and laid out like the device results (cap == per-frame stride):
+    // the keypoints and descriptors go straight into them, with no staging buffer and no host-side unpacking.
+    const bool direct = kps && desc && cap == P.totalNodes && is_pinned_host(kps) && is_pinned_host(desc);
     ORBX_CUDA(cudaMemcpyAsync(ex->h_out, base, sizeof(int) * B, cudaMemcpyDeviceToHost, ex->stream));
-    ORBX_CUDA(cudaMemcpyAsync(ex->h_out + kOff, base + kOff, sizeof(orbx_kp) * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
-    ORBX_CUDA(cudaMemcpyAsync(ex->h_out + dOff, base + dOff, (size_t)32 * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
+    if (direct) {
+        ORBX_CUDA(cudaMemcpyAsync(kps, base + kOff, sizeof(orbx_kp) * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
+        ORBX_CUDA(cudaMemcpyAsync(desc, base + dOff, (size_t)32 * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
+    } else {
+        ORBX_CUDA(cudaMemcpyAsync(ex->h_out + kOff, base + kOff, sizeof(orbx_kp) * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
+        ORBX_CUDA(cudaMemcpyAsync(ex->h_out + dOff, base + dOff, (size_t)32 * P.totalNodes * B, cudaMemcpyDeviceToHost, ex->stream));
+    }
     ORBX_CUDA(cudaStreamSynchronize(ex->stream));
-    (void)capB;
     int rc = ORBX_OK;
     const int* hc = (const int*)ex->h_out;
     const orbx_kp* hk = (const orbx_kp*)(ex->h_out + kOff);
@@ -598,6 +611,7 @@ static int fetch_impl(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, 
     for (int b = 0; b < B; b++) {
         const int cnt = hc[b];
         if (n) n[b] = cnt;
+        if (direct) continue;
         int m = cnt;
         if (m > cap) { m = cap; rc = ORBX_ERR_CAPACITY; set_error("frame %d produced %d keypoints, capacity %d", b, cnt, cap); }
         if (kps && m > 0) memcpy(kps + (size_t)b * cap, hk + (size_t)b * P.totalNodes, sizeof(orbx_kp) * m);
