@@ -10,6 +10,7 @@
 
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 #include "orbx.h"
 #include "orbx_cv_shim.h"
@@ -196,6 +197,119 @@ public:
         return n;
     }
 
+    // ---- LocalMapping / LoopClosing / relocalisation searches.  ProjectedPoints carries, per MapPoint that passed the reference's
+    // skip tests, xy = projection (u, v), xr = u - bf * invz (Fuse only), level = nPredictedLevel, descriptors = GetDescriptor().
+
+    // Project MapPoints into a KeyFrame and search for duplicated MapPoints (ORBmatcher.cc:827-975).  vnBestIdx[i] = key-frame
+    // feature point i fuses into, -1 = none; the caller then applies :940-957 (Replace / AddObservation) to those features.
+    int Fuse(const FrameView& KF, const std::vector<float>& vuRight, const std::vector<float>& vScaleFactors,
+             const std::vector<float>& vInvLevelSigma2, const ProjectedPoints& P, std::vector<int>& vnBestIdx, const float th = 3.0)
+    {
+        return fuse(KF, &vuRight, vScaleFactors, &vInvLevelSigma2, P, vnBestIdx, th, 1);
+    }
+    // Project MapPoints into a KeyFrame using a given Sim3 and search for duplicated MapPoints (ORBmatcher.cc:977-1102).
+    int Fuse(const FrameView& KF, const std::vector<float>& vScaleFactors, const ProjectedPoints& P, std::vector<int>& vnBestIdx, const float th)
+    {
+        return fuse(KF, nullptr, vScaleFactors, nullptr, P, vnBestIdx, th, 0);
+    }
+
+    // Search matches between MapPoints seen in KF1 and KF2 transforming by a Sim3 [s12*R12|t12] (ORBmatcher.cc:1104-1328).
+    // P12: one entry PER FEATURE of key frame 1 (level < 0 where :1145-1173 skip the feature), projected into key frame 2; P21 likewise.
+    // vnMatches12[i1] = i2 where the two directions agree, -1 otherwise.
+    int SearchBySim3(const FrameView& KF1, const FrameView& KF2, const std::vector<float>& vScaleFactors, const ProjectedPoints& P12,
+                     const ProjectedPoints& P21, std::vector<int>& vnMatches12, const float th)
+    {
+        std::vector<orbx_kp> k1 = pack(*KF1.keys), k2 = pack(*KF2.keys);
+        vnMatches12.assign(k1.size(), -1);
+        int n = 0;
+        if (orbm_search_by_sim3(m_, k1.data(), KF1.descriptors->ptr<uint8_t>(0), (int)k1.size(), k2.data(), KF2.descriptors->ptr<uint8_t>(0),
+                                (int)k2.size(), KF2.minX, KF2.maxX, KF2.minY, KF2.maxY, vScaleFactors.data(), (int)vScaleFactors.size(),
+                                P12.xy.data(), P12.level.data(), P12.descriptors.data(), P21.xy.data(), P21.level.data(), P21.descriptors.data(),
+                                th, vnMatches12.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_sim3");
+        return n;
+    }
+
+    // Project MapPoints using a Similarity Transformation and search matches, used in loop detection (ORBmatcher.cc:290-403).
+    // vbMatched[j] = vpMatched[j] != NULL on entry; vnMatch[j] = point this call stores into vpMatched[j], -1 = untouched.
+    int SearchByProjection(const FrameView& KF, const std::vector<uint8_t>& vbMatched, const std::vector<float>& vScaleFactors,
+                           const ProjectedPoints& P, std::vector<int>& vnMatch, int th)
+    {
+        std::vector<orbx_kp> k = pack(*KF.keys);
+        vnMatch.assign(k.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection_sim3(m_, k.data(), KF.descriptors->ptr<uint8_t>(0), vbMatched.data(), (int)k.size(), KF.minX, KF.maxX, KF.minY,
+                                           KF.maxY, vScaleFactors.data(), (int)vScaleFactors.size(), P.xy.data(), P.level.data(),
+                                           P.descriptors.data(), (int)P.level.size(), (float)th, vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection_sim3");
+        return n;
+    }
+
+    // Project MapPoints seen in a KeyFrame into the Frame and search matches, used in relocalisation (ORBmatcher.cc:1474-1601).
+    // vbOccupied[j] = CurrentFrame.mvpMapPoints[j] != NULL; P.viewCosOrAngle = pKF->mvKeysUn[i].angle.
+    int SearchByProjection(const FrameView& CurrentFrame, const std::vector<uint8_t>& vbOccupied, const std::vector<float>& vScaleFactors,
+                           const ProjectedPoints& P, std::vector<int>& vnMatch, const float th, const int ORBdist)
+    {
+        std::vector<orbx_kp> k = pack(*CurrentFrame.keys);
+        vnMatch.assign(k.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection_kf(m_, k.data(), CurrentFrame.descriptors->ptr<uint8_t>(0), vbOccupied.data(), (int)k.size(), CurrentFrame.minX,
+                                         CurrentFrame.maxX, CurrentFrame.minY, CurrentFrame.maxY, vScaleFactors.data(), (int)vScaleFactors.size(),
+                                         P.xy.data(), P.level.data(), P.viewCosOrAngle.data(), P.descriptors.data(), (int)P.level.size(), th, ORBdist,
+                                         mbCheckOrientation, vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection_kf");
+        return n;
+    }
+
+    // What SearchForTriangulation reads from a KeyFrame besides FrameView.
+    struct KeyFrameState {
+        const std::vector<uint8_t>* hasMapPoint;    // pKF->GetMapPoint(idx) != NULL
+        const std::vector<float>* uRight;           // KeyFrame::mvuRight
+        const FeatureVectorCSR* featVec;            // KeyFrame::mFeatVec
+    };
+    // Matching to triangulate new MapPoints, checking the epipolar constraint (ORBmatcher.cc:657-825).  F12: 3x3 CV_32F;
+    // (ex, ey): the epipole in the second image (:667-672); vScaleFactors2 / vLevelSigma2_2 of pKF2.
+    int SearchForTriangulation(const FrameView& KF1, const KeyFrameState& S1, const FrameView& KF2, const KeyFrameState& S2, const cv::Mat& F12,
+                               float ex, float ey, const std::vector<float>& vScaleFactors2, const std::vector<float>& vLevelSigma2_2,
+                               std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo)
+    {
+        std::vector<orbx_kp> k1 = pack(*KF1.keys), k2 = pack(*KF2.keys);
+        std::vector<int> m12(k1.size(), -1);
+        float F[9];
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) F[3 * r + c] = F12.ptr<float>(r)[c];
+        int n = 0;
+        if (orbm_search_for_triangulation(m_, k1.data(), KF1.descriptors->ptr<uint8_t>(0), (int)k1.size(), S1.hasMapPoint->data(), S1.uRight->data(),
+                                          S1.featVec->node.data(), S1.featVec->off.data(), S1.featVec->idx.data(), (int)S1.featVec->node.size(),
+                                          k2.data(), KF2.descriptors->ptr<uint8_t>(0), (int)k2.size(), S2.hasMapPoint->data(), S2.uRight->data(),
+                                          S2.featVec->node.data(), S2.featVec->off.data(), S2.featVec->idx.data(), (int)S2.featVec->node.size(),
+                                          F, ex, ey, vScaleFactors2.data(), vLevelSigma2_2.data(), (int)vScaleFactors2.size(), bOnlyStereo,
+                                          mbCheckOrientation, m12.data(), &n) != ORBX_OK)
+            fail("orbm_search_for_triangulation");
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve(n);
+        for (size_t i = 0; i < m12.size(); i++)                                  // :818-823
+            if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)m12[i]));
+        return n;
+    }
+
+    // MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:252-312) for a batch of MapPoints: vvDescriptors[p] = the vDescriptors the
+    // reference collects for point p (:270-276).  Returns BestIdx per point (-1 when it has no descriptor); the caller then does
+    // mDescriptor = vDescriptors[BestIdx].clone() (:308-311).
+    std::vector<int> ComputeDistinctiveDescriptors(const std::vector<std::vector<cv::Mat> >& vvDescriptors)
+    {
+        std::vector<int> off(1, 0), best(vvDescriptors.size(), -1);
+        std::vector<uint8_t> rows;
+        for (size_t p = 0; p < vvDescriptors.size(); p++) {
+            for (size_t i = 0; i < vvDescriptors[p].size(); i++)
+                rows.insert(rows.end(), vvDescriptors[p][i].ptr<uint8_t>(0), vvDescriptors[p][i].ptr<uint8_t>(0) + 32);
+            off.push_back((int)(rows.size() / 32));
+        }
+        if (orbm_distinctive_descriptors(m_, rows.data(), off.data(), (int)vvDescriptors.size(), best.data()) != ORBX_OK)
+            fail("orbm_distinctive_descriptors");
+        return best;
+    }
+
     // Frame::ComputeStereoMatches (Frame.cc:481-655): fills mvuRight / mvDepth, returns the surviving matches.  maxD is
     // explicit: the reference reads an uninitialised mb there (Frame.cc:511 vs :114); the intended value is fx.
     int ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<cv::KeyPoint>& keysLeft, const cv::Mat& descLeft,
@@ -218,6 +332,18 @@ public:
     static const int HISTO_LENGTH = 30;
 
 protected:
+    int fuse(const FrameView& KF, const std::vector<float>* vuRight, const std::vector<float>& vScaleFactors,
+             const std::vector<float>* vInvLevelSigma2, const ProjectedPoints& P, std::vector<int>& vnBestIdx, float th, int stereoChi2)
+    {
+        std::vector<orbx_kp> k = pack(*KF.keys);
+        vnBestIdx.assign(P.level.size(), -1);
+        int n = 0;
+        if (orbm_fuse(m_, k.data(), KF.descriptors->ptr<uint8_t>(0), vuRight ? vuRight->data() : nullptr, (int)k.size(), KF.minX, KF.maxX, KF.minY,
+                      KF.maxY, vScaleFactors.data(), vInvLevelSigma2 ? vInvLevelSigma2->data() : nullptr, (int)vScaleFactors.size(), P.xy.data(),
+                      P.xr.data(), P.level.data(), P.descriptors.data(), (int)P.level.size(), th, stereoChi2, vnBestIdx.data(), &n) != ORBX_OK)
+            fail("orbm_fuse");
+        return n;
+    }
     static std::vector<orbx_kp> pack(const std::vector<cv::KeyPoint>& v)
     {
         std::vector<orbx_kp> o(v.size());

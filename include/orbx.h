@@ -221,6 +221,68 @@ int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k1, const ui
                        const int* node2, const int* off2, const int* idx2, int nn2,
                        float nnratio, int checkOri, int* matches, int* nmatches);
 
+/* ---- the LocalMapping / LoopClosing / relocalisation searches.  As above, the caller runs the reference's own skip tests
+ * and projection (isBad, spAlreadyFound, depth sign, IsInImage, distance range, viewing angle, PredictScale) and passes, per
+ * surviving MapPoint, the projection, the predicted level and GetDescriptor(). ---- */
+
+/* The inner loop shared by Fuse (src/ORBmatcher.cc:886-935, :1059-1077) and SearchBySim3 (:1183-1203, :1263-1283), for nq
+ * queries in ONE kernel: KeyFrame::GetFeaturesInArea(u, v, r) (src/KeyFrame.cc:572-611) -> skip[idx] (optional, fixed for the
+ * call) -> octave in [qlevel-1, qlevel] -> optional chi-square gate of Fuse (inv_level_sigma2 != NULL: needs u_right and qur,
+ * :898-922) -> FIRST minimum of the Hamming distance in visiting order.  qlevel[i] < 0 skips query i.
+ * best_idx[i] = -1 / best_dist[i] = 256 when no candidate survives. */
+int orbm_search_in_area(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* skip, int n,
+                        float minX, float maxX, float minY, float maxY, const float* qxy, const float* qur, const float* qr,
+                        const int* qlevel, const uint8_t* qdesc, int nq, const float* inv_level_sigma2, int nlevels,
+                        int* best_idx, int* best_dist);
+
+/* ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (src/ORBmatcher.cc:827-975; stereo_chi2 = 1, proj_ur = u - bf*invz) and
+ * Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint) (:977-1102; stereo_chi2 = 0, u_right / proj_ur / inv_level_sigma2 unused).
+ * best_idx[i] = key-frame feature MapPoint i fuses into (bestDist <= TH_LOW), -1 = none; *nfused = how many.  Replace /
+ * AddObservation on that feature (:940-957, :1083-1095) stay with the caller: the search reads no state they change. */
+int orbm_fuse(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const float* u_right, int n,
+              float minX, float maxX, float minY, float maxY, const float* sf, const float* inv_level_sigma2, int nlevels,
+              const float* proj_xy, const float* proj_ur, const int* level, const uint8_t* mp_desc, int nmp, float th, int stereo_chi2,
+              int* best_idx, int* nfused);
+
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1104-1328).  proj12_xy / level12 / mp1_desc: n1 entries, MapPoint of feature i1
+ * of key frame 1 projected into key frame 2 (level12[i1] < 0: no point, already matched, bad, or failed :1160-1173);
+ * proj21_* likewise for key frame 2 into 1.  match12[i1] = i2 where both directions agree (:1305-1322), else -1. */
+int orbm_search_by_sim3(orbx_matcher* m, const orbx_kp* k1, const uint8_t* d1, int n1, const orbx_kp* k2, const uint8_t* d2, int n2,
+                        float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                        const float* proj12_xy, const int* level12, const uint8_t* mp1_desc,
+                        const float* proj21_xy, const int* level21, const uint8_t* mp2_desc, float th, int* match12, int* nfound);
+
+/* ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403), loop detection.
+ * matched[j] = vpMatched[j] != NULL on entry.  feature_match[j] = point stored into vpMatched[j] by this call, -1 = untouched. */
+int orbm_search_by_projection_sim3(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const uint8_t* matched, int n,
+                                   float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                   const float* proj_xy, const int* level, const uint8_t* mp_desc, int nmp, float th,
+                                   int* feature_match, int* nmatches);
+
+/* ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1474-1601),
+ * relocalisation.  occupied[j] = CurrentFrame.mvpMapPoints[j] != NULL; level = nPredictedLevel; kf_angle = pKF->mvKeysUn[i].angle. */
+int orbm_search_by_projection_kf(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, const uint8_t* occupied, int n,
+                                 float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                 const float* proj_xy, const int* level, const float* kf_angle, const uint8_t* mp_desc, int nmp,
+                                 float th, int ORBdist, int checkOri, int* feature_match, int* nmatches);
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-825) with CheckDistEpipolarLine (:140-157).  has_mp[i] = the key
+ * frame's feature i already has a MapPoint; u_right = mvuRight; feature vectors as CSR (see orbm_search_by_bow); F12 row-major
+ * 3x3 floats; (ex, ey) = epipole in image 2 (:667-672); sf2 / sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.
+ * matches12[i1] = i2 or -1 (vMatchedPairs = the pairs with matches12[i1] >= 0, in i1 order). */
+int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint8_t* d1, int n1, const uint8_t* has_mp1, const float* u_right1,
+                                  const int* node1, const int* off1, const int* idx1, int nn1,
+                                  const orbx_kp* k2, const uint8_t* d2, int n2, const uint8_t* has_mp2, const float* u_right2,
+                                  const int* node2, const int* off2, const int* idx2, int nn2,
+                                  const float* F12, float ex, float ey, const float* sf2, const float* sigma2_2, int nlevels,
+                                  int onlyStereo, int checkOri, int* matches12, int* nmatches);
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:252-312) for npoints MapPoints in one launch.  The descriptors observing
+ * point p (pKF->mDescriptors.row(idx) over mObservations in map order, bad key frames left out, :270-276) are rows off[p] ..
+ * off[p+1] of desc (32 bytes each); best[p] = index WITHIN those rows of the descriptor with the least median Hamming distance
+ * to the others (:297-311; the first such row), -1 for a point without observations (the reference returns early, :266-278). */
+int orbm_distinctive_descriptors(orbx_matcher* m, const uint8_t* desc, const int* off, int npoints, int* best);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:481-655).  left/right = extractor handles whose LAST call processed the
  * two images (their device pyramids are read in place; frame = index inside that batch).  Keypoints/descriptors are
  * HOST arrays as returned by orbx_extract.  maxD is explicit (the reference reads an uninitialised mb, src/Frame.cc:511

@@ -74,6 +74,20 @@ def lib():
         L.orbo_search_by_projection_frame.argtypes = [vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp]
         L.orbo_search_by_bow.restype = i
         L.orbo_search_by_bow.argtypes = [i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp]
+        L.orbo_search_in_area.argtypes = [vp, vp, vp, vp, i, f, f, f, f, vp, vp, vp, vp, vp, i, vp, vp, vp]
+        L.orbo_fuse.restype = i
+        L.orbo_fuse.argtypes = [vp, vp, vp, i, f, f, f, f, vp, vp, i, vp, vp, vp, vp, i, f, i, vp]
+        L.orbo_search_by_sim3.restype = i
+        L.orbo_search_by_sim3.argtypes = [vp, vp, i, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, f, vp]
+        L.orbo_search_by_projection_sim3.restype = i
+        L.orbo_search_by_projection_sim3.argtypes = [vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, i, f, vp]
+        L.orbo_search_by_projection_kf.restype = i
+        L.orbo_search_by_projection_kf.argtypes = [vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, i, f, i, i, vp]
+        L.orbo_search_for_triangulation.restype = i
+        L.orbo_search_for_triangulation.argtypes = [vp, vp, i, vp, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, i, vp, f, f, vp, vp, i, i, i, vp]
+        L.orbo_distinctive_descriptor.restype = i
+        L.orbo_distinctive_descriptor.argtypes = [vp, i]
+        L.orbo_distinctive_descriptors.argtypes = [vp, vp, i, vp]
         L.orbo_stereo_matches.restype = i
         L.orbo_stereo_matches.argtypes = [vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, f, f, f, vp, vp]
         _lib = L
@@ -306,6 +320,98 @@ def search_by_bow(k1, d1, valid1, fv1, k2, d2, fv2, valid2=None, nnratio=0.7, ch
     n = lib().orbo_search_by_bow(variant, _p(k1), _p(d1), len(k1), _p(valid1), _p(n1_), _p(o1_), _p(i1_), len(n1_), _p(k2), _p(d2), len(k2),
                                  _pn(v2), _p(n2_), _p(o2_), _p(i2_), len(n2_), float(nnratio), int(checkOri), _p(out))
     return n, out[:nout]
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, np.int32)
+
+
+def search_in_area(kps, desc, bounds, qxy, qr, qlevel, qdesc, u_right=None, skip=None, qur=None, inv_level_sigma2=None):
+    """The window + level + (optional chi-square) + argmin loop shared by Fuse and SearchBySim3 (ORBmatcher.cc:886-935,
+    :1059-1077, :1183-1203) -> (best_idx, best_dist)."""
+    kps = np.ascontiguousarray(kps)
+    desc, qdesc = _u8(desc), _u8(qdesc)
+    qxy, qr, qlevel = _f32(qxy), _f32(qr), _i32(qlevel)
+    ur = None if u_right is None else _f32(u_right)
+    sk = None if skip is None else _u8(skip)
+    qu = None if qur is None else _f32(qur)
+    inv = None if inv_level_sigma2 is None else _f32(inv_level_sigma2)
+    nq = len(qlevel)
+    bi, bd = np.zeros(max(nq, 1), np.int32), np.zeros(max(nq, 1), np.int32)
+    lib().orbo_search_in_area(_p(kps), _p(desc), _pn(ur), _pn(sk), len(kps), *[float(b) for b in bounds], _p(qxy), _pn(qu), _p(qr),
+                              _p(qlevel), _p(qdesc), nq, _pn(inv), _p(bi), _p(bd))
+    return bi[:nq], bd[:nq]
+
+
+def fuse(kps, desc, u_right, bounds, sf, inv_level_sigma2, proj_xy, proj_ur, level, mp_desc, th=3.0, stereo_chi2=True):
+    """ORBmatcher::Fuse(KF, MapPoints, th) (ORBmatcher.cc:827-975) / Fuse(KF, Scw, ...) (:977-1102, stereo_chi2=False)
+    -> (nFused, best_idx per point)."""
+    kps = np.ascontiguousarray(kps)
+    desc, mp_desc = _u8(desc), _u8(mp_desc)
+    u_right, sf, inv, proj_xy, proj_ur, level = _f32(u_right), _f32(sf), _f32(inv_level_sigma2), _f32(proj_xy), _f32(proj_ur), _i32(level)
+    out = np.zeros(max(len(level), 1), np.int32)
+    n = lib().orbo_fuse(_p(kps), _p(desc), _p(u_right), len(kps), *[float(b) for b in bounds], _p(sf), _p(inv), len(sf), _p(proj_xy),
+                        _p(proj_ur), _p(level), _p(mp_desc), len(level), float(th), int(stereo_chi2), _p(out))
+    return n, out[:len(level)]
+
+
+def search_by_sim3(k1, d1, k2, d2, bounds, sf, proj12_xy, level12, mp1_desc, proj21_xy, level21, mp2_desc, th=7.5):
+    """ORBmatcher::SearchBySim3 (ORBmatcher.cc:1104-1328) -> (nFound, match12)."""
+    k1, k2 = np.ascontiguousarray(k1), np.ascontiguousarray(k2)
+    d1, d2, m1, m2 = _u8(d1), _u8(d2), _u8(mp1_desc), _u8(mp2_desc)
+    sf, p12, p21, l12, l21 = _f32(sf), _f32(proj12_xy), _f32(proj21_xy), _i32(level12), _i32(level21)
+    out = np.zeros(max(len(k1), 1), np.int32)
+    n = lib().orbo_search_by_sim3(_p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), *[float(b) for b in bounds], _p(sf), len(sf),
+                                  _p(p12), _p(l12), _p(m1), _p(p21), _p(l21), _p(m2), float(th), _p(out))
+    return n, out[:len(k1)]
+
+
+def search_by_projection_sim3(kps, desc, matched, bounds, sf, proj_xy, level, mp_desc, th=10.0):
+    """ORBmatcher::SearchByProjection(KF, Scw, vpPoints, vpMatched, th) (ORBmatcher.cc:290-403) -> (nmatches, feature_match)."""
+    kps = np.ascontiguousarray(kps)
+    desc, mp_desc, matched = _u8(desc), _u8(mp_desc), _u8(matched)
+    sf, proj_xy, level = _f32(sf), _f32(proj_xy), _i32(level)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orbo_search_by_projection_sim3(_p(kps), _p(desc), _p(matched), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                             _p(proj_xy), _p(level), _p(mp_desc), len(level), float(th), _p(fm))
+    return n, fm[:len(kps)]
+
+
+def search_by_projection_kf(kps, desc, occupied, bounds, sf, proj_xy, level, kf_angle, mp_desc, th=10.0, orb_dist=100, checkOri=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, KF, sAlreadyFound, th, ORBdist) (ORBmatcher.cc:1474-1601)."""
+    kps = np.ascontiguousarray(kps)
+    desc, mp_desc, occupied = _u8(desc), _u8(mp_desc), _u8(occupied)
+    sf, proj_xy, level, kf_angle = _f32(sf), _f32(proj_xy), _i32(level), _f32(kf_angle)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orbo_search_by_projection_kf(_p(kps), _p(desc), _p(occupied), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                           _p(proj_xy), _p(level), _p(kf_angle), _p(mp_desc), len(level), float(th), int(orb_dist),
+                                           int(checkOri), _p(fm))
+    return n, fm[:len(kps)]
+
+
+def search_for_triangulation(k1, d1, has_mp1, u_right1, fv1, k2, d2, has_mp2, u_right2, fv2, F12, epipole, sf2, sigma2_2,
+                             only_stereo=False, checkOri=True):
+    """ORBmatcher::SearchForTriangulation (ORBmatcher.cc:657-825) -> (nmatches, matches12)."""
+    k1, k2 = np.ascontiguousarray(k1), np.ascontiguousarray(k2)
+    d1, d2, h1, h2 = _u8(d1), _u8(d2), _u8(has_mp1), _u8(has_mp2)
+    u1, u2, F, sf2, sg = _f32(u_right1), _f32(u_right2), _f32(np.asarray(F12).reshape(9)), _f32(sf2), _f32(sigma2_2)
+    n1_, o1_, i1_ = [_i32(a) for a in fv1]
+    n2_, o2_, i2_ = [_i32(a) for a in fv2]
+    out = np.zeros(max(len(k1), 1), np.int32)
+    n = lib().orbo_search_for_triangulation(_p(k1), _p(d1), len(k1), _p(h1), _p(u1), _p(n1_), _p(o1_), _p(i1_), len(n1_),
+                                            _p(k2), _p(d2), len(k2), _p(h2), _p(u2), _p(n2_), _p(o2_), _p(i2_), len(n2_),
+                                            _p(F), float(epipole[0]), float(epipole[1]), _p(sf2), _p(sg), len(sf2),
+                                            int(only_stereo), int(checkOri), _p(out))
+    return n, out[:len(k1)]
+
+
+def distinctive_descriptors(desc, off):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:281-311) for many MapPoints: observations of point p are rows
+    off[p]..off[p+1] of desc -> index (within the point's rows) of its most distinctive descriptor, -1 when it has none."""
+    desc, off = _u8(desc), _i32(off)
+    best = np.zeros(max(len(off) - 1, 1), np.int32)
+    lib().orbo_distinctive_descriptors(_p(desc), _p(off), len(off) - 1, _p(best))
+    return best[:len(off) - 1]
 
 
 def stereo_matches(kl, dl, kr, dr, pyrL, pyrR, sf, isf, bf, maxD, minD=0.0):

@@ -463,4 +463,309 @@ int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl, const orbo
     return kept;
 }
 
+
+// ================================================================================================================
+// The searches of the LocalMapping / LoopClosing threads.  MapPoint / KeyFrame reads are plain arrays again: the caller
+// runs the reference's own skip tests and projection (isBad, spAlreadyFound, depth sign, IsInImage, distance range, viewing
+// angle, PredictScale) and passes, per surviving point, the projection (u, v[, ur]), the predicted level and the descriptor.
+
+// The inner loop shared by Fuse(KF, MapPoints) (ORBmatcher.cc:886-935), Fuse(KF, Scw) (:1059-1077) and SearchBySim3
+// (:1183-1203, :1263-1283): KeyFrame::GetFeaturesInArea(u, v, radius) (KeyFrame.cc:572-611: the Frame grid without a level
+// filter), keep octave in [level-1, level], optionally the chi-square reprojection test of Fuse (:898-922), first minimum
+// of the Hamming distance in visiting order.  best_idx = -1 / best_dist = 256 when nothing survives.
+static void area_best(const orbo::Grid& g, const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* skip,
+                      float u, float v, float ur, float radius, int nPredictedLevel, const uint8_t* dMP,
+                      const float* invLevelSigma2, std::vector<int>& vIndices, int& bestIdx, int& bestDist)
+{
+    using namespace orbo;
+    bestDist = 256;
+    bestIdx = -1;
+    grid_query(g, kps, u, v, radius, -1, -1, vIndices);
+    for (int idx : vIndices) {
+        if (skip && skip[idx]) continue;
+        const orbo_kp& kp = kps[idx];
+        const int kpLevel = kp.octave;
+        if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+        if (invLevelSigma2) {
+            if (u_right[idx] >= 0) {
+                const float ex = u - kp.x, ey = v - kp.y, er = ur - u_right[idx];
+                const float e2 = ex * ex + ey * ey + er * er;
+                if (e2 * invLevelSigma2[kpLevel] > 7.8) continue;
+            } else {
+                const float ex = u - kp.x, ey = v - kp.y;
+                const float e2 = ex * ex + ey * ey;
+                if (e2 * invLevelSigma2[kpLevel] > 5.99) continue;
+            }
+        }
+        const int dist = descriptor_distance(dMP, desc + 32 * (size_t)idx);
+        if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+    }
+}
+
+void orbo_search_in_area(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* skip, int n,
+                         float minX, float maxX, float minY, float maxY, const float* qxy, const float* qur, const float* qr,
+                         const int* qlevel, const uint8_t* qdesc, int nq, const float* inv_level_sigma2, int* best_idx, int* best_dist)
+{
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> tmp;
+    for (int i = 0; i < nq; i++)
+        area_best(G->g, kps, desc, u_right, skip, qxy[2 * i], qxy[2 * i + 1], qur ? qur[i] : 0.0f, qr[i], qlevel[i],
+                  qdesc + 32 * (size_t)i, inv_level_sigma2, tmp, best_idx[i], best_dist[i]);
+    orbo_grid_destroy(G);
+}
+
+// ---- ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (:827-975; stereo_chi2 = 1) and Fuse(KeyFrame*, Scw, vpPoints, th,
+// vpReplacePoint) (:977-1102; stereo_chi2 = 0).  best_idx[i] = the key frame feature point i fuses into (bestDist <= TH_LOW,
+// :938 / :1081), -1 otherwise; what happens to that feature's MapPoint (Replace / AddObservation) is map bookkeeping of the caller.
+// Returns the number of points with a feature (nFused).
+int orbo_fuse(const orbo_kp* kps, const uint8_t* desc, const float* u_right, int n, float minX, float maxX, float minY, float maxY,
+              const float* sf, const float* inv_level_sigma2, int nlevels, const float* proj_xy, const float* proj_ur,
+              const int* level, const uint8_t* mp_desc, int nmp, float th, int stereo_chi2, int* best_idx)
+{
+    using namespace orbo;
+    (void)nlevels;
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> tmp;
+    int nFused = 0;
+    for (int i = 0; i < nmp; i++) {
+        const float radius = th * sf[level[i]];
+        int bestIdx, bestDist;
+        area_best(G->g, kps, desc, u_right, nullptr, proj_xy[2 * i], proj_xy[2 * i + 1], stereo_chi2 ? proj_ur[i] : 0.0f, radius, level[i],
+                  mp_desc + 32 * (size_t)i, stereo_chi2 ? inv_level_sigma2 : nullptr, tmp, bestIdx, bestDist);
+        best_idx[i] = -1;
+        if (bestDist <= TH_LOW) { best_idx[i] = bestIdx; nFused++; }
+    }
+    orbo_grid_destroy(G);
+    return nFused;
+}
+
+// ---- ORBmatcher::SearchBySim3 (:1104-1328).  Direction 1->2: the MapPoints of key frame 1 that pass :1145-1180 projected
+// into key frame 2 (proj12_xy, level12, desc of the MapPoint; level12[i] < 0 = point skipped), direction 2->1 likewise.
+// match12[i1] = i2 where both directions agree (:1309-1322), -1 otherwise.  Returns nFound.
+int orbo_search_by_sim3(const orbo_kp* k1, const uint8_t* d1, int n1, const orbo_kp* k2, const uint8_t* d2, int n2,
+                        float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                        const float* proj12_xy, const int* level12, const uint8_t* mp1_desc,
+                        const float* proj21_xy, const int* level21, const uint8_t* mp2_desc, float th, int* match12)
+{
+    using namespace orbo;
+    (void)nlevels;
+    std::vector<int> vnMatch1(n1, -1), vnMatch2(n2, -1), tmp;
+    orbo_grid* G2 = orbo_grid_build(k2, n2, minX, maxX, minY, maxY);
+    for (int i1 = 0; i1 < n1; i1++) {
+        if (level12[i1] < 0) continue;
+        int bestIdx, bestDist;
+        area_best(G2->g, k2, d2, nullptr, nullptr, proj12_xy[2 * i1], proj12_xy[2 * i1 + 1], 0.0f, th * sf[level12[i1]], level12[i1],
+                  mp1_desc + 32 * (size_t)i1, nullptr, tmp, bestIdx, bestDist);
+        if (bestDist <= TH_HIGH) vnMatch1[i1] = bestIdx;
+    }
+    orbo_grid_destroy(G2);
+    orbo_grid* G1 = orbo_grid_build(k1, n1, minX, maxX, minY, maxY);
+    for (int i2 = 0; i2 < n2; i2++) {
+        if (level21[i2] < 0) continue;
+        int bestIdx, bestDist;
+        area_best(G1->g, k1, d1, nullptr, nullptr, proj21_xy[2 * i2], proj21_xy[2 * i2 + 1], 0.0f, th * sf[level21[i2]], level21[i2],
+                  mp2_desc + 32 * (size_t)i2, nullptr, tmp, bestIdx, bestDist);
+        if (bestDist <= TH_HIGH) vnMatch2[i2] = bestIdx;
+    }
+    orbo_grid_destroy(G1);
+    int nFound = 0;
+    for (int i1 = 0; i1 < n1; i1++) {
+        match12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { match12[i1] = idx2; nFound++; }
+    }
+    return nFound;
+}
+
+// ---- ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (:290-403).  matched_in[j] = vpMatched[j] != NULL
+// on entry; the points passed :316-351; a feature that receives a point is skipped by the later points (:375-376, :394).
+// feature_match[j] = index of the point stored into vpMatched[j] by this call, -1 = untouched.
+int orbo_search_by_projection_sim3(const orbo_kp* kps, const uint8_t* desc, const uint8_t* matched_in, int n,
+                                   float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                   const float* proj_xy, const int* level, const uint8_t* mp_desc, int nmp, float th, int* feature_match)
+{
+    using namespace orbo;
+    (void)nlevels;
+    std::vector<uint8_t> matched(matched_in, matched_in + n);
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> tmp;
+    int nmatches = 0;
+    for (int i = 0; i < nmp; i++) {
+        int bestIdx, bestDist;
+        area_best(G->g, kps, desc, nullptr, matched.data(), proj_xy[2 * i], proj_xy[2 * i + 1], 0.0f, th * sf[level[i]], level[i],
+                  mp_desc + 32 * (size_t)i, nullptr, tmp, bestIdx, bestDist);
+        if (bestDist <= TH_LOW) { feature_match[bestIdx] = i; matched[bestIdx] = 1; nmatches++; }
+    }
+    orbo_grid_destroy(G);
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist) (:1474-1601), the
+// relocalisation search.  occupied_in[j] = CurrentFrame.mvpMapPoints[j] != NULL; points of the key frame that passed
+// :1494-1523, with level = nPredictedLevel and kf_angle = pKF->mvKeysUn[i].angle.
+int orbo_search_by_projection_kf(const orbo_kp* kps, const uint8_t* desc, const uint8_t* occupied_in, int n,
+                                 float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                 const float* proj_xy, const int* level, const float* kf_angle, const uint8_t* mp_desc, int nmp,
+                                 float th, int ORBdist, int checkOri, int* feature_match)
+{
+    using namespace orbo;
+    (void)nlevels;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    for (int j = 0; j < n; j++) feature_match[j] = -1;
+    orbo_grid* G = orbo_grid_build(kps, n, minX, maxX, minY, maxY);
+    std::vector<int> vIndices2;
+    for (int i = 0; i < nmp; i++) {
+        const int nPredictedLevel = level[i];
+        const float radius = th * sf[nPredictedLevel];
+        grid_query(G->g, kps, proj_xy[2 * i], proj_xy[2 * i + 1], radius, nPredictedLevel - 1, nPredictedLevel + 1, vIndices2);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = mp_desc + 32 * (size_t)i;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            if (occupied[i2]) continue;
+            const int dist = descriptor_distance(dMP, desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBdist) {
+            feature_match[bestIdx2] = i;
+            occupied[bestIdx2] = 1;
+            nmatches++;
+            if (checkOri) {
+                float rot = kf_angle[i] - kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    orbo_grid_destroy(G);
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int j : rotHist[i]) { feature_match[j] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// ---- ORBmatcher::SearchForTriangulation (:657-825) with CheckDistEpipolarLine (:140-157).  has_mp1/has_mp2[i] = the key
+// frame's feature already has a MapPoint (:699-703, :721-725); F12 row-major 3x3; (ex, ey) the epipole in image 2 (:667-672);
+// sf2 / sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.  matches12[i1] = i2 or -1 (the vMatchedPairs list in index order).
+int orbo_search_for_triangulation(const orbo_kp* k1, const uint8_t* d1, int n1, const uint8_t* has_mp1, const float* u_right1,
+                                  const int* node1, const int* off1, const int* idx1, int nn1,
+                                  const orbo_kp* k2, const uint8_t* d2, int n2, const uint8_t* has_mp2, const float* u_right2,
+                                  const int* node2, const int* off2, const int* idx2, int nn2,
+                                  const float* F12, float ex, float ey, const float* sf2, const float* sigma2_2, int nlevels,
+                                  int onlyStereo, int checkOri, int* matches12)
+{
+    using namespace orbo;
+    (void)nlevels;
+    int nmatches = 0;
+    std::vector<uint8_t> vbMatched2(n2, 0);
+    for (int i = 0; i < n1; i++) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int a = 0, b = 0;
+    while (a < nn1 && b < nn2) {
+        if (node1[a] == node2[b]) {
+            for (int p1 = off1[a]; p1 < off1[a + 1]; p1++) {
+                const int i1 = idx1[p1];
+                if (has_mp1[i1]) continue;
+                const bool bStereo1 = u_right1[i1] >= 0;
+                if (onlyStereo && !bStereo1) continue;
+                const orbo_kp& kp1 = k1[i1];
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (int p2 = off2[b]; p2 < off2[b + 1]; p2++) {
+                    const int i2 = idx2[p2];
+                    if (vbMatched2[i2] || has_mp2[i2]) continue;
+                    const bool bStereo2 = u_right2[i2] >= 0;
+                    if (onlyStereo && !bStereo2) continue;
+                    const int dist = descriptor_distance(d1 + 32 * (size_t)i1, d2 + 32 * (size_t)i2);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const orbo_kp& kp2 = k2[i2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - kp2.x, distey = ey - kp2.y;
+                        if (distex * distex + distey * distey < 100 * sf2[kp2.octave]) continue;
+                    }
+                    // CheckDistEpipolarLine (:140-157)
+                    const float la = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                    const float lb = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                    const float lc = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                    const float num = la * kp2.x + lb * kp2.y + lc;
+                    const float den = la * la + lb * lb;
+                    if (den == 0) continue;
+                    const float dsqr = num * num / den;
+                    if (dsqr < 3.84 * sigma2_2[kp2.octave]) { bestIdx2 = i2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    matches12[i1] = bestIdx2;
+                    vbMatched2[bestIdx2] = 1;
+                    nmatches++;
+                    if (checkOri) {
+                        float rot = kp1.angle - k2[bestIdx2].angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)std::round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back(i1);
+                    }
+                }
+            }
+            a++; b++;
+        } else if (node1[a] < node2[b]) {
+            a = (int)(std::lower_bound(node1, node1 + nn1, node2[b]) - node1);
+        } else {
+            b = (int)(std::lower_bound(node2, node2 + nn2, node1[a]) - node2);
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int j : rotHist[i]) { vbMatched2[matches12[j]] = 0; matches12[j] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+
+// ---- MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:252-312), the descriptor-level part (:281-311): of the n
+// descriptors observing one MapPoint (rows of desc, in std::map<KeyFrame*, size_t> iteration order, bad key frames already
+// removed), the index of the one with the least median distance to the rest.  -1 for n = 0 (:266-267, :277-278 return early).
+int orbo_distinctive_descriptor(const uint8_t* desc, int n)
+{
+    using namespace orbo;
+    if (n <= 0) return -1;
+    const size_t N = (size_t)n;
+    std::vector<float> Distances(N * N);
+    for (size_t i = 0; i < N; i++) {
+        Distances[i * N + i] = 0;
+        for (size_t j = i + 1; j < N; j++) {
+            const int distij = descriptor_distance(desc + 32 * i, desc + 32 * j);
+            Distances[i * N + j] = distij;
+            Distances[j * N + i] = distij;
+        }
+    }
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (size_t i = 0; i < N; i++) {
+        std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + (i + 1) * N);
+        std::sort(vDists.begin(), vDists.end());
+        const int median = vDists[0.5 * (N - 1)];
+        if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+    }
+    return BestIdx;
+}
+
+// the same for npoints MapPoints at once: observations of point p are rows off[p] .. off[p+1] of desc
+void orbo_distinctive_descriptors(const uint8_t* desc, const int* off, int npoints, int* best)
+{
+    for (int p = 0; p < npoints; p++) best[p] = orbo_distinctive_descriptor(desc + 32 * (size_t)off[p], off[p + 1] - off[p]);
+}
+
 } // extern "C"

@@ -106,6 +106,36 @@ int orbo_search_by_bow(int variant, const orbo_kp* k1, const uint8_t* d1, int n1
                        const int* node2, const int* off2, const int* idx2, int nn2,
                        float nnratio, int checkOri, int* matches);
 
+/* the LocalMapping / LoopClosing searches (Fuse x2 ORBmatcher.cc:827-1102, SearchBySim3 :1104-1328, SearchByProjection(KF, Scw)
+ * :290-403, SearchByProjection(Frame, KF) :1474-1601, SearchForTriangulation :657-825); see orb_matcher.cpp */
+void orbo_search_in_area(const orbo_kp* kps, const uint8_t* desc, const float* u_right, const uint8_t* skip, int n,
+                         float minX, float maxX, float minY, float maxY, const float* qxy, const float* qur, const float* qr,
+                         const int* qlevel, const uint8_t* qdesc, int nq, const float* inv_level_sigma2, int* best_idx, int* best_dist);
+int orbo_fuse(const orbo_kp* kps, const uint8_t* desc, const float* u_right, int n, float minX, float maxX, float minY, float maxY,
+              const float* sf, const float* inv_level_sigma2, int nlevels, const float* proj_xy, const float* proj_ur,
+              const int* level, const uint8_t* mp_desc, int nmp, float th, int stereo_chi2, int* best_idx);
+int orbo_search_by_sim3(const orbo_kp* k1, const uint8_t* d1, int n1, const orbo_kp* k2, const uint8_t* d2, int n2,
+                        float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                        const float* proj12_xy, const int* level12, const uint8_t* mp1_desc,
+                        const float* proj21_xy, const int* level21, const uint8_t* mp2_desc, float th, int* match12);
+int orbo_search_by_projection_sim3(const orbo_kp* kps, const uint8_t* desc, const uint8_t* matched_in, int n,
+                                   float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                   const float* proj_xy, const int* level, const uint8_t* mp_desc, int nmp, float th, int* feature_match);
+int orbo_search_by_projection_kf(const orbo_kp* kps, const uint8_t* desc, const uint8_t* occupied_in, int n,
+                                 float minX, float maxX, float minY, float maxY, const float* sf, int nlevels,
+                                 const float* proj_xy, const int* level, const float* kf_angle, const uint8_t* mp_desc, int nmp,
+                                 float th, int ORBdist, int checkOri, int* feature_match);
+int orbo_search_for_triangulation(const orbo_kp* k1, const uint8_t* d1, int n1, const uint8_t* has_mp1, const float* u_right1,
+                                  const int* node1, const int* off1, const int* idx1, int nn1,
+                                  const orbo_kp* k2, const uint8_t* d2, int n2, const uint8_t* has_mp2, const float* u_right2,
+                                  const int* node2, const int* off2, const int* idx2, int nn2,
+                                  const float* F12, float ex, float ey, const float* sf2, const float* sigma2_2, int nlevels,
+                                  int onlyStereo, int checkOri, int* matches12);
+
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:281-311): index of the descriptor with the least median distance */
+int orbo_distinctive_descriptor(const uint8_t* desc, int n);
+void orbo_distinctive_descriptors(const uint8_t* desc, const int* off, int npoints, int* best);
+
 int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl,
                         const orbo_kp* kr, const uint8_t* dr, int nr,
                         const uint8_t* const* pyrL, const uint8_t* const* pyrR,

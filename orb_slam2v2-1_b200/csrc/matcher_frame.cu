@@ -13,16 +13,6 @@
 
 namespace orbx {
 
-constexpr int GRID_COLS = 64, GRID_ROWS = 48;      // FRAME_GRID_COLS / FRAME_GRID_ROWS, include/Frame.h:37-38
-constexpr int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:37-39
-
-struct GridParams { float minX, minY, invW, invH; };
-
-__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
-{
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 // ------------------------------------------------------------------------------------------------ GetFeaturesInArea
 // One warp per query.  The CSR grid is stored column-major (cell = ix * 48 + iy), i.e. in the reference's own loop
@@ -118,7 +108,7 @@ __global__ void __launch_bounds__(256) k_cand_dist(const uint4* __restrict__ q, 
 }
 
 // Frame::AssignFeaturesToGrid / PosInGrid (Frame.cc:230-245, 397-407) as a stable counting sort into CSR
-static void build_grid_host(const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY, GridParams& gp,
+void build_grid_host(const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY, GridParams& gp,
                             std::vector<int>& start, std::vector<int>& entries)
 {
     gp.minX = minX;
@@ -216,7 +206,7 @@ int orbm_grid_candidates(orbx_matcher* m, const orbx_kp* kps, int n, float minX,
 namespace orbx {
 
 // ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1603-1644) on bin sizes
-static void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
 {
     int max1 = 0, max2 = 0, max3 = 0;
     for (int i = 0; i < L; i++) {
@@ -347,7 +337,7 @@ namespace orbx {
 
 // Candidates (GetFeaturesInArea with a per-query level range) and their Hamming distances for nq queries against one
 // frame, on the device; the CSR comes back to the host for the sequential replay of the reference's greedy loops.
-static int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
+int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
                               const float* qxy, const float* qr, const int* qlev2, const uint8_t* qdesc, int nq,
                               std::vector<int>& off, std::vector<int>& idx, std::vector<int>& dist)
 {
@@ -396,7 +386,7 @@ static int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t
 }
 
 // distances of host CSR candidate lists (queries q against rows of t) on the device
-static int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, const std::vector<int>& off,
+int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, const std::vector<int>& off,
                          const std::vector<int>& idx, std::vector<int>& dist)
 {
     const int total = off[nq];

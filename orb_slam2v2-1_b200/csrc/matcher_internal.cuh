@@ -1,6 +1,7 @@
 // matcher_internal.cuh -- internal declarations shared by the matcher translation units.
 #pragma once
 #include "orbx_common.cuh"
+#include <vector>
 
 namespace orbx {
 
@@ -35,6 +36,30 @@ struct orbx_matcher {
 };
 
 namespace orbx {
+
+constexpr int GRID_COLS = 64, GRID_ROWS = 48;      // FRAME_GRID_COLS / FRAME_GRID_ROWS, include/Frame.h:37-38
+constexpr int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // src/ORBmatcher.cc:37-39
+
+struct GridParams { float minX, minY, invW, invH; };
+
+#ifdef __CUDACC__
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+#endif
+
+// matcher_frame.cu
+void build_grid_host(const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY, GridParams& gp,
+                     std::vector<int>& start, std::vector<int>& entries);
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3);
+int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
+                       const float* qxy, const float* qr, const int* qlev2, const uint8_t* qdesc, int nq,
+                       std::vector<int>& off, std::vector<int>& idx, std::vector<int>& dist);
+int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, const std::vector<int>& off,
+                  const std::vector<int>& idx, std::vector<int>& dist);
+
 int bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int th_low, float nnratio,
                       int* d_bi, int* d_bd, int* d_sd, uint8_t* d_acc);
 }

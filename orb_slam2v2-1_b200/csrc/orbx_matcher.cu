@@ -14,12 +14,6 @@
 
 namespace orbx {
 
-__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
-{
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
-
 // Brute-force variant: POPC issues at 16 lanes/clk/SM against 64 for LOP3 (tools/int_pipe_bench.cu), so eight POPCs per pair
 // bind the scan.  Two carry-save adders (sum = a^b^c, carry = majority, one LOP3 each) fold six of the eight xor words into
 // two "ones" and two "twos" words: 6 POPCs + 4 LOP3s give the same integer, and the POPC and ALU pipes end up balanced.

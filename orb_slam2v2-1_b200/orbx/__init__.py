@@ -83,6 +83,14 @@ def lib():
         "orbm_search_by_projection": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp]),
         "orbm_search_by_projection_frame": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp, vp]),
         "orbm_search_by_bow": (i, [vp, i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp, vp]),
+        "orbm_search_in_area": (i, [vp, vp, vp, vp, vp, i, f, f, f, f, vp, vp, vp, vp, vp, i, vp, i, vp, vp]),
+        "orbm_fuse": (i, [vp, vp, vp, vp, i, f, f, f, f, vp, vp, i, vp, vp, vp, vp, i, f, i, vp, vp]),
+        "orbm_search_by_sim3": (i, [vp, vp, vp, i, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, vp, vp, f, vp, vp]),
+        "orbm_search_by_projection_sim3": (i, [vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, i, f, vp, vp]),
+        "orbm_search_by_projection_kf": (i, [vp, vp, vp, vp, i, f, f, f, f, vp, i, vp, vp, vp, vp, i, f, i, i, vp, vp]),
+        "orbm_search_for_triangulation": (i, [vp, vp, vp, i, vp, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, i, vp, f, f, vp, vp, i,
+                                              i, i, vp, vp]),
+        "orbm_distinctive_descriptors": (i, [vp, vp, vp, i, vp]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
     }
@@ -465,6 +473,118 @@ def _stereo_batch(self, left, right, bf, maxD, minD=0.0):
 
 
 ORBmatcher.ComputeStereoMatchesBatch = _stereo_batch
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, np.int32)
+
+
+def _search_in_area(self, kps, desc, bounds, qxy, qr, qlevel, qdesc, u_right=None, skip=None, qur=None, inv_level_sigma2=None, nlevels=8):
+    """Window + level + (optional chi-square) + Hamming argmin for a batch of projected points, one kernel
+    (the loop shared by Fuse and SearchBySim3, src/ORBmatcher.cc:886-935).  Returns (best_idx, best_dist)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc, qdesc = _u8(desc).reshape(-1, 32), _u8(qdesc).reshape(-1, 32)
+    qxy, qr, qlevel = _f32(qxy), _f32(qr), _i32(qlevel)
+    ur = None if u_right is None else _f32(u_right)
+    sk = None if skip is None else _u8(skip)
+    qu = None if qur is None else _f32(qur)
+    inv = None if inv_level_sigma2 is None else _f32(inv_level_sigma2)
+    nq = len(qlevel)
+    bi, bd = np.zeros(max(nq, 1), np.int32), np.zeros(max(nq, 1), np.int32)
+    _check(self._L.orbm_search_in_area(self._h, _p(kps), _p(desc), _p(ur), _p(sk), len(kps), *[float(b) for b in bounds], _p(qxy), _p(qu),
+                                       _p(qr), _p(qlevel), _p(qdesc), nq, _p(inv), nlevels if inv is None else len(inv), _p(bi), _p(bd)))
+    return bi[:nq], bd[:nq]
+
+
+def _fuse(self, kps, desc, u_right, bounds, sf, inv_level_sigma2, proj_xy, proj_ur, level, mp_desc, th=3.0, stereo_chi2=True):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:827-975) or, with stereo_chi2=False, Fuse(pKF, Scw, vpPoints, th,
+    vpReplacePoint) (:977-1102).  Returns (nFused, best_idx[point] or -1)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc, mp_desc = _u8(desc).reshape(-1, 32), _u8(mp_desc).reshape(-1, 32)
+    u_right, sf, inv, proj_xy, proj_ur, level = _f32(u_right), _f32(sf), _f32(inv_level_sigma2), _f32(proj_xy), _f32(proj_ur), _i32(level)
+    out = np.zeros(max(len(level), 1), np.int32)
+    nf = C.c_int(0)
+    _check(self._L.orbm_fuse(self._h, _p(kps), _p(desc), _p(u_right), len(kps), *[float(b) for b in bounds], _p(sf), _p(inv), len(sf),
+                             _p(proj_xy), _p(proj_ur), _p(level), _p(mp_desc), len(level), float(th), int(stereo_chi2), _p(out), C.byref(nf)))
+    return nf.value, out[:len(level)]
+
+
+def _search_by_sim3(self, k1, d1, k2, d2, bounds, sf, proj12_xy, level12, mp1_desc, proj21_xy, level21, mp2_desc, th=7.5):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1104-1328).  Returns (nFound, match12)."""
+    k1, k2 = np.ascontiguousarray(k1, KP_DTYPE), np.ascontiguousarray(k2, KP_DTYPE)
+    d1, d2, m1, m2 = _u8(d1).reshape(-1, 32), _u8(d2).reshape(-1, 32), _u8(mp1_desc).reshape(-1, 32), _u8(mp2_desc).reshape(-1, 32)
+    sf, p12, p21, l12, l21 = _f32(sf), _f32(proj12_xy), _f32(proj21_xy), _i32(level12), _i32(level21)
+    out = np.zeros(max(len(k1), 1), np.int32)
+    nf = C.c_int(0)
+    _check(self._L.orbm_search_by_sim3(self._h, _p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), *[float(b) for b in bounds], _p(sf), len(sf),
+                                       _p(p12), _p(l12), _p(m1), _p(p21), _p(l21), _p(m2), float(th), _p(out), C.byref(nf)))
+    return nf.value, out[:len(k1)]
+
+
+def _search_by_projection_sim3(self, kps, desc, matched, bounds, sf, proj_xy, level, mp_desc, th=10.0):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc, mp_desc, matched = _u8(desc).reshape(-1, 32), _u8(mp_desc).reshape(-1, 32), _u8(matched)
+    sf, proj_xy, level = _f32(sf), _f32(proj_xy), _i32(level)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    nm = C.c_int(0)
+    _check(self._L.orbm_search_by_projection_sim3(self._h, _p(kps), _p(desc), _p(matched), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                                  _p(proj_xy), _p(level), _p(mp_desc), len(level), float(th), _p(fm), C.byref(nm)))
+    return nm.value, fm[:len(kps)]
+
+
+def _search_by_projection_kf(self, kps, desc, occupied, bounds, sf, proj_xy, level, kf_angle, mp_desc, th=10.0, orb_dist=100):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1474-1601)."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc, mp_desc, occupied = _u8(desc).reshape(-1, 32), _u8(mp_desc).reshape(-1, 32), _u8(occupied)
+    sf, proj_xy, level, kf_angle = _f32(sf), _f32(proj_xy), _i32(level), _f32(kf_angle)
+    fm = np.zeros(max(len(kps), 1), np.int32)
+    nm = C.c_int(0)
+    _check(self._L.orbm_search_by_projection_kf(self._h, _p(kps), _p(desc), _p(occupied), len(kps), *[float(b) for b in bounds], _p(sf), len(sf),
+                                                _p(proj_xy), _p(level), _p(kf_angle), _p(mp_desc), len(level), float(th), int(orb_dist),
+                                                int(self.mbCheckOrientation), _p(fm), C.byref(nm)))
+    return nm.value, fm[:len(kps)]
+
+
+def _search_for_triangulation(self, k1, d1, has_mp1, u_right1, fv1, k2, d2, has_mp2, u_right2, fv2, F12, epipole, sf2, sigma2_2,
+                              only_stereo=False):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-825).  Returns (nmatches, matches12)."""
+    k1, k2 = np.ascontiguousarray(k1, KP_DTYPE), np.ascontiguousarray(k2, KP_DTYPE)
+    d1, d2, h1, h2 = _u8(d1).reshape(-1, 32), _u8(d2).reshape(-1, 32), _u8(has_mp1), _u8(has_mp2)
+    u1, u2, F, sf2, sg = _f32(u_right1), _f32(u_right2), _f32(np.asarray(F12).reshape(9)), _f32(sf2), _f32(sigma2_2)
+    n1_, o1_, i1_ = [_i32(a) for a in fv1]
+    n2_, o2_, i2_ = [_i32(a) for a in fv2]
+    out = np.zeros(max(len(k1), 1), np.int32)
+    nm = C.c_int(0)
+    _check(self._L.orbm_search_for_triangulation(self._h, _p(k1), _p(d1), len(k1), _p(h1), _p(u1), _p(n1_), _p(o1_), _p(i1_), len(n1_),
+                                                 _p(k2), _p(d2), len(k2), _p(h2), _p(u2), _p(n2_), _p(o2_), _p(i2_), len(n2_),
+                                                 _p(F), float(epipole[0]), float(epipole[1]), _p(sf2), _p(sg), len(sf2),
+                                                 int(only_stereo), int(self.mbCheckOrientation), _p(out), C.byref(nm)))
+    return nm.value, out[:len(k1)]
+
+
+def _distinctive_descriptors(self, desc, off):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:252-312) for many MapPoints: the observations of point p are
+    rows off[p]..off[p+1] of desc.  Returns, per point, the index within its rows of the most distinctive descriptor (-1: none)."""
+    desc, off = _u8(desc).reshape(-1, 32), _i32(off)
+    npts = len(off) - 1
+    best = np.zeros(max(npts, 1), np.int32)
+    _check(self._L.orbm_distinctive_descriptors(self._h, _p(desc), _p(off), npts, _p(best)))
+    return best[:npts]
+
+
+ORBmatcher.ComputeDistinctiveDescriptors = _distinctive_descriptors
+ORBmatcher.SearchInArea = _search_in_area
+ORBmatcher.last_launches = lambda self: self._L.orbm_last_launches(self._h)
+ORBmatcher.Fuse = _fuse
+ORBmatcher.SearchBySim3 = _search_by_sim3
+ORBmatcher.SearchByProjectionSim3 = _search_by_projection_sim3
+ORBmatcher.SearchByProjectionKF = _search_by_projection_kf
+ORBmatcher.SearchForTriangulation = _search_for_triangulation
 
 
 def version():

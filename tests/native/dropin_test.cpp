@@ -1,7 +1,8 @@
 // Exercises the drop-in C++ headers (include/ORBextractor.h, include/ORBmatcher.h) the way Frame.cc uses the reference
 // classes.  usage: dropin_test in.raw w h nfeatures out.bin
 // out.bin: int32 n | n x 28-byte keypoints | n x 32 descriptor bytes | int32 levels | per level int32 w,h + bytes |
-//          int32 nmatch_self | n int32 matches (SearchBruteForce of the descriptors against themselves)
+//          int32 nmatch_self | n int32 matches (SearchBruteForce of the descriptors against themselves) | int32 d01 |
+//          int32 nFused | n int32 (Fuse, chi-square gate) | int32 nFused | n int32 (Fuse, Sim3) | int32 nFound | n int32 (SearchBySim3)
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -44,6 +45,28 @@ int main(int argc, char** argv)
         m.resize(n, -1);
         fwrite(m.data(), 4, n, o);
         fwrite(&d01, 4, 1, o);
+        // the map-side searches through the C++ wrappers, every feature re-projected onto itself one pixel to the right:
+        // Fuse (mono chi-square gate), Fuse with a Sim3 (no gate), SearchBySim3 both ways on the same key frame
+        ORB_SLAM2::FrameView view = { &keys, &desc, 0.0f, (float)w, 0.0f, (float)h };
+        std::vector<float> sf = ex->GetScaleFactors(), isg = ex->GetInverseScaleSigmaSquares(), uR(n, -1.0f);
+        ORB_SLAM2::ORBmatcher::ProjectedPoints P;
+        for (int i = 0; i < n; i++) {
+            P.xy.push_back(keys[i].pt.x + 1.0f);
+            P.xy.push_back(keys[i].pt.y);
+            P.xr.push_back(-1.0f);
+            P.level.push_back(keys[i].octave);
+            P.descriptors.insert(P.descriptors.end(), desc.ptr<uint8_t>(i), desc.ptr<uint8_t>(i) + 32);
+        }
+        std::vector<int> f1, f2, s12;
+        const int nf1 = matcher.Fuse(view, uR, sf, isg, P, f1, 3.0f);
+        const int nf2 = matcher.Fuse(view, sf, P, f2, 4.0f);
+        const int ns = matcher.SearchBySim3(view, view, sf, P, P, s12, 7.5f);
+        fwrite(&nf1, 4, 1, o);
+        fwrite(f1.data(), 4, n, o);
+        fwrite(&nf2, 4, 1, o);
+        fwrite(f2.data(), 4, n, o);
+        fwrite(&ns, 4, 1, o);
+        fwrite(s12.data(), 4, n, o);
         fclose(o);
         printf("ok %d keypoints, %d self matches, scale[1]=%g\n", n, nm, ex->GetScaleFactors()[1]);
         delete ex;

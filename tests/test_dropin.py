@@ -70,9 +70,25 @@ def test_dropin_matches_oracle(tmp_path, w, h, nf, seed):
         assert np.array_equal(lev, oe.level_padded(l)[19:-19, 19:-19]), "mvImagePyramid[%d]" % l
     nm, = struct.unpack_from("<i", b, p); p += 4
     m = np.frombuffer(b, dtype=np.int32, count=n, offset=p); p += 4 * n
-    d01, = struct.unpack_from("<i", b, p)
+    d01, = struct.unpack_from("<i", b, p); p += 4
     bi, bd, sd = O.match_bruteforce(odesc, odesc)
     acc = (bd <= 50) & (bd.astype(np.float32) < np.float32(0.9) * sd.astype(np.float32))
     assert nm == int(acc.sum())
     assert np.array_equal(m, np.where(acc, bi, -1))
     assert d01 == O.descriptor_distance(odesc[0], odesc[1])
+    # map-side searches through the C++ wrappers (Fuse x2, SearchBySim3) against the oracle on the same re-projection
+    bounds = (0.0, float(w), 0.0, float(h))
+    sf, _, _, isg = oe.scale_tables()
+    xy = np.stack([okps["x"] + np.float32(1.0), okps["y"]], 1).astype(np.float32)
+    ur, xr = np.full(n, -1, np.float32), np.full(n, -1, np.float32)
+    for th, chi2 in [(3.0, True), (4.0, False)]:
+        nf, = struct.unpack_from("<i", b, p); p += 4
+        got = np.frombuffer(b, dtype=np.int32, count=n, offset=p); p += 4 * n
+        on, obi = O.fuse(okps, odesc, ur, bounds, sf, isg, xy, xr, okps["octave"], odesc, th, chi2)
+        assert nf == on and np.array_equal(got, obi)
+        assert nf > n // 2
+    ns, = struct.unpack_from("<i", b, p); p += 4
+    got = np.frombuffer(b, dtype=np.int32, count=n, offset=p); p += 4 * n
+    on, om = O.search_by_sim3(okps, odesc, okps, odesc, bounds, sf, xy, okps["octave"], odesc, xy, okps["octave"], odesc, 7.5)
+    assert ns == on and np.array_equal(got, om)
+    assert ns > n // 2
