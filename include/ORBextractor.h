@@ -40,11 +40,30 @@ public:
     {
         if (image.empty()) return;                                    // :1046-1047
         cv::Mat im = image.getMat();
+        run(im.ptr<uint8_t>(0), im.cols, im.rows, im.step, 1, false, keypoints, descriptors);
+    }
+
+    // The same on a colour image: cvtColor(im, im, CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImage*
+    // (Tracking.cc:280-305, :320-334, :350-364) runs on the device in front of the pyramid; channels = 3 or 4, bRGB = mbRGB.
+    // mvImagePyramid[0] is then the grey image the reference would have produced.
+    void ExtractColor(const uint8_t* data, int cols, int rows, size_t step, int channels, bool bRGB, std::vector<cv::KeyPoint>& keypoints,
+                      cv::OutputArray descriptors)
+    {
+        if (!data || cols <= 0 || rows <= 0) return;
+        run(data, cols, rows, step, channels, bRGB, keypoints, descriptors);
+    }
+
+private:
+    void run(const uint8_t* data, int cols, int rows, size_t step, int channels, bool bRGB, std::vector<cv::KeyPoint>& keypoints,
+             cv::OutputArray descriptors)
+    {
         int cap = orbx_max_keypoints(h_), n = 0;
         for (int attempt = 0; attempt < 2; attempt++) {
             kbuf_.resize(cap);
             dbuf_.resize((size_t)cap * 32);
-            const int rc = orbx_extract(h_, im.ptr<uint8_t>(0), im.cols, im.rows, im.step, kbuf_.data(), dbuf_.data(), cap, &n);
+            const uint8_t* one[1] = {data};
+            const int rc = channels == 1 ? orbx_extract(h_, data, cols, rows, step, kbuf_.data(), dbuf_.data(), cap, &n)
+                                         : orbx_extract_color_batch(h_, one, 1, cols, rows, step, channels, bRGB, kbuf_.data(), dbuf_.data(), cap, &n);
             if (rc == ORBX_OK) break;
             if (rc != ORBX_ERR_CAPACITY || attempt == 1) fail("orbx_extract");
             cap = n;
@@ -73,6 +92,8 @@ public:
                 if (orbx_pyramid_level(h_, 0, l, 0, mvImagePyramid[l].ptr<uint8_t>(0), mvImagePyramid[l].step) != ORBX_OK) fail("orbx_pyramid_level");
             }
     }
+
+public:
 
     int inline GetLevels() { return nlevels_; }
     float inline GetScaleFactor() { return scaleFactor_; }

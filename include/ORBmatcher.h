@@ -310,6 +310,35 @@ public:
         return best;
     }
 
+    // ---- Frame glue (the per-keypoint maps of the Frame constructors).  K4 = (fx, fy, cx, cy); distCoef = mDistCoef as floats
+    // (k1, k2, p1, p2[, k3]).
+    // Frame::UndistortKeyPoints (Frame.cc:419-449): mvKeysUn from mvKeys.
+    void UndistortKeyPoints(const std::vector<cv::KeyPoint>& vKeys, const float K4[4], const std::vector<float>& distCoef,
+                            std::vector<cv::KeyPoint>& vKeysUn)
+    {
+        std::vector<orbx_kp> k = pack(vKeys), u(k.size());
+        if (orbm_undistort_keypoints(m_, k.data(), (int)k.size(), K4[0], K4[1], K4[2], K4[3], distCoef.data(), (int)distCoef.size(), u.data()) != ORBX_OK)
+            fail("orbm_undistort_keypoints");
+        vKeysUn = vKeys;
+        for (size_t i = 0; i < u.size(); i++) { vKeysUn[i].pt.x = u[i].x; vKeysUn[i].pt.y = u[i].y; }
+    }
+    // Frame::ComputeImageBounds (Frame.cc:451-479): bounds4 = (mnMinX, mnMaxX, mnMinY, mnMaxY).
+    void ComputeImageBounds(int cols, int rows, const float K4[4], const std::vector<float>& distCoef, float bounds4[4])
+    {
+        if (orbm_image_bounds(m_, cols, rows, K4[0], K4[1], K4[2], K4[3], distCoef.data(), (int)distCoef.size(), bounds4) != ORBX_OK)
+            fail("orbm_image_bounds");
+    }
+    // Frame::ComputeStereoFromRGBD (Frame.cc:658-679): imDepth = CV_32F image (data pointer, size, row step in bytes).
+    void ComputeStereoFromRGBD(const std::vector<cv::KeyPoint>& vKeys, const std::vector<cv::KeyPoint>& vKeysUn, const float* imDepth, int cols,
+                               int rows, size_t step, float bf, std::vector<float>& vuRight, std::vector<float>& vDepth)
+    {
+        std::vector<orbx_kp> k = pack(vKeys), u = pack(vKeysUn);
+        vuRight.assign(k.size(), -1.0f);
+        vDepth.assign(k.size(), -1.0f);
+        if (orbm_stereo_from_rgbd(m_, k.data(), u.data(), (int)k.size(), imDepth, cols, rows, step, bf, vuRight.data(), vDepth.data()) != ORBX_OK)
+            fail("orbm_stereo_from_rgbd");
+    }
+
     // Frame::ComputeStereoMatches (Frame.cc:481-655): fills mvuRight / mvDepth, returns the surviving matches.  maxD is
     // explicit: the reference reads an uninitialised mb there (Frame.cc:511 vs :114); the intended value is fx.
     int ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<cv::KeyPoint>& keysLeft, const cv::Mat& descLeft,

@@ -86,6 +86,16 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, in
  * apart; pitch must be a multiple of 4).  Enqueues the whole extraction on the handle's stream and returns without
  * synchronising; results stay in the handle's device workspace until orbx_fetch / the next extract call. */
 int orbx_extract_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w, int h, size_t pitch, size_t frame_stride);
+/* Colour input: cvtColor(im, im, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) of Tracking::GrabImageStereo / RGBD /
+ * Monocular (src/Tracking.cc:280-305, :320-334, :350-364) fused into the ingestion: channels = 3 or 4 interleaved bytes per
+ * pixel, rgb = 1 when byte 0 is red (mbRGB), 0 when it is blue.  OpenCV's 8-bit arithmetic, (R*9798 + G*19235 + B*3735 + 2^14) >> 15,
+ * bit-exact; then exactly orbx_extract_batch / orbx_extract_device on the grey planes (which the handle owns: orbx_pyramid_level 0
+ * returns the grey image).  Device form: pointer, pitch and frame stride multiples of 4 (3 channels) or 16 (4 channels). */
+int orbx_extract_color_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, int w, int h, size_t stride, int channels, int rgb,
+                             orbx_kp* kps, uint8_t* desc, int cap, int* n);
+int orbx_extract_color_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w, int h, size_t pitch, size_t frame_stride,
+                              int channels, int rgb);
+
 /* Waits for the handle's stream and copies the results of the last orbx_extract_device call to HOST buffers laid out
  * as in orbx_extract_batch. */
 int orbx_fetch(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, int* n);
@@ -299,6 +309,21 @@ int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_extractor* r
  * count; nmatched: B ints. */
 int orbm_stereo_matches_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float bf, float minD, float maxD,
                               float* uRight, float* depth, int cap, int* nmatched);
+
+/* ---- Frame glue between the extractor and the matcher (src/Frame.cc). ----
+ * cv::undistortPoints(pts, pts, mK, mDistCoef, cv::Mat(), mK) as called at src/Frame.cc:438 and :464: dist = (k1, k2, p1, p2[, k3, ...]),
+ * 4 to 12 coefficients, OpenCV's 5-iteration fixed point in double precision; bit-exact against cv2 4.13 on the golden vectors. */
+int orbm_undistort_points(orbx_matcher* m, const float* pts, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist,
+                          float* out);
+/* Frame::UndistortKeyPoints (src/Frame.cc:419-449): out = mvKeysUn (a copy of kps when k1 == 0; out may alias kps). */
+int orbm_undistort_keypoints(orbx_matcher* m, const orbx_kp* kps, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist,
+                             orbx_kp* out);
+/* Frame::ComputeImageBounds (src/Frame.cc:451-479): bounds4 = (mnMinX, mnMaxX, mnMinY, mnMaxY). */
+int orbm_image_bounds(orbx_matcher* m, int cols, int rows, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* bounds4);
+/* Frame::ComputeStereoFromRGBD (src/Frame.cc:658-679): im_depth = the CV_32F depth image (h rows of w floats, stride_bytes apart);
+ * u_right / depth receive n floats (-1 where the depth is not positive). */
+int orbm_stereo_from_rgbd(orbx_matcher* m, const orbx_kp* kps, const orbx_kp* kps_un, int n, const float* im_depth, int w, int h,
+                          size_t stride_bytes, float bf, float* u_right, float* depth);
 
 /* Text of the last error raised on the calling thread ("" if none). */
 const char* orbx_last_error(void);

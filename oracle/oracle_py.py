@@ -88,6 +88,11 @@ def lib():
         L.orbo_distinctive_descriptor.restype = i
         L.orbo_distinctive_descriptor.argtypes = [vp, i]
         L.orbo_distinctive_descriptors.argtypes = [vp, vp, i, vp]
+        L.orbo_cvt_gray.argtypes = [vp, i, i, sz, i, i, vp, sz]
+        L.orbo_undistort_points.argtypes = [vp, i, f, f, f, f, vp, i, vp]
+        L.orbo_undistort_keypoints.argtypes = [vp, i, f, f, f, f, vp, i, vp]
+        L.orbo_image_bounds.argtypes = [i, i, f, f, f, f, vp, i, vp]
+        L.orbo_stereo_from_rgbd.argtypes = [vp, vp, i, vp, sz, f, vp, vp]
         L.orbo_stereo_matches.restype = i
         L.orbo_stereo_matches.argtypes = [vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, f, f, f, vp, vp]
         _lib = L
@@ -403,6 +408,47 @@ def search_for_triangulation(k1, d1, has_mp1, u_right1, fv1, k2, d2, has_mp2, u_
                                             _p(F), float(epipole[0]), float(epipole[1]), _p(sf2), _p(sg), len(sf2),
                                             int(only_stereo), int(checkOri), _p(out))
     return n, out[:len(k1)]
+
+
+def cvt_gray(img, rgb=True):
+    """cvtColor(img, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) (Tracking.cc:280-305); img: H x W x (3|4) uint8."""
+    img = _u8(img)
+    h, w, cn = img.shape
+    out = np.zeros((h, w), np.uint8)
+    lib().orbo_cvt_gray(_p(img), w, h, img.strides[0], cn, int(rgb), _p(out), w)
+    return out
+
+
+def undistort_points(pts, K4, dist):
+    """cv::undistortPoints(pts, K, dist, noArray(), K) (Frame.cc:438); K4 = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+    pts, dist = _f32(pts).reshape(-1, 2), _f32(dist).reshape(-1)
+    out = np.zeros_like(pts)
+    lib().orbo_undistort_points(_p(pts), len(pts), *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out))
+    return out
+
+
+def undistort_keypoints(kps, K4, dist):
+    """Frame::UndistortKeyPoints (Frame.cc:419-449) -> mvKeysUn."""
+    kps, dist = np.ascontiguousarray(kps), _f32(dist).reshape(-1)
+    out = np.zeros_like(kps)
+    lib().orbo_undistort_keypoints(_p(kps), len(kps), *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out))
+    return out
+
+
+def image_bounds(cols, rows, K4, dist):
+    """Frame::ComputeImageBounds (Frame.cc:451-479) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    dist = _f32(dist).reshape(-1)
+    out = np.zeros(4, np.float32)
+    lib().orbo_image_bounds(cols, rows, *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out))
+    return out
+
+
+def stereo_from_rgbd(kps, kps_un, im_depth, bf):
+    """Frame::ComputeStereoFromRGBD (Frame.cc:658-679) -> (mvuRight, mvDepth)."""
+    kps, kps_un, im = np.ascontiguousarray(kps), np.ascontiguousarray(kps_un), _f32(im_depth)
+    uR, dep = np.zeros(len(kps), np.float32), np.zeros(len(kps), np.float32)
+    lib().orbo_stereo_from_rgbd(_p(kps), _p(kps_un), len(kps), _p(im), im.strides[0], float(bf), _p(uR), _p(dep))
+    return uR, dep
 
 
 def distinctive_descriptors(desc, off):

@@ -768,4 +768,75 @@ void orbo_distinctive_descriptors(const uint8_t* desc, const int* off, int npoin
     for (int p = 0; p < npoints; p++) best[p] = orbo_distinctive_descriptor(desc + 32 * (size_t)off[p], off[p + 1] - off[p]);
 }
 
+
+// ---- Frame glue around the extractor (Frame.cc:419-479, :658-679).
+// cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) (Frame.cc:438, :464): OpenCV is an un-vendored dependency; this is its
+// published algorithm (calib3d undistortPoints, 5 fixed-point iterations, no EPS test with the default TermCriteria(MAX_ITER, 5, 0.01)),
+// in double, checked bit for bit against cv2 4.13.0 on tests/golden/undistort_s9000.npz.  dist = (k1, k2, p1, p2[, k3]).
+void orbo_undistort_points(const float* pts, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* out)
+{
+    double k[12] = {0};
+    for (int i = 0; i < ndist && i < 12; i++) k[i] = dist[i];
+    const double dfx = fx, dfy = fy, dcx = cx, dcy = cy, ifx = 1.0 / dfx, ify = 1.0 / dfy;
+    for (int i = 0; i < n; i++) {
+        const double u = pts[2 * i], v = pts[2 * i + 1];
+        double x = (u - dcx) * ifx, y = (v - dcy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - dcx) * ifx; y = (v - dcy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        out[2 * i] = (float)(dfx * x + dcx);
+        out[2 * i + 1] = (float)(dfy * y + dcy);
+    }
+}
+
+// Frame::UndistortKeyPoints (Frame.cc:419-449): mvKeysUn = mvKeys when k1 == 0, else the same keypoints with pt undistorted.
+void orbo_undistort_keypoints(const orbo_kp* kps, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist, orbo_kp* out)
+{
+    for (int i = 0; i < n; i++) out[i] = kps[i];
+    if (dist[0] == 0.0) return;
+    std::vector<float> mat(2 * (size_t)n), und(2 * (size_t)n);
+    for (int i = 0; i < n; i++) { mat[2 * i] = kps[i].x; mat[2 * i + 1] = kps[i].y; }
+    orbo_undistort_points(mat.data(), n, fx, fy, cx, cy, dist, ndist, und.data());
+    for (int i = 0; i < n; i++) { out[i].x = und[2 * i]; out[i].y = und[2 * i + 1]; }
+}
+
+// Frame::ComputeImageBounds (Frame.cc:451-479) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)
+void orbo_image_bounds(int cols, int rows, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* bounds4)
+{
+    if (dist[0] != 0.0) {
+        const float mat[8] = {0.0f, 0.0f, (float)cols, 0.0f, 0.0f, (float)rows, (float)cols, (float)rows};
+        float u[8];
+        orbo_undistort_points(mat, 4, fx, fy, cx, cy, dist, ndist, u);
+        bounds4[0] = std::min(u[0], u[4]);
+        bounds4[1] = std::max(u[2], u[6]);
+        bounds4[2] = std::min(u[1], u[3]);
+        bounds4[3] = std::max(u[5], u[7]);
+    } else {
+        bounds4[0] = 0.0f; bounds4[1] = (float)cols; bounds4[2] = 0.0f; bounds4[3] = (float)rows;
+    }
+}
+
+// Frame::ComputeStereoFromRGBD (Frame.cc:658-679): imDepth.at<float>(v, u) with float v, u truncates to int indices.
+void orbo_stereo_from_rgbd(const orbo_kp* kps, const orbo_kp* kps_un, int n, const float* im_depth, size_t stride_bytes, float bf,
+                           float* u_right, float* depth)
+{
+    for (int i = 0; i < n; i++) {
+        u_right[i] = -1;
+        depth[i] = -1;
+        const float v = kps[i].y, u = kps[i].x;
+        const float d = *(const float*)((const uint8_t*)im_depth + (size_t)(int)v * stride_bytes + sizeof(float) * (size_t)(int)u);
+        if (d > 0) {
+            depth[i] = d;
+            u_right[i] = kps_un[i].x - bf / d;
+        }
+    }
+}
+
 } // extern "C"

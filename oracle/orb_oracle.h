@@ -58,6 +58,8 @@ void orbo_gauss7(const uint8_t* src, int w, int h, size_t sstride, uint8_t* dst,
 // cv::FAST(roi, kps, threshold, true) on a w x h view; writes x,y,response triples; returns count.
 int orbo_fast(const uint8_t* roi, int w, int h, size_t stride, int threshold, int nms, int* xyr, int cap);
 float orbo_fast_atan2(float y, float x);
+/* cvtColor RGB/BGR/RGBA/BGRA -> GRAY, OpenCV 8-bit fixed point (Tracking.cc:280-305) */
+void orbo_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels, int rgb, uint8_t* dst, size_t dstride);
 // DistributeOctTree alone (ORBextractor.cc:539-763): in xyr triples -> selected indices (into the input) in output order.
 int orbo_distribute(const int* xyr, int n, int minX, int maxX, int minY, int maxY, int N, int tie_mode, int* out_idx, int cap);
 
@@ -135,6 +137,14 @@ int orbo_search_for_triangulation(const orbo_kp* k1, const uint8_t* d1, int n1, 
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:281-311): index of the descriptor with the least median distance */
 int orbo_distinctive_descriptor(const uint8_t* desc, int n);
 void orbo_distinctive_descriptors(const uint8_t* desc, const int* off, int npoints, int* best);
+
+/* Frame glue: cv::undistortPoints as called at Frame.cc:438/:464, Frame::UndistortKeyPoints (:419-449), ComputeImageBounds
+ * (:451-479), ComputeStereoFromRGBD (:658-679) */
+void orbo_undistort_points(const float* pts, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* out);
+void orbo_undistort_keypoints(const orbo_kp* kps, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist, orbo_kp* out);
+void orbo_image_bounds(int cols, int rows, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* bounds4);
+void orbo_stereo_from_rgbd(const orbo_kp* kps, const orbo_kp* kps_un, int n, const float* im_depth, size_t stride_bytes, float bf,
+                           float* u_right, float* depth);
 
 int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl,
                         const orbo_kp* kr, const uint8_t* dr, int nr,

@@ -217,4 +217,18 @@ int orbo_fast(const uint8_t* roi, int w, int h, size_t stride, int threshold, in
     return n;
 }
 float orbo_fast_atan2(float y, float x) { return orbo::fast_atan2(y, x); }
+
+// cvtColor(src, dst, CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) as called by Tracking::GrabImage* (Tracking.cc:280-305,
+// :320-334, :350-364).  OpenCV (un-vendored dependency; arithmetic checked against cv2 4.13.0, tests/golden/cvtcolor_*.npz):
+// 8-bit path RGB2Gray<uchar>, coefficients RY15 = 9798, GY15 = 19235, BY15 = 3735, CV_DESCALE(x, 15) = (x + (1 << 14)) >> 15.
+void orbo_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels, int rgb, uint8_t* dst, size_t dstride)
+{
+    const int cr = 9798, cg = 19235, cb = 3735;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            const uint8_t* p = src + (size_t)y * sstride + (size_t)x * channels;
+            const int r = rgb ? p[0] : p[2], g = p[1], b = rgb ? p[2] : p[0];
+            dst[(size_t)y * dstride + x] = (uint8_t)((r * cr + g * cg + b * cb + (1 << 14)) >> 15);
+        }
+}
 }

@@ -6,6 +6,7 @@
 // All arithmetic that decides a keypoint or a descriptor bit is integer or individually-rounded float
 // (__fmul_rn/__fadd_rn/__fdiv_rn): nvcc must not contract anything here.
 #include "extract_kernels.cuh"
+#include <algorithm>
 #include "sincosf_glibc.h"
 #include <float.h>
 
@@ -962,6 +963,58 @@ void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int s
 {
     dim3 blk(32, 8), grd((w + 2 * border + 31) / 32, (h + 2 * border + 7) / 8);
     k_reflect_copy<<<grd, blk, 0, s>>>(src, w, h, spitch, dst, border, dpitch);
+}
+
+// ------------------------------------------------------------------------------------------------ grey conversion
+// cvtColor(im, im, CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of Tracking::GrabImage* (src/Tracking.cc:280-305, :320-334,
+// :350-364) written straight into the level-0 planes.  OpenCV's 8-bit path: (R*9798 + G*19235 + B*3735 + (1 << 14)) >> 15.
+// A thread makes 4 output pixels (one word) from 3 (CN = 3) or 4 (CN = 4) input words.
+__device__ __forceinline__ uint32_t gray1(uint32_t px, int c0, int c1, int c2)
+{
+    return ((px & 0xFF) * c0 + ((px >> 8) & 0xFF) * c1 + ((px >> 16) & 0xFF) * c2 + (1 << 14)) >> 15;
+}
+
+template <int CN>
+__global__ void __launch_bounds__(256) k_gray(const uint8_t* __restrict__ src, size_t spitch, size_t sframe, uint8_t* __restrict__ dst,
+                                               int w, int h, size_t dpitch, size_t dframe, int c0, int c1, int c2)
+{
+    const int w4 = (w + 3) >> 2;
+    const uint8_t* sf = src + blockIdx.y * sframe;
+    uint8_t* df = dst + blockIdx.y * dframe;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < w4 * h; i += gridDim.x * blockDim.x) {
+        const int y = i / w4, x4 = i - y * w4;
+        const uint8_t* row = sf + (size_t)y * spitch + (size_t)x4 * 4 * CN;
+        uint32_t p0, p1, p2, p3;
+        if (4 * x4 + 4 <= w) {
+            const uint32_t* r32 = reinterpret_cast<const uint32_t*>(row);
+            if (CN == 4) {
+                const uint4 v = *reinterpret_cast<const uint4*>(row);
+                p0 = v.x; p1 = v.y; p2 = v.z; p3 = v.w;
+            } else {
+                const uint32_t a = r32[0], b = r32[1], c = r32[2];
+                p0 = a;
+                p1 = __byte_perm(a, b, 0x6543);
+                p2 = __byte_perm(b, c, 0x5432);
+                p3 = c >> 8;
+            }
+        } else {                                  // ragged last word of a row: byte loads, never past w * CN
+            uint32_t px[4] = {0, 0, 0, 0};
+            for (int k = 0; k < w - 4 * x4; k++) px[k] = row[CN * k] | (row[CN * k + 1] << 8) | (row[CN * k + 2] << 16);
+            p0 = px[0]; p1 = px[1]; p2 = px[2]; p3 = px[3];
+        }
+        const uint32_t g = gray1(p0, c0, c1, c2) | (gray1(p1, c0, c1, c2) << 8) | (gray1(p2, c0, c1, c2) << 16) | (gray1(p3, c0, c1, c2) << 24);
+        *reinterpret_cast<uint32_t*>(df + (size_t)y * dpitch + 4 * x4) = g;
+    }
+}
+
+void launch_gray(cudaStream_t s, const uint8_t* src, size_t spitch, size_t sframe, uint8_t* dst, int w, int h, size_t dpitch, size_t dframe,
+                 int channels, int rgb, int B)
+{
+    const int c0 = rgb ? 9798 : 3735, c1 = 19235, c2 = rgb ? 3735 : 9798;      // RY15, GY15, BY15 in memory order
+    const int w4 = (w + 3) >> 2;
+    dim3 grd(std::min((w4 * h + 255) / 256, 148 * 8), B);
+    if (channels == 4) k_gray<4><<<grd, 256, 0, s>>>(src, spitch, sframe, dst, w, h, dpitch, dframe, c0, c1, c2);
+    else k_gray<3><<<grd, 256, 0, s>>>(src, spitch, sframe, dst, w, h, dpitch, dframe, c0, c1, c2);
 }
 
 }  // namespace orbx

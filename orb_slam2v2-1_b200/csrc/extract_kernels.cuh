@@ -44,6 +44,10 @@ void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, c
 // padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
 void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch);
 
+// cvtColor RGB(A)/BGR(A) -> GRAY (Tracking.cc:280-305) of B frames into level-0 planes; src rows 4-byte aligned (16 for 4 channels)
+void launch_gray(cudaStream_t s, const uint8_t* src, size_t spitch, size_t sframe, uint8_t* dst, int w, int h, size_t dpitch, size_t dframe,
+                 int channels, int rgb, int B);
+
 size_t fast_smem_bytes(const Plan& P);
 size_t octree_smem_bytes(int capS, int sortCap);
 

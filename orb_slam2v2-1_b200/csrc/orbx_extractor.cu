@@ -70,6 +70,8 @@ struct orbx_extractor {
     uint8_t* h_in = nullptr;           // pinned staging
     uint8_t* h_out = nullptr;
     size_t h_in_bytes = 0, h_out_bytes = 0;
+    uint8_t* d_color = nullptr;        // colour staging of the host-input path (orbx_extract_color_batch)
+    size_t colorBytes = 0;
     uint8_t* d_scratch = nullptr;      // copy-out scratch (padded level)
     size_t scratchBytes = 0;
 
@@ -86,6 +88,7 @@ static void free_shape(orbx_extractor* ex)
     cudaFree(ex->d_xtab); ex->d_xtab = nullptr;
     cudaFree(ex->d_ytab); ex->d_ytab = nullptr;
     cudaFree(ex->d_lv0); ex->d_lv0 = nullptr;
+    cudaFree(ex->d_color); ex->d_color = nullptr; ex->colorBytes = 0;
     cudaFree(ex->d_pool); ex->d_pool = nullptr;
     cudaFree(ex->d_scratch); ex->d_scratch = nullptr; ex->scratchBytes = 0;
     if (ex->h_in) cudaFreeHost(ex->h_in);
@@ -575,6 +578,68 @@ int orbx_extract_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w,
     ex->bufs.lv0Pitch = pitch;
     ex->bufs.lv0Frame = frame_stride;
     return enqueue(ex, B);
+}
+
+static int fetch_impl(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, int* n);
+
+static int color_args_ok(const char* who, int channels)
+{
+    if (channels != 3 && channels != 4) { set_error("%s: channels must be 3 or 4", who); return 0; }
+    return 1;
+}
+
+int orbx_extract_color_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w, int h, size_t pitch, size_t frame_stride,
+                              int channels, int rgb)
+{
+    if (!ex || !d_imgs || B < 1 || w <= 0 || h <= 0) { set_error("orbx_extract_color_device: bad argument"); return ORBX_ERR_ARG; }
+    if (!color_args_ok("orbx_extract_color_device", channels)) return ORBX_ERR_ARG;
+    const size_t al = channels == 4 ? 16 : 4;
+    if ((pitch % al) || (frame_stride % al) || ((uintptr_t)d_imgs % al) || pitch < (size_t)w * channels) {
+        set_error("orbx_extract_color_device: pointer, pitch and frame stride must be multiples of %d and pitch >= w * channels", (int)al);
+        return ORBX_ERR_ARG;
+    }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    int rc = ensure_shape(ex, w, h, B);
+    if (rc) return rc;
+    launch_gray(ex->stream, d_imgs, pitch, frame_stride, ex->d_lv0, w, h, ex->lv0Pitch, ex->lv0Frame, channels, rgb, B);
+    ex->bufs.lv0 = ex->d_lv0;
+    ex->bufs.lv0Pitch = ex->lv0Pitch;
+    ex->bufs.lv0Frame = ex->lv0Frame;
+    rc = enqueue(ex, B);
+    if (rc) return rc;
+    ex->lastLaunches += 1;
+    return ORBX_OK;
+}
+
+int orbx_extract_color_batch(orbx_extractor* ex, const uint8_t* const* imgs, int B, int w, int h, size_t stride, int channels, int rgb,
+                             orbx_kp* kps, uint8_t* desc, int cap, int* n)
+{
+    if (!ex || !imgs || B < 1 || cap < 0) { set_error("orbx_extract_color_batch: bad argument"); return ORBX_ERR_ARG; }
+    if (!color_args_ok("orbx_extract_color_batch", channels)) return ORBX_ERR_ARG;
+    if (w <= 0 || h <= 0) {
+        if (n) for (int b = 0; b < B; b++) n[b] = 0;
+        return ORBX_OK;
+    }
+    if (stride < (size_t)w * channels) { set_error("orbx_extract_color_batch: stride < w * channels"); return ORBX_ERR_ARG; }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    int rc = ensure_shape(ex, w, h, B);
+    if (rc) return rc;
+    const size_t cpitch = align_up((size_t)w * channels, 32), cframe = align_up(cpitch * h, 256);
+    if (ex->colorBytes < cframe * B) {
+        ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+        cudaFree(ex->d_color);
+        ex->d_color = nullptr;
+        ex->colorBytes = 0;
+        ORBX_CUDA(cudaMalloc(&ex->d_color, cframe * std::max(B, ex->maxBatch)));
+        ex->colorBytes = cframe * std::max(B, ex->maxBatch);
+    }
+    for (int b = 0; b < B; b++) {
+        if (!imgs[b]) { set_error("orbx_extract_color_batch: imgs[%d] is null", b); return ORBX_ERR_ARG; }
+        ORBX_CUDA(cudaMemcpy2DAsync(ex->d_color + (size_t)b * cframe, cpitch, imgs[b], stride, (size_t)w * channels, h, cudaMemcpyHostToDevice, ex->stream));
+    }
+    rc = orbx_extract_color_device(ex, ex->d_color, B, w, h, cpitch, cframe, channels, rgb);
+    if (rc) return rc;
+    return fetch_impl(ex, kps, desc, cap, n);
 }
 
 // copies the packed output block (counts | kps | desc) of the last call to the pinned buffer and unpacks it

@@ -91,6 +91,12 @@ def lib():
         "orbm_search_for_triangulation": (i, [vp, vp, vp, i, vp, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, i, vp, f, f, vp, vp, i,
                                               i, i, vp, vp]),
         "orbm_distinctive_descriptors": (i, [vp, vp, vp, i, vp]),
+        "orbx_extract_color_batch": (i, [vp, vp, i, i, i, C.c_size_t, i, i, vp, vp, i, vp]),
+        "orbx_extract_color_device": (i, [vp, vp, i, i, i, C.c_size_t, C.c_size_t, i, i]),
+        "orbm_undistort_points": (i, [vp, vp, i, f, f, f, f, vp, i, vp]),
+        "orbm_undistort_keypoints": (i, [vp, vp, i, f, f, f, f, vp, i, vp]),
+        "orbm_image_bounds": (i, [vp, i, i, f, f, f, f, vp, i, vp]),
+        "orbm_stereo_from_rgbd": (i, [vp, vp, vp, i, vp, i, i, C.c_size_t, f, vp, vp]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
     }
@@ -224,6 +230,32 @@ class ORBextractor:
                 break
             cap = int(n.max())
         return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
+
+    def extract_color_batch(self, images, rgb=True):
+        """images: sequence of equally-shaped H x W x (3|4) uint8 arrays (RGB(A) when rgb, else BGR(A)): grey conversion
+        (Tracking.cc:280-305) + extraction on the device -> list of (kps, desc)."""
+        imgs = [_u8(im) for im in images]
+        B = len(imgs)
+        hh, ww, cn = imgs[0].shape
+        assert all(im.shape == (hh, ww, cn) for im in imgs)
+        ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
+        cap = max(self.max_keypoints(), 64)
+        for _ in range(2):
+            kps = np.zeros((B, cap), KP_DTYPE)
+            desc = np.zeros((B, cap, 32), np.uint8)
+            n = np.zeros(B, np.int32)
+            rc = _check(self._L.orbx_extract_color_batch(self._h, ptrs, B, ww, hh, ww * cn, cn, int(rgb), _p(kps), _p(desc), cap, _p(n)),
+                        allow=(ERR_CAPACITY,))
+            self.last_batch = B
+            if rc == OK:
+                break
+            cap = int(n.max())
+        return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
+
+    def extract_color_device(self, d_ptr, B, w, h, pitch, frame_stride, channels, rgb=True):
+        """Device-resident colour frames: grey conversion into the handle's level-0 planes, then the extraction (no synchronisation)."""
+        _check(self._L.orbx_extract_color_device(self._h, C.c_void_p(d_ptr), B, w, h, pitch, frame_stride, channels, int(rgb)))
+        self.last_batch = B
 
     def extract_device(self, d_ptr, B, w, h, pitch, frame_stride):
         """Enqueue extraction of B device-resident frames on the handle's stream (no synchronisation)."""
@@ -578,6 +610,43 @@ def _distinctive_descriptors(self, desc, off):
 
 
 ORBmatcher.ComputeDistinctiveDescriptors = _distinctive_descriptors
+def _undistort_points(self, pts, K4, dist):
+    """cv::undistortPoints(pts, K, dist, noArray(), K) as used by Frame (src/Frame.cc:438, :464); K4 = (fx, fy, cx, cy)."""
+    pts, dist = _f32(pts).reshape(-1, 2), _f32(dist).reshape(-1)
+    out = np.zeros_like(pts)
+    _check(self._L.orbm_undistort_points(self._h, _p(pts), len(pts), *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out)))
+    return out
+
+
+def _undistort_keypoints(self, kps, K4, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:419-449) -> mvKeysUn."""
+    kps, dist = np.ascontiguousarray(kps, KP_DTYPE), _f32(dist).reshape(-1)
+    out = np.zeros_like(kps)
+    _check(self._L.orbm_undistort_keypoints(self._h, _p(kps), len(kps), *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out)))
+    return out
+
+
+def _image_bounds(self, cols, rows, K4, dist):
+    """Frame::ComputeImageBounds (src/Frame.cc:451-479) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    dist = _f32(dist).reshape(-1)
+    out = np.zeros(4, np.float32)
+    _check(self._L.orbm_image_bounds(self._h, cols, rows, *[float(np.float32(v)) for v in K4], _p(dist), len(dist), _p(out)))
+    return out
+
+
+def _stereo_from_rgbd(self, kps, kps_un, im_depth, bf):
+    """Frame::ComputeStereoFromRGBD (src/Frame.cc:658-679) -> (mvuRight, mvDepth)."""
+    kps, kps_un, im = np.ascontiguousarray(kps, KP_DTYPE), np.ascontiguousarray(kps_un, KP_DTYPE), _f32(im_depth)
+    uR, dep = np.zeros(len(kps), np.float32), np.zeros(len(kps), np.float32)
+    _check(self._L.orbm_stereo_from_rgbd(self._h, _p(kps), _p(kps_un), len(kps), _p(im), im.shape[1], im.shape[0], im.strides[0], float(bf),
+                                         _p(uR), _p(dep)))
+    return uR, dep
+
+
+ORBmatcher.UndistortPoints = _undistort_points
+ORBmatcher.UndistortKeyPoints = _undistort_keypoints
+ORBmatcher.ComputeImageBounds = _image_bounds
+ORBmatcher.ComputeStereoFromRGBD = _stereo_from_rgbd
 ORBmatcher.SearchInArea = _search_in_area
 ORBmatcher.last_launches = lambda self: self._L.orbm_last_launches(self._h)
 ORBmatcher.Fuse = _fuse
