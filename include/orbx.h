@@ -325,6 +325,25 @@ int orbm_image_bounds(orbx_matcher* m, int cols, int rows, float fx, float fy, f
 int orbm_stereo_from_rgbd(orbx_matcher* m, const orbx_kp* kps, const orbx_kp* kps_un, int n, const float* im_depth, int w, int h,
                           size_t stride_bytes, float bf, float* u_right, float* depth);
 
+/* ---- ORBVocabulary (include/ORBVocabulary.h:31-32 = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) ----
+ * The tree is handed over as arrays, numbered as loadFromTextFile numbers it (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1351-1436):
+ * node 0 = root, node i (file line i) has parent[i] < i, a 32-byte descriptor and a weight; children keep file order; the nodes
+ * without children are the words, numbered in file order.  scoring / weighting are DBoW2's enums (L1_NORM = 0 ... DOT_PRODUCT = 5;
+ * TF_IDF = 0, TF, IDF, BINARY).  Device memory: 40 bytes per node. */
+typedef struct orbx_vocabulary orbx_vocabulary;
+int orbv_create(int device, int k, int L, int scoring, int weighting, const int* parent, const uint8_t* desc, const double* weight, int nnodes,
+                orbx_vocabulary** out);
+void orbv_destroy(orbx_vocabulary* v);
+int orbv_size(const orbx_vocabulary* v);                  /* number of words, TemplatedVocabulary::size() */
+/* transform(feature, word_id, weight, nid, levelsup) (:1231-1270) for n descriptors in one launch.  node_id = the ancestor at level
+ * L - levelsup; for a leaf that sits above that level the reference leaves it uninitialised - here it is the leaf itself. */
+int orbv_transform_raw(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id, double* weight, int* node_id);
+/* transform(features, BowVector, FeatureVector, levelsup) (:1140-1207) as Frame::ComputeBoW calls it (src/Frame.cc:410-417, levelsup 4).
+ * BowVector: *nbow (id, value) pairs in map order into bow_id / bow_val (capacity n).  FeatureVector as CSR in map order: *nfv nodes
+ * into fv_node (capacity n), fv_off (capacity n + 1), feature indices into fv_idx (capacity n) - the layout orbm_search_by_bow takes. */
+int orbv_transform(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* bow_id, double* bow_val, int* nbow,
+                   int* fv_node, int* fv_off, int* fv_idx, int* nfv);
+
 /* Text of the last error raised on the calling thread ("" if none). */
 const char* orbx_last_error(void);
 /* Library/build identification, e.g. "orbx 0.1 sm_100a". */

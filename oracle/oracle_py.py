@@ -93,6 +93,12 @@ def lib():
         L.orbo_undistort_keypoints.argtypes = [vp, i, f, f, f, f, vp, i, vp]
         L.orbo_image_bounds.argtypes = [i, i, f, f, f, f, vp, i, vp]
         L.orbo_stereo_from_rgbd.argtypes = [vp, vp, i, vp, sz, f, vp, vp]
+        L.orbo_voc_create.restype = vp
+        L.orbo_voc_create.argtypes = [i, i, i, i, vp, vp, vp, i]
+        L.orbo_voc_destroy.argtypes = [vp]
+        L.orbo_voc_transform_raw.argtypes = [vp, vp, i, i, vp, vp, vp]
+        L.orbo_voc_transform.restype = i
+        L.orbo_voc_transform.argtypes = [vp, vp, i, i, vp, vp, vp, vp, vp, vp]
         L.orbo_stereo_matches.restype = i
         L.orbo_stereo_matches.argtypes = [vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, i, f, f, f, vp, vp]
         _lib = L
@@ -449,6 +455,38 @@ def stereo_from_rgbd(kps, kps_un, im_depth, bf):
     uR, dep = np.zeros(len(kps), np.float32), np.zeros(len(kps), np.float32)
     lib().orbo_stereo_from_rgbd(_p(kps), _p(kps_un), len(kps), _p(im), im.strides[0], float(bf), _p(uR), _p(dep))
     return uR, dep
+
+
+class OracleVocabulary:
+    """ORBVocabulary (DBoW2::TemplatedVocabulary<FORB>) over arrays: parent[i] of node i (node 0 = root), 32-byte node descriptors,
+    node weights.  scoring / weighting use DBoW2's enum values (L1_NORM = 0, TF_IDF = 0)."""
+
+    def __init__(self, k, L, parent, desc, weight, scoring=0, weighting=0):
+        self.parent, self.desc, self.weight = _i32(parent), _u8(desc), np.ascontiguousarray(weight, np.float64)
+        self.L = lib()
+        self.h = self.L.orbo_voc_create(k, L, scoring, weighting, _p(self.parent), _p(self.desc), _p(self.weight), len(self.parent))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orbo_voc_destroy(self.h)
+            self.h = None
+
+    def transform_raw(self, desc, levelsup=4):
+        desc = _u8(desc)
+        n = len(desc)
+        wid, nid, w = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        self.L.orbo_voc_transform_raw(self.h, _p(desc), n, levelsup, _p(wid), _p(w), _p(nid))
+        return wid[:n], w[:n], nid[:n]
+
+    def transform(self, desc, levelsup=4):
+        """-> (bow ids, bow values), (fv nodes, fv offsets, fv feature indices)"""
+        desc = _u8(desc)
+        n = len(desc)
+        bid, bval = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fo, fi = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nfv = C.c_int(0)
+        nb = self.L.orbo_voc_transform(self.h, _p(desc), n, levelsup, _p(bid), _p(bval), _p(fn), _p(fo), _p(fi), C.byref(nfv))
+        return (bid[:nb], bval[:nb]), (fn[:nfv.value], fo[:nfv.value + 1], fi[:fo[nfv.value]])
 
 
 def distinctive_descriptors(desc, off):

@@ -146,6 +146,14 @@ void orbo_image_bounds(int cols, int rows, float fx, float fy, float cx, float c
 void orbo_stereo_from_rgbd(const orbo_kp* kps, const orbo_kp* kps_un, int n, const float* im_depth, size_t stride_bytes, float bf,
                            float* u_right, float* depth);
 
+/* ORBVocabulary::transform (DBoW2 TemplatedVocabulary.h:1140-1270) on a tree given as arrays; see orb_vocabulary.cpp */
+typedef struct orbo_vocabulary orbo_vocabulary;
+orbo_vocabulary* orbo_voc_create(int k, int L, int scoring, int weighting, const int* parent, const uint8_t* desc, const double* weight, int nnodes);
+void orbo_voc_destroy(orbo_vocabulary* v);
+void orbo_voc_transform_raw(const orbo_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id, double* weight, int* node_id);
+int orbo_voc_transform(const orbo_vocabulary* voc, const uint8_t* desc, int n, int levelsup, int* bow_id, double* bow_val,
+                       int* fv_node, int* fv_off, int* fv_idx, int* nfv);
+
 int orbo_stereo_matches(const orbo_kp* kl, const uint8_t* dl, int nl,
                         const orbo_kp* kr, const uint8_t* dr, int nr,
                         const uint8_t* const* pyrL, const uint8_t* const* pyrR,

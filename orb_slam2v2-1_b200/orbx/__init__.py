@@ -97,6 +97,11 @@ def lib():
         "orbm_undistort_keypoints": (i, [vp, vp, i, f, f, f, f, vp, i, vp]),
         "orbm_image_bounds": (i, [vp, i, i, f, f, f, f, vp, i, vp]),
         "orbm_stereo_from_rgbd": (i, [vp, vp, vp, i, vp, i, i, C.c_size_t, f, vp, vp]),
+        "orbv_create": (i, [i, i, i, i, i, vp, vp, vp, i, vp]),
+        "orbv_destroy": (None, [vp]),
+        "orbv_size": (i, [vp]),
+        "orbv_transform_raw": (i, [vp, vp, i, i, vp, vp, vp]),
+        "orbv_transform": (i, [vp, vp, i, i, vp, vp, vp, vp, vp, vp, vp]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
     }
@@ -654,6 +659,68 @@ ORBmatcher.SearchBySim3 = _search_by_sim3
 ORBmatcher.SearchByProjectionSim3 = _search_by_projection_sim3
 ORBmatcher.SearchByProjectionKF = _search_by_projection_kf
 ORBmatcher.SearchForTriangulation = _search_for_triangulation
+
+
+class ORBVocabulary:
+    """Mirror of the reference's ORBVocabulary (include/ORBVocabulary.h:31-32, DBoW2::TemplatedVocabulary<FORB>) over the orbv_* C ABI:
+    the tree lives on the device, transform() descends all descriptors of a frame in one launch."""
+    L1_NORM, L2_NORM, CHI_SQUARE, KL, BHATTACHARYYA, DOT_PRODUCT = range(6)
+    TF_IDF, TF, IDF, BINARY = range(4)
+
+    def __init__(self, k, L, parent, desc, weight, scoring=0, weighting=0, device=0):
+        self._L = lib()
+        self._h = C.c_void_p()
+        self.k, self.L, self.scoring, self.weighting = k, L, scoring, weighting
+        parent, desc, weight = _i32(parent), _u8(desc).reshape(-1, 32), np.ascontiguousarray(weight, np.float64)
+        _check(self._L.orbv_create(device, k, L, scoring, weighting, _p(parent), _p(desc), _p(weight), len(parent), C.byref(self._h)))
+
+    def __del__(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._L.orbv_destroy(self._h)
+            self._h = C.c_void_p()
+
+    @staticmethod
+    def parse_text(filename):
+        """The ORBvoc.txt format of loadFromTextFile (TemplatedVocabulary.h:1351-1436): header `k L scoring weighting`, then one line
+        per node: parent, is-leaf flag, 32 descriptor bytes, weight.  Returns (k, L, scoring, weighting, parent, desc, weight)."""
+        with open(filename) as f:
+            k, L, scoring, weighting = [int(t) for t in f.readline().split()[:4]]
+            parent, desc, weight = [0], [np.zeros(32, np.uint8)], [0.0]
+            for line in f:
+                t = line.split()
+                if len(t) < 35:
+                    continue
+                parent.append(int(t[0]))
+                desc.append(np.array([int(b) for b in t[2:34]], np.uint8))
+                weight.append(float(t[34]))
+        return k, L, scoring, weighting, np.asarray(parent, np.int32), np.stack(desc), np.asarray(weight, np.float64)
+
+    @classmethod
+    def loadFromTextFile(cls, filename, device=0):
+        k, L, scoring, weighting, parent, desc, weight = cls.parse_text(filename)
+        return cls(k, L, parent, desc, weight, scoring, weighting, device)
+
+    def size(self):
+        return self._L.orbv_size(self._h)
+
+    def transform_raw(self, desc, levelsup=4):
+        """Per-descriptor (word id, weight, node id at level L - levelsup)."""
+        desc = _u8(desc).reshape(-1, 32)
+        n = len(desc)
+        wid, nid, w = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        _check(self._L.orbv_transform_raw(self._h, _p(desc), n, levelsup, _p(wid), _p(w), _p(nid)))
+        return wid[:n], w[:n], nid[:n]
+
+    def transform(self, desc, levelsup=4):
+        """transform(features, BowVec, FeatVec, levelsup) (src/Frame.cc:410-417) -> ((bow ids, bow values), (fv nodes, offsets, indices));
+        the second tuple is the CSR form ORBmatcher.SearchByBoW takes."""
+        desc = _u8(desc).reshape(-1, 32)
+        n = len(desc)
+        bid, bval = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64)
+        fn, fo, fi = np.zeros(max(n, 1), np.int32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nb, nf = C.c_int(0), C.c_int(0)
+        _check(self._L.orbv_transform(self._h, _p(desc), n, levelsup, _p(bid), _p(bval), C.byref(nb), _p(fn), _p(fo), _p(fi), C.byref(nf)))
+        return (bid[:nb.value], bval[:nb.value]), (fn[:nf.value], fo[:nf.value + 1], fi[:fo[nf.value]])
 
 
 def version():

@@ -1,5 +1,5 @@
 // Exercises the drop-in C++ headers (include/ORBextractor.h, include/ORBmatcher.h) the way Frame.cc uses the reference
-// classes.  usage: dropin_test in.raw w h nfeatures out.bin
+// classes.  usage: dropin_test in.raw w h nfeatures out.bin [vocabulary.txt]
 // out.bin: int32 n | n x 28-byte keypoints | n x 32 descriptor bytes | int32 levels | per level int32 w,h + bytes |
 //          int32 nmatch_self | n int32 matches (SearchBruteForce of the descriptors against themselves) | int32 d01 |
 //          int32 nFused | n int32 (Fuse, chi-square gate) | int32 nFused | n int32 (Fuse, Sim3) | int32 nFound | n int32 (SearchBySim3)
@@ -8,6 +8,7 @@
 #include <vector>
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#include "ORBVocabulary.h"
 
 int main(int argc, char** argv)
 {
@@ -67,6 +68,28 @@ int main(int argc, char** argv)
         fwrite(f2.data(), 4, n, o);
         fwrite(&ns, 4, 1, o);
         fwrite(s12.data(), 4, n, o);
+        // Frame::ComputeBoW (Frame.cc:410-417) through the ORBVocabulary drop-in, when a vocabulary file is given
+        int nb = -1;
+        if (argc > 6) {
+            ORB_SLAM2::ORBVocabulary voc;
+            if (!voc.loadFromTextFile(argv[6])) return 4;
+            std::vector<cv::Mat> vCurrentDesc;                                              // Converter::toDescriptorVector
+            for (int i = 0; i < n; i++) vCurrentDesc.push_back(desc.row(i));
+            ORB_SLAM2::BowVector bow;
+            ORB_SLAM2::FeatureVector fv;
+            voc.transform(vCurrentDesc, bow, fv, 4);
+            nb = (int)bow.size();
+            fwrite(&nb, 4, 1, o);
+            for (ORB_SLAM2::BowVector::const_iterator it = bow.begin(); it != bow.end(); ++it) { fwrite(&it->first, 4, 1, o); fwrite(&it->second, 8, 1, o); }
+            const int nf = (int)fv.size();
+            fwrite(&nf, 4, 1, o);
+            for (ORB_SLAM2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+                const int cnt = (int)it->second.size();
+                fwrite(&it->first, 4, 1, o);
+                fwrite(&cnt, 4, 1, o);
+                fwrite(it->second.data(), 4, cnt, o);
+            }
+        }
         fclose(o);
         printf("ok %d keypoints, %d self matches, scale[1]=%g\n", n, nm, ex->GetScaleFactors()[1]);
         delete ex;

@@ -145,3 +145,41 @@ def triangulation_scene(seed):
     return dict(k1=k1, d1=d1, has_mp1=(rng.random(len(k1)) < 0.3).astype(np.uint8), u_right1=ur(len(k1)), fv1=feature_vector(d1, 16),
                 k2=k2, d2=d2, has_mp2=(rng.random(len(k2)) < 0.3).astype(np.uint8), u_right2=ur(len(k2)), fv2=feature_vector(d2, 16),
                 F12=F.astype(np.float32), epipole=(np.float32(300.25), np.float32(200.5)))
+
+
+def synthetic_vocabulary(seed, k=10, L=3, shallow_leaf_prob=0.08, desc_pool=None):
+    """A k-ary vocabulary tree numbered the way DBoW2 saves it (saveToTextFile walks nodes in id order; ids were assigned in
+    breadth-first creation order): children cluster around their parent (a few flipped bits), a few branches stop early (leaves
+    above level L, as k-means leaves them in ORBvoc.txt), two siblings per node are identical (distance ties), a few words are
+    stopped (weight 0).  Returns (k, L, parent, desc, weight)."""
+    rng = np.random.default_rng(seed + 17)
+    parent, desc, weight, level = [0], [np.zeros(32, np.uint8)], [0.0], [0]
+    frontier = [0]
+    for lv in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            base = desc_pool[rng.integers(0, len(desc_pool))] if (lv == 1 and desc_pool is not None) else desc[p]
+            kids = flip_bits(np.repeat(base[None], k, 0), rng, 90 if lv == 1 else 40)
+            kids[rng.integers(0, k)] = kids[rng.integers(0, k)]
+            for c in range(k):
+                parent.append(p); desc.append(kids[c]); weight.append(0.0); level.append(lv)
+                if lv < L and rng.random() > shallow_leaf_prob:
+                    nxt.append(len(parent) - 1)
+        frontier = nxt
+    parent = np.asarray(parent, np.int32)
+    has_child = np.zeros(len(parent), bool)
+    has_child[parent[1:]] = True
+    weight = np.where(has_child, 0.0, rng.uniform(0.5, 9.0, len(parent)))
+    weight[(~has_child) & (rng.random(len(parent)) < 0.03)] = 0.0
+    weight[0] = 0.0
+    return k, L, parent, np.stack(desc).astype(np.uint8), weight.astype(np.float64)
+
+
+def write_vocabulary_text(path, k, L, parent, desc, weight, scoring=0, weighting=0):
+    """saveToTextFile (TemplatedVocabulary.h:1441-1468)."""
+    has_child = np.zeros(len(parent), bool)
+    has_child[parent[1:]] = True
+    with open(path, "w") as f:
+        f.write("%d %d  %d %d\n" % (k, L, scoring, weighting))
+        for i in range(1, len(parent)):
+            f.write("%d %d %s %r\n" % (parent[i], 0 if has_child[i] else 1, " ".join(str(int(b)) for b in desc[i]), float(weight[i])))

@@ -51,7 +51,10 @@ def test_dropin_matches_oracle(tmp_path, w, h, nf, seed):
     raw = tmp_path / "in.raw"
     raw.write_bytes(img.tobytes())
     out = tmp_path / "out.bin"
-    subprocess.check_call([exe, str(raw), str(w), str(h), str(nf), str(out)])
+    import scenes
+    voc = scenes.synthetic_vocabulary(seed, 10, 5)
+    scenes.write_vocabulary_text(str(tmp_path / "voc.txt"), *voc)
+    subprocess.check_call([exe, str(raw), str(w), str(h), str(nf), str(out), str(tmp_path / "voc.txt")])
     b = out.read_bytes()
     n, = struct.unpack_from("<i", b, 0)
     p = 4
@@ -92,3 +95,16 @@ def test_dropin_matches_oracle(tmp_path, w, h, nf, seed):
     on, om = O.search_by_sim3(okps, odesc, okps, odesc, bounds, sf, xy, okps["octave"], odesc, xy, okps["octave"], odesc, 7.5)
     assert ns == on and np.array_equal(got, om)
     assert ns > n // 2
+    # Frame::ComputeBoW through include/ORBVocabulary.h (text loader + transform, levelsup 4)
+    (obid, obval), (ofn, ofo, ofi) = O.OracleVocabulary(*voc).transform(odesc, 4)
+    nb, = struct.unpack_from("<i", b, p); p += 4
+    assert nb == len(obid) and nb > 100
+    rec = np.frombuffer(b, dtype=np.dtype([("id", "<u4"), ("v", "<f8")]), count=nb, offset=p); p += 12 * nb
+    assert np.array_equal(rec["id"], obid) and rec["v"].tobytes() == obval.tobytes()
+    nfv, = struct.unpack_from("<i", b, p); p += 4
+    assert nfv == len(ofn)
+    for a in range(nfv):
+        node, cnt = struct.unpack_from("<Ii", b, p); p += 8
+        idx = np.frombuffer(b, dtype=np.uint32, count=cnt, offset=p); p += 4 * cnt
+        assert node == ofn[a] and np.array_equal(idx, ofi[ofo[a]:ofo[a + 1]])
+    assert p == len(b)
