@@ -74,14 +74,17 @@ static int undistort(orbx_matcher* m, const float* in, int n, int stride, const 
     Carver cv(m->arena);
     const size_t oI = cv.take(bytes);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     float* d = (float*)(m->arena.base + oI);
-    ORBX_CUDA(cudaMemcpyAsync(d, in, bytes, cudaMemcpyHostToDevice, m->stream));
+    Xfer x(m->arena);
+    x.up(oI, in, bytes);
+    ORBX_CUDA(x.send());
     k_undistort<<<(n + 255) / 256, 256, 0, m->stream>>>(d, n, stride, C, d);          // in place, like the reference (:438)
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
-    ORBX_CUDA(cudaMemcpyAsync(out, d, bytes, cudaMemcpyDeviceToHost, m->stream));
-    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    x.down(out, oI, bytes);
+    ORBX_CUDA(x.fetch());
     return ORBX_OK;
 }
 

@@ -354,17 +354,20 @@ int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc,
                  oQ = cv.take(sizeof(float) * 2 * (size_t)nq), oR = cv.take(sizeof(float) * (size_t)nq), oL = cv.take(sizeof(int) * 2 * (size_t)nq),
                  oO = cv.take(sizeof(int) * ((size_t)nq + 1)), oQD = cv.take((size_t)nq * 32), oTD = cv.take((size_t)n * 32);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oK, kps, sizeof(orbx_kp) * (size_t)n, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy, sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr, sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oL, qlev2, sizeof(int) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQD, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oTD, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);
+    x.up(oK, kps, sizeof(orbx_kp) * (size_t)n);
+    x.up(oS, start.data(), sizeof(int) * start.size());
+    x.up(oE, entries.data(), sizeof(int) * entries.size());
+    x.up(oQ, qxy, sizeof(float) * 2 * (size_t)nq);
+    x.up(oR, qr, sizeof(float) * (size_t)nq);
+    x.up(oL, qlev2, sizeof(int) * 2 * (size_t)nq);
+    x.up(oQD, qdesc, (size_t)nq * 32);
+    x.up(oTD, desc, (size_t)n * 32);
+    ORBX_CUDA(x.send());
     int* d_idx = nullptr;
     int total = 0;
     rc = grid_candidates_dev(m, (const orbx_kp*)(B + oK), (const int*)(B + oS), (const int*)(B + oE), gp, (const float*)(B + oQ),
@@ -376,12 +379,17 @@ int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc,
     m->lastLaunches = 4;
     idx.resize(std::max(total, 1));
     dist.resize(std::max(total, 1));
-    ORBX_CUDA(cudaMemcpyAsync(off.data(), B + oO, sizeof(int) * ((size_t)nq + 1), cudaMemcpyDeviceToHost, s));
+    // offsets through the arena's pinned mirror, the two candidate arrays (contiguous in arena2) through arena2's: two copies
+    rc = m->arena2.mirror();
+    if (rc) return rc;
+    if (total > 0)
+        ORBX_CUDA(cudaMemcpyAsync(m->arena2.pin, m->arena2.base, idx_bytes(total) + sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+    x.down(off.data(), oO, sizeof(int) * ((size_t)nq + 1));
+    ORBX_CUDA(x.fetch());
     if (total > 0) {
-        ORBX_CUDA(cudaMemcpyAsync(idx.data(), d_idx, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
-        ORBX_CUDA(cudaMemcpyAsync(dist.data(), d_dist, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
+        memcpy(idx.data(), m->arena2.pin, sizeof(int) * (size_t)total);
+        memcpy(dist.data(), m->arena2.pin + idx_bytes(total), sizeof(int) * (size_t)total);
     }
-    ORBX_CUDA(cudaStreamSynchronize(s));
     return ORBX_OK;
 }
 
@@ -397,18 +405,21 @@ int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, i
     const size_t oQ = cv.take((size_t)nq * 32), oT = cv.take((size_t)nt * 32), oO = cv.take(sizeof(int) * ((size_t)nq + 1)),
                  oI = cv.take(sizeof(int) * (size_t)total), oD = cv.take(sizeof(int) * (size_t)total);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oQ, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oT, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oO, off.data(), sizeof(int) * ((size_t)nq + 1), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oI, idx.data(), sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);
+    x.up(oQ, q, (size_t)nq * 32);
+    x.up(oT, t, (size_t)nt * 32);
+    x.up(oO, off.data(), sizeof(int) * ((size_t)nq + 1));
+    x.up(oI, idx.data(), sizeof(int) * (size_t)total);
+    ORBX_CUDA(x.send());
     k_cand_dist<<<(nq + 7) / 8, 256, 0, s>>>((const uint4*)(B + oQ), nq, (const uint4*)(B + oT), (const int*)(B + oO), (const int*)(B + oI), (int*)(B + oD));
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
-    ORBX_CUDA(cudaMemcpyAsync(dist.data(), B + oD, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(dist.data(), oD, sizeof(int) * (size_t)total);
+    ORBX_CUDA(x.fetch());
     return ORBX_OK;
 }
 

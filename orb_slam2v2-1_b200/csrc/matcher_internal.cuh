@@ -1,6 +1,7 @@
 // matcher_internal.cuh -- internal declarations shared by the matcher translation units.
 #pragma once
 #include "orbx_common.cuh"
+#include <string.h>
 #include <vector>
 
 namespace orbx {
@@ -14,7 +15,54 @@ struct Arena {
     uint8_t* base = nullptr;
     size_t cap = 0;
     cudaStream_t stream = nullptr;
+    uint8_t* pin = nullptr;        // page-locked host mirror (same offsets), allocated on first use by mirror()
+    size_t pinCap = 0;
     int reserve(size_t bytes);
+    int mirror();
+    void release();
+};
+// The host-array entry points move a dozen small arrays per call.  Issued one by one from pageable memory each costs a driver
+// round trip; Xfer gathers them in the arena's pinned mirror instead and moves them with ONE copy per direction.
+struct Xfer {
+    Arena& A;
+    size_t upEnd = 0, dnBeg = (size_t)-1, dnEnd = 0;
+    struct Out { void* dst; size_t off, bytes; };
+    Out outs[8];
+    int nOut = 0;
+    explicit Xfer(Arena& a) : A(a) {}
+    struct Big { const void* src; size_t off, bytes; };
+    Big bigs[4];
+    int nBig = 0;
+    void up(size_t off, const void* src, size_t bytes)
+    {
+        if (!bytes) return;
+        if (bytes > (1u << 20) && nBig < 4) { bigs[nBig++] = Big{src, off, bytes}; return; }      // large arrays: no extra host copy
+        memcpy(A.pin + off, src, bytes);
+        if (off + bytes > upEnd) upEnd = off + bytes;
+    }
+    cudaError_t send()
+    {
+        cudaError_t e = upEnd ? cudaMemcpyAsync(A.base, A.pin, upEnd, cudaMemcpyHostToDevice, A.stream) : cudaSuccess;
+        for (int i = 0; i < nBig && e == cudaSuccess; i++)      // after the gathered block, which may span their (stale) mirror range
+            e = cudaMemcpyAsync(A.base + bigs[i].off, bigs[i].src, bigs[i].bytes, cudaMemcpyHostToDevice, A.stream);
+        return e;
+    }
+    void down(void* dst, size_t off, size_t bytes)
+    {
+        if (!bytes) return;
+        outs[nOut++] = Out{dst, off, bytes};
+        if (off < dnBeg) dnBeg = off;
+        if (off + bytes > dnEnd) dnEnd = off + bytes;
+    }
+    cudaError_t fetch()       // one device-to-host copy, waits for the stream, scatters to the caller's arrays
+    {
+        cudaError_t e = cudaSuccess;
+        if (nOut) e = cudaMemcpyAsync(A.pin + dnBeg, A.base + dnBeg, dnEnd - dnBeg, cudaMemcpyDeviceToHost, A.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(A.stream);
+        if (e == cudaSuccess)
+            for (int i = 0; i < nOut; i++) memcpy(outs[i].dst, A.pin + outs[i].off, outs[i].bytes);
+        return e;
+    }
 };
 struct Carver {
     size_t off = 0;

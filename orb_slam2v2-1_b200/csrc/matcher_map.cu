@@ -204,21 +204,24 @@ static int area_best(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, c
                  oL = cv.take(sizeof(int) * (size_t)nq), oQD = cv.take((size_t)nq * 32), oSg = cv.take(sizeof(float) * (size_t)std::max(nlevels, 1)),
                  oBI = cv.take(sizeof(int) * (size_t)nq), oBD = cv.take(sizeof(int) * (size_t)nq);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oK, kps, sizeof(orbx_kp) * (size_t)n, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oTD, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
-    if (u_right) ORBX_CUDA(cudaMemcpyAsync(B + oU, u_right, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, s));
-    if (skip) ORBX_CUDA(cudaMemcpyAsync(B + oSk, skip, (size_t)n, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy, sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
-    if (qur) ORBX_CUDA(cudaMemcpyAsync(B + oQU, qur, sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr, sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oL, qlevel, sizeof(int) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQD, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    if (inv_sigma2) ORBX_CUDA(cudaMemcpyAsync(B + oSg, inv_sigma2, sizeof(float) * (size_t)nlevels, cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);
+    x.up(oK, kps, sizeof(orbx_kp) * (size_t)n);
+    x.up(oS, start.data(), sizeof(int) * start.size());
+    x.up(oE, entries.data(), sizeof(int) * entries.size());
+    x.up(oTD, desc, (size_t)n * 32);
+    if (u_right) x.up(oU, u_right, sizeof(float) * (size_t)n);
+    if (skip) x.up(oSk, skip, (size_t)n);
+    x.up(oQ, qxy, sizeof(float) * 2 * (size_t)nq);
+    if (qur) x.up(oQU, qur, sizeof(float) * (size_t)nq);
+    x.up(oR, qr, sizeof(float) * (size_t)nq);
+    x.up(oL, qlevel, sizeof(int) * (size_t)nq);
+    x.up(oQD, qdesc, (size_t)nq * 32);
+    if (inv_sigma2) x.up(oSg, inv_sigma2, sizeof(float) * (size_t)nlevels);
+    ORBX_CUDA(x.send());
     k_area_best<<<(nq + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oK), (const uint4*)(B + oTD), u_right ? (const float*)(B + oU) : nullptr,
                                              skip ? (const uint8_t*)(B + oSk) : nullptr, (const int*)(B + oS), (const int*)(B + oE), gp,
                                              (const float*)(B + oQ), qur ? (const float*)(B + oQU) : nullptr, (const float*)(B + oR),
@@ -226,9 +229,9 @@ static int area_best(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, c
                                              (int*)(B + oBI), (int*)(B + oBD));
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
-    ORBX_CUDA(cudaMemcpyAsync(best_idx, B + oBI, sizeof(int) * (size_t)nq, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(best_dist, B + oBD, sizeof(int) * (size_t)nq, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(best_idx, oBI, sizeof(int) * (size_t)nq);
+    x.down(best_dist, oBD, sizeof(int) * (size_t)nq);
+    ORBX_CUDA(x.fetch());
     return ORBX_OK;
 }
 
@@ -475,21 +478,24 @@ int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint
                  oQ = cv.take(sizeof(int) * (size_t)nq), oO = cv.take(sizeof(int) * ((size_t)nq + 1)), oI = cv.take(sizeof(int) * (size_t)total),
                  oD = cv.take(sizeof(int) * (size_t)total);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oK1, k1, sizeof(orbx_kp) * (size_t)n1, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oD1, d1, (size_t)n1 * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oU1, u_right1, sizeof(float) * (size_t)n1, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oK2, k2, sizeof(orbx_kp) * (size_t)n2, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oD2, d2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oU2, u_right2, sizeof(float) * (size_t)n2, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oH2, has_mp2, (size_t)n2, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oSF, sf2, sizeof(float) * (size_t)nlevels, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oSG, sigma2_2, sizeof(float) * (size_t)nlevels, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qfeat.data(), sizeof(int) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oO, off.data(), sizeof(int) * ((size_t)nq + 1), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oI, idx.data(), sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);
+    x.up(oK1, k1, sizeof(orbx_kp) * (size_t)n1);
+    x.up(oD1, d1, (size_t)n1 * 32);
+    x.up(oU1, u_right1, sizeof(float) * (size_t)n1);
+    x.up(oK2, k2, sizeof(orbx_kp) * (size_t)n2);
+    x.up(oD2, d2, (size_t)n2 * 32);
+    x.up(oU2, u_right2, sizeof(float) * (size_t)n2);
+    x.up(oH2, has_mp2, (size_t)n2);
+    x.up(oSF, sf2, sizeof(float) * (size_t)nlevels);
+    x.up(oSG, sigma2_2, sizeof(float) * (size_t)nlevels);
+    x.up(oQ, qfeat.data(), sizeof(int) * (size_t)nq);
+    x.up(oO, off.data(), sizeof(int) * ((size_t)nq + 1));
+    x.up(oI, idx.data(), sizeof(int) * (size_t)total);
+    ORBX_CUDA(x.send());
     TriParams T;
     memcpy(T.F, F12, sizeof(T.F));
     T.ex = ex;
@@ -502,8 +508,8 @@ int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
     std::vector<int> dist(total);
-    ORBX_CUDA(cudaMemcpyAsync(dist.data(), B + oD, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(dist.data(), oD, sizeof(int) * (size_t)total);
+    ORBX_CUDA(x.fetch());
     // sequential replay of the greedy part: vbMatched2 and the running bestDist (ties replace, `dist > bestDist` at :729)
     std::vector<uint8_t> vbMatched2(n2, 0);
     std::vector<int> rotHist[HISTO_LENGTH];
@@ -564,17 +570,20 @@ int orbm_distinctive_descriptors(orbx_matcher* m, const uint8_t* desc, const int
     Carver cv(m->arena);
     const size_t oD = cv.take((size_t)std::max(total, 1) * 32), oO = cv.take(sizeof(int) * ((size_t)npoints + 1)), oB = cv.take(sizeof(int) * (size_t)npoints);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    if (total > 0) ORBX_CUDA(cudaMemcpyAsync(B + oD, desc, (size_t)total * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oO, off, sizeof(int) * ((size_t)npoints + 1), cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);
+    x.up(oO, off, sizeof(int) * ((size_t)npoints + 1));
+    if (total > 0) x.up(oD, desc, (size_t)total * 32);
+    ORBX_CUDA(x.send());
     const int blocks = std::min((npoints + DD_WARPS - 1) / DD_WARPS, m->smCount * 8);
     k_distinctive<<<blocks, DD_WARPS * 32, 0, s>>>((const uint4*)(B + oD), (const int*)(B + oO), npoints, (int*)(B + oB));
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
-    ORBX_CUDA(cudaMemcpyAsync(best, B + oB, sizeof(int) * (size_t)npoints, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(best, oB, sizeof(int) * (size_t)npoints);
+    ORBX_CUDA(x.fetch());
     return ORBX_OK;
 }
 

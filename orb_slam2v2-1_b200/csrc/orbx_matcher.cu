@@ -170,6 +170,25 @@ int Arena::reserve(size_t bytes)
     return ORBX_OK;
 }
 
+int Arena::mirror()
+{
+    if (pinCap >= cap) return ORBX_OK;
+    if (pin) cudaFreeHost(pin);
+    pin = nullptr;
+    pinCap = 0;
+    ORBX_CUDA(cudaMallocHost(&pin, cap));
+    pinCap = cap;
+    return ORBX_OK;
+}
+
+void Arena::release()
+{
+    cudaFree(base);
+    if (pin) cudaFreeHost(pin);
+    base = pin = nullptr;
+    cap = pinCap = 0;
+}
+
 int bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int th_low, float nnratio,
                       int* d_bi, int* d_bd, int* d_sd, uint8_t* d_acc)
 {
@@ -232,8 +251,8 @@ void orbm_destroy(orbx_matcher* m)
     if (!m) return;
     cudaSetDevice(m->device);
     if (m->stream) cudaStreamSynchronize(m->stream);
-    cudaFree(m->arena.base);
-    cudaFree(m->arena2.base);
+    m->arena.release();
+    m->arena2.release();
     cudaFree(m->d_partial);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;

@@ -58,17 +58,20 @@ static int descend(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup,
     const size_t oF = cv.take((size_t)n * 32), oW = cv.take(sizeof(int) * (size_t)n), oV = cv.take(sizeof(double) * (size_t)n),
                  oN = cv.take(sizeof(int) * (size_t)n);
     int rc = v->arena.reserve(cv.total());
+    if (!rc) rc = v->arena.mirror();
     if (rc) return rc;
     uint8_t* B = v->arena.base;
     cudaStream_t s = v->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oF, desc, (size_t)n * 32, cudaMemcpyHostToDevice, s));
+    Xfer x(v->arena);
+    x.up(oF, desc, (size_t)n * 32);
+    ORBX_CUDA(x.send());
     k_voc_descend<<<(n + 7) / 8, 256, 0, s>>>((const uint4*)(B + oF), n, v->d_childStart, v->d_childId, v->d_childDesc, v->d_wordId, v->d_weight,
                                               v->L - levelsup, (int*)(B + oW), (double*)(B + oV), (int*)(B + oN));
     ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpyAsync(word, B + oW, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(weight, B + oV, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(node, B + oN, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(word, oW, sizeof(int) * (size_t)n);
+    x.down(weight, oV, sizeof(double) * (size_t)n);
+    x.down(node, oN, sizeof(int) * (size_t)n);
+    ORBX_CUDA(x.fetch());
     return ORBX_OK;
 }
 
@@ -134,7 +137,7 @@ void orbv_destroy(orbx_vocabulary* v)
     cudaSetDevice(v->device);
     if (v->stream) cudaStreamSynchronize(v->stream);
     cudaFree(v->d_childStart); cudaFree(v->d_childId); cudaFree(v->d_childDesc); cudaFree(v->d_wordId); cudaFree(v->d_weight);
-    cudaFree(v->arena.base);
+    v->arena.release();
     if (v->stream) cudaStreamDestroy(v->stream);
     delete v;
 }
