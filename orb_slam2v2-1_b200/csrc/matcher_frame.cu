@@ -869,16 +869,60 @@ __global__ void k_stereo_prep(const orbx_kp* __restrict__ kr, const int* __restr
     tab[(size_t)f * stride + i] = make_int4(minr, maxr, k.octave, __float_as_int(k.x));
 }
 
+// vRowIndices (Frame.cc:490-508) at a granularity of STEREO_BAND rows: for every band of a pair, the right keypoints whose
+// row range touches it, in index order.  One CTA per pair: count per band (a warp per band, ballots), scan, ordered fill.
+// A left keypoint then scans one band list (a few dozen entries) instead of every right keypoint of the frame.
+constexpr int STEREO_BAND = 8, STEREO_LIST_FACTOR = 4;      // a row range spans at most 18 rows = 4 bands of 8
+
+__global__ void __launch_bounds__(256) k_stereo_bands(const int* __restrict__ cntR, int stride, const int4* __restrict__ tab, int nBands,
+                                                      int* __restrict__ bandStart, int* __restrict__ bandList)
+{
+    extern __shared__ int s_cnt[];                               // nBands + 1
+    const int f = blockIdx.x, w = threadIdx.x >> 5, lane = threadIdx.x & 31, nr = min(cntR[f], stride);
+    const int4* tf = tab + (size_t)f * stride;
+    int* start = bandStart + (size_t)f * (nBands + 1);
+    int* list = bandList + (size_t)f * stride * STEREO_LIST_FACTOR;
+    for (int pass = 0; pass < 2; pass++) {
+        for (int b = w; b < nBands; b += 8) {
+            const int r0 = b * STEREO_BAND, r1 = r0 + STEREO_BAND - 1;
+            int n = pass ? s_cnt[b] : 0;
+            for (int c0 = 0; c0 < nr; c0 += 32) {
+                const int c = c0 + lane;
+                bool hit = false;
+                if (c < nr) {
+                    const int4 t = __ldg(&tf[c]);
+                    hit = t.x <= r1 && t.y >= r0;
+                }
+                const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+                if (pass && hit) list[n + __popc(m & ((1u << lane) - 1))] = c;
+                n += __popc(m);
+            }
+            if (!pass && lane == 0) s_cnt[b] = n;
+        }
+        __syncthreads();
+        if (!pass) {
+            if (threadIdx.x == 0) {
+                int acc = 0;
+                for (int b = 0; b < nBands; b++) { const int t = s_cnt[b]; s_cnt[b] = acc; acc += t; }
+                s_cnt[nBands] = acc;
+            }
+            __syncthreads();
+            for (int b = threadIdx.x; b <= nBands; b += 256) start[b] = s_cnt[b];
+        }
+    }
+}
+
 // One warp per (pair, left keypoint).  Candidates = right keypoints whose row band contains the left row, visited in
 // index order like vRowIndices (Frame.cc:521-563); the refinement is stereo_refine.
 __global__ void __launch_bounds__(256) k_stereo_batch(const orbx_kp* __restrict__ kl, const uint4* __restrict__ dl, const int* __restrict__ cntL,
                                                       int strideL, const orbx_kp* __restrict__ kr, const uint4* __restrict__ dr,
                                                       const int* __restrict__ cntR, int strideR, const int4* __restrict__ tab,
+                                                      const int* __restrict__ bandStart, const int* __restrict__ bandList, int nBands,
                                                       StereoBatchView VB, float bf, float minD, float maxD, int cap,
                                                       float* __restrict__ uRight, float* __restrict__ depth, int* __restrict__ bestSad)
 {
     const int f = blockIdx.y, iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    const int nl = cntL[f], nr = cntR[f];
+    const int nl = cntL[f];
     if (iL >= nl || iL >= cap) return;
     const size_t oo = (size_t)f * cap + iL;
     if (lane == 0) { uRight[oo] = -1.0f; depth[oo] = -1.0f; bestSad[oo] = -1; }
@@ -894,7 +938,10 @@ __global__ void __launch_bounds__(256) k_stereo_batch(const orbx_kp* __restrict_
     const int4* tf = tab + (size_t)f * strideR;
     const uint4* drf = dr + 2 * (size_t)f * strideR;
     uint32_t best = KEY_NONE;
-    for (int c = lane; c < nr; c += 32) {
+    const int* bs = bandStart + (size_t)f * (nBands + 1) + row / STEREO_BAND;
+    const int* bl = bandList + (size_t)f * strideR * STEREO_LIST_FACTOR;
+    for (int p = bs[0] + lane, pe = bs[1]; p < pe; p += 32) {
+        const int c = __ldg(&bl[p]);
         const int4 t = __ldg(&tf[c]);
         if (row < t.x || row > t.y) continue;
         if (t.z < levelL - 1 || t.z > levelL + 1) continue;
@@ -999,19 +1046,23 @@ extern "C" int orbm_stereo_matches_batch(orbx_matcher* m, orbx_extractor* left, 
     if ((rc = orbx_results_device(left, &dkl, &ddl, &dcl, &sl)) || (rc = orbx_results_device(right, &dkr, &ddr, &dcr, &sr))) return rc;
     ORBX_CUDA(cudaSetDevice(m->device));
     Carver cv(m->arena);
+    const int nBands = (V.nRows + STEREO_BAND - 1) / STEREO_BAND;
     const size_t oT = cv.take(sizeof(int4) * (size_t)B * sr), oU = cv.take(sizeof(float) * (size_t)B * cap), oD = cv.take(sizeof(float) * (size_t)B * cap),
-                 oS = cv.take(sizeof(int) * (size_t)B * cap), oN = cv.take(sizeof(int) * (size_t)B);
+                 oS = cv.take(sizeof(int) * (size_t)B * cap), oN = cv.take(sizeof(int) * (size_t)B),
+                 oBS = cv.take(sizeof(int) * (size_t)B * (nBands + 1)), oBL = cv.take(sizeof(int) * (size_t)B * sr * STEREO_LIST_FACTOR);
     if ((rc = m->arena.reserve(cv.total()))) return rc;
     uint8_t* A = m->arena.base;
     cudaStream_t s = m->stream;
     k_stereo_prep<<<dim3((sr + 255) / 256, B), 256, 0, s>>>(dkr, dcr, sr, V, (int4*)(A + oT));
     // left keypoints beyond cap would be dropped: cap must cover the per-frame keypoint stride of the handle
     const int nlMax = std::min(sl, cap);
-    k_stereo_batch<<<dim3((nlMax + 7) / 8, B), 256, 0, s>>>(dkl, (const uint4*)ddl, dcl, sl, dkr, (const uint4*)ddr, dcr, sr, (const int4*)(A + oT), V,
+    k_stereo_bands<<<B, 256, sizeof(int) * (size_t)(nBands + 1), s>>>(dcr, sr, (const int4*)(A + oT), nBands, (int*)(A + oBS), (int*)(A + oBL));
+    k_stereo_batch<<<dim3((nlMax + 7) / 8, B), 256, 0, s>>>(dkl, (const uint4*)ddl, dcl, sl, dkr, (const uint4*)ddr, dcr, sr, (const int4*)(A + oT),
+                                                          (const int*)(A + oBS), (const int*)(A + oBL), nBands, V,
                                                           bf, minD, maxD, cap, (float*)(A + oU), (float*)(A + oD), (int*)(A + oS));
     k_stereo_median<<<B, 256, 0, s>>>(dcl, cap, (const int*)(A + oS), (float*)(A + oU), (float*)(A + oD), (int*)(A + oN));
     ORBX_CUDA(cudaGetLastError());
-    m->lastLaunches = 3;
+    m->lastLaunches = 4;
     ORBX_CUDA(cudaMemcpyAsync(uRight, A + oU, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaMemcpyAsync(depth, A + oD, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
     if (nmatched) ORBX_CUDA(cudaMemcpyAsync(nmatched, A + oN, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, s));
