@@ -29,7 +29,7 @@ __device__ __forceinline__ int level_of_cell(const Plan& P, int cell)
 // ------------------------------------------------------------------------------------------------ pyramid
 // cv::resize INTER_LINEAR, 8-bit: 11-bit coefficients (host tables), horizontal pass H = S[sx]*a0 + S[sx+1]*a1 in int32,
 // vertical pass (((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2  (always within 0..255: the weights sum to 2048).
-// One CTA = a tile of 128 output columns x RS_TILE_H output rows, in two phases:
+// One CTA = a tile of 128 output columns x RS_TILE_H output rows (or 64 x 2*RS_TILE_H, see GX below), in two phases:
 //   1. horizontal pass of every source row the tile touches, once, into shared memory (H >> 4 as u16, one uint2 per
 //      group of 4 output columns: the kernel is bound by L1/shared-memory wavefronts, so the narrow format wins).  The (left, right) source bytes of two adjacent output columns span at most 4
 //      bytes (level ratio <= 2), i.e. two aligned words: one PRMT (selector precomputed per column group on the host)
@@ -42,64 +42,84 @@ constexpr int RS_TILE_H = 64;
 
 struct ResizeCols { int4 a, b; };   // a = {word of pair 01, word of pair 23, sel01, sel23}; b = 4 x (a0 | a1 << 16)
 
+// GX = column groups per tile row: 32 (a warp = one row of 128 output columns) or 16 (a warp = two rows of 64 columns, tiles
+// twice as tall).  The host picks per level whichever leaves fewer lanes idle in the last tile column (widths such as 533 = 134
+// groups waste 16 % of the lanes at GX = 32 and 7 % at GX = 16).
+template <int GX>
 __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src, int spitch, size_t sframe,
                                                 uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dframe,
                                                 const ResizeCols* __restrict__ xtab, const int4* __restrict__ ytab)
 {
+    constexpr int RPW = 32 / GX, RSTEP = 8 * RPW, TILE_H = RS_TILE_H * RPW;
     extern __shared__ uint2 Hs[];                                  // [source row of the tile][column group], 4 x u16
-    const int f = blockIdx.z, tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int g = min(blockIdx.x * 32 + tx, (dw - 1) >> 2);        // column group (clamped: idle lanes repeat the last one)
-    const int oy0 = blockIdx.y * RS_TILE_H, oy1 = min(oy0 + RS_TILE_H, dh);
+    const int f = blockIdx.z, lane = threadIdx.x & 31, tx = lane % GX, ty = (threadIdx.x >> 5) * RPW + lane / GX;
+    const int g = min(blockIdx.x * GX + tx, (dw - 1) >> 2);        // column group (clamped: idle lanes repeat the last one)
+    const int oy0 = blockIdx.y * TILE_H, oy1 = min(oy0 + TILE_H, dh);
     const int sFirst = __ldg(&ytab[oy0]).x, n = __ldg(&ytab[oy1 - 1]).y - sFirst + 1;
     const int4 ca = __ldg(&xtab[g].a), cb = __ldg(&xtab[g].b);
     const uint32_t* S = reinterpret_cast<const uint32_t*>(src + (size_t)f * sframe + (size_t)sFirst * spitch);
     const int wpitch = spitch >> 2;
+    // pointer stepping: two running row pointers (pair 01 / pair 23)
+    const uint32_t* p01 = S + (size_t)ty * wpitch + ca.x;
+    const uint32_t* p23 = S + (size_t)ty * wpitch + ca.y;
+    const size_t rstep = (size_t)wpitch * RSTEP;
 #pragma unroll 4
-    for (int r = ty; r < n; r += 8) {
-        const uint32_t* row = S + (size_t)r * wpitch;
-        const uint32_t wa = __ldg(row + ca.x), wb = __ldg(row + ca.x + 1), wc = __ldg(row + ca.y), wd = __ldg(row + ca.y + 1);
+    for (int r = ty; r < n; r += RSTEP, p01 += rstep, p23 += rstep) {
+        const uint32_t wa = __ldg(p01), wb = __ldg(p01 + 1), wc = __ldg(p23), wd = __ldg(p23 + 1);
         const uint32_t W01 = __byte_perm(wa, wb, ca.z), W23 = __byte_perm(wc, wd, ca.w);
         // H >> 4 <= 32640 fits 16 bits: (H1 >> 4) << 16 | (H0 >> 4) == ((H1 << 12) & 0xFFFF0000) | (H0 >> 4), the merge on the FMA pipe
         const unsigned H0 = __dp2a_lo((unsigned)cb.x, W01, 0u), H1 = __dp2a_hi((unsigned)cb.y, W01, 0u);
         const unsigned H2 = __dp2a_lo((unsigned)cb.z, W23, 0u), H3 = __dp2a_hi((unsigned)cb.w, W23, 0u);
-        Hs[r * 32 + tx] = make_uint2((H1 >> 4) * 65536u + (H0 >> 4), (H3 >> 4) * 65536u + (H2 >> 4));
+        Hs[r * GX + tx] = make_uint2((H1 >> 4) * 65536u + (H0 >> 4), (H3 >> 4) * 65536u + (H2 >> 4));
     }
     __syncthreads();
-    if (blockIdx.x * 32 + tx > ((dw - 1) >> 2)) return;
+    if (blockIdx.x * GX + tx > ((dw - 1) >> 2)) return;
     uint8_t* D = dst + (size_t)f * dframe + (size_t)g * 4;
 #pragma unroll 2
-    for (int dy = oy0 + ty; dy < oy1; dy += 8) {
+    for (int dy = oy0 + ty; dy < oy1; dy += RSTEP) {
         const int4 yy = __ldg(&ytab[dy]);                          // {sy0, sy1 (clamped), b0, b1}
-        const uint2 h0 = Hs[(yy.x - sFirst) * 32 + tx], h1 = Hs[(yy.y - sFirst) * 32 + tx];
+        const uint2 h0 = Hs[(yy.x - sFirst) * GX + tx], h1 = Hs[(yy.y - sFirst) * GX + tx];
         const unsigned b0 = (unsigned)yy.z, b1 = (unsigned)yy.w;
         const unsigned v0 = ((b0 * (h0.x & 0xFFFFu)) >> 16) + (((b1 * (h1.x & 0xFFFFu)) >> 16) + 2u);      // <= 1022, >> 2 below
         const unsigned v1 = ((b0 * (h0.x >> 16)) >> 16) + (((b1 * (h1.x >> 16)) >> 16) + 2u);
         const unsigned v2 = ((b0 * (h0.y & 0xFFFFu)) >> 16) + (((b1 * (h1.y & 0xFFFFu)) >> 16) + 2u);
         const unsigned v3 = ((b0 * (h0.y >> 16)) >> 16) + (((b1 * (h1.y >> 16)) >> 16) + 2u);
         // pack: (v0 | v1 << 16) >> 2 has v0 >> 2 in byte 0 and v1 >> 2 in byte 2 (v < 1024)
-        const unsigned p01 = (v1 * 65536u + v0) >> 2, p23 = (v3 * 65536u + v2) >> 2;
-        *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = __byte_perm(p01, p23, 0x6420);     // pitch is a multiple of 32: the last word may pad
+        const unsigned p01v = (v1 * 65536u + v0) >> 2, p23v = (v3 * 65536u + v2) >> 2;
+        *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = __byte_perm(p01v, p23v, 0x6420);     // pitch is a multiple of 32: the last word may pad
     }
 }
 
 // shared memory for a level pair: source rows one tile can touch
-size_t resize_smem_bytes(int sh, int dh)
+static size_t resize_smem_bytes(int sh, int dh, int gx)
 {
-    const int rows = (int)((double)RS_TILE_H * sh / dh) + 4;
-    return (size_t)rows * 32 * sizeof(uint2);
+    const int tileH = RS_TILE_H * (32 / gx);
+    const int rows = (int)((double)tileH * sh / dh) + 4;
+    return (size_t)rows * gx * sizeof(uint2);
+}
+
+template <int GX>
+static void launch_resize_gx(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
+                             size_t dframe, const void* xtab, const int4* ytab, int B, int sh)
+{
+    const size_t smem = resize_smem_bytes(sh, dh, GX);
+    static thread_local size_t configured = 48 * 1024;
+    if (smem > configured) {
+        cudaFuncSetAttribute(k_resize<GX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    const int tileH = RS_TILE_H * (32 / GX);
+    dim3 grd(((dw + 3) / 4 + GX - 1) / GX, (dh + tileH - 1) / tileH, B);
+    k_resize<GX><<<grd, 256, smem, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
 }
 
 void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe, uint8_t* dst, int dw, int dh, int dpitch,
                    size_t dframe, const void* xtab, const int4* ytab, int B, int sh)
 {
-    const size_t smem = resize_smem_bytes(sh, dh);
-    static thread_local size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaFuncSetAttribute(k_resize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
-    dim3 grd(((dw + 3) / 4 + 31) / 32, (dh + RS_TILE_H - 1) / RS_TILE_H, B);
-    k_resize<<<grd, 256, smem, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
+    const int groups = (dw + 3) / 4;
+    const double u32 = (double)groups / (((groups + 31) / 32) * 32), u16 = (double)groups / (((groups + 15) / 16) * 16);
+    if (u16 > u32 + 0.03) launch_resize_gx<16>(s, src, spitch, sframe, dst, dw, dh, dpitch, dframe, xtab, ytab, B, sh);
+    else launch_resize_gx<32>(s, src, spitch, sframe, dst, dw, dh, dpitch, dframe, xtab, ytab, B, sh);
 }
 
 // ------------------------------------------------------------------------------------------------ FAST per cell
