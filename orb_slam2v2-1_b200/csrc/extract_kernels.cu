@@ -124,10 +124,12 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 
 // ------------------------------------------------------------------------------------------------ FAST per cell
 // One WARP per cell (four cells per CTA): everything below is warp-synchronous, no block barrier and no shared-memory atomic.
-//   1. the cell ROI is staged in shared memory as aligned 32-bit words;
-//   2. pre-filter on 4 pixels at a time: a 9-arc always contains two adjacent compass pixels (ring positions 0, 4, 8, 12),
-//      so a corner needs |p - centre| > t on such a pair; |.| comes from the native VABSDIFF4.U8 and the threshold test is
-//      SWAR on the four bytes; survivors are appended in row-major order to the warp's private list (ballot ranks);
+//   1. the cell ROI is staged in shared memory with a compile-time row pitch TP (64 bytes, 128 for very wide cells), its
+//      origin on a 16-byte boundary of the level row, so that a lane copies 16 bytes per LDGSTS;
+//   2. pre-filter on 8 pixels per lane (two words): a 9-arc always contains two adjacent compass pixels (ring positions
+//      0, 4, 8, 12), so a corner needs |p - centre| > t on such a pair; |.| comes from the native VABSDIFF4.U8 and the
+//      threshold test is SWAR on the bytes; survivors are appended in row-major order to the warp's private list
+//      (positions from a shuffle scan of the per-lane counts);
 //   3. exact score of the survivors (packed s16x2 min/max, VIMNMX) into a u8 score map (0 = not a corner);
 //   4. NMS + emission from the list, which is already in cv::FAST's output order.
 // The cell is processed at iniThFAST first and, only if that yields no keypoint, again at minThFAST
@@ -143,7 +145,8 @@ constexpr int FAST_WARPS = 4;
 __device__ __forceinline__ unsigned vmin3s2(unsigned a, unsigned b, unsigned c) { return __vmins2(__vmins2(a, b), c); }
 __device__ __forceinline__ unsigned vmax3s2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
 
-__device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch)
+template <int pitch>
+__device__ __forceinline__ int fast_raw_score(const uint8_t* c)
 {
     const int v = c[0];
     unsigned r[16];
@@ -168,134 +171,201 @@ __device__ __forceinline__ int fast_raw_score(const uint8_t* c, int pitch)
     return max(b, d);
 }
 
-// shared memory of one warp: tile words | score map | survivor list
-__host__ __device__ inline int fast_warp_smem(int wCell, int hCell)
+// shared memory of one warp: tile (rows of TP bytes) | score map | survivor list
+__host__ __device__ inline int fast_warp_smem(int wCell, int hCell, int tp)
 {
-    const int tile = (hCell + 6) * (((wCell + 6 + 3 + 3) >> 2) << 2);
-    const int sc = (hCell + 2) * ((wCell + 2 + 3) & ~3);
-    const int list = ((wCell * hCell * 2) + 3) & ~3;
-    return (tile + sc + list + 15) & ~15;
+    const int tile = (hCell + 6) * tp;
+    const int sc = ((hCell + 2) * ((wCell + 2 + 3) & ~3) + 15) & ~15;
+    const int list = ((wCell * hCell * 2) + 15) & ~15;
+    return tile + sc + list;
 }
 
 size_t fast_smem_bytes(const Plan& P)
 {
     int m = 0;
-    for (int l = 0; l < P.nlevels; l++) m = max(m, fast_warp_smem(P.lv[l].wCell, P.lv[l].hCell));
+    for (int l = 0; l < P.nlevels; l++) m = max(m, fast_warp_smem(P.lv[l].wCell, P.lv[l].hCell, P.fastPitch));
     return (size_t)m * FAST_WARPS;
 }
 
+// Cell table (two uint4 per cell, per image shape; built by fast_cell_record on the host):
+//   a = {iniX | iniY << 16, tw | th << 16 (0 = skipped cell), level | xoff << 4 | yoff << 16, cell index inside the level}
+//   b = {recipS | rpiS << 20 | nq << 26, recipZ | rpiZ << 20 | nd << 26, dx0 | scp << 8 | dFirst << 16, 0}
+// nq = 16-byte pieces per tile row, rpiS = 32 / nq tile rows staged per warp iteration; nd = 8-byte columns that cover the
+// detection zone, rpiZ = 32 / nd zone rows filtered per warp iteration; recip* = 65536 / n + 1 (lane / n by multiply-shift);
+// dx0 = iniX - tile origin, scp = pitch of the score map, dFirst = first 8-byte column of the zone.
+void fast_cell_record(const LevelGeom& G, int level, int i, int j, uint4* rec)
+{
+    const int iniX = MIN_BORDER + j * G.wCell, iniY = MIN_BORDER + i * G.hCell;
+    const int maxX = min(iniX + G.wCell + 6, G.maxBX), maxY = min(iniY + G.hCell + 6, G.maxBY);
+    const int tw = maxX - iniX, th = maxY - iniY;
+    const bool skip = iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7;
+    uint4 a, b = make_uint4(0, 0, 0, 0);
+    a.x = (unsigned)iniX | ((unsigned)iniY << 16);
+    a.y = skip ? 0u : ((unsigned)tw | ((unsigned)th << 16));
+    a.z = (unsigned)level | ((unsigned)(j * G.wCell) << 4) | ((unsigned)(i * G.hCell) << 16);
+    a.w = (unsigned)(i * G.nCols + j);
+    if (!skip) {
+        const int dx0 = iniX & 15, nq = (dx0 + tw + 15) >> 4, rpiS = 32 / nq;
+        const int zx0 = dx0 + 3, zx1 = zx0 + tw - 6, dFirst = zx0 >> 3, nd = ((zx1 - 1) >> 3) - dFirst + 1, rpiZ = 32 / nd;
+        const int scp = (tw - 6 + 2 + 3) & ~3;
+        b.x = (unsigned)(65536 / nq + 1) | ((unsigned)rpiS << 20) | ((unsigned)nq << 26);      // recip <= 65537: 17 bits
+        b.y = (unsigned)(65536 / nd + 1) | ((unsigned)rpiZ << 20) | ((unsigned)nd << 26);
+        b.z = (unsigned)dx0 | ((unsigned)scp << 8) | ((unsigned)dFirst << 16);
+    }
+    rec[0] = a;
+    rec[1] = b;
+}
+
+// tile pitch that fits every cell of the plan: 64 bytes unless a cell row (from its 16-byte-aligned origin) is longer
+int fast_tile_pitch(const Plan& P)
+{
+    int need = 0;
+    for (int l = 0; l < P.nlevels; l++) {
+        const LevelGeom& G = P.lv[l];
+        for (int j = 0; j < G.nCols; j++) {
+            const int iniX = MIN_BORDER + j * G.wCell, maxX = min(iniX + G.wCell + 6, G.maxBX);
+            if (iniX >= G.maxBX - 6 || maxX - iniX < 7) continue;
+            need = max(need, (((iniX & 15) + maxX - iniX + 15) >> 4) << 4);
+        }
+    }
+    return need <= 64 ? 64 : (need <= 128 ? 128 : 0);
+}
+
+__device__ __forceinline__ unsigned swar_gt(unsigned a, unsigned K) { return ((a & 0x7F7F7F7Fu) + K) | a; }    // bit 7 of a byte: byte > t
+
+template <int TP>
 __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F, int smemPerWarp, int f, int cell, uint8_t* smem)
 {
+    constexpr int TPW = TP / 4;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (cell >= P.totalCells) return;
     const unsigned FULL = 0xFFFFFFFFu, ltmask = (1u << lane) - 1;
-    // cell ROI (ORBextractor.cc:791-806): [iniX, maxX) x [iniY, maxY), overlap of 6 px with the next cell -- from the per-shape
-    // cell table: {iniX | iniY << 16, tw | th << 16 (0 = skipped cell), level | xoff << 4 | yoff << 16, cell index in the level}
-    const uint4 ct = __ldg(&F.cellTab[cell]);
+    const uint4 ct = __ldg(&F.cellTab[2 * cell]);
     int* cntOut = F.cellCount + (size_t)f * P.totalCells + cell;
     if (ct.y == 0) {                                      // skipped cell / ROI too small for cv::FAST
         if (lane == 0) *cntOut = 0;
         return;
     }
+    const uint4 cu = __ldg(&F.cellTab[2 * cell + 1]);
+    // cell ROI (ORBextractor.cc:791-806): [iniX, iniX + tw) x [iniY, iniY + th), overlap of 6 px with the next cell
     const int iniX = ct.x & 0xFFFF, iniY = ct.x >> 16, tw = ct.y & 0xFFFF, th = ct.y >> 16;
     const int l = ct.z & 15, xoff = (ct.z >> 4) & 0xFFF, yoff = ct.z >> 16;
     const LevelGeom& G = P.lv[l];
-    const int maxX = iniX + tw;
     const int iw = tw - 6, ih = th - 6;                   // detection zone: no corner within 3 px of the ROI edge
-    const int ax = iniX & ~3;                             // word-aligned tile origin
-    const int dx0 = iniX - ax;
-    const int tpw = (maxX - ax + 3) >> 2, tp = tpw * 4;   // tile pitch in words / bytes
-    const int scp = (iw + 2 + 3) & ~3;                    // score-map pitch: 1-px zero frame
+    const int dx0 = cu.z & 0xFF, scp = (cu.z >> 8) & 0xFF, dFirst = (cu.z >> 16) & 0xFF;
     uint8_t* tile = smem + (size_t)wid * smemPerWarp;
-    uint8_t* sc = tile + th * tp;
-    uint16_t* list = reinterpret_cast<uint16_t*>(sc + (ih + 2) * scp);
-    uint32_t* tileW = reinterpret_cast<uint32_t*>(tile);
+    uint8_t* sc = tile + th * TP;                         // score map: (ih + 2) x scp, 1-px zero frame
+    const int scBytes = ((ih + 2) * scp + 15) & ~15;
+    uint16_t* list = reinterpret_cast<uint16_t*>(sc + scBytes);
+    const uint32_t* tileW = reinterpret_cast<const uint32_t*>(tile);
 
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below.
-        // lane = (row r0, word c0) of a block of rpiS = 32 / tpw whole tile rows: no index arithmetic inside the loop
-        const int rpiS = (ct.w >> 16) & 15;
-        const int r0 = (int)(((unsigned)lane * (65536u / (unsigned)tpw + 1)) >> 16), c0 = lane - r0 * tpw;
+        // lane = (row r0, 16-byte piece q0) of a block of rpiS whole tile rows: no index arithmetic inside the loop
+        const int nq = cu.x >> 26, rpiS = (cu.x >> 20) & 0x3F;
+        const int r0 = (int)(((unsigned)lane * (cu.x & 0xFFFFFu)) >> 16), q0 = lane - r0 * nq;
         if (r0 < rpiS) {
-            const uint8_t* p = img + (size_t)(iniY + r0) * pitch + ax + 4 * c0;
-            unsigned sdst = (unsigned)__cvta_generic_to_shared(tileW) + 4u * (unsigned)lane;
+            const uint8_t* p = img + (size_t)(iniY + r0) * pitch + (iniX - dx0) + 16 * q0;
+            unsigned sdst = (unsigned)__cvta_generic_to_shared(tile) + (unsigned)(r0 * TP + 16 * q0);
             const size_t pstep = (size_t)rpiS * pitch;
-            const unsigned sstep = 4u * (unsigned)(rpiS * tpw);
-            for (int r = r0; r < th; r += rpiS) {
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(p));
-                p += pstep;
-                sdst += sstep;
+            const unsigned sstep = (unsigned)(rpiS * TP);
+            // level 0 may be the caller's device image, only 4-byte aligned: same layout from 4-byte copies
+            const bool wide = l > 0 || ((((size_t)F.lv0) | F.lv0Pitch | F.lv0Frame) & 15) == 0;
+            if (wide) {
+                for (int r = r0; r < th; r += rpiS, p += pstep, sdst += sstep)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(p));
+            } else {
+                for (int r = r0; r < th; r += rpiS, p += pstep, sdst += sstep) {
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(p));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 4), "l"(p + 4));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 8), "l"(p + 8));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 12), "l"(p + 12));
+                }
             }
         }
     }
-    // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih); word items of the zone
+    // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih)
     const int zx0 = dx0 + 3, zx1 = zx0 + iw;
-    const int wFirst = zx0 >> 2, nwz = ((zx1 - 1) >> 2) - wFirst + 1;
-    // pre-filter work items: lane = (row zr0, word column zc) of a block of rpiZ = 32 / nwz zone rows
-    const int rpiZ = (ct.w >> 20) & 15;
-    const int zr0 = (int)(((unsigned)lane * (65536u / (unsigned)nwz + 1)) >> 16), zc = lane - zr0 * nwz;
+    // pre-filter work items: lane = (row zr0, 8-byte column zc) of a block of rpiZ zone rows
+    const int nd = cu.y >> 26, rpiZ = (cu.y >> 20) & 0x3F;
+    const int zr0 = (int)(((unsigned)lane * (cu.y & 0xFFFFFu)) >> 16), zc = lane - zr0 * nd;
     const bool zactive = zr0 < rpiZ;
-    unsigned zm;                                          // bytes of word column wFirst + zc that lie inside the zone
-    {
-        const int wc = wFirst + zc;
-        const int lo = max(zx0 - 4 * wc, 0), hi = min(zx1 - 4 * wc, 4);
-        zm = (hi >= 4 ? 0xFFFFFFFFu : ((1u << (8 * hi)) - 1)) & ~((1u << (8 * lo)) - 1);
-        if (!zactive) zm = 0;
+    const int bc = 8 * (dFirst + zc);                     // tile column of the item's first pixel
+    unsigned zm0 = 0, zm1 = 0;                            // bytes of the item that lie inside the zone
+    if (zactive) {
+        const int lo = min(max(zx0 - bc, 0), 8), hi = min(max(zx1 - bc, 0), 8);
+        const unsigned long long m = (hi >= 8 ? ~0ull : ((1ull << (8 * hi)) - 1)) & ~(lo >= 8 ? ~0ull : ((1ull << (8 * lo)) - 1));
+        zm0 = (unsigned)m & 0x80808080u;
+        zm1 = (unsigned)(m >> 32) & 0x80808080u;
     }
     uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)(ct.w & 0xFFFF) * G.slotCap;
-    const int scWords = ((ih + 2) * scp) >> 2;
+    const int scBias = 1 - zx0 - 2 * scp;                 // score-map index of tile pixel (row, col) = row * scp + col + scBias
     int total = 0;
     asm volatile("cp.async.wait_all;" ::: "memory");
 
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? P.iniTh : P.minTh;
         if (pass == 1 && (total > 0 || P.minTh == P.iniTh)) break;
-        for (int i = lane; i < scWords; i += 32) reinterpret_cast<uint32_t*>(sc)[i] = 0;
+        for (int i = lane; i < (scBytes >> 4); i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         // ---- pre-filter
         const unsigned K = (unsigned)(127 - min(t, 127)) * 0x01010101u;     // byte > t  <=>  bit 7 of ((byte & 0x7f) + 127 - t) | byte
         int n = 0;
-        const uint32_t* w = tileW + (3 + zr0) * tpw + wFirst + zc;
-        int e = ((3 + zr0) << 8) | ((wFirst + zc) << 2);
-        for (int row0 = zr0; row0 - zr0 < ih; row0 += rpiZ, w += rpiZ * tpw, e += rpiZ << 8) {
-            unsigned comb = 0;
+        const uint32_t* w = tileW + (3 + zr0) * TPW + 2 * (dFirst + zc);
+        int e = (3 + zr0) * TP + bc;                      // list entry = byte offset of the pixel in the tile
+        for (int row0 = zr0; row0 - zr0 < ih; row0 += rpiZ, w += rpiZ * TPW, e += rpiZ * TP) {
+            unsigned comb0 = 0, comb1 = 0;
             if (zactive && row0 < ih) {
-                const unsigned C = w[0], Lw = w[-1], Rw = w[1], U = w[-3 * tpw], D = w[3 * tpw];
-                const unsigned P12 = __funnelshift_r(Lw, C, 8), P4 = __funnelshift_r(C, Rw, 24);
-                const unsigned a0 = __vabsdiffu4(D, C), a8 = __vabsdiffu4(U, C), a4 = __vabsdiffu4(P4, C), a12 = __vabsdiffu4(P12, C);
-                const unsigned g0 = ((a0 & 0x7F7F7F7Fu) + K) | a0, g8 = ((a8 & 0x7F7F7F7Fu) + K) | a8;
-                const unsigned g4 = ((a4 & 0x7F7F7F7Fu) + K) | a4, g12 = ((a12 & 0x7F7F7F7Fu) + K) | a12;
-                comb = (g0 | g8) & (g4 | g12) & 0x80808080u & zm;
+                const uint2 C = *reinterpret_cast<const uint2*>(w);
+                const uint2 U = *reinterpret_cast<const uint2*>(w - 3 * TPW), D = *reinterpret_cast<const uint2*>(w + 3 * TPW);
+                const unsigned Lw = w[-1], Rw = w[2];
+                const unsigned L0 = __funnelshift_r(Lw, C.x, 8), R0 = __funnelshift_r(C.x, C.y, 24);     // x - 3, x + 3
+                const unsigned L1 = __funnelshift_r(C.x, C.y, 8), R1 = __funnelshift_r(C.y, Rw, 24);
+                const unsigned v0 = swar_gt(__vabsdiffu4(D.x, C.x), K) | swar_gt(__vabsdiffu4(U.x, C.x), K);
+                const unsigned h0 = swar_gt(__vabsdiffu4(L0, C.x), K) | swar_gt(__vabsdiffu4(R0, C.x), K);
+                const unsigned v1 = swar_gt(__vabsdiffu4(D.y, C.y), K) | swar_gt(__vabsdiffu4(U.y, C.y), K);
+                const unsigned h1 = swar_gt(__vabsdiffu4(L1, C.y), K) | swar_gt(__vabsdiffu4(R1, C.y), K);
+                comb0 = v0 & h0 & zm0;
+                comb1 = v1 & h1 & zm1;
             }
-            if (__ballot_sync(FULL, comb != 0) == 0) continue;
-            // ordered append: cnt = surviving bytes of this lane (0..4); exclusive prefix over the lanes from three ballots
-            const unsigned cnt = (((comb >> 7) & 0x01010101u) * 0x01010101u) >> 24;
-            const unsigned B0 = __ballot_sync(FULL, cnt & 1u), B1 = __ballot_sync(FULL, cnt & 2u), B2 = __ballot_sync(FULL, cnt & 4u);
-            int pos = n + __popc(B0 & ltmask) + 2 * __popc(B1 & ltmask) + 4 * __popc(B2 & ltmask);
-            n = __shfl_sync(FULL, pos + (int)cnt, 31);
-            if (comb & 0x80u) list[pos++] = (uint16_t)e;
-            if (comb & 0x8000u) list[pos++] = (uint16_t)(e + 1);
-            if (comb & 0x800000u) list[pos++] = (uint16_t)(e + 2);
-            if (comb & 0x80000000u) list[pos++] = (uint16_t)(e + 3);
+            if (__ballot_sync(FULL, (comb0 | comb1) != 0) == 0) continue;
+            // ordered append: cnt = surviving pixels of this lane (0..8), positions from an inclusive shuffle scan
+            const int cnt = __popc((comb0 >> 7) | (comb1 >> 6));
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int up = __shfl_up_sync(FULL, inc, o);
+                if (lane >= o) inc += up;
+            }
+            int pos = n + inc - cnt;
+            n += __shfl_sync(FULL, inc, 31);
+            if (comb0 & 0x80u) list[pos++] = (uint16_t)e;
+            if (comb0 & 0x8000u) list[pos++] = (uint16_t)(e + 1);
+            if (comb0 & 0x800000u) list[pos++] = (uint16_t)(e + 2);
+            if (comb0 & 0x80000000u) list[pos++] = (uint16_t)(e + 3);
+            if (comb1 & 0x80u) list[pos++] = (uint16_t)(e + 4);
+            if (comb1 & 0x8000u) list[pos++] = (uint16_t)(e + 5);
+            if (comb1 & 0x800000u) list[pos++] = (uint16_t)(e + 6);
+            if (comb1 & 0x80000000u) list[pos++] = (uint16_t)(e + 7);
         }
         __syncwarp();
         // ---- exact score of the survivors
         for (int k = lane; k < n; k += 32) {
-            const int e = list[k];
-            const int row = e >> 8, col = e & 0xFF;
-            const int raw = fast_raw_score(tile + row * tp + col, tp);
-            if (raw > t) sc[(row - 2) * scp + (col - zx0 + 1)] = (uint8_t)raw;
+            const unsigned e = list[k];
+            const int raw = fast_raw_score<TP>(tile + e);
+            if (raw > t) sc[(int)((e / TP) * scp + (e & (TP - 1))) + scBias] = (uint8_t)raw;
         }
         __syncwarp();
         // ---- NMS (strict >, neighbours outside the zone or not corners count as 0) + emission in list order
         for (int k0 = 0; k0 < n; k0 += 32) {
             const int k = k0 + lane;
             bool keep = false;
-            int e = 0, v = 0;
+            unsigned e = 0;
+            int v = 0;
             if (k < n) {
                 e = list[k];
-                const uint8_t* s = sc + ((e >> 8) - 2) * scp + ((e & 0xFF) - zx0 + 1);
+                const uint8_t* s = sc + (int)((e / TP) * scp + (e & (TP - 1))) + scBias;
                 v = s[0];
                 if (v) {
                     const int m1 = max(max((int)s[-1], (int)s[1]), max((int)s[-scp - 1], (int)s[-scp]));
@@ -306,7 +376,7 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             const unsigned kb = __ballot_sync(FULL, keep);
             if (keep) {
                 // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
-                const int x = (e & 0xFF) - dx0 + xoff, y = (e >> 8) + yoff;
+                const int x = (int)(e & (TP - 1)) - dx0 + xoff, y = (int)(e / TP) + yoff;
                 out[total + __popc(kb & ltmask)] = pack_key(x, y, v - 1);
             }
             total += __popc(kb);
@@ -316,21 +386,32 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     if (lane == 0) *cntOut = total;
 }
 
-__global__ void __launch_bounds__(FAST_WARPS * 32) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
+#ifndef FAST_MINB
+#define FAST_MINB 9
+#endif
+template <int TP>
+__global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    fast_cell_body(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem);
+    fast_cell_body<TP>(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem);
+}
+
+template <int TP>
+static void launch_fast_cells_tp(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
+{
+    static thread_local size_t configured = 48 * 1024;
+    if (smemBytes > configured) {      // small levels can have cells of up to 61 x 61 pixels
+        cudaFuncSetAttribute(k_fast_cells<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        configured = smemBytes;
+    }
+    dim3 grd((P.totalCells + FAST_WARPS - 1) / FAST_WARPS, B);
+    k_fast_cells<TP><<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS));
 }
 
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
 {
-    static thread_local size_t configured = 48 * 1024;
-    if (smemBytes > configured) {      // small levels can have cells of up to 61 x 61 pixels
-        cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        configured = smemBytes;
-    }
-    dim3 grd((P.totalCells + FAST_WARPS - 1) / FAST_WARPS, B);
-    k_fast_cells<<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS));
+    if (P.fastPitch == 64) launch_fast_cells_tp<64>(s, P, F, B, smemBytes);
+    else launch_fast_cells_tp<128>(s, P, F, B, smemBytes);
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree
@@ -777,35 +858,6 @@ void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
 {
     dim3 grd((P.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, B);
     k_blur<<<grd, BLUR_WARPS * 32, 0, s>>>(P, F);
-}
-
-// Horizontal fusion of the two independent stages that follow the pyramid: cell FAST keeps the ALU pipe busy (min / max /
-// SWAR compares), the blur lives on the dot-product (IDP) pipe.  One launch whose blocks are FAST blocks and blur blocks
-// interleaved in index order, so that every SM holds warps of both kinds and the two pipes overlap; the quadtree (which
-// needs the FAST output) and the descriptors (which need both) follow as before.
-#ifndef FB_MINB
-#define FB_MINB 6
-#endif
-__global__ void __launch_bounds__(FAST_WARPS * 32, FB_MINB) k_fast_blur(const Plan P, const FrameBufs F, int smemPerWarp, int nF, int nB)
-{
-    extern __shared__ __align__(16) uint8_t smem[];
-    const int x = blockIdx.x, T = nF + nB, wid = threadIdx.x >> 5;
-    const int kb = (int)(((long long)x * nB) / T);                       // blur blocks before x
-    const bool isBlur = (int)(((long long)(x + 1) * nB) / T) > kb;
-    if (isBlur) blur_tile_body(P, F, blockIdx.y, kb * FAST_WARPS + wid);
-    else fast_cell_body(P, F, smemPerWarp, blockIdx.y, (x - kb) * FAST_WARPS + wid, smem);
-}
-
-void launch_fast_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
-{
-    static thread_local size_t configured = 48 * 1024;
-    if (smemBytes > configured) {
-        cudaFuncSetAttribute(k_fast_blur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        configured = smemBytes;
-    }
-    const int nF = (P.totalCells + FAST_WARPS - 1) / FAST_WARPS, nB = (P.totalBlurTiles + FAST_WARPS - 1) / FAST_WARPS;
-    dim3 grd(nF + nB, B);
-    k_fast_blur<<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS), nF, nB);
 }
 
 // ------------------------------------------------------------------------------------------------ orientation + rBRIEF

@@ -20,7 +20,7 @@ struct FrameBufs {
     orbx_kp* kps;                  // B x totalNodes
     uint8_t* desc;                 // B x totalNodes x 32
     int* counts;                   // B
-    const uint4* cellTab;          // totalCells (per shape, shared by all frames): FAST cell geometry, see fast_cell_body
+    const uint4* cellTab;          // 2 x totalCells (per shape, shared by all frames): FAST cell geometry, see fast_cell_record
 };
 
 struct UMaxTable { int v[16]; };
@@ -37,8 +37,6 @@ void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B,
 cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, size_t smemBytes);
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
-// both of the above in one launch (FAST and blur blocks interleaved so that their pipes overlap on every SM)
-void launch_fast_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
 void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B);
 // padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
@@ -49,6 +47,8 @@ void launch_gray(cudaStream_t s, const uint8_t* src, size_t spitch, size_t sfram
                  int channels, int rgb, int B);
 
 size_t fast_smem_bytes(const Plan& P);
+int fast_tile_pitch(const Plan& P);                                       // 64 or 128; 0 = a cell is too wide
+void fast_cell_record(const LevelGeom& G, int level, int i, int j, uint4* rec);   // the two table entries of cell (i, j)
 size_t octree_smem_bytes(int capS, int sortCap);
 
 }  // namespace orbx

@@ -60,7 +60,7 @@ struct Plan {
     int totalCells;         // per frame
     int totalNodes;         // per frame: sum of nodeCap == stride of the keypoint outputs
     int totalBlurTiles;     // per frame
-    int pad_;
+    int fastPitch;          // row pitch (bytes) of the FAST cell tiles in shared memory: 64 or 128 (fast_tile_pitch)
     unsigned long long pyrSlab, blurSlab, slotSlab, keySlab;   // per-frame sizes (bytes / entries)
     LevelGeom lv[MAX_LEVELS];
 };

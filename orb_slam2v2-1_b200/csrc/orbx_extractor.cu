@@ -49,7 +49,6 @@ struct orbx_extractor {
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
 
     int device = 0, maxBatch = 1, fmaMode = 0;
-    bool fuseFastBlur = false;         // FAST and blur in one launch (ORBX_FUSE=1 in the environment; measured slower than two launches)
     cudaStream_t stream = nullptr;
     float4* d_patT = nullptr;          // rBRIEF pattern as floats: patT[bit * 32 + byte] = (x0, y0, x1, y1)
     uint2* d_icTab = nullptr;          // IC_Angle weight words (see extract_kernels.cuh)
@@ -165,6 +164,8 @@ static int build_plan(orbx_extractor* ex, int w, int h)
     int sc = 1;
     while (sc < capS) sc <<= 1;
     ex->sortCap = sc;
+    P.fastPitch = fast_tile_pitch(P);
+    if (!P.fastPitch) { set_error("a FAST cell is wider than the 128-byte tile of the cell kernel"); return ORBX_ERR_ARG; }
     ex->fastSmem = fast_smem_bytes(P);
     ex->octSmem = octree_smem_bytes(capS, sc);
     if (ex->octSmem > 227 * 1024) { set_error("quadtree needs %zu bytes of shared memory (> 227 KB): nfeatures too large", ex->octSmem); return ORBX_ERR_ARG; }
@@ -271,7 +272,7 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     const size_t oSlots = take(sizeof(uint32_t) * P.slotSlab * cap), oKeys = take(sizeof(uint32_t) * P.keySlab * cap);
     const size_t oKnode = take(sizeof(uint16_t) * P.keySlab * cap);
     const size_t oLK = take(sizeof(uint32_t) * P.totalNodes * cap), oLC = take(sizeof(int) * MAX_LEVELS * cap);
-    const size_t oCT = take(sizeof(uint4) * P.totalCells);
+    const size_t oCT = take(sizeof(uint4) * 2 * P.totalCells);
     // outputs contiguous: counts | kps | desc  (one D2H copy)
     const size_t oOut = off;
     const size_t oCounts = take(sizeof(int) * cap), oKps = take(sizeof(orbx_kp) * P.totalNodes * cap);
@@ -293,25 +294,11 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     F.counts = (int*)(base + oCounts);
     F.cellTab = (const uint4*)(base + oCT);
     {   // FAST cell table (ComputeKeyPointsOctTree :789-806)
-        std::vector<uint4> tab(P.totalCells);
+        std::vector<uint4> tab(2 * (size_t)P.totalCells);
         for (int l = 0; l < ex->nlevels; l++) {
             const LevelGeom& G = P.lv[l];
             for (int i = 0; i < G.nRows; i++)
-                for (int j = 0; j < G.nCols; j++) {
-                    const int iniX = MIN_BORDER + j * G.wCell, iniY = MIN_BORDER + i * G.hCell;
-                    const int maxX = std::min(iniX + G.wCell + 6, G.maxBX), maxY = std::min(iniY + G.hCell + 6, G.maxBY);
-                    const int tw = maxX - iniX, th = maxY - iniY;
-                    const bool skip = iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7;
-                    uint4 r;
-                    r.x = (unsigned)iniX | ((unsigned)iniY << 16);
-                    r.y = skip ? 0u : ((unsigned)tw | ((unsigned)th << 16));
-                    r.z = (unsigned)l | ((unsigned)(j * G.wCell) << 4) | ((unsigned)(i * G.hCell) << 16);
-                    // rows per warp iteration of the staging loop (32 / tile words per row) and of the pre-filter (32 / zone words per row)
-                    const int ax = iniX & ~3, tpw = (maxX - ax + 3) >> 2;
-                    const int zx0 = iniX - ax + 3, zx1 = zx0 + tw - 6, nwz = skip ? 1 : ((zx1 - 1) >> 2) - (zx0 >> 2) + 1;
-                    r.w = (unsigned)(i * G.nCols + j) | ((unsigned)std::min(std::max(32 / std::max(tpw, 1), 1), 15) << 16) | ((unsigned)std::min(std::max(32 / nwz, 1), 15) << 20);
-                    tab[G.cellBase + i * G.nCols + j] = r;
-                }
+                for (int j = 0; j < G.nCols; j++) fast_cell_record(G, l, i, j, &tab[2 * (size_t)(G.cellBase + i * G.nCols + j)]);
         }
         ORBX_CUDA(cudaMemcpyAsync(base + oCT, tab.data(), sizeof(uint4) * tab.size(), cudaMemcpyHostToDevice, ex->stream));
         ORBX_CUDA(cudaStreamSynchronize(ex->stream));
@@ -345,16 +332,15 @@ static int enqueue(orbx_extractor* ex, int B)
         launches++;
     }
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
-    if (ex->fuseFastBlur) launch_fast_blur(s, P, F, B, ex->fastSmem);      // stage 2 = FAST + blur, stage 4 empty
-    else launch_fast_cells(s, P, F, B, ex->fastSmem);
+    launch_fast_cells(s, P, F, B, ex->fastSmem);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octSmem));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
-    if (!ex->fuseFastBlur) launch_blur(s, P, F, B);
+    launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
-    launches += ex->fuseFastBlur ? 3 : 4;
+    launches += 4;
     ORBX_CUDA(cudaGetLastError());
     ex->lastLaunches = launches;
     ex->lastB = B;
@@ -391,7 +377,6 @@ int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, in
     ex->minThFAST = minThFAST;
     ex->device = device;
     ex->maxBatch = max_batch;
-    if (const char* e = getenv("ORBX_FUSE")) ex->fuseFastBlur = atoi(e) != 0;
 
     // scale tables: float chain, the member scaleFactor is a double (ORBextractor.cc:415-431)
     ex->mvScaleFactor.resize(nlevels);
