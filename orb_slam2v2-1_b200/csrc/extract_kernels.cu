@@ -419,8 +419,13 @@ void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B,
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree
-constexpr int OCT_THREADS = 256;       // several (level, frame) problems per SM hide each other's barrier and memory latency
-constexpr int OCT_KEYS_SMEM = 4096;    // candidates of a level kept in shared memory when they fit (else the global workspace)
+#ifndef OCT_THREADS_N
+#define OCT_THREADS_N 128
+#define OCT_MINB 10
+#define OCT_KEYS_N 1536
+#endif
+constexpr int OCT_THREADS = OCT_THREADS_N;   // the kernel is bound by barrier and memory latency: many small CTAs per SM hide each other's (measured: 256 x 4 CTAs 0.236 ms, 128 x 10 CTAs 0.198 ms, 64 x 10 0.30 ms per 512 frames)
+constexpr int OCT_KEYS_SMEM = OCT_KEYS_N;    // candidates of a level kept in shared memory when they fit (else the global workspace)
 
 // in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
 __device__ int block_exclusive_scan(int* a, int n, int* wsum)
@@ -471,7 +476,7 @@ size_t octree_smem_bytes(int capS, int sortCap)
 // is an array in list order, rebuilt every pass with prefix sums; every candidate carries the position of its node.
 // Tie-break of the "largest first" phase (ORBextractor.cc:684 sorts by (size, heap address)): creation order, later
 // first == smaller list position first (the portable definition of the oracle, tie_mode 0).
-__global__ void __launch_bounds__(OCT_THREADS, 4) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
+__global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     __shared__ int wsum[33];
