@@ -80,6 +80,8 @@ struct orbx_matcher {
     orbx::Arena arena, arena2;     // arena2: buffers whose size is known only after a device count
     uint2* d_partial = nullptr;
     size_t partialCap = 0;
+    int* d_tickets = nullptr;      // brute force: arrivals per query block (k_bf_scan), zero between calls
+    int ticketCap = 0;
     int lastLaunches = 0;
 };
 
