@@ -9,6 +9,7 @@
 #include <algorithm>
 #include "sincosf_glibc.h"
 #include <float.h>
+#include <stdlib.h>
 
 namespace orbx {
 
@@ -419,18 +420,17 @@ void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B,
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree
-#ifndef OCT_THREADS_N
-#define OCT_THREADS_N 128
-#define OCT_MINB 10
-#define OCT_KEYS_N 1536
-#endif
-constexpr int OCT_THREADS = OCT_THREADS_N;   // the kernel is bound by barrier and memory latency: many small CTAs per SM hide each other's (measured: 256 x 4 CTAs 0.236 ms, 128 x 10 CTAs 0.198 ms, 64 x 10 0.30 ms per 512 frames)
-constexpr int OCT_KEYS_SMEM = OCT_KEYS_N;    // candidates of a level kept in shared memory when they fit (else the global workspace)
+// The kernel is bound by barrier and memory latency, so many small CTAs per SM hide each other's: for the usual quotas
+// (a few hundred nodes per level) 128 threads x 10 CTAs per SM with 1536 candidates in shared memory (measured per 512
+// 640x480 frames: 256 x 4 CTAs 0.236 ms, 128 x 10 CTAs 0.198 ms, 64 x 10 0.30 ms); levels with thousands of candidates
+// (1080p, nfeatures = 4000) keep the 256-thread form with 4096 candidates in shared memory.
+struct OctSmall { static constexpr int THREADS = 128, MINB = 10, KEYS = 1536; };
+struct OctLarge { static constexpr int THREADS = 256, MINB = 4, KEYS = 4096; };
 
 // in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
+template <int T>                       // compile-time: the per-thread chunk is a shift, not an integer division
 __device__ int block_exclusive_scan(int* a, int n, int* wsum)
 {
-    constexpr int T = OCT_THREADS;      // compile-time: the per-thread chunk is a shift, not an integer division
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + T - 1) / T;
     const int b = min(tid * per, n), e = min(b + per, n);
@@ -463,8 +463,20 @@ __device__ int block_exclusive_scan(int* a, int n, int* wsum)
     return total;
 }
 
-size_t octree_smem_bytes(int capS, int sortCap)
+// small form only when the quotas are small (<= ~300 nodes per level) and the launch has at least two waves of small CTAs;
+// otherwise a (level, frame) problem is the critical path and the larger CTA finishes it sooner (measured: 752x480
+// nf=1200 x 192 frames 0.160 vs 0.129 ms, 1241x376 nf=2000 x 512 frames 0.40 vs 0.32 ms, 640x480 nf=1000 x 64 frames
+// 0.087 vs 0.055 ms, in favour of the large form; 640x480 nf=1000 x 512 frames 0.198 vs 0.236 ms in favour of the small one)
+static bool octree_large(const Plan& P, int B, int capS)
 {
+    static const int thr = getenv("ORBX_OCT_THR") ? atoi(getenv("ORBX_OCT_THR")) : 300;       // tuning override
+    return capS > thr || (long long)B * P.nlevels < 2LL * 148 * OctSmall::MINB;
+}
+
+// shared memory of the larger form (the limit check at plan time); launch_octree sizes the launch itself
+size_t octree_smem_bytes(int capS, int sortCap, int keysCap)
+{
+    const int OCT_KEYS_SMEM = keysCap > 0 ? keysCap : OctLarge::KEYS;
     // rectA, rectB (short4) | cntA, cntB | cc[4] | chBeg | tmp | skey[sortCap] | rankOf, mapS (u16) | childPos[4] (u16)
     // ... | keys (u32) and node positions (u16) of up to OCT_KEYS_SMEM candidates
     const size_t nodes = ((size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 8) + (size_t)sortCap * 4 + 15) & ~(size_t)15;
@@ -476,12 +488,15 @@ size_t octree_smem_bytes(int capS, int sortCap)
 // is an array in list order, rebuilt every pass with prefix sums; every candidate carries the position of its node.
 // Tie-break of the "largest first" phase (ORBextractor.cc:684 sorts by (size, heap address)): creation order, later
 // first == smaller list position first (the portable definition of the oracle, tie_mode 0).
-__global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
+template <class CFG>
+__global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P, const FrameBufs F, int capS, int sortCap)
 {
+    constexpr int OCT_KEYS_SMEM = CFG::KEYS;
     extern __shared__ __align__(16) uint8_t smraw[];
     __shared__ int wsum[33];
     __shared__ int s_k, s_nexp, s_m;
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, T = OCT_THREADS, lane = tid & 31, wid = tid >> 5;
+    constexpr int T = CFG::THREADS;
+    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const LevelGeom& G = P.lv[l];
 
     short4* rA = reinterpret_cast<short4*>(smraw);
@@ -510,7 +525,7 @@ __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, 
     // candidate order of the reference: cell row, cell column, then cv::FAST's row-major order inside the cell
     for (int i = tid; i < ncell; i += T) cellOff[i] = cellCount[i];
     __syncthreads();
-    const int n = block_exclusive_scan(cellOff, ncell, wsum);
+    const int n = block_exclusive_scan<T>(cellOff, ncell, wsum);
     if (n == 0) {
         if (tid == 0) *outCount = 0;
         return;
@@ -557,7 +572,7 @@ __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, 
         for (int p = tid; p < m; p += T) { tmp[p] = cA[p] > 1; rankOf[p] = 0xFFFF; }
         if (tid == 0) { s_k = 0x7FFFFFFF; s_nexp = 0; }
         __syncthreads();
-        const int np = block_exclusive_scan(tmp, m, wsum);
+        const int np = block_exclusive_scan<T>(tmp, m, wsum);
         if (np == 0) break;                                   // nothing to split: list size cannot change
         if (!lf) {
             for (int p = tid; p < m; p += T) if (cA[p] > 1) skey[tmp[p]] = (uint32_t)p;      // list order (:606)
@@ -612,7 +627,7 @@ __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, 
         for (int r = tid; r < np; r += T)
             chBeg[r] = (cc[4 * r] > 0) + (cc[4 * r + 1] > 0) + (cc[4 * r + 2] > 0) + (cc[4 * r + 3] > 0);
         __syncthreads();
-        const int totalCh = block_exclusive_scan(chBeg, np, wsum);
+        const int totalCh = block_exclusive_scan<T>(chBeg, np, wsum);
         int k = np;
         if (lf) {
             for (int r = tid; r < np; r += T) {
@@ -627,7 +642,7 @@ __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, 
         // ---- new list = reverse(children) ++ unsplit nodes
         for (int p = tid; p < m; p += T) tmp[p] = (int)rankOf[p] >= k;
         __syncthreads();
-        block_exclusive_scan(tmp, m, wsum);
+        block_exclusive_scan<T>(tmp, m, wsum);
         for (int p = tid; p < m; p += T)
             if ((int)rankOf[p] >= k) {
                 const int q = C + tmp[p];
@@ -684,17 +699,25 @@ __global__ void __launch_bounds__(OCT_THREADS, OCT_MINB) k_octree(const Plan P, 
     if (tid == 0) *outCount = m;
 }
 
-cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, size_t smemBytes)
+template <class CFG>
+static cudaError_t launch_octree_cfg(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap)
 {
+    const size_t smemBytes = octree_smem_bytes(capS, sortCap, CFG::KEYS);
     static thread_local size_t configured = 0;
     if (smemBytes > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        cudaError_t e = cudaFuncSetAttribute(k_octree<CFG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
         if (e != cudaSuccess) return e;
         configured = smemBytes;
     }
     dim3 grd(P.nlevels, B);
-    k_octree<<<grd, OCT_THREADS, smemBytes, s>>>(P, F, capS, sortCap);
+    k_octree<CFG><<<grd, CFG::THREADS, smemBytes, s>>>(P, F, capS, sortCap);
     return cudaSuccess;
+}
+
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap)
+{
+    return octree_large(P, B, capS) ? launch_octree_cfg<OctLarge>(s, P, F, B, capS, sortCap)
+                                    : launch_octree_cfg<OctSmall>(s, P, F, B, capS, sortCap);
 }
 
 // ------------------------------------------------------------------------------------------------ Gaussian blur

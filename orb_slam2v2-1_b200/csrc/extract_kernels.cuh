@@ -34,7 +34,7 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 // per-cell FAST-9/16 + NMS + ini/min retry, all levels and frames (ComputeKeyPointsOctTree cell loop, :789-829)
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);
 // DistributeOctTree (:539-763), one CTA per (level, frame)
-cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, size_t smemBytes);
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap);
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
@@ -49,6 +49,6 @@ void launch_gray(cudaStream_t s, const uint8_t* src, size_t spitch, size_t sfram
 size_t fast_smem_bytes(const Plan& P);
 int fast_tile_pitch(const Plan& P);                                       // 64 or 128; 0 = a cell is too wide
 void fast_cell_record(const LevelGeom& G, int level, int i, int j, uint4* rec);   // the two table entries of cell (i, j)
-size_t octree_smem_bytes(int capS, int sortCap);
+size_t octree_smem_bytes(int capS, int sortCap, int keysCap = 0);   // keysCap 0: the larger of the two kernel forms
 
 }  // namespace orbx

@@ -334,7 +334,7 @@ static int enqueue(orbx_extractor* ex, int B)
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     launch_fast_cells(s, P, F, B, ex->fastSmem);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
-    ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octSmem));
+    ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
