@@ -81,12 +81,13 @@ __global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ src,
         const int4 yy = __ldg(&ytab[dy]);                          // {sy0, sy1 (clamped), b0, b1}
         const uint2 h0 = Hs[(yy.x - sFirst) * GX + tx], h1 = Hs[(yy.y - sFirst) * GX + tx];
         const unsigned b0 = (unsigned)yy.z, b1 = (unsigned)yy.w;
-        const unsigned v0 = ((b0 * (h0.x & 0xFFFFu)) >> 16) + (((b1 * (h1.x & 0xFFFFu)) >> 16) + 2u);      // <= 1022, >> 2 below
-        const unsigned v1 = ((b0 * (h0.x >> 16)) >> 16) + (((b1 * (h1.x >> 16)) >> 16) + 2u);
-        const unsigned v2 = ((b0 * (h0.y & 0xFFFFu)) >> 16) + (((b1 * (h1.y & 0xFFFFu)) >> 16) + 2u);
-        const unsigned v3 = ((b0 * (h0.y >> 16)) >> 16) + (((b1 * (h1.y >> 16)) >> 16) + 2u);
-        // pack: (v0 | v1 << 16) >> 2 has v0 >> 2 in byte 0 and v1 >> 2 in byte 2 (v < 1024)
-        const unsigned p01v = (v1 * 65536u + v0) >> 2, p23v = (v3 * 65536u + v2) >> 2;
+        // v = ((b0 * H0) >> 16) + ((b1 * H1) >> 16) + 2 <= 1022: the upper halves of two products are gathered by one PRMT
+        // each and both pixels of a pair are summed as u16x2 in one add; (v >> 2) then sits in bytes 0 and 2 of the shifted word
+        const unsigned A01 = __byte_perm(b0 * (h0.x & 0xFFFFu), b0 * (h0.x >> 16), 0x7632);
+        const unsigned B01 = __byte_perm(b1 * (h1.x & 0xFFFFu), b1 * (h1.x >> 16), 0x7632);
+        const unsigned A23 = __byte_perm(b0 * (h0.y & 0xFFFFu), b0 * (h0.y >> 16), 0x7632);
+        const unsigned B23 = __byte_perm(b1 * (h1.y & 0xFFFFu), b1 * (h1.y >> 16), 0x7632);
+        const unsigned p01v = (A01 + B01 + 0x00020002u) >> 2, p23v = (A23 + B23 + 0x00020002u) >> 2;
         *reinterpret_cast<uint32_t*>(D + (size_t)dy * dpitch) = __byte_perm(p01v, p23v, 0x6420);     // pitch is a multiple of 32: the last word may pad
     }
 }
