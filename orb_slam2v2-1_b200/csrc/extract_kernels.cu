@@ -424,9 +424,10 @@ void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B,
 // The kernel is bound by barrier and memory latency, so many small CTAs per SM hide each other's: for the usual quotas
 // (a few hundred nodes per level) 128 threads x 10 CTAs per SM with 1536 candidates in shared memory (measured per 512
 // 640x480 frames: 256 x 4 CTAs 0.236 ms, 128 x 10 CTAs 0.198 ms, 64 x 10 0.30 ms); levels with thousands of candidates
-// (1080p, nfeatures = 4000) keep the 256-thread form with 4096 candidates in shared memory.
+// keep the 256-thread form (512 threads for 1080p, nfeatures = 4000) with 4096 candidates in shared memory.
 struct OctSmall { static constexpr int THREADS = 128, MINB = 10, KEYS = 1536; };
 struct OctLarge { static constexpr int THREADS = 256, MINB = 4, KEYS = 4096; };
+struct OctHuge { static constexpr int THREADS = 512, MINB = 2, KEYS = 4096; };
 
 // in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
 template <int T>                       // compile-time: the per-thread chunk is a shift, not an integer division
@@ -717,6 +718,10 @@ static cudaError_t launch_octree_cfg(cudaStream_t s, const Plan& P, const FrameB
 
 cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap)
 {
+    // quotas of many hundreds of nodes (1080p, nfeatures = 4000): level 0 of one frame is the critical path of the launch, and
+    // 512 threads finish it sooner (64 frames: 0.44 -> 0.27 ms; 1024 threads: no further gain)
+    static const int hthr = getenv("ORBX_OCT_HUGE") ? atoi(getenv("ORBX_OCT_HUGE")) : 600;
+    if (capS > hthr) return launch_octree_cfg<OctHuge>(s, P, F, B, capS, sortCap);
     return octree_large(P, B, capS) ? launch_octree_cfg<OctLarge>(s, P, F, B, capS, sortCap)
                                     : launch_octree_cfg<OctSmall>(s, P, F, B, capS, sortCap);
 }
