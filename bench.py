@@ -366,7 +366,7 @@ def run_ours(args):
     pipeline_gbs = B_ALG * value / world / 1e9
     traffic, traffic_src = None, None
     try:      # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same shape), scaled to B frames
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01e_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01f_traffic.json")))
         per_frame = sum(tr["dram_bytes_per_frame"][k] for k in top.split("+"))
         traffic, traffic_src = per_frame * B, tr["source"]
     except Exception:
