@@ -136,6 +136,28 @@ def cpu_port_throughput(frames, seconds_budget, threads):
     return sum(done) / el, sum(done), threads
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL writes its version banner to stdout when the
+    box sets NCCL_DEBUG): route file descriptor 1 to stderr for the run and keep the real stdout for the result line."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -161,7 +183,7 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def pin_to_gpu_numa_node(local):
@@ -270,7 +292,13 @@ def run_ours(args):
     # ---- e2e: host buffers through orbx_extract_batch, 3 handles on 3 host threads so that H2D, kernels and D2H overlap
     import ctypes as C
     L = orbx.lib()
-    pinned = torch.from_numpy(host).pin_memory()
+    if args.e2e_wc:      # frames in write-combined page-locked memory: the host only writes them, the copy engine reads them unsnooped
+        pinned_in = orbx.PinnedArray(host.shape, np.uint8, write_combined=True)
+        pinned_in.array[...] = host
+        base_ptr = pinned_in.ptr
+    else:
+        pinned = torch.from_numpy(host).pin_memory()
+        base_ptr = pinned.data_ptr()
     chunk = min(args.e2e_chunk, B)
     nthreads = args.e2e_threads
     workers = [orbx.ORBextractor(*PARAMS, device=local, max_batch=chunk) for _ in range(nthreads)]
@@ -282,7 +310,6 @@ def run_ours(args):
     pin_k = [torch.zeros((chunk, cap, 28), dtype=torch.uint8).pin_memory() for _ in range(nthreads)]
     pin_d = [torch.zeros((chunk, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(nthreads)]
     outs = [(pin_k[t].numpy().view(orbx.KP_DTYPE).reshape(chunk, cap), pin_d[t].numpy(), np.zeros(chunk, np.int32)) for t in range(nthreads)]
-    base_ptr = pinned.data_ptr()
     chunks = [(c0, min(chunk, B - c0)) for c0 in range(0, B, chunk)]
 
     def e2e_worker(t, nsteps):
@@ -398,7 +425,7 @@ def run_ours(args):
                 "numa": numa},
         "roofline": roofline, "cpu_baseline": cpu, "match": match,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -412,8 +439,10 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads (= extractor handles) of the e2e leg")
+    ap.add_argument("--e2e-wc", type=int, default=0, help="1: e2e input frames in write-combined page-locked memory")
     ap.add_argument("--e2e-chunk", type=int, default=128, help="frames per orbx_extract_batch call in the e2e leg")
     args = ap.parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

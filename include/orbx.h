@@ -56,6 +56,11 @@ void orbx_destroy(orbx_extractor* ex);
  * 1 = FMA-contracted the way g++ -O3 -march=native compiles the reference on an FMA host. */
 int orbx_set_fma_mode(orbx_extractor* ex, int fma_mode);
 
+/* Tuning / test knob for DistributeOctTree (src/ORBextractor.cc:539-763): the quadtree kernel exists in three forms that
+ * give identical results and differ in CTA size; 0 = chosen per launch from the quotas and the batch size (default),
+ * 1 = 128 threads, 2 = 256 threads, 3 = 512 threads. */
+int orbx_set_octree_form(orbx_extractor* ex, int form);
+
 /* Replaces the by-value accessors GetLevels / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
  * GetInverseScaleSigmaSquares (include/ORBextractor.h:63-83).  Each non-null pointer receives nlevels floats. */
 int orbx_levels(const orbx_extractor* ex);
@@ -343,6 +348,13 @@ int orbv_transform_raw(orbx_vocabulary* v, const uint8_t* desc, int n, int level
  * into fv_node (capacity n), fv_off (capacity n + 1), feature indices into fv_idx (capacity n) - the layout orbm_search_by_bow takes. */
 int orbv_transform(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* bow_id, double* bow_val, int* nbow,
                    int* fv_node, int* fv_off, int* fv_idx, int* nfv);
+
+/* Page-locked host memory for the image / result arrays of the batch calls (orbx_extract_batch writes results straight into
+ * page-locked caller arrays, and contiguous page-locked frames travel as one copy).  write_combined = 1 asks for
+ * write-combined pages: not cached or snooped by the CPU, meant for buffers the host only WRITES (camera frames on their way
+ * to the device); never for result arrays.  Returns ORBX_ERR_CUDA when the allocation fails. */
+int orbx_alloc_pinned(size_t bytes, int write_combined, void** out);
+int orbx_free_pinned(void* p);
 
 /* Text of the last error raised on the calling thread ("" if none). */
 const char* orbx_last_error(void);

@@ -716,14 +716,15 @@ static cudaError_t launch_octree_cfg(cudaStream_t s, const Plan& P, const FrameB
     return cudaSuccess;
 }
 
-cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap)
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, int form)
 {
     // quotas of many hundreds of nodes (1080p, nfeatures = 4000): level 0 of one frame is the critical path of the launch, and
     // 512 threads finish it sooner (64 frames: 0.44 -> 0.27 ms; 1024 threads: no further gain)
     static const int hthr = getenv("ORBX_OCT_HUGE") ? atoi(getenv("ORBX_OCT_HUGE")) : 600;
-    if (capS > hthr) return launch_octree_cfg<OctHuge>(s, P, F, B, capS, sortCap);
-    return octree_large(P, B, capS) ? launch_octree_cfg<OctLarge>(s, P, F, B, capS, sortCap)
-                                    : launch_octree_cfg<OctSmall>(s, P, F, B, capS, sortCap);
+    if (form == 0) form = capS > hthr ? 3 : (octree_large(P, B, capS) ? 2 : 1);
+    if (form == 3) return launch_octree_cfg<OctHuge>(s, P, F, B, capS, sortCap);
+    if (form == 2) return launch_octree_cfg<OctLarge>(s, P, F, B, capS, sortCap);
+    return launch_octree_cfg<OctSmall>(s, P, F, B, capS, sortCap);
 }
 
 // ------------------------------------------------------------------------------------------------ Gaussian blur

@@ -34,7 +34,7 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 // per-cell FAST-9/16 + NMS + ini/min retry, all levels and frames (ComputeKeyPointsOctTree cell loop, :789-829)
 void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);
 // DistributeOctTree (:539-763), one CTA per (level, frame)
-cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap);
+cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, int form = 0);   // form: orbx_set_octree_form
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)

@@ -60,6 +60,7 @@ struct orbx_extractor {
     FrameBufs bufs{};
     int capS = 0, sortCap = 0;
     size_t fastSmem = 0, octSmem = 0;
+    int octForm = 0;                   // orbx_set_octree_form: 0 = automatic
     std::vector<int> xtabOff, ytabOff;
     int* d_xtab = nullptr;            // 8 ints per group of 4 output columns, all levels
     int4* d_ytab = nullptr;
@@ -334,7 +335,7 @@ static int enqueue(orbx_extractor* ex, int B)
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     launch_fast_cells(s, P, F, B, ex->fastSmem);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
-    ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap));
+    ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octForm));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
@@ -354,6 +355,20 @@ extern "C" {
 
 const char* orbx_last_error(void) { return g_err.c_str(); }
 const char* orbx_version(void) { return "orbx 0.1 sm_100a"; }
+
+int orbx_alloc_pinned(size_t bytes, int write_combined, void** out)
+{
+    if (!out || bytes == 0) { set_error("orbx_alloc_pinned: bad argument"); return ORBX_ERR_ARG; }
+    *out = nullptr;
+    ORBX_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocPortable | (write_combined ? cudaHostAllocWriteCombined : 0)));
+    return ORBX_OK;
+}
+
+int orbx_free_pinned(void* p)
+{
+    if (p) ORBX_CUDA(cudaFreeHost(p));
+    return ORBX_OK;
+}
 
 int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device, int max_batch,
                 orbx_extractor** out)
@@ -476,6 +491,13 @@ int orbx_set_fma_mode(orbx_extractor* ex, int fma_mode)
     if (!ex) { set_error("null handle"); return ORBX_ERR_ARG; }
     ex->fmaMode = fma_mode ? 1 : 0;
     ex->plan.fmaMode = ex->fmaMode;
+    return ORBX_OK;
+}
+
+int orbx_set_octree_form(orbx_extractor* ex, int form)
+{
+    if (!ex || form < 0 || form > 3) { set_error("orbx_set_octree_form: form must be 0..3"); return ORBX_ERR_ARG; }
+    ex->octForm = form;
     return ORBX_OK;
 }
 

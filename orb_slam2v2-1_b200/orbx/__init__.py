@@ -42,7 +42,10 @@ def lib():
     sig = {
         "orbx_create": (i, [i, f, i, i, i, i, i, vp]),
         "orbx_destroy": (None, [vp]),
+        "orbx_alloc_pinned": (i, [sz, i, vp]),
+        "orbx_free_pinned": (i, [vp]),
         "orbx_set_fma_mode": (i, [vp, i]),
+        "orbx_set_octree_form": (i, [vp, i]),
         "orbx_levels": (i, [vp]),
         "orbx_scale_tables": (i, [vp, vp, vp, vp, vp]),
         "orbx_features_per_level": (i, [vp, vp]),
@@ -191,6 +194,10 @@ class ORBextractor:
 
     def set_fma_mode(self, mode):
         _check(self._L.orbx_set_fma_mode(self._h, int(mode)))
+
+    def set_octree_form(self, form):
+        """0 = automatic, 1 / 2 / 3 = the 128- / 256- / 512-thread form of the quadtree kernel (identical results)."""
+        _check(self._L.orbx_set_octree_form(self._h, int(form)))
 
     def max_keypoints(self):
         return self._L.orbx_max_keypoints(self._h)
@@ -725,3 +732,28 @@ class ORBVocabulary:
 
 def version():
     return lib().orbx_version().decode()
+
+
+class PinnedArray:
+    """A page-locked numpy array from orbx_alloc_pinned (include/orbx.h); write_combined=True for buffers the host only
+    writes (frames on their way to the device).  Keep the object alive while `.array` is in use."""
+
+    def __init__(self, shape, dtype=np.uint8, write_combined=False):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        _check(lib().orbx_alloc_pinned(C.c_size_t(max(self.nbytes, 1)), int(write_combined), C.byref(p)))
+        self.ptr = p.value
+        buf = (C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().orbx_free_pinned(C.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

@@ -146,3 +146,46 @@ def test_device_resident_input():
     res = ex.fetch()
     for b in range(B):
         _compare_frame(ex, oe, imgs[b], stages=False, result=res[b])
+
+
+def test_device_input_with_4_byte_alignment_only():
+    """Level 0 given as a device image whose rows are only 4-byte aligned: the FAST cell tiles are then staged by 4-byte
+    copies (extract_kernels.cu, fast_cell_body) and must give the same bytes as the 16-byte path."""
+    import torch
+    B, W, H, pitch = 3, 640, 480, 644
+    imgs = np.stack([synth.rects(W, H, 1400 + i) for i in range(B)])
+    buf = torch.zeros(4 + B * H * pitch, dtype=torch.uint8, device="cuda")
+    view = buf[4:].view(B, H, pitch)                       # base pointer 4 bytes past a 256-byte boundary
+    view[:, :, :W] = torch.from_numpy(imgs).cuda()
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    torch.cuda.synchronize()
+    assert view.data_ptr() % 16 == 4
+    ex.extract_device(view.data_ptr(), B, W, H, pitch, pitch * H)
+    res = ex.fetch()
+    for b in range(B):
+        _compare_frame(ex, oe, imgs[b], stages=False, result=res[b])
+
+
+def test_levels_with_one_or_two_cell_columns():
+    """Levels whose active width is just under 60 px have ONE cell column of up to 59 px; widths just under 90 px give two
+    columns of 44-45 px: the widest FAST cell tiles there are (with the reference's 30-px cells a tile row never exceeds
+    64 bytes from its 16-byte-aligned origin, so the 128-byte tile form of the kernel is a guard, not a reachable path)."""
+    for (w, h) in [(91, 140), (105, 121), (121, 92), (150, 91), (178, 96)]:
+        ex = orbx.ORBextractor(200, 1.2, 2, 20, 7)
+        oe = O.OracleExtractor(200, 1.2, 2, 20, 7)
+        _compare_frame(ex, oe, synth.rects(w, h, 3 * w + h))
+        _compare_frame(ex, oe, synth.texture(w, h, w + 7), stages=False)
+
+
+@pytest.mark.parametrize("form", [1, 2, 3])
+def test_every_quadtree_kernel_form(form):
+    """The quadtree kernel has three CTA sizes picked per launch (small batches in the test suite always get the 256-thread
+    one): force each and compare everything.  The KITTI shape has levels with more candidates than the 128-thread form keeps
+    in shared memory (global-workspace path)."""
+    for (w, h, nf, seed) in [(640, 480, 1000, 1500), (1241, 376, 2000, 1501)]:
+        ex = orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+        ex.set_octree_form(form)
+        oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
+        _compare_frame(ex, oe, synth.rects(w, h, seed))
+        _compare_frame(ex, oe, synth.texture(w, h, seed + 10), stages=False)
