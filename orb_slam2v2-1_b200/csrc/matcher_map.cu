@@ -83,6 +83,48 @@ __global__ void __launch_bounds__(256) k_area_best(const orbx_kp* __restrict__ k
 // stereo flags, the Hamming threshold, the epipole distance (:735-741) or CheckDistEpipolarLine (:140-157) gets 1000.
 struct TriParams { float F[9]; float ex, ey; int onlyStereo; };
 
+struct TriQuery {       // per-warp constants of one untracked feature of the first key frame
+    uint4 qa, qb;
+    float la, lb, lc, den;
+    bool stereo1;
+};
+
+__device__ __forceinline__ TriQuery tri_query(const orbx_kp* __restrict__ k1, const uint4* __restrict__ d1, const float* __restrict__ uR1,
+                                              int f1, const TriParams& T)
+{
+    TriQuery Q;
+    const orbx_kp kp1 = k1[f1];
+    Q.stereo1 = uR1[f1] >= 0;
+    Q.qa = __ldg(&d1[2 * (size_t)f1]);
+    Q.qb = __ldg(&d1[2 * (size_t)f1 + 1]);
+    // epipolar line in the second image, l = x1' F12 (:143-145), left to right, no contraction
+    Q.la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[0]), __fmul_rn(kp1.y, T.F[3])), T.F[6]);
+    Q.lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[1]), __fmul_rn(kp1.y, T.F[4])), T.F[7]);
+    Q.lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[2]), __fmul_rn(kp1.y, T.F[5])), T.F[8]);
+    Q.den = __fadd_rn(__fmul_rn(Q.la, Q.la), __fmul_rn(Q.lb, Q.lb));
+    return Q;
+}
+
+// distance of candidate f2, or 1000 when a state-independent gate rejects it
+__device__ __forceinline__ int tri_candidate(const TriQuery& Q, int f2, const orbx_kp* __restrict__ k2, const uint4* __restrict__ d2,
+                                             const float* __restrict__ uR2, const uint8_t* __restrict__ hasMp2,
+                                             const float* __restrict__ sf2, const float* __restrict__ sigma2, const TriParams& T)
+{
+    const bool stereo2 = uR2[f2] >= 0;
+    if (hasMp2[f2] || (T.onlyStereo && !stereo2)) return 1000;
+    const int d = hamming256(Q.qa, Q.qb, __ldg(&d2[2 * (size_t)f2]), __ldg(&d2[2 * (size_t)f2 + 1]));
+    if (d > TH_LOW) return 1000;
+    const orbx_kp kp2 = k2[f2];
+    if (!Q.stereo1 && !stereo2) {
+        const float distex = __fsub_rn(T.ex, kp2.x), distey = __fsub_rn(T.ey, kp2.y);
+        if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.0f, sf2[kp2.octave])) return 1000;
+    }
+    const float num = __fadd_rn(__fadd_rn(__fmul_rn(Q.la, kp2.x), __fmul_rn(Q.lb, kp2.y)), Q.lc);
+    if (Q.den == 0) return 1000;
+    const float dsqr = __fdiv_rn(__fmul_rn(num, num), Q.den);
+    return (double)dsqr < __dmul_rn(3.84, (double)sigma2[kp2.octave]) ? d : 1000;
+}
+
 __global__ void __launch_bounds__(256) k_triangulation_dist(const orbx_kp* __restrict__ k1, const uint4* __restrict__ d1,
                                                             const float* __restrict__ uR1, const int* __restrict__ qfeat, int nq,
                                                             const orbx_kp* __restrict__ k2, const uint4* __restrict__ d2,
@@ -93,41 +135,44 @@ __global__ void __launch_bounds__(256) k_triangulation_dist(const orbx_kp* __res
 {
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (qi >= nq) return;
-    const int f1 = qfeat[qi];
-    const orbx_kp kp1 = k1[f1];
-    const bool stereo1 = uR1[f1] >= 0;
-    const uint4 qa = __ldg(&d1[2 * (size_t)f1]), qb = __ldg(&d1[2 * (size_t)f1 + 1]);
-    // epipolar line in the second image, l = x1' F12 (:143-145), left to right, no contraction
-    const float la = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[0]), __fmul_rn(kp1.y, T.F[3])), T.F[6]);
-    const float lb = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[1]), __fmul_rn(kp1.y, T.F[4])), T.F[7]);
-    const float lc = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, T.F[2]), __fmul_rn(kp1.y, T.F[5])), T.F[8]);
-    const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
-    for (int c = off[qi] + lane; c < off[qi + 1]; c += 32) {
-        const int f2 = idx[c];
-        int out = 1000;
-        const bool stereo2 = uR2[f2] >= 0;
-        if (!hasMp2[f2] && !(T.onlyStereo && !stereo2)) {
-            const int d = hamming256(qa, qb, __ldg(&d2[2 * (size_t)f2]), __ldg(&d2[2 * (size_t)f2 + 1]));
-            if (d <= TH_LOW) {
-                const orbx_kp kp2 = k2[f2];
-                bool ok = true;
-                if (!stereo1 && !stereo2) {
-                    const float distex = __fsub_rn(T.ex, kp2.x), distey = __fsub_rn(T.ey, kp2.y);
-                    if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.0f, sf2[kp2.octave])) ok = false;
-                }
-                if (ok) {
-                    const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, kp2.x), __fmul_rn(lb, kp2.y)), lc);
-                    if (den == 0) ok = false;
-                    else {
-                        const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
-                        ok = (double)dsqr < __dmul_rn(3.84, (double)sigma2[kp2.octave]);
-                    }
-                }
-                if (ok) out = d;
-            }
+    const TriQuery Q = tri_query(k1, d1, uR1, qfeat[qi], T);
+    for (int c = off[qi] + lane; c < off[qi + 1]; c += 32) dist[c] = tri_candidate(Q, idx[c], k2, d2, uR2, hasMp2, sf2, sigma2, T);
+}
+
+// The same scan, but only the candidates that pass every gate are written back: the host replay (vbMatched2, running best)
+// never looks at the others.  A query = one feature of key frame 1 and the range [q.y, q.z) of its vocabulary node's bucket
+// in idx2 (no per-query copy of the bucket); survivors go, in candidate order, into the query's slot of TRI_SLOT entries
+// (f2 | distance << 24); cnt[q] counts them all, so the host sees an overflow and falls back to k_triangulation_dist.
+constexpr int TRI_SLOT = 16;
+
+__global__ void __launch_bounds__(256) k_triangulation_compact(const orbx_kp* __restrict__ k1, const uint4* __restrict__ d1,
+                                                               const float* __restrict__ uR1, const int4* __restrict__ query, int nq,
+                                                               const orbx_kp* __restrict__ k2, const uint4* __restrict__ d2,
+                                                               const float* __restrict__ uR2, const uint8_t* __restrict__ hasMp2,
+                                                               const float* __restrict__ sf2, const float* __restrict__ sigma2,
+                                                               TriParams T, const int* __restrict__ idx2, int* __restrict__ cnt,
+                                                               uint32_t* __restrict__ slots)
+{
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (qi >= nq) return;
+    const int4 q = query[qi];
+    const TriQuery Q = tri_query(k1, d1, uR1, q.x, T);
+    int n = 0;
+    for (int c0 = q.y; c0 < q.z; c0 += 32) {
+        const int c = c0 + lane;
+        int f2 = 0, d = 1000;
+        if (c < q.z) {
+            f2 = idx2[c];
+            d = tri_candidate(Q, f2, k2, d2, uR2, hasMp2, sf2, sigma2, T);
         }
-        dist[c] = out;
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, d != 1000);
+        if (d != 1000) {
+            const int pos = n + __popc(m & ((1u << lane) - 1));
+            if (pos < TRI_SLOT) slots[(size_t)qi * TRI_SLOT + pos] = (uint32_t)f2 | ((uint32_t)d << 24);
+        }
+        n += __popc(m);
     }
+    if (lane == 0) cnt[qi] = n;
 }
 
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:281-311), one warp per MapPoint.  Row i of the distance matrix is
@@ -444,8 +489,14 @@ int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint
     for (int i = 0; i < n1; i++) matches12[i] = -1;
     for (int j = 0; j < n2; j++)
         if (k2[j].octave < 0 || k2[j].octave >= nlevels) { set_error("orbm_search_for_triangulation: octave out of range"); return ORBX_ERR_ARG; }
-    // merge-join on the node id (:693-786): each untracked feature of a common node becomes a query over that node's bucket
-    std::vector<int> qfeat, off(1, 0), idx;
+    if (n2 >= (1 << 24)) { set_error("orbm_search_for_triangulation: more than 2^24 features"); return ORBX_ERR_ARG; }
+    const int nidx2 = nn2 > 0 ? off2[nn2] : 0;
+    for (int p2 = 0; p2 < nidx2; p2++)
+        if (idx2[p2] < 0 || idx2[p2] >= n2) { set_error("orbm_search_for_triangulation: feature index out of range"); return ORBX_ERR_ARG; }
+    // merge-join on the node id (:693-786): each untracked feature of a common node becomes a query over that node's bucket,
+    // given as a range of idx2 (the bucket is not copied per query)
+    std::vector<int4> query;
+    long long total = 0;
     int a = 0, b = 0;
     while (a < nn1 && b < nn2) {
         if (node1[a] == node2[b]) {
@@ -454,12 +505,8 @@ int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint
                 if (f1 < 0 || f1 >= n1) { set_error("orbm_search_for_triangulation: feature index out of range"); return ORBX_ERR_ARG; }
                 if (has_mp1[f1]) continue;                                                   // :699-703
                 if (onlyStereo && !(u_right1[f1] >= 0)) continue;                            // :705-709
-                qfeat.push_back(f1);
-                for (int p2 = off2[b]; p2 < off2[b + 1]; p2++) {
-                    if (idx2[p2] < 0 || idx2[p2] >= n2) { set_error("orbm_search_for_triangulation: feature index out of range"); return ORBX_ERR_ARG; }
-                    idx.push_back(idx2[p2]);
-                }
-                off.push_back((int)idx.size());
+                query.push_back(make_int4(f1, off2[b], off2[b + 1], 0));
+                total += off2[b + 1] - off2[b];
             }
             a++; b++;
         } else if (node1[a] < node2[b]) {
@@ -468,61 +515,105 @@ int orbm_search_for_triangulation(orbx_matcher* m, const orbx_kp* k1, const uint
             b = (int)(std::lower_bound(node2, node2 + nn2, node1[a]) - node2);
         }
     }
-    const int nq = (int)qfeat.size(), total = off[nq];
+    const int nq = (int)query.size();
     if (nq == 0 || total == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(m->device));
     Carver cv(m->arena);
     const size_t oK1 = cv.take(sizeof(orbx_kp) * (size_t)n1), oD1 = cv.take((size_t)n1 * 32), oU1 = cv.take(sizeof(float) * (size_t)n1),
                  oK2 = cv.take(sizeof(orbx_kp) * (size_t)n2), oD2 = cv.take((size_t)n2 * 32), oU2 = cv.take(sizeof(float) * (size_t)n2),
                  oH2 = cv.take((size_t)n2), oSF = cv.take(sizeof(float) * (size_t)nlevels), oSG = cv.take(sizeof(float) * (size_t)nlevels),
-                 oQ = cv.take(sizeof(int) * (size_t)nq), oO = cv.take(sizeof(int) * ((size_t)nq + 1)), oI = cv.take(sizeof(int) * (size_t)total),
-                 oD = cv.take(sizeof(int) * (size_t)total);
+                 oQ = cv.take(sizeof(int4) * (size_t)nq), oI = cv.take(sizeof(int) * (size_t)nidx2),
+                 oC = cv.take(sizeof(int) * (size_t)nq), oS = cv.take(sizeof(uint32_t) * (size_t)nq * TRI_SLOT);
     int rc = m->arena.reserve(cv.total());
     if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    Xfer x(m->arena);
-    x.up(oK1, k1, sizeof(orbx_kp) * (size_t)n1);
-    x.up(oD1, d1, (size_t)n1 * 32);
-    x.up(oU1, u_right1, sizeof(float) * (size_t)n1);
-    x.up(oK2, k2, sizeof(orbx_kp) * (size_t)n2);
-    x.up(oD2, d2, (size_t)n2 * 32);
-    x.up(oU2, u_right2, sizeof(float) * (size_t)n2);
-    x.up(oH2, has_mp2, (size_t)n2);
-    x.up(oSF, sf2, sizeof(float) * (size_t)nlevels);
-    x.up(oSG, sigma2_2, sizeof(float) * (size_t)nlevels);
-    x.up(oQ, qfeat.data(), sizeof(int) * (size_t)nq);
-    x.up(oO, off.data(), sizeof(int) * ((size_t)nq + 1));
-    x.up(oI, idx.data(), sizeof(int) * (size_t)total);
-    ORBX_CUDA(x.send());
     TriParams T;
     memcpy(T.F, F12, sizeof(T.F));
     T.ex = ex;
     T.ey = ey;
     T.onlyStereo = onlyStereo;
-    k_triangulation_dist<<<(nq + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oK1), (const uint4*)(B + oD1), (const float*)(B + oU1), (const int*)(B + oQ), nq,
-                                                      (const orbx_kp*)(B + oK2), (const uint4*)(B + oD2), (const float*)(B + oU2),
-                                                      (const uint8_t*)(B + oH2), (const float*)(B + oSF), (const float*)(B + oSG), T,
-                                                      (const int*)(B + oO), (const int*)(B + oI), (int*)(B + oD));
-    ORBX_CUDA(cudaGetLastError());
-    m->lastLaunches = 1;
-    std::vector<int> dist(total);
-    x.down(dist.data(), oD, sizeof(int) * (size_t)total);
-    ORBX_CUDA(x.fetch());
+    std::vector<int> cnt(nq);
+    std::vector<uint32_t> slots((size_t)nq * TRI_SLOT);
+    {
+        Xfer x(m->arena);
+        x.up(oK1, k1, sizeof(orbx_kp) * (size_t)n1);
+        x.up(oD1, d1, (size_t)n1 * 32);
+        x.up(oU1, u_right1, sizeof(float) * (size_t)n1);
+        x.up(oK2, k2, sizeof(orbx_kp) * (size_t)n2);
+        x.up(oD2, d2, (size_t)n2 * 32);
+        x.up(oU2, u_right2, sizeof(float) * (size_t)n2);
+        x.up(oH2, has_mp2, (size_t)n2);
+        x.up(oSF, sf2, sizeof(float) * (size_t)nlevels);
+        x.up(oSG, sigma2_2, sizeof(float) * (size_t)nlevels);
+        x.up(oQ, query.data(), sizeof(int4) * (size_t)nq);
+        x.up(oI, idx2, sizeof(int) * (size_t)nidx2);
+        ORBX_CUDA(x.send());
+        k_triangulation_compact<<<(nq + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oK1), (const uint4*)(B + oD1), (const float*)(B + oU1),
+                                                             (const int4*)(B + oQ), nq, (const orbx_kp*)(B + oK2), (const uint4*)(B + oD2),
+                                                             (const float*)(B + oU2), (const uint8_t*)(B + oH2), (const float*)(B + oSF),
+                                                             (const float*)(B + oSG), T, (const int*)(B + oI), (int*)(B + oC), (uint32_t*)(B + oS));
+        ORBX_CUDA(cudaGetLastError());
+        m->lastLaunches = 1;
+        x.down(cnt.data(), oC, sizeof(int) * (size_t)nq);
+        x.down(slots.data(), oS, sizeof(uint32_t) * (size_t)nq * TRI_SLOT);
+        ORBX_CUDA(x.fetch());
+    }
+    // candidates that passed the gates, per query, in candidate order: (f2 | distance << 24)
+    std::vector<int> eoff(nq + 1, 0);
+    std::vector<uint32_t> ent;
+    bool overflow = false;
+    for (int q = 0; q < nq; q++) overflow |= cnt[q] > TRI_SLOT;
+    if (!overflow) {
+        for (int q = 0; q < nq; q++) {
+            ent.insert(ent.end(), slots.begin() + (size_t)q * TRI_SLOT, slots.begin() + (size_t)q * TRI_SLOT + cnt[q]);
+            eoff[q + 1] = (int)ent.size();
+        }
+    } else {
+        // a query with more than TRI_SLOT surviving candidates: every distance comes back (one more launch)
+        std::vector<int> off(nq + 1, 0), qfeat(nq);
+        for (int q = 0; q < nq; q++) { qfeat[q] = query[q].x; off[q + 1] = off[q] + (query[q].z - query[q].y); }
+        std::vector<int> idx((size_t)off[nq]), dist((size_t)off[nq]);
+        for (int q = 0; q < nq; q++) std::copy(idx2 + query[q].y, idx2 + query[q].z, idx.begin() + off[q]);
+        Carver cv2(m->arena2);
+        const size_t oF = cv2.take(sizeof(int) * (size_t)nq), oO = cv2.take(sizeof(int) * ((size_t)nq + 1)),
+                     oX = cv2.take(sizeof(int) * idx.size()), oD = cv2.take(sizeof(int) * idx.size());
+        rc = m->arena2.reserve(cv2.total());
+        if (!rc) rc = m->arena2.mirror();
+        if (rc) return rc;
+        uint8_t* B2 = m->arena2.base;
+        Xfer x(m->arena2);
+        x.up(oF, qfeat.data(), sizeof(int) * (size_t)nq);
+        x.up(oO, off.data(), sizeof(int) * ((size_t)nq + 1));
+        x.up(oX, idx.data(), sizeof(int) * idx.size());
+        ORBX_CUDA(x.send());
+        k_triangulation_dist<<<(nq + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oK1), (const uint4*)(B + oD1), (const float*)(B + oU1),
+                                                          (const int*)(B2 + oF), nq, (const orbx_kp*)(B + oK2), (const uint4*)(B + oD2),
+                                                          (const float*)(B + oU2), (const uint8_t*)(B + oH2), (const float*)(B + oSF),
+                                                          (const float*)(B + oSG), T, (const int*)(B2 + oO), (const int*)(B2 + oX), (int*)(B2 + oD));
+        ORBX_CUDA(cudaGetLastError());
+        m->lastLaunches = 2;
+        x.down(dist.data(), oD, sizeof(int) * dist.size());
+        ORBX_CUDA(x.fetch());
+        for (int q = 0; q < nq; q++) {
+            for (int c = off[q]; c < off[q + 1]; c++)
+                if (dist[c] <= TH_LOW) ent.push_back((uint32_t)idx[c] | ((uint32_t)dist[c] << 24));
+            eoff[q + 1] = (int)ent.size();
+        }
+    }
     // sequential replay of the greedy part: vbMatched2 and the running bestDist (ties replace, `dist > bestDist` at :729)
     std::vector<uint8_t> vbMatched2(n2, 0);
     std::vector<int> rotHist[HISTO_LENGTH];
     const float factor = 1.0f / HISTO_LENGTH;
     int nm = 0;
     for (int q = 0; q < nq; q++) {
-        const int f1 = qfeat[q];
+        const int f1 = query[q].x;
         int bestDist = TH_LOW, bestIdx2 = -1;
-        for (int c = off[q]; c < off[q + 1]; c++) {
-            const int f2 = idx[c];
+        for (int c = eoff[q]; c < eoff[q + 1]; c++) {
+            const int f2 = (int)(ent[c] & 0xFFFFFFu), d = (int)(ent[c] >> 24);
             if (vbMatched2[f2]) continue;
-            const int d = dist[c];
-            if (d > TH_LOW || d > bestDist) continue;
+            if (d > bestDist) continue;
             bestIdx2 = f2;
             bestDist = d;
         }

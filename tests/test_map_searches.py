@@ -344,6 +344,30 @@ def test_cuda_search_for_triangulation(seed, only_stereo, check):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("check", [True, False])
+def test_cuda_search_for_triangulation_many_survivors(check):
+    """The device writes back at most 16 gate-passing candidates per query and falls back to the full distance list when a
+    query has more: 40 copies of one feature (same descriptor, same position) in the second key frame force that path."""
+    import orbx
+    s = dict(scenes.triangulation_scene(1002))
+    k2, d2 = s["k2"].copy(), s["d2"].copy()
+    has2, ur2 = s["has_mp2"].copy(), s["u_right2"].copy()
+    # a correspondence the plain scene matches: its copies overwrite 40 other rows of key frame 2
+    n0, mt0 = O.search_for_triangulation(*_tri_args(s), False, check)
+    f1 = int(np.flatnonzero(mt0 >= 0)[5])
+    f2 = int(mt0[f1])
+    rows = [j for j in range(len(k2)) if j != f2][100:140]
+    for j in rows:
+        k2[j], d2[j], has2[j], ur2[j] = k2[f2], d2[f2], 0, ur2[f2]
+    s.update(k2=k2, d2=d2, has_mp2=has2, u_right2=ur2, fv2=scenes.feature_vector(d2, 16))
+    m = orbx.ORBmatcher(0.6, check)
+    n, mt = m.SearchForTriangulation(*_tri_args(s), False)
+    on, omt = O.search_for_triangulation(*_tri_args(s), False, check)
+    assert n == on and np.array_equal(mt, omt)
+    assert m.last_launches() == 2 and n > 40          # the fallback ran
+
+
+@pytest.mark.gpu
 def test_cuda_map_searches_empty_inputs():
     import orbx
     s = scenes.fuse_scene(1000)
