@@ -338,6 +338,12 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             if (__ballot_sync(FULL, (comb0 | comb1) != 0) == 0) continue;
             // ordered append: cnt = surviving pixels of this lane (0..8), positions from an inclusive shuffle scan
             const int cnt = __popc((comb0 >> 7) | (comb1 >> 6));
+#ifdef FAST_APPEND_BALLOT
+            const unsigned B0 = __ballot_sync(FULL, cnt & 1), B1 = __ballot_sync(FULL, cnt & 2), B2 = __ballot_sync(FULL, cnt & 4),
+                           B3 = __ballot_sync(FULL, cnt & 8);
+            int pos = n + __popc(B0 & ltmask) + 2 * __popc(B1 & ltmask) + 4 * __popc(B2 & ltmask) + 8 * __popc(B3 & ltmask);
+            n += __popc(B0) + 2 * __popc(B1) + 4 * __popc(B2) + 8 * __popc(B3);
+#else
             int inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -346,6 +352,7 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             }
             int pos = n + inc - cnt;
             n += __shfl_sync(FULL, inc, 31);
+#endif
             if (comb0 & 0x80u) list[pos++] = (uint16_t)e;
             if (comb0 & 0x8000u) list[pos++] = (uint16_t)(e + 1);
             if (comb0 & 0x800000u) list[pos++] = (uint16_t)(e + 2);
@@ -357,12 +364,34 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         }
         __syncwarp();
         // ---- exact score of the survivors
+#ifdef FAST_CORNER_LIST
+        // survivors that are corners (raw > t) are compacted in place (ballot ranks keep the order): the NMS below then
+        // visits corners only, about half of the survivors
+        int nc = 0;
+        for (int k0 = 0; k0 < n; k0 += 32) {
+            const int k = k0 + lane;
+            unsigned e = 0;
+            bool isc = false;
+            if (k < n) {
+                e = list[k];
+                const int raw = fast_raw_score<TP>(tile + e);
+                isc = raw > t;
+                if (isc) sc[(int)((e / TP) * scp + (e & (TP - 1))) + scBias] = (uint8_t)raw;
+            }
+            const unsigned cb = __ballot_sync(FULL, isc);            // also orders this iteration's reads before its writes
+            if (isc) list[nc + __popc(cb & ltmask)] = (uint16_t)e;   // nc <= k0: never ahead of the entries still to be read
+            nc += __popc(cb);
+        }
+        n = nc;
+        __syncwarp();
+#else
         for (int k = lane; k < n; k += 32) {
             const unsigned e = list[k];
             const int raw = fast_raw_score<TP>(tile + e);
             if (raw > t) sc[(int)((e / TP) * scp + (e & (TP - 1))) + scBias] = (uint8_t)raw;
         }
         __syncwarp();
+#endif
         // ---- NMS (strict >, neighbours outside the zone or not corners count as 0) + emission in list order
         for (int k0 = 0; k0 < n; k0 += 32) {
             const int k = k0 + lane;

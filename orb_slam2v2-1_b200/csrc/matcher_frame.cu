@@ -549,6 +549,67 @@ extern "C" int orbm_search_by_projection_frame(orbx_matcher* m, const orbx_kp* k
     return ORBX_OK;
 }
 
+namespace orbx {
+
+// SearchByBoW inner scan (ORBmatcher.cc:205-226, :571-596) for one feature of the first key frame over the bucket of its
+// vocabulary node in the second (a range [q.y, q.z) of idx2, visited in stored order): the BOW_TOP smallest keys
+// distance << 22 | position, ascending.  "Already matched" is the only state the reference's loop reads, so the host replay
+// walks these few keys instead of every distance; when the taken features exhaust them it rescans that one bucket itself.
+constexpr int BOW_TOP = 8;      // with 4 keys about one query in nine needs the host rescan (synthetic key frames), with 8 one in eighty
+
+__global__ void __launch_bounds__(256) k_bow_top(const uint4* __restrict__ d1, const int4* __restrict__ query, int nq,
+                                                 const uint4* __restrict__ d2, const uint8_t* __restrict__ valid2,
+                                                 const int* __restrict__ idx2, uint4* __restrict__ top)
+{
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (qi >= nq) return;
+    const int4 q = query[qi];
+    const uint4 qa = __ldg(&d1[2 * (size_t)q.x]), qb = __ldg(&d1[2 * (size_t)q.x + 1]);
+    uint32_t t[BOW_TOP];             // this lane's smallest keys, ascending
+#pragma unroll
+    for (int r = 0; r < BOW_TOP; r++) t[r] = KEY_NONE;
+    for (int c = q.y + lane; c < q.z; c += 32) {
+        const int f2 = idx2[c];
+        if (valid2 && !valid2[f2]) continue;
+        const int d = hamming256(qa, qb, __ldg(&d2[2 * (size_t)f2]), __ldg(&d2[2 * (size_t)f2 + 1]));
+        uint32_t key = ((uint32_t)d << KEY_SHIFT) | (uint32_t)(c - q.y);
+        if (key < t[BOW_TOP - 1]) {
+#pragma unroll
+            for (int r = 0; r < BOW_TOP; r++) {          // insertion: key sinks to its place, the largest falls out
+                const uint32_t lo = min(t[r], key), hi = max(t[r], key);
+                t[r] = lo;
+                key = hi;
+            }
+        }
+    }
+    uint32_t out[BOW_TOP];
+#pragma unroll
+    for (int r = 0; r < BOW_TOP; r++) {
+        const uint32_t g = __reduce_min_sync(0xFFFFFFFFu, t[0]);
+        out[r] = g;
+        if (t[0] == g) {
+#pragma unroll
+            for (int k = 0; k + 1 < BOW_TOP; k++) t[k] = t[k + 1];
+            t[BOW_TOP - 1] = KEY_NONE;
+        }
+    }
+    if (lane == 0) {
+        top[2 * (size_t)qi] = make_uint4(out[0], out[1], out[2], out[3]);
+        top[2 * (size_t)qi + 1] = make_uint4(out[4], out[5], out[6], out[7]);
+    }
+}
+
+static inline int hamming256_host(const uint8_t* a, const uint8_t* b)
+{
+    uint64_t x[4], y[4];
+    memcpy(x, a, 32);
+    memcpy(y, b, 32);
+    return __builtin_popcountll(x[0] ^ y[0]) + __builtin_popcountll(x[1] ^ y[1]) + __builtin_popcountll(x[2] ^ y[2]) +
+           __builtin_popcountll(x[3] ^ y[3]);
+}
+
+}  // namespace orbx
+
 extern "C" int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k1, const uint8_t* d1, int n1, const uint8_t* valid1,
                                   const int* node1, const int* off1, const int* idx1, int nn1,
                                   const orbx_kp* k2, const uint8_t* d2, int n2, const uint8_t* valid2,
@@ -564,9 +625,14 @@ extern "C" int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k
     if (nmatches) *nmatches = 0;
     const int nout = variant == 0 ? n2 : n1;
     for (int i = 0; i < nout; i++) matches[i] = -1;
+    if (n2 >= (int)KEY_POS_MASK) { set_error("orbm_search_by_bow: too many features"); return ORBX_ERR_ARG; }
+    const int nidx2 = nn2 > 0 ? off2[nn2] : 0;
+    for (int p2 = 0; p2 < nidx2; p2++)
+        if (idx2[p2] < 0 || idx2[p2] >= n2) { set_error("orbm_search_by_bow: feature index out of range"); return ORBX_ERR_ARG; }
     // merge-join of the two feature vectors on the node id (:180-264): every valid feature of a common node of the first
-    // key frame becomes a query whose candidates are the features of the same node in the second, in stored order
-    std::vector<int> qfeat, off(1, 0), idx;
+    // key frame becomes a query whose candidates are the features of the same node in the second, in stored order -- a range
+    // of idx2, not a copy
+    std::vector<int4> query;
     int a = 0, b = 0;
     while (a < nn1 && b < nn2) {
         if (node1[a] == node2[b]) {
@@ -574,12 +640,7 @@ extern "C" int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k
                 const int f1 = idx1[p1];
                 if (f1 < 0 || f1 >= n1) { set_error("orbm_search_by_bow: feature index out of range"); return ORBX_ERR_ARG; }
                 if (!valid1[f1]) continue;
-                qfeat.push_back(f1);
-                for (int p2 = off2[b]; p2 < off2[b + 1]; p2++) {
-                    if (idx2[p2] < 0 || idx2[p2] >= n2) { set_error("orbm_search_by_bow: feature index out of range"); return ORBX_ERR_ARG; }
-                    idx.push_back(idx2[p2]);
-                }
-                off.push_back((int)idx.size());
+                query.push_back(make_int4(f1, off2[b], off2[b + 1], 0));
             }
             a++; b++;
         } else if (node1[a] < node2[b]) {
@@ -588,28 +649,65 @@ extern "C" int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k
             b = (int)(std::lower_bound(node2, node2 + nn2, node1[a]) - node2);
         }
     }
-    const int nq = (int)qfeat.size();
+    const int nq = (int)query.size();
     if (nq == 0) return ORBX_OK;
-    std::vector<uint8_t> qdesc((size_t)nq * 32);
-    for (int q = 0; q < nq; q++) memcpy(&qdesc[(size_t)q * 32], d1 + (size_t)qfeat[q] * 32, 32);
-    std::vector<int> dist;
-    int rc = csr_distances(m, qdesc.data(), nq, d2, n2, off, idx, dist);
-    if (rc) return rc;
+    std::vector<uint32_t> top((size_t)nq * BOW_TOP);
+    {
+        ORBX_CUDA(cudaSetDevice(m->device));
+        Carver cv(m->arena);
+        const size_t oD1 = cv.take((size_t)n1 * 32), oD2 = cv.take((size_t)std::max(n2, 1) * 32), oV2 = cv.take((size_t)std::max(n2, 1)),
+                     oQ = cv.take(sizeof(int4) * (size_t)nq), oI = cv.take(sizeof(int) * (size_t)std::max(nidx2, 1)),
+                     oT = cv.take(sizeof(uint32_t) * (size_t)nq * BOW_TOP);
+        int rc = m->arena.reserve(cv.total());
+        if (!rc) rc = m->arena.mirror();
+        if (rc) return rc;
+        uint8_t* B = m->arena.base;
+        Xfer x(m->arena);
+        x.up(oD1, d1, (size_t)n1 * 32);
+        x.up(oD2, d2, (size_t)n2 * 32);
+        if (variant == 1) x.up(oV2, valid2, (size_t)n2);
+        x.up(oQ, query.data(), sizeof(int4) * (size_t)nq);
+        x.up(oI, idx2, sizeof(int) * (size_t)nidx2);
+        ORBX_CUDA(x.send());
+        k_bow_top<<<(nq + 7) / 8, 256, 0, m->stream>>>((const uint4*)(B + oD1), (const int4*)(B + oQ), nq, (const uint4*)(B + oD2),
+                                                       variant == 1 ? (const uint8_t*)(B + oV2) : nullptr, (const int*)(B + oI), (uint4*)(B + oT));
+        ORBX_CUDA(cudaGetLastError());
+        m->lastLaunches = 1;
+        x.down(top.data(), oT, sizeof(uint32_t) * (size_t)nq * BOW_TOP);
+        ORBX_CUDA(x.fetch());
+    }
     // sequential replay: features of the second frame taken by earlier queries are skipped (:209, :576)
     std::vector<uint8_t> taken2(n2, 0);
     std::vector<int> rotHist[HISTO_LENGTH];
     const float factor = 1.0f / HISTO_LENGTH;
     int nm = 0;
     for (int q = 0; q < nq; q++) {
-        const int f1 = qfeat[q];
+        const int f1 = query[q].x, qs = query[q].y, qe = query[q].z;
         int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
-        for (int c = off[q]; c < off[q + 1]; c++) {
-            const int f2 = idx[c];
+        const uint32_t* keys = &top[(size_t)q * BOW_TOP];
+        int found = 0;
+        bool complete = false;          // the keys seen so far cover every candidate that can still matter
+        for (int r = 0; r < BOW_TOP && found < 2; r++) {
+            const int d = (int)(keys[r] >> KEY_SHIFT);
+            if (d >= 256) { complete = true; break; }                       // the rest never passes `dist < bestDist`
+            const int f2 = idx2[qs + (int)(keys[r] & KEY_POS_MASK)];
             if (taken2[f2]) continue;
-            if (variant == 1 && !valid2[f2]) continue;
-            const int d = dist[c];
-            if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdx2 = f2; }
-            else if (d < bestDist2) bestDist2 = d;
+            if (found == 0) { bestDist1 = d; bestIdx2 = f2; }
+            else bestDist2 = d;
+            found++;
+        }
+        const bool lowSoFar = variant == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;
+        if (found < 2 && !complete && qe - qs > BOW_TOP && (found == 0 || lowSoFar)) {
+            // the taken features used up the returned keys: rescan this bucket here, exactly as the reference does
+            bestDist1 = 256; bestIdx2 = -1; bestDist2 = 256;
+            for (int c = qs; c < qe; c++) {
+                const int f2 = idx2[c];
+                if (taken2[f2]) continue;
+                if (variant == 1 && !valid2[f2]) continue;
+                const int d = hamming256_host(d1 + (size_t)f1 * 32, d2 + (size_t)f2 * 32);
+                if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdx2 = f2; }
+                else if (d < bestDist2) bestDist2 = d;
+            }
         }
         const bool low = variant == 0 ? bestDist1 <= TH_LOW : bestDist1 < TH_LOW;      // :228 vs :598
         if (low && (float)bestDist1 < nnratio * (float)bestDist2) {

@@ -239,6 +239,35 @@ def test_cuda_search_by_bow(seed, variant, nnratio, check):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("variant", [0, 1])
+def test_cuda_search_by_bow_when_the_best_candidates_are_taken(variant):
+    """The device returns the four smallest distances of every query; ten queries with one and the same descriptor compete
+    for twelve near-copies of it, so from the fifth on all four are already matched and the bucket is rescanned on the host."""
+    import orbx
+    b = dict(scenes.bow_scene(2002))
+    rng = np.random.default_rng(5)
+    d1, d2 = b["d1"].copy(), b["d2"].copy()
+    v1, v2 = b["valid1"].copy(), b["valid2"].copy()
+    D = d1[17].copy()
+    for i in range(40, 50):
+        d1[i], v1[i] = D, 1
+    for j in range(200, 212):
+        d2[j] = D
+        v2[j] = 1
+        flip = rng.choice(np.arange(8, 256), size=j - 200, replace=False)      # 0..11 flipped bits, first byte (the node) kept
+        for bit in flip:
+            d2[j, bit >> 3] ^= np.uint8(1 << (bit & 7))
+    b.update(d1=d1, d2=d2, valid1=v1, valid2=v2, fv1=scenes.feature_vector(d1), fv2=scenes.feature_vector(d2))
+    for nnratio, check in [(0.99, False), (0.8, True)]:
+        m = orbx.ORBmatcher(nnratio, check)
+        vv = None if variant == 0 else b["valid2"]
+        n, mt = m.SearchByBoW(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], vv)
+        on, omt = O.search_by_bow(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], vv, nnratio, check)
+        assert n == on and np.array_equal(mt, omt)
+    assert n > 50
+
+
+@pytest.mark.gpu
 def test_cuda_searches_empty_inputs():
     import orbx
     s = scenes.projection_scene(1000)

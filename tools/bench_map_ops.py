@@ -32,7 +32,53 @@ def line(name, unit, work, t_gpu, t_cpu, **kw):
     print(json.dumps(dict(op=name, unit=unit, gpu=work / t_gpu, cpu_1_thread=work / t_cpu, gpu_ms=t_gpu * 1e3, cpu_ms=t_cpu * 1e3, **kw)), flush=True)
 
 
+def tracking_searches():
+    """The searches Tracking makes on every frame, named by BASELINE.json's north_star: SearchForInitialization (mono
+    initialisation, 2 * nFeatures extractor, windowSize 100), SearchByProjection(Frame, local MapPoints),
+    SearchByProjection(CurrentFrame, LastFrame), SearchByBoW(KF, Frame) and SearchByBoW(KF, KF)."""
+    from orbx import synth
+    ex = orbx.ORBextractor(2000, 1.2, 8, 20, 7)
+    img1 = synth.rects(640, 480, 1000)
+    rng = np.random.default_rng(1000)
+    img2 = np.clip(np.roll(img1, 3, axis=1).astype(np.int16) + rng.integers(-3, 4, img1.shape), 0, 255).astype(np.uint8)
+    k1, d1 = ex(img1)
+    k2, d2 = ex(img2)
+    bounds = (0.0, 640.0, 0.0, 480.0)
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    mi = orbx.ORBmatcher(0.9, True)
+    tg, (n, m12, _) = timed(lambda: mi.SearchForInitialization(k1, d1, k2, d2, bounds, prev, 100), 30)
+    tc, (on, om12, _) = timed(lambda: O.search_for_initialization(k1, d1, k2, d2, bounds, prev, 100, 0.9, True), 5)
+    assert n == on and np.array_equal(m12, om12)
+    line("SearchForInitialization", "calls/s", 1, tg, tc, features=(len(k1), len(k2)), matches=int(n))
+
+    s = scenes.projection_scene(1000)
+    a = (s["kps"], s["desc"], s["u_right"], s["occupied"], scenes.BOUNDS, scenes.SF, s["proj_xy"], s["proj_xr"], s["level"])
+    mp = orbx.ORBmatcher(0.8, True)
+    tg, (n, fm) = timed(lambda: mp.SearchByProjection(*a, s["view_cos"], s["mp_desc"], s["mp_has_obs"], 3.0), 50)
+    tc, (on, ofm) = timed(lambda: O.search_by_projection(*a, s["view_cos"], s["mp_desc"], s["mp_has_obs"], 3.0, 0.8), 10)
+    assert n == on and np.array_equal(fm, ofm)
+    line("SearchByProjection(Frame, MapPoints)", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n))
+    mf = orbx.ORBmatcher(0.9, True)
+    tg, (n, fm) = timed(lambda: mf.SearchByProjectionFrame(*a, s["angle"], s["mp_desc"], s["mp_has_obs"], 15.0, 0), 50)
+    tc, (on, ofm) = timed(lambda: O.search_by_projection_frame(*a, s["angle"], s["mp_desc"], s["mp_has_obs"], 15.0, 0, True), 10)
+    assert n == on and np.array_equal(fm, ofm)
+    line("SearchByProjection(CurrentFrame, LastFrame)", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n))
+
+    b = scenes.bow_scene(2000)
+    mb = orbx.ORBmatcher(0.7, True)
+    tg, (n, mt) = timed(lambda: mb.SearchByBoW(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], None), 50)
+    tc, (on, omt) = timed(lambda: O.search_by_bow(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], None, 0.7, True), 10)
+    assert n == on and np.array_equal(mt, omt)
+    line("SearchByBoW(KF, Frame)", "calls/s", 1, tg, tc, features=(len(b["k1"]), len(b["k2"])), matches=int(n))
+    mb2 = orbx.ORBmatcher(0.8, True)
+    tg, (n, mt) = timed(lambda: mb2.SearchByBoW(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], b["valid2"]), 50)
+    tc, (on, omt) = timed(lambda: O.search_by_bow(b["k1"], b["d1"], b["valid1"], b["fv1"], b["k2"], b["d2"], b["fv2"], b["valid2"], 0.8, True), 10)
+    assert n == on and np.array_equal(mt, omt)
+    line("SearchByBoW(KF, KF)", "calls/s", 1, tg, tc, features=(len(b["k1"]), len(b["k2"])), matches=int(n))
+
+
 def main():
+    tracking_searches()
     m = orbx.ORBmatcher(0.7, True)
     # ---- Fuse: 8 key frames' worth of points against one key frame (LocalMapping::SearchInNeighbors fuses ~20 x 1000 points)
     s = scenes.fuse_scene(1000)
