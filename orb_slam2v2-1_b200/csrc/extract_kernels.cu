@@ -133,8 +133,9 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 //      0, 4, 8, 12), so a corner needs |p - centre| > t on such a pair; |.| comes from the native VABSDIFF4.U8 and the
 //      threshold test is SWAR on the bytes; survivors are appended in row-major order to the warp's private list
 //      (positions from a shuffle scan of the per-lane counts);
-//   3. exact score of the survivors (packed s16x2 min/max, VIMNMX) into a u8 score map (0 = not a corner);
-//   4. NMS + emission from the list, which is already in cv::FAST's output order.
+//   3. exact score of the survivors (packed s16x2 min/max, VIMNMX) into a u8 score map (0 = not a corner); the survivors
+//      that are corners are compacted in place, in order;
+//   4. NMS + emission from that list, which is already in cv::FAST's output order.
 // The cell is processed at iniThFAST first and, only if that yields no keypoint, again at minThFAST
 // (ORBextractor.cc:809-816): kept(t) = raw > t and raw > every neighbour's raw, so each pass is exact on its own.
 #ifndef FAST_WARPS_N
@@ -338,12 +339,6 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             if (__ballot_sync(FULL, (comb0 | comb1) != 0) == 0) continue;
             // ordered append: cnt = surviving pixels of this lane (0..8), positions from an inclusive shuffle scan
             const int cnt = __popc((comb0 >> 7) | (comb1 >> 6));
-#ifdef FAST_APPEND_BALLOT
-            const unsigned B0 = __ballot_sync(FULL, cnt & 1), B1 = __ballot_sync(FULL, cnt & 2), B2 = __ballot_sync(FULL, cnt & 4),
-                           B3 = __ballot_sync(FULL, cnt & 8);
-            int pos = n + __popc(B0 & ltmask) + 2 * __popc(B1 & ltmask) + 4 * __popc(B2 & ltmask) + 8 * __popc(B3 & ltmask);
-            n += __popc(B0) + 2 * __popc(B1) + 4 * __popc(B2) + 8 * __popc(B3);
-#else
             int inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -352,7 +347,6 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             }
             int pos = n + inc - cnt;
             n += __shfl_sync(FULL, inc, 31);
-#endif
             if (comb0 & 0x80u) list[pos++] = (uint16_t)e;
             if (comb0 & 0x8000u) list[pos++] = (uint16_t)(e + 1);
             if (comb0 & 0x800000u) list[pos++] = (uint16_t)(e + 2);
@@ -364,7 +358,6 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         }
         __syncwarp();
         // ---- exact score of the survivors
-#ifdef FAST_CORNER_LIST
         // survivors that are corners (raw > t) are compacted in place (ballot ranks keep the order): the NMS below then
         // visits corners only, about half of the survivors
         int nc = 0;
@@ -384,14 +377,6 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         }
         n = nc;
         __syncwarp();
-#else
-        for (int k = lane; k < n; k += 32) {
-            const unsigned e = list[k];
-            const int raw = fast_raw_score<TP>(tile + e);
-            if (raw > t) sc[(int)((e / TP) * scp + (e & (TP - 1))) + scBias] = (uint8_t)raw;
-        }
-        __syncwarp();
-#endif
         // ---- NMS (strict >, neighbours outside the zone or not corners count as 0) + emission in list order
         for (int k0 = 0; k0 < n; k0 += 32) {
             const int k = k0 + lane;
