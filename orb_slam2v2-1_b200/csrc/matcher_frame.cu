@@ -772,13 +772,25 @@ __device__ __forceinline__ void stereo_refine(int lane, const orbx_kp& kpL, int 
         const int dy = p / 11 - w, dx = p % 11 - w;
         const int a = (int)IL[(size_t)(cv + dy) * pL + cu + dx] - cL;
         const uint8_t* rrow = IR + (size_t)(cv + dy) * pR + cr + dx - Ls;
+        // |a - (r - cR)| = |(a + cR) - r|: one add and one sum-of-absolute-differences instruction per shift
 #pragma unroll
-        for (int k = 0; k < 11; k++) sad[k] += abs(a - ((int)rrow[k] - cRk[k]));
+        for (int k = 0; k < 11; k++) sad[k] = (int)__sad(a + cRk[k], (int)rrow[k], (unsigned)sad[k]);
     }
+    // a lane's partial sums are below 2^12 and a whole SAD is at most 121 * 510 < 2^16: two shifts share a register in the
+    // butterfly (6 x 5 shuffles instead of 11 x 5)
+    {
+        unsigned pk[6];
 #pragma unroll
-    for (int k = 0; k < 11; k++)
+        for (int k = 0; k < 5; k++) pk[k] = (unsigned)sad[2 * k] | ((unsigned)sad[2 * k + 1] << 16);
+        pk[5] = (unsigned)sad[10];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sad[k] += __shfl_xor_sync(0xFFFFFFFFu, sad[k], o);
+        for (int k = 0; k < 6; k++)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) pk[k] += __shfl_xor_sync(0xFFFFFFFFu, pk[k], o);
+#pragma unroll
+        for (int k = 0; k < 5; k++) { sad[2 * k] = (int)(pk[k] & 0xFFFFu); sad[2 * k + 1] = (int)(pk[k] >> 16); }
+        sad[10] = (int)pk[5];
+    }
     if (lane != 0) return;
     int bestDist = INT_MAX, bestincR = 0;
 #pragma unroll
@@ -975,11 +987,18 @@ constexpr int STEREO_BAND = 8, STEREO_LIST_FACTOR = 4;      // a row range spans
 __global__ void __launch_bounds__(256) k_stereo_bands(const int* __restrict__ cntR, int stride, const int4* __restrict__ tab, int nBands,
                                                       int* __restrict__ bandStart, int* __restrict__ bandList)
 {
-    extern __shared__ int s_cnt[];                               // nBands + 1
+    extern __shared__ int s_cnt[];                               // nBands + 1, then the row ranges of the right keypoints
     const int f = blockIdx.x, w = threadIdx.x >> 5, lane = threadIdx.x & 31, nr = min(cntR[f], stride);
     const int4* tf = tab + (size_t)f * stride;
     int* start = bandStart + (size_t)f * (nBands + 1);
     int* list = bandList + (size_t)f * stride * STEREO_LIST_FACTOR;
+    // every band scans every right keypoint twice: keep (first row | last row << 16) in shared memory
+    unsigned* s_rng = reinterpret_cast<unsigned*>(s_cnt + nBands + 1);
+    for (int c = threadIdx.x; c < nr; c += 256) {
+        const int4 t = __ldg(&tf[c]);
+        s_rng[c] = (unsigned)t.x | ((unsigned)t.y << 16);
+    }
+    __syncthreads();
     for (int pass = 0; pass < 2; pass++) {
         for (int b = w; b < nBands; b += 8) {
             const int r0 = b * STEREO_BAND, r1 = r0 + STEREO_BAND - 1;
@@ -988,8 +1007,8 @@ __global__ void __launch_bounds__(256) k_stereo_bands(const int* __restrict__ cn
                 const int c = c0 + lane;
                 bool hit = false;
                 if (c < nr) {
-                    const int4 t = __ldg(&tf[c]);
-                    hit = t.x <= r1 && t.y >= r0;
+                    const unsigned t = s_rng[c];
+                    hit = (int)(t & 0xFFFFu) <= r1 && (int)(t >> 16) >= r0;
                 }
                 const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
                 if (pass && hit) list[n + __popc(m & ((1u << lane) - 1))] = c;
@@ -1145,25 +1164,32 @@ extern "C" int orbm_stereo_matches_batch(orbx_matcher* m, orbx_extractor* left, 
     ORBX_CUDA(cudaSetDevice(m->device));
     Carver cv(m->arena);
     const int nBands = (V.nRows + STEREO_BAND - 1) / STEREO_BAND;
-    const size_t oT = cv.take(sizeof(int4) * (size_t)B * sr), oU = cv.take(sizeof(float) * (size_t)B * cap), oD = cv.take(sizeof(float) * (size_t)B * cap),
-                 oS = cv.take(sizeof(int) * (size_t)B * cap), oN = cv.take(sizeof(int) * (size_t)B),
+    // results first (uRight | depth | counts are one device-to-host copy into the page-locked mirror), workspace after
+    const size_t oU = cv.take(sizeof(float) * (size_t)B * cap), oD = cv.take(sizeof(float) * (size_t)B * cap), oN = cv.take(sizeof(int) * (size_t)B),
+                 oEnd = cv.take(0), oT = cv.take(sizeof(int4) * (size_t)B * sr), oS = cv.take(sizeof(int) * (size_t)B * cap),
                  oBS = cv.take(sizeof(int) * (size_t)B * (nBands + 1)), oBL = cv.take(sizeof(int) * (size_t)B * sr * STEREO_LIST_FACTOR);
-    if ((rc = m->arena.reserve(cv.total()))) return rc;
+    if ((rc = m->arena.reserve(cv.total())) || (rc = m->arena.mirror())) return rc;
     uint8_t* A = m->arena.base;
     cudaStream_t s = m->stream;
     k_stereo_prep<<<dim3((sr + 255) / 256, B), 256, 0, s>>>(dkr, dcr, sr, V, (int4*)(A + oT));
     // left keypoints beyond cap would be dropped: cap must cover the per-frame keypoint stride of the handle
     const int nlMax = std::min(sl, cap);
-    k_stereo_bands<<<B, 256, sizeof(int) * (size_t)(nBands + 1), s>>>(dcr, sr, (const int4*)(A + oT), nBands, (int*)(A + oBS), (int*)(A + oBL));
+    const size_t bandSmem = sizeof(int) * ((size_t)(nBands + 1) + (size_t)sr);
+    if (bandSmem > 48 * 1024) {
+        if (bandSmem > 227 * 1024) { set_error("orbm_stereo_matches_batch: too many keypoints per frame for the row-band kernel"); return ORBX_ERR_ARG; }
+        ORBX_CUDA(cudaFuncSetAttribute(k_stereo_bands, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bandSmem));
+    }
+    k_stereo_bands<<<B, 256, bandSmem, s>>>(dcr, sr, (const int4*)(A + oT), nBands, (int*)(A + oBS), (int*)(A + oBL));
     k_stereo_batch<<<dim3((nlMax + 7) / 8, B), 256, 0, s>>>(dkl, (const uint4*)ddl, dcl, sl, dkr, (const uint4*)ddr, dcr, sr, (const int4*)(A + oT),
                                                           (const int*)(A + oBS), (const int*)(A + oBL), nBands, V,
                                                           bf, minD, maxD, cap, (float*)(A + oU), (float*)(A + oD), (int*)(A + oS));
     k_stereo_median<<<B, 256, 0, s>>>(dcl, cap, (const int*)(A + oS), (float*)(A + oU), (float*)(A + oD), (int*)(A + oN));
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 4;
-    ORBX_CUDA(cudaMemcpyAsync(uRight, A + oU, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(depth, A + oD, sizeof(float) * (size_t)B * cap, cudaMemcpyDeviceToHost, s));
-    if (nmatched) ORBX_CUDA(cudaMemcpyAsync(nmatched, A + oN, sizeof(int) * (size_t)B, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(m->arena.pin + oU, A + oU, oEnd - oU, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(uRight, m->arena.pin + oU, sizeof(float) * (size_t)B * cap);
+    memcpy(depth, m->arena.pin + oD, sizeof(float) * (size_t)B * cap);
+    if (nmatched) memcpy(nmatched, m->arena.pin + oN, sizeof(int) * (size_t)B);
     return ORBX_OK;
 }
