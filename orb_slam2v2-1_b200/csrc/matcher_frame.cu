@@ -748,20 +748,27 @@ struct StereoView {
 // Sub-pixel refinement of one left keypoint against its best right candidate (Frame.cc:566-637): 11-shift 11x11 SAD on the
 // unblurred level of the left keypoint, parabola fit, disparity test.  Whole warp; lane 0 writes the three outputs
 // (pre-initialised to -1 by the caller).
-__device__ __forceinline__ void stereo_refine(int lane, const orbx_kp& kpL, int levelL, float uL, float uR0, const StereoView& V,
+struct StereoLevel {      // what the refinement reads of the left keypoint's pyramid level
+    const uint8_t* IL;
+    const uint8_t* IR;
+    int pL, pR, colsR;
+    float sf, isf;
+};
+
+__device__ __forceinline__ void stereo_refine(int lane, const orbx_kp& kpL, float uL, float uR0, const StereoLevel& V,
                                               float bf, float minD, float maxD, float* uRightOut, float* depthOut, int* sadOut)
 {
-    const float scaleFactor = V.isf[levelL];
+    const float scaleFactor = V.isf;
     const float scaleduL = roundf(__fmul_rn(kpL.x, scaleFactor));
     const float scaledvL = roundf(__fmul_rn(kpL.y, scaleFactor));
     const float scaleduR0 = roundf(__fmul_rn(uR0, scaleFactor));
     const int w = 5, Ls = 5;
     const float iniu = scaleduR0 + Ls - w, endu = scaleduR0 + Ls + w + 1;        // small integers: exact
-    if (iniu < 0 || endu >= (float)V.colsR[levelL]) return;
+    if (iniu < 0 || endu >= (float)V.colsR) return;
     const int cu = (int)scaleduL, cv = (int)scaledvL, cr = (int)scaleduR0;
-    const uint8_t* IL = V.L[levelL];
-    const uint8_t* IR = V.R[levelL];
-    const int pL = V.pitchL[levelL], pR = V.pitchR[levelL];
+    const uint8_t* IL = V.IL;
+    const uint8_t* IR = V.IR;
+    const int pL = V.pL, pR = V.pR;
     const int cL = IL[(size_t)cv * pL + cu];
     int cR = 0;                                                 // centre of the right window at shift lane - 5
     if (lane < 11) cR = IR[(size_t)cv * pR + cr + lane - Ls];
@@ -803,7 +810,7 @@ __device__ __forceinline__ void stereo_refine(int lane, const orbx_kp& kpL, int 
         if (k == bestincR + Ls) { d1 = (float)sad[k - 1]; d2 = (float)sad[k]; d3 = (float)sad[k + 1]; }
     const float deltaR = __fdiv_rn(__fsub_rn(d1, d3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
     if (deltaR < -1 || deltaR > 1) return;                      // a NaN (flat triple) passes, as in the reference
-    float bestuR = __fmul_rn(V.sf[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestincR), deltaR));
+    float bestuR = __fmul_rn(V.sf, __fadd_rn(__fadd_rn(scaleduR0, (float)bestincR), deltaR));
     float disparity = __fsub_rn(uL, bestuR);
     if (disparity >= minD && disparity < maxD) {
         if (disparity <= 0) {
@@ -853,7 +860,8 @@ __global__ void __launch_bounds__(256) k_stereo(const orbx_kp* __restrict__ kl, 
     if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
     const int bestIdxR = rowEntries[s + (int)(best & KEY_POS_MASK)];
 
-    stereo_refine(lane, kpL, levelL, uL, kr[bestIdxR].x, V, bf, minD, maxD, uRight + iL, depth + iL, bestSad + iL);
+    const StereoLevel SL = {V.L[levelL], V.R[levelL], V.pitchL[levelL], V.pitchR[levelL], V.colsR[levelL], V.sf[levelL], V.isf[levelL]};
+    stereo_refine(lane, kpL, uL, kr[bestIdxR].x, SL, bf, minD, maxD, uRight + iL, depth + iL, bestSad + iL);
 }
 
 }  // namespace orbx
@@ -1073,10 +1081,9 @@ __global__ void __launch_bounds__(256) k_stereo_batch(const orbx_kp* __restrict_
     if (best == KEY_NONE || (int)(best >> KEY_SHIFT) >= (TH_HIGH + TH_LOW) / 2) return;
     const int bestIdxR = (int)(best & KEY_POS_MASK);
     if (levelL < 0 || levelL >= VB.nlev) return;
-    StereoView V;
-#pragma unroll
-    for (int l = 0; l < MAX_LEVELS; l++) { V.sf[l] = VB.sf[l]; V.isf[l] = VB.isf[l]; V.colsR[l] = VB.colsR[l]; V.pitchL[l] = VB.pitchL[l]; V.pitchR[l] = VB.pitchR[l]; V.L[l] = VB.L[l] + (size_t)f * VB.frameL[l]; V.R[l] = VB.R[l] + (size_t)f * VB.frameR[l]; }
-    stereo_refine(lane, kpL, levelL, uL, __int_as_float(__ldg(&tf[bestIdxR]).w), V, bf, minD, maxD, uRight + oo, depth + oo, bestSad + oo);
+    const StereoLevel SL = {VB.L[levelL] + (size_t)f * VB.frameL[levelL], VB.R[levelL] + (size_t)f * VB.frameR[levelL], VB.pitchL[levelL],
+                            VB.pitchR[levelL], VB.colsR[levelL], VB.sf[levelL], VB.isf[levelL]};
+    stereo_refine(lane, kpL, uL, __int_as_float(__ldg(&tf[bestIdxR]).w), SL, bf, minD, maxD, uRight + oo, depth + oo, bestSad + oo);
 }
 
 // Median cut (Frame.cc:641-654) of one pair per CTA: the reference sorts (SAD, index) pairs and takes the SAD at position
