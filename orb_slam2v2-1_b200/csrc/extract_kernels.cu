@@ -529,7 +529,6 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
 
     const int ncell = G.nCols * G.nRows;
     const int* cellCount = F.cellCount + (size_t)f * P.totalCells + G.cellBase;
-    int* cellOff = F.cellOff + (size_t)f * P.totalCells + G.cellBase;
     const uint32_t* slots = F.slots + (size_t)f * P.slotSlab + G.slotOff;
     uint32_t* keys = F.keys + (size_t)f * P.keySlab + G.keyOff;
     uint16_t* knode = F.knode + (size_t)f * P.keySlab + G.keyOff;
@@ -538,31 +537,67 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
     uint32_t* outKeys = F.levelKeys + (size_t)f * P.totalNodes + G.nodeBase;
     int* outCount = F.levelCount + (size_t)f * MAX_LEVELS + l;
 
-    // candidate order of the reference: cell row, cell column, then cv::FAST's row-major order inside the cell
-    for (int i = tid; i < ncell; i += T) cellOff[i] = cellCount[i];
+    // candidate order of the reference: cell row, cell column, then cv::FAST's row-major order inside the cell.  A thread owns
+    // a run of consecutive cells: it sums their counts, a block scan of the sums gives the position of its first candidate,
+    // and it copies its cells' candidates there (cells hold ~5 candidates each: a warp per cell left most lanes idle and the
+    // dependent count -> candidates loads of 273 cells in a row on 4 warps were the longest phase of the kernel).
+    const int nIni = G.nIni;
+    int* rootCnt = cc;          // scratch: nIni <= capS
+    for (int i = tid; i < nIni; i += T) rootCnt[i] = 0;
+    const int per = (ncell + T - 1) / T;
+    const int c0 = min(tid * per, ncell), c1 = min(c0 + per, ncell);
+    int mine = 0;
+    for (int c = c0; c < c1; c++) mine += __ldg(&cellCount[c]);
+    int inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) wsum[wid] = inc;
     __syncthreads();
-    const int n = block_exclusive_scan<T>(cellOff, ncell, wsum);
+    if (wid == 0) {
+        const int v = lane < (T >> 5) ? wsum[lane] : 0;
+        int vi = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
+            if (lane >= o) vi += t;
+        }
+        wsum[lane] = vi - v;
+        if (lane == 31) wsum[32] = vi;
+    }
+    __syncthreads();
+    const int n = wsum[32];
+    int at = wsum[wid] + inc - mine;
+    __syncthreads();            // wsum is reused by the scans below
     if (n == 0) {
         if (tid == 0) *outCount = 0;
         return;
     }
     if (n <= OCT_KEYS_SMEM) { keys = keysS; knode = knodeS; }
-    const int nIni = G.nIni;
-    int* rootCnt = cc;          // scratch: nIni <= capS
-    for (int i = tid; i < nIni; i += T) rootCnt[i] = 0;
-    __syncthreads();
-    for (int c = wid; c < ncell; c += T / 32) {
-        const int cnt = cellCount[c], off = cellOff[c];
+    for (int c = c0; c < c1; c++) {
+        const int cnt = __ldg(&cellCount[c]);
         const uint32_t* src = slots + (size_t)c * G.slotCap;
-        for (int e = lane; e < cnt; e += 32) {
-            const uint32_t key = src[e];
-            int root = 0;                                             // vpIniNodes[kp.pt.x/hX] (:569); one root: no division
-            if (nIni > 1) root = min((int)__fdiv_rn((float)key_x(key), G.hX), nIni - 1);
-            keys[off + e] = key;
-            knode[off + e] = (uint16_t)root;
-            atomicAdd(&rootCnt[root], 1);
+        for (int e0 = 0; e0 < cnt; e0 += 4) {
+            uint32_t kk[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) kk[j] = e0 + j < cnt ? __ldg(&src[e0 + j]) : 0u;       // four loads in flight
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (e0 + j < cnt) {
+                    int root = 0;                                             // vpIniNodes[kp.pt.x/hX] (:569); one root: no division
+                    if (nIni > 1) {
+                        root = min((int)__fdiv_rn((float)key_x(kk[j]), G.hX), nIni - 1);
+                        atomicAdd(&rootCnt[root], 1);
+                    }
+                    keys[at] = kk[j];
+                    knode[at] = (uint16_t)root;
+                    at++;
+                }
         }
     }
+    if (nIni == 1 && tid == 0) rootCnt[0] = n;
     __syncthreads();
     if (tid == 0) {
         int m0 = 0;

@@ -11,7 +11,6 @@ struct FrameBufs {
     uint8_t* pyr;                  // B x Plan::pyrSlab      levels 1..L-1, unblurred (mvImagePyramid interiors)
     uint8_t* blur;                 // B x Plan::blurSlab     7x7 Gaussian of every level
     int* cellCount;                // B x totalCells         FAST candidates kept per cell
-    int* cellOff;                  // B x totalCells         exclusive scan of cellCount inside a level
     uint32_t* slots;               // B x slotSlab           per-cell candidate slots (packed keys, row-major inside a cell)
     uint32_t* keys;                // B x keySlab            per-level compacted candidates in reference order
     uint16_t* knode;               // B x keySlab            node position (12 bits) | quadrant << 12 of every candidate

@@ -269,7 +269,7 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += align_up(bytes, 256); return o; };
     const size_t oPyr = take(P.pyrSlab * cap), oBlur = take(P.blurSlab * cap);
-    const size_t oCnt = take(sizeof(int) * P.totalCells * cap), oOff = take(sizeof(int) * P.totalCells * cap);
+    const size_t oCnt = take(sizeof(int) * P.totalCells * cap);
     const size_t oSlots = take(sizeof(uint32_t) * P.slotSlab * cap), oKeys = take(sizeof(uint32_t) * P.keySlab * cap);
     const size_t oKnode = take(sizeof(uint16_t) * P.keySlab * cap);
     const size_t oLK = take(sizeof(uint32_t) * P.totalNodes * cap), oLC = take(sizeof(int) * MAX_LEVELS * cap);
@@ -286,7 +286,6 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     F.pyr = base + oPyr;
     F.blur = base + oBlur;
     F.cellCount = (int*)(base + oCnt);
-    F.cellOff = (int*)(base + oOff);
     F.slots = (uint32_t*)(base + oSlots);
     F.keys = (uint32_t*)(base + oKeys);
     F.knode = (uint16_t*)(base + oKnode);
