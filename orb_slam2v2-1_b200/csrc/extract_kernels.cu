@@ -479,14 +479,14 @@ __device__ int block_exclusive_scan(int* a, int n, int* wsum)
     return total;
 }
 
-// small form only when the quotas are small (<= ~300 nodes per level) and the launch has at least two waves of small CTAs;
-// otherwise a (level, frame) problem is the critical path and the larger CTA finishes it sooner (measured: 752x480
-// nf=1200 x 192 frames 0.160 vs 0.129 ms, 1241x376 nf=2000 x 512 frames 0.40 vs 0.32 ms, 640x480 nf=1000 x 64 frames
-// 0.087 vs 0.055 ms, in favour of the large form; 640x480 nf=1000 x 512 frames 0.198 vs 0.236 ms in favour of the small one)
+// small form when the quotas are small (nfeatures = 1000: 229 nodes at most per level) and the launch has about a wave of
+// small CTAs; otherwise a (level, frame) problem is the critical path and the larger CTA finishes it sooner.  Measured per
+// launch, small / large form: 640x480 nf=1000 x 512 frames 0.134 / 0.197 ms, x 128 frames 0.054 / 0.062 ms; 752x480 nf=1200
+// x 192 frames 0.111 / 0.101 ms; 1241x376 nf=2000 x 128 frames 0.113 / 0.082 ms, x 512 frames 0.281 / 0.245 ms.
 static bool octree_large(const Plan& P, int B, int capS)
 {
-    static const int thr = getenv("ORBX_OCT_THR") ? atoi(getenv("ORBX_OCT_THR")) : 300;       // tuning override
-    return capS > thr || (long long)B * P.nlevels < 2LL * 148 * OctSmall::MINB;
+    static const int thr = getenv("ORBX_OCT_THR") ? atoi(getenv("ORBX_OCT_THR")) : 250;       // tuning override
+    return capS > thr || (long long)B * P.nlevels < 1000;
 }
 
 // shared memory of the larger form (the limit check at plan time); launch_octree sizes the launch itself

@@ -15,6 +15,8 @@ dev = torch.zeros((B, H, pitch), dtype=torch.uint8, device="cuda")
 for i in range(B):
     dev[i, :, :W] = torch.from_numpy(distinct[i % 4]).cuda()
 ex = orbx.ORBextractor(nf, 1.2, 8, 20, 7, max_batch=B)
+if os.environ.get("ORBX_FORM"):
+    ex.set_octree_form(int(os.environ["ORBX_FORM"]))      # 1 / 2 / 3 = 128 / 256 / 512 threads
 for _ in range(2):
     ex.extract_device(dev.data_ptr(), B, W, H, pitch, pitch * H)
 ex.sync()
