@@ -158,6 +158,9 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+PROFILE_TAG = "r01g"        # the committed ncu capture the traffic / instruction figures come from (profiles/<tag>_*)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -384,18 +387,26 @@ def run_ours(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     alg = stage_alg_bytes(NF)
-    if acc["blur"] < 0.02 * acc["fast_cells"]:       # FAST and blur run as one fused launch (k_fast_blur): one stage, summed bytes
-        acc["fast_cells+blur"] = acc.pop("fast_cells") + acc.pop("blur")
-        alg["fast_cells+blur"] = alg.pop("fast_cells") + alg.pop("blur")
     top = max(acc, key=acc.get)
     top_bytes = alg[top] if alg[top] > 0 else alg["fast_cells"]
     achieved = top_bytes * B / (acc[top] / 1e3) / 1e9
     pipeline_gbs = B_ALG * value / world / 1e9
-    traffic, traffic_src = None, None
+    traffic, traffic_src, issue = None, None, None
     try:      # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (same shape), scaled to B frames
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01f_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", PROFILE_TAG + "_traffic.json")))
         per_frame = sum(tr["dram_bytes_per_frame"][k] for k in top.split("+"))
         traffic, traffic_src = per_frame * B, tr["source"]
+        # the resource that does bind this integer path: warp-instruction issue slots (148 SMs x 4 schedulers x SM clock);
+        # instruction counts per frame from the same capture, rate = this run's frames/s
+        inst = tr.get("warp_instructions_per_frame")
+        if inst:
+            smclk = float(peaks.get("sm_max_mhz", 1965.0)) * 1e6
+            issue_peak = 148 * 4 * smclk
+            issue = {"warp_instructions_per_frame": inst, "total_per_frame": sum(inst.values()),
+                     "achieved_warp_inst_per_s": sum(inst.values()) * value / world, "peak_warp_inst_per_s": issue_peak,
+                     "frac": sum(inst.values()) * value / world / issue_peak,
+                     "note": "issue-slot utilisation of the whole extraction (ncu instruction counts x measured frames/s); "
+                             "north_star names the HBM roofline, ncu shows the integer pipes bind"}
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -403,7 +414,8 @@ def run_ours(args):
                 "algorithmic_bytes_per_launch": top_bytes * B,
                 "stage_ms": acc, "stage_alg_bytes_per_frame": alg,
                 "pipeline": {"alg_bytes_per_frame": B_ALG, "achieved": pipeline_gbs, "frac": pipeline_gbs / peak,
-                             "note": "whole extraction per GPU: B_alg x frames/s / peak"}}
+                             "note": "whole extraction per GPU: B_alg x frames/s / peak"},
+                "issue_slots": issue}
     cpu = None
     if world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
