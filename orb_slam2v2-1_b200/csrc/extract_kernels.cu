@@ -855,7 +855,9 @@ __device__ __forceinline__ BlurEdge blur_edge(int x, int w)
 
 // One strip of rows [y0, y1) of one lane's 4 columns.  INTERIOR: the strip needs no vertical reflection (rows y0-3 ..
 // y1+2 all exist), so the source pointers simply advance by one pitch per row.
-template <bool INTERIOR>
+// PLAIN: no lane of the warp touches the left or right image border (every lane loads L, C, R as they are): the border
+// selectors and their predicated PRMTs drop out.
+template <bool INTERIOR, bool PLAIN>
 __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ img, int pitch, int h, int x, int y0, int y1, const BlurEdge E,
                                            uint8_t* __restrict__ dst, int dpitch)
 {
@@ -864,15 +866,15 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ img, int 
     for (int k = 0; k < 4; k++) Pw[5][k] = 0;
     int rr = INTERIOR ? y0 - 3 : reflect1(y0 - 3, h);
     const uint8_t* pc = img + (size_t)(unsigned)rr * (unsigned)pitch + x;
-    const uint8_t* pr = pc + E.dR;
+    const uint8_t* pr = pc + (PLAIN ? 4 : E.dR);
     // iteration i handles source row r = y0 - 3 + i and, from i = 6 on, emits output row y = r - 3
 #define BLUR_ROW(J, EMIT)                                                                                             \
     {                                                                                                                 \
         unsigned L = 0, C, R = 0;                                                                                     \
-        if (E.loadL) L = __ldg(reinterpret_cast<const unsigned*>(pc - 4));                                            \
+        if (PLAIN || E.loadL) L = __ldg(reinterpret_cast<const unsigned*>(pc - 4));                                   \
         C = __ldg(reinterpret_cast<const unsigned*>(pc));                                                             \
-        if (E.loadR) R = __ldg(reinterpret_cast<const unsigned*>(pr));                                                \
-        if (E.edge) {                                                                                                 \
+        if (PLAIN || E.loadR) R = __ldg(reinterpret_cast<const unsigned*>(pr));                                       \
+        if (!PLAIN && E.edge) {                                                                                       \
             const unsigned X = __byte_perm(L, C, E.s1), FL = __byte_perm(L, C, E.sL), FC = __byte_perm(C, L, E.sC);   \
             R = __byte_perm(X, R, E.s2); L = FL; C = FC;                                                              \
         }                                                                                                             \
@@ -931,8 +933,11 @@ __device__ __forceinline__ void blur_tile_body(const Plan& P, const FrameBufs& F
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     const BlurEdge E = blur_edge(x, w);
     uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)(unsigned)y0 * (unsigned)G.pitch + x;
-    if (y0 >= 3 && y1 + 3 <= h) blur_strip<true>(img, pitch, h, x, y0, y1, E, dst, G.pitch);      // warp-uniform
-    else blur_strip<false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
+    const bool plain = tx > 0 && tx * BLUR_COLS + 31 * 4 + 8 <= w;                                    // warp-uniform, like the next test
+    if (y0 >= 3 && y1 + 3 <= h) {
+        if (plain) blur_strip<true, true>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
+        else blur_strip<true, false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
+    } else blur_strip<false, false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
 }
 
 #undef TAPS4
