@@ -131,8 +131,9 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
 //      origin on a 16-byte boundary of the level row, so that a lane copies 16 bytes per LDGSTS;
 //   2. pre-filter on 8 pixels per lane (two words): a 9-arc always contains two adjacent compass pixels (ring positions
 //      0, 4, 8, 12), so a corner needs |p - centre| > t on such a pair; |.| comes from the native VABSDIFF4.U8 and the
-//      threshold test is SWAR on the bytes; survivors are appended in row-major order to the warp's private list
-//      (positions from a shuffle scan of the per-lane counts);
+//      threshold test is SWAR on the bytes; the 8 result bits of a lane go into a per-row bit mask (one multiply gathers
+//      them), and the survivor list is built in row-major order with one lane per row (shuffle scan of the row counts,
+//      then each lane expands its row's set bits);
 //   3. exact score of the survivors (packed s16x2 min/max, VIMNMX) into a u8 score map (0 = not a corner); the survivors
 //      that are corners are compacted in place, in order;
 //   4. NMS + emission from that list, which is already in cv::FAST's output order.
@@ -314,31 +315,43 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? P.iniTh : P.minTh;
         if (pass == 1 && (total > 0 || P.minTh == P.iniTh)) break;
-        for (int i = lane; i < (scBytes >> 4); i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
+        // ---- pre-filter: every lane leaves the 8 survivor bits of its item in a per-row bit mask (kept in the score-map
+        // region, which is not needed yet); the ordered list is then built with one lane per row
+        constexpr int RMW_MAX = TP / 32;                  // mask words per row: 8 * nd bits, nd <= TP / 8
+        const int rmw = (nd + 3) >> 2, rmb = rmw * 4;
+        for (int i = lane; i < ((ih * rmb + 15) >> 4); i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
         __syncwarp();
-        // ---- pre-filter
         const unsigned K = (unsigned)(127 - min(t, 127)) * 0x01010101u;     // byte > t  <=>  bit 7 of ((byte & 0x7f) + 127 - t) | byte
+        {
+            const uint32_t* w = tileW + (3 + zr0) * TPW + 2 * (dFirst + zc);
+            uint8_t* mk = sc + zr0 * rmb + zc;
+            if (zactive)
+                for (int row0 = zr0; row0 < ih; row0 += rpiZ, w += rpiZ * TPW, mk += rpiZ * rmb) {
+                    const uint2 C = *reinterpret_cast<const uint2*>(w);
+                    const uint2 U = *reinterpret_cast<const uint2*>(w - 3 * TPW), D = *reinterpret_cast<const uint2*>(w + 3 * TPW);
+                    const unsigned Lw = w[-1], Rw = w[2];
+                    const unsigned L0 = __funnelshift_r(Lw, C.x, 8), R0 = __funnelshift_r(C.x, C.y, 24);     // x - 3, x + 3
+                    const unsigned L1 = __funnelshift_r(C.x, C.y, 8), R1 = __funnelshift_r(C.y, Rw, 24);
+                    const unsigned v0 = swar_gt(__vabsdiffu4(D.x, C.x), K) | swar_gt(__vabsdiffu4(U.x, C.x), K);
+                    const unsigned h0 = swar_gt(__vabsdiffu4(L0, C.x), K) | swar_gt(__vabsdiffu4(R0, C.x), K);
+                    const unsigned v1 = swar_gt(__vabsdiffu4(D.y, C.y), K) | swar_gt(__vabsdiffu4(U.y, C.y), K);
+                    const unsigned h1 = swar_gt(__vabsdiffu4(L1, C.y), K) | swar_gt(__vabsdiffu4(R1, C.y), K);
+                    // bit 7 of the 8 bytes -> 8 adjacent bits: bits 8i + 4k of t8 land on bits 24 + 4k + i of the product
+                    const unsigned t8 = ((v0 & h0 & zm0) >> 7) | ((v1 & h1 & zm1) >> 3);
+                    *mk = (uint8_t)((t8 * 0x01020408u) >> 24);
+                }
+        }
+        __syncwarp();
         int n = 0;
-        const uint32_t* w = tileW + (3 + zr0) * TPW + 2 * (dFirst + zc);
-        int e = (3 + zr0) * TP + bc;                      // list entry = byte offset of the pixel in the tile
-        for (int row0 = zr0; row0 - zr0 < ih; row0 += rpiZ, w += rpiZ * TPW, e += rpiZ * TP) {
-            unsigned comb0 = 0, comb1 = 0;
-            if (zactive && row0 < ih) {
-                const uint2 C = *reinterpret_cast<const uint2*>(w);
-                const uint2 U = *reinterpret_cast<const uint2*>(w - 3 * TPW), D = *reinterpret_cast<const uint2*>(w + 3 * TPW);
-                const unsigned Lw = w[-1], Rw = w[2];
-                const unsigned L0 = __funnelshift_r(Lw, C.x, 8), R0 = __funnelshift_r(C.x, C.y, 24);     // x - 3, x + 3
-                const unsigned L1 = __funnelshift_r(C.x, C.y, 8), R1 = __funnelshift_r(C.y, Rw, 24);
-                const unsigned v0 = swar_gt(__vabsdiffu4(D.x, C.x), K) | swar_gt(__vabsdiffu4(U.x, C.x), K);
-                const unsigned h0 = swar_gt(__vabsdiffu4(L0, C.x), K) | swar_gt(__vabsdiffu4(R0, C.x), K);
-                const unsigned v1 = swar_gt(__vabsdiffu4(D.y, C.y), K) | swar_gt(__vabsdiffu4(U.y, C.y), K);
-                const unsigned h1 = swar_gt(__vabsdiffu4(L1, C.y), K) | swar_gt(__vabsdiffu4(R1, C.y), K);
-                comb0 = v0 & h0 & zm0;
-                comb1 = v1 & h1 & zm1;
+        for (int r0 = 0; r0 < ih; r0 += 32) {
+            const int r = r0 + lane;
+            unsigned m[RMW_MAX];
+            int cnt = 0;
+#pragma unroll
+            for (int j = 0; j < RMW_MAX; j++) {
+                m[j] = (r < ih && j < rmw) ? reinterpret_cast<const unsigned*>(sc)[r * rmw + j] : 0u;
+                cnt += __popc(m[j]);
             }
-            if (__ballot_sync(FULL, (comb0 | comb1) != 0) == 0) continue;
-            // ordered append: cnt = surviving pixels of this lane (0..8), positions from an inclusive shuffle scan
-            const int cnt = __popc((comb0 >> 7) | (comb1 >> 6));
             int inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -347,15 +360,13 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             }
             int pos = n + inc - cnt;
             n += __shfl_sync(FULL, inc, 31);
-            if (comb0 & 0x80u) list[pos++] = (uint16_t)e;
-            if (comb0 & 0x8000u) list[pos++] = (uint16_t)(e + 1);
-            if (comb0 & 0x800000u) list[pos++] = (uint16_t)(e + 2);
-            if (comb0 & 0x80000000u) list[pos++] = (uint16_t)(e + 3);
-            if (comb1 & 0x80u) list[pos++] = (uint16_t)(e + 4);
-            if (comb1 & 0x8000u) list[pos++] = (uint16_t)(e + 5);
-            if (comb1 & 0x800000u) list[pos++] = (uint16_t)(e + 6);
-            if (comb1 & 0x80000000u) list[pos++] = (uint16_t)(e + 7);
+            const int e0 = (3 + r) * TP + 8 * dFirst;     // list entry = byte offset of the pixel in the tile
+#pragma unroll
+            for (int j = 0; j < RMW_MAX; j++)
+                for (unsigned mm = m[j]; mm; mm &= mm - 1) list[pos++] = (uint16_t)(e0 + 32 * j + __ffs(mm) - 1);
         }
+        __syncwarp();
+        for (int i = lane; i < (scBytes >> 4); i += 32) reinterpret_cast<uint4*>(sc)[i] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         // ---- exact score of the survivors
         // survivors that are corners (raw > t) are compacted in place (ballot ranks keep the order): the NMS below then
