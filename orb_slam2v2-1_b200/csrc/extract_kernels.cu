@@ -281,8 +281,19 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             // level 0 may be the caller's device image, only 4-byte aligned: same layout from 4-byte copies
             const bool wide = l > 0 || ((((size_t)F.lv0) | F.lv0Pitch | F.lv0Frame) & 15) == 0;
             if (wide) {
-                for (int r = r0; r < th; r += rpiS, p += pstep, sdst += sstep)
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(p));
+                // the usual cell (38 rows, 8 or 10 rows per iteration) needs 4 or 5 copies: straight-line code for those,
+                // a loop for the rows of taller cells
+                constexpr int FLAT = 5;
+#pragma unroll
+                for (int it = 0; it < FLAT; it++)
+                    if (r0 + it * rpiS < th)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst + (unsigned)it * sstep), "l"(p + (size_t)it * pstep));
+                if (r0 + FLAT * rpiS < th) {
+                    p += FLAT * pstep;
+                    sdst += FLAT * sstep;
+                    for (int r = r0 + FLAT * rpiS; r < th; r += rpiS, p += pstep, sdst += sstep)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(p));
+                }
             } else {
                 for (int r = r0; r < th; r += rpiS, p += pstep, sdst += sstep) {
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(p));
