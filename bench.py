@@ -158,7 +158,7 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
-PROFILE_TAG = "r01g"        # the committed ncu capture the traffic / instruction figures come from (profiles/<tag>_*)
+PROFILE_TAG = "r01h"        # the committed ncu capture the traffic / instruction figures come from (profiles/<tag>_*)
 
 
 def run_reference(args):
