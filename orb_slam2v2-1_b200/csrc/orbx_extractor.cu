@@ -78,13 +78,33 @@ struct orbx_extractor {
     int lastB = 0;                     // frames of the last call (0 = none)
     int lastLaunches = 0;
     bool profile = false;              // record an event after every stage of enqueue()
+
+    // Small batches (the reference's one frame per call) are launch-bound: the 11 launches of a call are captured into a CUDA
+    // graph the second time the same (batch, level-0 buffer, knobs) comes by and replayed from then on.
+    struct GraphKey {
+        int B = 0, form = 0, fma = 0;
+        const void* lv0 = nullptr;
+        unsigned long long pitch = 0, frame = 0;
+        bool operator==(const GraphKey& o) const { return B == o.B && form == o.form && fma == o.fma && lv0 == o.lv0 && pitch == o.pitch && frame == o.frame; }
+    };
+    GraphKey graphKey, seenKey;
+    cudaGraphExec_t graphExec = nullptr;
+    bool graphsOff = false;            // capture failed once on this handle, or ORBX_GRAPHS=0
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace orbx {
 
+static void drop_graph(orbx_extractor* ex)
+{
+    if (ex->graphExec) cudaGraphExecDestroy(ex->graphExec);
+    ex->graphExec = nullptr;
+    ex->graphKey = ex->seenKey = orbx_extractor::GraphKey();
+}
+
 static void free_shape(orbx_extractor* ex)
 {
+    drop_graph(ex);
     cudaFree(ex->d_xtab); ex->d_xtab = nullptr;
     cudaFree(ex->d_ytab); ex->d_ytab = nullptr;
     cudaFree(ex->d_lv0); ex->d_lv0 = nullptr;
@@ -313,15 +333,13 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     return ORBX_OK;
 }
 
-// The whole extraction of B frames on the handle's stream: ComputePyramid -> cell FAST -> DistributeOctTree ->
-// GaussianBlur -> orientation + descriptors (operator(), ORBextractor.cc:1043-1105).
-static int enqueue(orbx_extractor* ex, int B)
+// The 11 kernel launches of one call, in stream order.
+static int launch_all(orbx_extractor* ex, int B, bool prof)
 {
     const Plan& P = ex->plan;
     const FrameBufs& F = ex->bufs;
     cudaStream_t s = ex->stream;
     int launches = 0;
-    const bool prof = ex->profile;
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     for (int l = 1; l < ex->nlevels; l++) {
         const uint8_t* src = l == 1 ? F.lv0 : F.pyr + P.lv[l - 1].planeOff;
@@ -341,9 +359,53 @@ static int enqueue(orbx_extractor* ex, int B)
     launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     launches += 4;
-    ORBX_CUDA(cudaGetLastError());
     ex->lastLaunches = launches;
+    return ORBX_OK;
+}
+
+constexpr int GRAPH_MAX_BATCH = 8;
+
+// The whole extraction of B frames on the handle's stream: ComputePyramid -> cell FAST -> DistributeOctTree ->
+// GaussianBlur -> orientation + descriptors (operator(), ORBextractor.cc:1043-1105).
+static int enqueue(orbx_extractor* ex, int B)
+{
+    static const bool graphsEnv = !(getenv("ORBX_GRAPHS") && atoi(getenv("ORBX_GRAPHS")) == 0);
+    cudaStream_t s = ex->stream;
     ex->lastB = B;
+    if (!ex->profile && graphsEnv && !ex->graphsOff && B <= GRAPH_MAX_BATCH) {
+        orbx_extractor::GraphKey key;
+        key.B = B; key.form = ex->octForm; key.fma = ex->plan.fmaMode;
+        key.lv0 = ex->bufs.lv0; key.pitch = ex->bufs.lv0Pitch; key.frame = ex->bufs.lv0Frame;
+        if (ex->graphExec && key == ex->graphKey) {
+            ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
+            return ORBX_OK;                                   // lastLaunches: the kernels inside the graph, as captured
+        }
+        if (key == ex->seenKey) {                             // second call in a row with these arguments: capture it
+            // (the first call ran plainly, so every cudaFuncSetAttribute of the launchers has already happened on this thread)
+            cudaGraph_t g = nullptr;
+            cudaGraphExec_t exec = nullptr;
+            bool ok = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+            if (ok) {
+                const int rc = launch_all(ex, B, false);
+                ok = cudaStreamEndCapture(s, &g) == cudaSuccess && rc == ORBX_OK && g != nullptr;
+            }
+            if (ok) ok = cudaGraphInstantiate(&exec, g, 0) == cudaSuccess;
+            if (g) cudaGraphDestroy(g);
+            if (ok) {
+                if (ex->graphExec) cudaGraphExecDestroy(ex->graphExec);
+                ex->graphExec = exec;
+                ex->graphKey = key;
+                ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
+                return ORBX_OK;
+            }
+            cudaGetLastError();                               // capture is a shortcut, never a requirement
+            ex->graphsOff = true;
+        }
+        ex->seenKey = key;
+    }
+    int rc = launch_all(ex, B, ex->profile);
+    if (rc) return rc;
+    ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
 }
 
