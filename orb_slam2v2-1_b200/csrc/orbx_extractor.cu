@@ -88,6 +88,8 @@ struct orbx_extractor {
         bool operator==(const GraphKey& o) const { return B == o.B && form == o.form && fma == o.fma && lv0 == o.lv0 && pitch == o.pitch && frame == o.frame; }
     };
     GraphKey graphKey, seenKey;
+    cudaStream_t stream2 = nullptr;    // small batches: the blur runs beside FAST + quadtree (it only needs the pyramid)
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
     cudaGraphExec_t graphExec = nullptr;
     bool graphsOff = false;            // capture failed once on this handle, or ORBX_GRAPHS=0
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -333,6 +335,8 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     return ORBX_OK;
 }
 
+constexpr int GRAPH_MAX_BATCH = 8;
+
 // The 11 kernel launches of one call, in stream order.
 static int launch_all(orbx_extractor* ex, int B, bool prof)
 {
@@ -350,11 +354,21 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
         launches++;
     }
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
+    // a few frames leave most of the GPU idle: the blur (which needs the pyramid only) runs on a second stream beside
+    // FAST + quadtree and joins before the descriptors; inside a captured graph this becomes a fork / join of nodes
+    const bool fork = !prof && B <= GRAPH_MAX_BATCH && ex->stream2 != nullptr;
+    if (fork) {
+        ORBX_CUDA(cudaEventRecord(ex->evFork, s));
+        ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->evFork, 0));
+        launch_blur(ex->stream2, P, F, B);
+        ORBX_CUDA(cudaEventRecord(ex->evJoin, ex->stream2));
+    }
     launch_fast_cells(s, P, F, B, ex->fastSmem);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octForm));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
-    launch_blur(s, P, F, B);
+    if (fork) ORBX_CUDA(cudaStreamWaitEvent(s, ex->evJoin, 0));
+    else launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
@@ -362,8 +376,6 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
     ex->lastLaunches = launches;
     return ORBX_OK;
 }
-
-constexpr int GRAPH_MAX_BATCH = 8;
 
 // The whole extraction of B frames on the handle's stream: ComputePyramid -> cell FAST -> DistributeOctTree ->
 // GaussianBlur -> orientation + descriptors (operator(), ORBextractor.cc:1043-1105).
@@ -494,6 +506,13 @@ int orbx_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, in
     for (int i = 0; i < 16; i++) ex->um.v[i] = ex->umax[i];
 
     if (!cuda_ok(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking), "cudaStreamCreate", __FILE__, __LINE__)) { delete ex; return ORBX_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&ex->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ex->evFork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ex->evJoin, cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();              // the second stream is an optimisation: without it everything runs on `stream`
+        if (ex->stream2) cudaStreamDestroy(ex->stream2);
+        ex->stream2 = nullptr;
+    }
     // rBRIEF pattern, transposed so that lane = descriptor byte reads consecutive entries, coordinates already as floats
     float4 patT[256];
     for (int byte = 0; byte < 32; byte++)
@@ -543,6 +562,9 @@ void orbx_destroy(orbx_extractor* ex)
     cudaFree(ex->d_icTab);
     for (int i = 0; i < 6; i++)
         if (ex->ev[i]) cudaEventDestroy(ex->ev[i]);
+    if (ex->stream2) cudaStreamDestroy(ex->stream2);
+    if (ex->evFork) cudaEventDestroy(ex->evFork);
+    if (ex->evJoin) cudaEventDestroy(ex->evJoin);
     if (ex->stream) cudaStreamDestroy(ex->stream);
     delete ex;
 }
