@@ -925,25 +925,28 @@ extern "C" int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_e
                  oDR = cv.take((size_t)nr * 32), oRS = cv.take(sizeof(int) * rowStart.size()), oRE = cv.take(sizeof(int) * rowEntries.size()),
                  oU = cv.take(sizeof(float) * (size_t)nl), oD = cv.take(sizeof(float) * (size_t)nl), oS = cv.take(sizeof(int) * (size_t)nl);
     rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oKL, kl, sizeof(orbx_kp) * (size_t)nl, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oDL, dl, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oKR, kr, sizeof(orbx_kp) * (size_t)nr, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oDR, dr, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oRS, rowStart.data(), sizeof(int) * rowStart.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oRE, rowEntries.data(), sizeof(int) * rowEntries.size(), cudaMemcpyHostToDevice, s));
+    Xfer x(m->arena);                 // one copy per direction through the page-locked mirror
+    x.up(oKL, kl, sizeof(orbx_kp) * (size_t)nl);
+    x.up(oDL, dl, (size_t)nl * 32);
+    x.up(oKR, kr, sizeof(orbx_kp) * (size_t)nr);
+    x.up(oDR, dr, (size_t)nr * 32);
+    x.up(oRS, rowStart.data(), sizeof(int) * rowStart.size());
+    x.up(oRE, rowEntries.data(), sizeof(int) * rowEntries.size());
+    ORBX_CUDA(x.send());
     k_stereo<<<(nl + 7) / 8, 256, 0, s>>>((const orbx_kp*)(B + oKL), (const uint4*)(B + oDL), nl, (const orbx_kp*)(B + oKR),
                                           (const uint4*)(B + oDR), (const int*)(B + oRS), (const int*)(B + oRE), nRows, V, bf, minD, maxD,
                                           (float*)(B + oU), (float*)(B + oD), (int*)(B + oS));
     ORBX_CUDA(cudaGetLastError());
     m->lastLaunches = 1;
     std::vector<int> sad(nl);
-    ORBX_CUDA(cudaMemcpyAsync(uRight, B + oU, sizeof(float) * (size_t)nl, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(depth, B + oD, sizeof(float) * (size_t)nl, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(sad.data(), B + oS, sizeof(int) * (size_t)nl, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    x.down(uRight, oU, sizeof(float) * (size_t)nl);
+    x.down(depth, oD, sizeof(float) * (size_t)nl);
+    x.down(sad.data(), oS, sizeof(int) * (size_t)nl);
+    ORBX_CUDA(x.fetch());
     // median cut (:641-654): sort (SAD, iL) pairs, drop everything at or above 1.5 * 1.4 * median
     std::vector<std::pair<int, int>> distIdx;
     for (int i = 0; i < nl; i++)
