@@ -259,16 +259,21 @@ extern "C" int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1
                  oQ = cv.take(sizeof(float) * 2 * (size_t)nq), oR = cv.take(sizeof(float) * (size_t)nq), oO = cv.take(sizeof(int) * ((size_t)nq + 1)),
                  oQD = cv.take((size_t)nq * 32), oTD = cv.take((size_t)n2 * 32);
     int rc = m->arena.reserve(cv.total());
+    if (!rc) rc = m->arena.mirror();
     if (rc) return rc;
     uint8_t* B = m->arena.base;
     cudaStream_t s = m->stream;
-    ORBX_CUDA(cudaMemcpyAsync(B + oK, k2, sizeof(orbx_kp) * (size_t)n2, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oS, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oE, entries.data(), sizeof(int) * entries.size(), cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQ, qxy.data(), sizeof(float) * 2 * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oR, qr.data(), sizeof(float) * (size_t)nq, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oQD, qdesc.data(), (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    ORBX_CUDA(cudaMemcpyAsync(B + oTD, d2, (size_t)n2 * 32, cudaMemcpyHostToDevice, s));
+    {
+        Xfer x(m->arena);             // the seven input arrays travel as one copy through the page-locked mirror
+        x.up(oK, k2, sizeof(orbx_kp) * (size_t)n2);
+        x.up(oS, start.data(), sizeof(int) * start.size());
+        x.up(oE, entries.data(), sizeof(int) * entries.size());
+        x.up(oQ, qxy.data(), sizeof(float) * 2 * (size_t)nq);
+        x.up(oR, qr.data(), sizeof(float) * (size_t)nq);
+        x.up(oQD, qdesc.data(), (size_t)nq * 32);
+        x.up(oTD, d2, (size_t)n2 * 32);
+        ORBX_CUDA(x.send());
+    }
     int* d_idx = nullptr;
     int total = 0;
     // GetFeaturesInArea(x, y, windowSize, level1, level1) with level1 == 0
