@@ -94,6 +94,7 @@ def main():
         # stereo association per pair on the device pyramids of the two handles (host keypoints in, uRight/depth out)
         m = orbx.ORBmatcher(0.6, True)
         nP = 32
+        m.ComputeStereoMatches(exL, exR, resL[0][0], resL[0][1], resR[0][0], resR[0][1], bf, fx, frame=0)      # warm-up: allocates the arena and its page-locked mirror
         t0 = time.perf_counter()
         nm = 0
         for b in range(nP):
