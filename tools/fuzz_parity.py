@@ -14,6 +14,28 @@ import oracle_py as O          # checker
 
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+
+# ---- brute-force matcher (a fifth of the budget): random set sizes (0, 1, ragged, several segments), clustered descriptors so
+# that equal distances and equal best / second occur; the same matcher handle throughout (its ticket counters must return to 0)
+t_end = time.time() + budget / 5
+m = orbx.ORBmatcher(0.9, True)
+nmatch = 0
+while time.time() < t_end:
+    nq, nt = int(rng.choice([0, 1, 31, 129, 777, 2000, 4100])), int(rng.choice([0, 1, 2, 33, 64, 65, 500, 3000, 9000]))
+    base = rng.integers(0, 256, (8, 32)).astype(np.uint8)
+    def cluster(n):
+        d = base[rng.integers(0, 8, n)].copy()
+        flips = rng.integers(0, 256, (n, 6))
+        on = rng.random((n, 6)) < 0.5
+        for j in range(6):
+            d[np.arange(n), flips[:, j] >> 3] ^= (on[:, j] * (1 << (flips[:, j] & 7))).astype(np.uint8)
+        return d
+    q, t = cluster(nq), cluster(nt)
+    bi, bd, sd = m.match_bruteforce(q, t)
+    obi, obd, osd = O.match_bruteforce(q, t)
+    assert np.array_equal(bi, obi) and np.array_equal(bd, obd) and np.array_equal(sd, osd), ("bruteforce", nq, nt)
+    nmatch += 1
+print("fuzz ok (matcher): %d brute-force problems index- and distance-equal to the oracle" % nmatch)
 t_end = time.time() + budget
 ncases = nframes = 0
 while time.time() < t_end:
