@@ -189,3 +189,30 @@ def test_every_quadtree_kernel_form(form):
         oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
         _compare_frame(ex, oe, synth.rects(w, h, seed))
         _compare_frame(ex, oe, synth.texture(w, h, seed + 10), stages=False)
+
+
+def test_batch_call_on_page_locked_arrays_from_the_library():
+    """orbx_alloc_pinned / orbx_free_pinned (include/orbx.h): frames back to back in write-combined page-locked memory travel as
+    one copy, results land directly in page-locked result arrays laid out with the handle's per-frame capacity."""
+    import ctypes as C
+    B, W, H = 5, 640, 480
+    imgs = np.stack([synth.rects(W, H, 1600 + i) for i in range(B)])
+    ex = orbx.ORBextractor(1000, 1.2, 8, 20, 7, max_batch=B)
+    oe = O.OracleExtractor(1000, 1.2, 8, 20, 7)
+    ex(imgs[0])                                            # plans the shape: max_keypoints is exact afterwards
+    cap = ex.max_keypoints()
+    fin = orbx.PinnedArray(imgs.shape, np.uint8, write_combined=True)
+    fin.array[...] = imgs
+    kp = orbx.PinnedArray((B, cap, 28), np.uint8)
+    de = orbx.PinnedArray((B, cap, 32), np.uint8)
+    n = np.zeros(B, np.int32)
+    L = orbx.lib()
+    ptrs = (C.c_void_p * B)(*[fin.ptr + i * W * H for i in range(B)])
+    rc = L.orbx_extract_batch(ex._h, ptrs, B, W, H, W, C.c_void_p(kp.ptr), C.c_void_p(de.ptr), cap, n.ctypes.data_as(C.c_void_p))
+    assert rc == 0, L.orbx_last_error().decode()
+    kps = kp.array.view(orbx.KP_DTYPE).reshape(B, cap)
+    for b in range(B):
+        ok, od = oe(imgs[b])
+        assert n[b] == len(ok) and kps[b, :n[b]].tobytes() == ok.tobytes() and np.array_equal(de.array[b, :n[b]], od)
+    for a in (fin, kp, de):
+        a.free()
