@@ -8,6 +8,7 @@
 #ifndef ORBEXTRACTOR_H
 #define ORBEXTRACTOR_H
 
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -27,6 +28,7 @@ public:
         : mvImagePyramid(nlevels), h_(nullptr), nlevels_(nlevels), scaleFactor_(scaleFactor)
     {
         if (orbx_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device, 1, &h_) != ORBX_OK) fail("orbx_create");
+        if (orbx_set_pyramid_mirror(h_, 1) != ORBX_OK) fail("orbx_set_pyramid_mirror");
         mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
         mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
         orbx_scale_tables(h_, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data());
@@ -71,7 +73,7 @@ private:
         keypoints.clear();
         keypoints.reserve(n);
         if (n == 0) descriptors.release();                             // :1064-1065
-        else descriptors.create(n, 32, cv::CV_8U);                     // :1068
+        else descriptors.create(n, 32, CV_8U);                        // :1068
         for (int i = 0; i < n; i++) {
             cv::KeyPoint kp;
             kp.pt.x = kbuf_[i].x; kp.pt.y = kbuf_[i].y; kp.size = kbuf_[i].size; kp.angle = kbuf_[i].angle;
@@ -82,14 +84,16 @@ private:
             cv::Mat d = descriptors.getMat();
             for (int i = 0; i < n; i++) memcpy(d.ptr<uint8_t>(i), &dbuf_[(size_t)i * 32], 32);
         }
-        // mvImagePyramid (read by Frame::ComputeStereoMatches, Frame.cc:488,578,590,595): host copies of the interiors.
-        // Callers that only match on the device (orbm_stereo_matches) can skip this with setPyramidDownload(false).
+        // mvImagePyramid (include/ORBextractor.h:85 of the reference; read by Frame::ComputeStereoMatches, Frame.cc:488,578,590,595):
+        // views of the handle's page-locked mirror, which the call above filled beside its kernels -- no copy, no launch and no
+        // synchronisation here.  Like the reference's buffers (re-allocated per call, :1114-1115) they hold the LAST frame only.
         if (downloadPyramid_)
             for (int l = 0; l < nlevels_; l++) {
                 int w, hh;
-                orbx_level_size(h_, l, &w, &hh);
-                mvImagePyramid[l].create(hh, w, cv::CV_8U);
-                if (orbx_pyramid_level(h_, 0, l, 0, mvImagePyramid[l].ptr<uint8_t>(0), mvImagePyramid[l].step) != ORBX_OK) fail("orbx_pyramid_level");
+                const uint8_t* p = nullptr;
+                size_t pitch = 0;
+                if (orbx_level_size(h_, l, &w, &hh) != ORBX_OK || orbx_pyramid_mirror(h_, l, &p, &pitch) != ORBX_OK) fail("orbx_pyramid_mirror");
+                mvImagePyramid[l] = cv::Mat(hh, w, CV_8U, const_cast<uint8_t*>(p), pitch);
             }
     }
 
@@ -105,7 +109,14 @@ public:
     std::vector<cv::Mat> mvImagePyramid;
 
     // extras of the replacement
-    void setPyramidDownload(bool on) { downloadPyramid_ = on; }
+    // off: mvImagePyramid stays empty and the call skips the 1 MB device-to-host copy (callers that associate stereo on the
+    // device with ORBmatcher::ComputeStereoMatches do not read it)
+    void setPyramidDownload(bool on)
+    {
+        downloadPyramid_ = on;
+        if (orbx_set_pyramid_mirror(h_, on ? 1 : 0) != ORBX_OK) fail("orbx_set_pyramid_mirror");
+        if (!on) for (size_t l = 0; l < mvImagePyramid.size(); l++) mvImagePyramid[l] = cv::Mat();
+    }
     orbx_extractor* handle() { return h_; }
 
 protected:

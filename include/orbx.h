@@ -125,6 +125,13 @@ int orbx_level_size(const orbx_extractor* ex, int level, int* w, int* h);
  * (w+38)x(h+38) buffer (BORDER_REFLECT_101 of the level itself, src/ORBextractor.cc:1113-1128); border = 0 gives the
  * w x h interior that mvImagePyramid[level] views.  dst_stride in bytes. */
 int orbx_pyramid_level(orbx_extractor* ex, int frame, int level, int border, uint8_t* dst, size_t dst_stride);
+/* Host mirror of frame 0's pyramid, for callers that read mvImagePyramid after every call (Frame::ComputeStereoMatches): with
+ * the mirror on, each extract call also copies the 8 interiors into ONE page-locked buffer of the handle (two copies on the copy
+ * engine, beside the FAST and quadtree kernels; no extra synchronisation), and orbx_pyramid_mirror returns the host address and
+ * row pitch of a level inside it.  The pointers stay valid until the next extract call or shape change on the handle; read them
+ * after a synchronous extract call or orbx_fetch / orbx_sync. */
+int orbx_set_pyramid_mirror(orbx_extractor* ex, int on);
+int orbx_pyramid_mirror(orbx_extractor* ex, int level, const uint8_t** ptr, size_t* pitch);
 /* Zero-copy device view of the same interior (for the device stereo matcher). */
 int orbx_pyramid_device(orbx_extractor* ex, int frame, int level, const uint8_t** d_ptr, size_t* pitch);
 
@@ -148,8 +155,14 @@ int orbx_debug_level_count(orbx_extractor* ex, int frame, int level, int* n);
 typedef struct orbx_matcher orbx_matcher;
 /* A matcher context = one CUDA stream + growable device scratch.  ORBmatcher itself is stateless apart from
  * (nnratio, checkOri) (src/ORBmatcher.cc:41-43); those stay arguments. */
+/* device = CUDA ordinal, or -1 for the calling thread's current device.  Contexts are recycled: orbm_destroy parks the
+ * context (stream and arenas alive) in a per-thread free list and the next orbm_create for that device takes it back, so the
+ * reference's habit of building an ORBmatcher on the stack per call (src/Tracking.cc:742,907,1012,1329,1502,1541) costs
+ * nothing.  orbm_trim really frees the calling thread's parked contexts; they are also freed when the thread exits. */
 int orbm_create(int device, orbx_matcher** out);
 void orbm_destroy(orbx_matcher* m);
+void orbm_trim(void);
+int orbm_device(const orbx_matcher* m);
 void* orbm_stream(orbx_matcher* m);
 /* Number of kernels the last matcher call launched. */
 int orbm_last_launches(const orbx_matcher* m);

@@ -13,9 +13,17 @@
 #include <memory>
 #include <vector>
 
-namespace cv {
+// macros, as in OpenCV's cvdef.h (user code writes CV_8U, never cv::CV_8U)
+#ifndef CV_8U
+#define CV_8U 0
+#define CV_32S 4
+#define CV_32F 5
+#define CV_64F 6
+#define CV_8UC1 CV_8U
+#define CV_32FC1 CV_32F
+#endif
 
-enum { CV_8U = 0, CV_8UC1 = 0 };
+namespace cv {
 
 template <typename T> struct Point_ {
     T x, y;
@@ -33,32 +41,45 @@ struct KeyPoint {
     KeyPoint() : size(0), angle(-1), response(0), octave(0), class_id(-1) {}
 };
 
-// 8-bit single-channel matrix: shared, reference-counted storage or a non-owning view with a row step
+// single-channel matrix (CV_8U descriptors and images, CV_32F poses): shared, reference-counted storage or a non-owning
+// view with a row step in bytes
 class Mat {
 public:
     int rows, cols;
     size_t step;
     uint8_t* data;
-    Mat() : rows(0), cols(0), step(0), data(nullptr) {}
-    Mat(int r, int c, int /*type*/) : rows(0), cols(0), step(0), data(nullptr) { create(r, c, CV_8U); }
-    Mat(int r, int c, int /*type*/, void* ext, size_t st = 0) : rows(r), cols(c), step(st ? st : (size_t)c), data((uint8_t*)ext) {}
-    void create(int r, int c, int /*type*/)
+    Mat() : rows(0), cols(0), step(0), data(nullptr), type_(CV_8U) {}
+    Mat(int r, int c, int type) : rows(0), cols(0), step(0), data(nullptr), type_(CV_8U) { create(r, c, type); }
+    Mat(int r, int c, int type, void* ext, size_t st = 0)
+        : rows(r), cols(c), step(st ? st : (size_t)c * esz(type)), data((uint8_t*)ext), type_(type) {}
+    void create(int r, int c, int type)
     {
-        if (r == rows && c == cols && own_ && step == (size_t)c) return;
-        own_.reset(new std::vector<uint8_t>((size_t)r * c));
-        rows = r; cols = c; step = (size_t)c;
+        if (r == rows && c == cols && own_ && type == type_ && step == (size_t)c * esz(type)) return;
+        own_.reset(new std::vector<uint8_t>((size_t)r * c * esz(type)));
+        rows = r; cols = c; type_ = type; step = (size_t)c * esz(type);
         data = own_->empty() ? nullptr : own_->data();
     }
     void release() { own_.reset(); rows = cols = 0; step = 0; data = nullptr; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-    int type() const { return CV_8UC1; }
-    bool isContinuous() const { return step == (size_t)cols; }
+    int type() const { return type_; }
+    size_t elemSize() const { return esz(type_); }
+    bool isContinuous() const { return step == (size_t)cols * esz(type_); }
     template <typename T> T* ptr(int r = 0) { return reinterpret_cast<T*>(data + (size_t)r * step); }
     template <typename T> const T* ptr(int r = 0) const { return reinterpret_cast<const T*>(data + (size_t)r * step); }
-    Mat row(int r) const { Mat m(1, cols, CV_8U, data + (size_t)r * step, step); m.own_ = own_; return m; }
+    template <typename T> T& at(int r, int c) { return ptr<T>(r)[c]; }
+    template <typename T> const T& at(int r, int c) const { return ptr<T>(r)[c]; }
+    Mat row(int r) const { Mat m(1, cols, type_, data + (size_t)r * step, step); m.own_ = own_; return m; }
+    Mat clone() const
+    {
+        Mat m(rows, cols, type_);
+        for (int r = 0; r < rows; r++) memcpy(m.data + (size_t)r * m.step, data + (size_t)r * step, (size_t)cols * esz(type_));
+        return m;
+    }
     Mat getMat() const { return *this; }
 private:
+    static size_t esz(int type) { return (type & 7) == CV_64F ? 8 : ((type & 7) >= CV_32S ? 4 : 1); }
     std::shared_ptr<std::vector<uint8_t>> own_;
+    int type_;
 };
 
 typedef const Mat& InputArray;

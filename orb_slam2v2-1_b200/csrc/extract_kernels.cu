@@ -10,8 +10,28 @@
 #include "sincosf_glibc.h"
 #include <float.h>
 #include <stdlib.h>
+#include <atomic>
+#include <mutex>
 
 namespace orbx {
+
+// Opt-in to more than 48 KB of dynamic shared memory.  The attribute belongs to the (kernel, device) pair, not to the host
+// thread: one table entry per device and kernel, raised under a lock so that a smaller request can never overwrite a larger one.
+struct SmemOptIn {
+    std::atomic<size_t> granted[64];
+    std::mutex lock;
+    template <class K> void ensure(K kernel, size_t bytes, size_t floor = 48 * 1024)
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        std::atomic<size_t>& g = granted[dev & 63];
+        if (bytes <= std::max(g.load(std::memory_order_acquire), floor)) return;
+        std::lock_guard<std::mutex> hold(lock);
+        if (bytes <= std::max(g.load(std::memory_order_acquire), floor)) return;
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        g.store(bytes, std::memory_order_release);
+    }
+};
 
 __device__ __forceinline__ const uint8_t* level_plane(const Plan& P, const FrameBufs& F, int f, int l, int& pitch)
 {
@@ -105,11 +125,8 @@ static void launch_resize_gx(cudaStream_t s, const uint8_t* src, int spitch, siz
                              size_t dframe, const void* xtab, const int4* ytab, int B, int sh)
 {
     const size_t smem = resize_smem_bytes(sh, dh, GX);
-    static thread_local size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaFuncSetAttribute(k_resize<GX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static SmemOptIn optin;
+    optin.ensure(k_resize<GX>, smem);
     const int tileH = RS_TILE_H * (32 / GX);
     dim3 grd(((dw + 3) / 4 + GX - 1) / GX, (dh + tileH - 1) / tileH, B);
     k_resize<GX><<<grd, 256, smem, s>>>(src, spitch, sframe, dst, dw, dh, dpitch, dframe, (const ResizeCols*)xtab, ytab);
@@ -441,11 +458,8 @@ __global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB) k_fast_cells(const
 template <int TP>
 static void launch_fast_cells_tp(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
 {
-    static thread_local size_t configured = 48 * 1024;
-    if (smemBytes > configured) {      // small levels can have cells of up to 61 x 61 pixels
-        cudaFuncSetAttribute(k_fast_cells<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        configured = smemBytes;
-    }
+    static SmemOptIn optin;            // small levels can have cells of up to 61 x 61 pixels
+    optin.ensure(k_fast_cells<TP>, smemBytes);
     dim3 grd((P.totalCells + FAST_WARPS - 1) / FAST_WARPS, B);
     k_fast_cells<TP><<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS));
 }
@@ -776,12 +790,9 @@ template <class CFG>
 static cudaError_t launch_octree_cfg(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap)
 {
     const size_t smemBytes = octree_smem_bytes(capS, sortCap, CFG::KEYS);
-    static thread_local size_t configured = 0;
-    if (smemBytes > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_octree<CFG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        if (e != cudaSuccess) return e;
-        configured = smemBytes;
-    }
+    static SmemOptIn optin;
+    optin.ensure(k_octree<CFG>, smemBytes);
+    if (cudaError_t e = cudaGetLastError()) return e;
     dim3 grd(P.nlevels, B);
     k_octree<CFG><<<grd, CFG::THREADS, smemBytes, s>>>(P, F, capS, sortCap);
     return cudaSuccess;

@@ -891,6 +891,7 @@ extern "C" int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_e
     StereoView V;
     memset(&V, 0, sizeof V);
     int nRows = 0;
+    int lvW[MAX_LEVELS] = {0}, lvH[MAX_LEVELS] = {0};
     rc = orbx_scale_tables(left, V.sf, V.isf, nullptr, nullptr);
     if (rc) return rc;
     for (int l = 0; l < nlev; l++) {
@@ -903,10 +904,31 @@ extern "C" int orbm_stereo_matches(orbx_matcher* m, orbx_extractor* left, orbx_e
         V.pitchL[l] = (int)pl;
         V.pitchR[l] = (int)pr;
         V.colsR[l] = wr;
+        lvW[l] = wl; lvH[l] = hl;
         if (l == 0) nRows = hl;        // mpORBextractorLeft->mvImagePyramid[0].rows (:488)
     }
-    for (int i = 0; i < nl; i++)
+    // The reference reads an 11 x 11 window around the left keypoint and 11 x 21 around the right one in mvImagePyramid[octave]
+    // (:578-595), which is always inside its 19-px padded buffers.  The device planes carry no border: keypoints of the paired
+    // extractors stay 19 px (16 for the +-1 level of the right image) inside a level, anything else is refused here.
+    for (int i = 0; i < nl; i++) {
         if (kl[i].octave < 0 || kl[i].octave >= nlev) { set_error("orbm_stereo_matches: left octave out of range"); return ORBX_ERR_ARG; }
+        const int l = kl[i].octave;
+        const float cu = roundf(kl[i].x * V.isf[l]), cv = roundf(kl[i].y * V.isf[l]);
+        if (!(cu >= 5 && cu < lvW[l] - 5 && cv >= 5 && cv < lvH[l] - 5)) {
+            set_error("orbm_stereo_matches: left keypoint %d lies within 5 px of the border of its level (not from this extractor?)", i);
+            return ORBX_ERR_ARG;
+        }
+    }
+    for (int i = 0; i < nr; i++) {
+        if (kr[i].octave < 0 || kr[i].octave >= nlev) { set_error("orbm_stereo_matches: right octave out of range"); return ORBX_ERR_ARG; }
+        for (int l = std::max(kr[i].octave - 1, 0); l <= std::min(kr[i].octave + 1, nlev - 1); l++) {
+            const float cr = roundf(kr[i].x * V.isf[l]);
+            if (!(cr >= 10 && cr < lvW[l] - 10)) {
+                set_error("orbm_stereo_matches: right keypoint %d lies within 10 px of the border of level %d (not from this extractor?)", i, l);
+                return ORBX_ERR_ARG;
+            }
+        }
+    }
     // row table (:490-508): right keypoint iR is registered in rows floor(y - r) .. ceil(y + r), r = 2 * scale[octave]
     std::vector<int> rowStart(nRows + 1, 0), rowEntries;
     std::vector<std::pair<int, int>> span(nr);

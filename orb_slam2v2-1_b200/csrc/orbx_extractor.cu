@@ -74,6 +74,10 @@ struct orbx_extractor {
     size_t colorBytes = 0;
     uint8_t* d_scratch = nullptr;      // copy-out scratch (padded level)
     size_t scratchBytes = 0;
+    // host mirror of frame 0's pyramid (orbx_set_pyramid_mirror): level 0 at offset 0 with pitch lv0Pitch, level l > 0 at
+    // lv0Frame + planeOff[l] with the device pitch; page-locked, filled by two copies that run beside FAST + quadtree
+    bool mirror = false;
+    uint8_t* h_pyr = nullptr;
 
     int lastB = 0;                     // frames of the last call (0 = none)
     int lastLaunches = 0;
@@ -82,10 +86,13 @@ struct orbx_extractor {
     // Small batches (the reference's one frame per call) are launch-bound: the 11 launches of a call are captured into a CUDA
     // graph the second time the same (batch, level-0 buffer, knobs) comes by and replayed from then on.
     struct GraphKey {
-        int B = 0, form = 0, fma = 0;
+        int B = 0, form = 0, fma = 0, mirror = 0;
         const void* lv0 = nullptr;
         unsigned long long pitch = 0, frame = 0;
-        bool operator==(const GraphKey& o) const { return B == o.B && form == o.form && fma == o.fma && lv0 == o.lv0 && pitch == o.pitch && frame == o.frame; }
+        bool operator==(const GraphKey& o) const
+        {
+            return B == o.B && form == o.form && fma == o.fma && mirror == o.mirror && lv0 == o.lv0 && pitch == o.pitch && frame == o.frame;
+        }
     };
     GraphKey graphKey, seenKey;
     cudaStream_t stream2 = nullptr;    // small batches: the blur runs beside FAST + quadtree (it only needs the pyramid)
@@ -115,7 +122,8 @@ static void free_shape(orbx_extractor* ex)
     cudaFree(ex->d_scratch); ex->d_scratch = nullptr; ex->scratchBytes = 0;
     if (ex->h_in) cudaFreeHost(ex->h_in);
     if (ex->h_out) cudaFreeHost(ex->h_out);
-    ex->h_in = ex->h_out = nullptr;
+    if (ex->h_pyr) cudaFreeHost(ex->h_pyr);
+    ex->h_in = ex->h_out = ex->h_pyr = nullptr;
     ex->W = ex->H = ex->capB = 0;
     ex->lastB = 0;
 }
@@ -331,11 +339,22 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     ex->h_in_bytes = ex->lv0Frame * cap;
     ORBX_CUDA(cudaMallocHost(&ex->h_in, ex->h_in_bytes));
     ORBX_CUDA(cudaMallocHost(&ex->h_out, ex->h_out_bytes));
+    if (ex->mirror) ORBX_CUDA(cudaMallocHost(&ex->h_pyr, ex->lv0Frame + P.pyrSlab));
     ex->W = w; ex->H = h; ex->capB = cap;
     return ORBX_OK;
 }
 
 constexpr int GRAPH_MAX_BATCH = 8;
+
+// frame 0's pyramid -> the page-locked host mirror (what the C++ class shows as mvImagePyramid)
+static cudaError_t mirror_pyramid(orbx_extractor* ex, cudaStream_t s)
+{
+    const Plan& P = ex->plan;
+    cudaError_t e = cudaMemcpy2DAsync(ex->h_pyr, ex->lv0Pitch, ex->bufs.lv0, ex->bufs.lv0Pitch, (size_t)ex->W, (size_t)ex->H, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess && ex->nlevels > 1)
+        e = cudaMemcpyAsync(ex->h_pyr + ex->lv0Frame, ex->bufs.pyr, P.pyrSlab, cudaMemcpyDeviceToHost, s);
+    return e;
+}
 
 // The 11 kernel launches of one call, in stream order.
 static int launch_all(orbx_extractor* ex, int B, bool prof)
@@ -361,6 +380,7 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
         ORBX_CUDA(cudaEventRecord(ex->evFork, s));
         ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->evFork, 0));
         launch_blur(ex->stream2, P, F, B);
+        if (ex->mirror) ORBX_CUDA(mirror_pyramid(ex, ex->stream2));      // the copy engine works while FAST + quadtree run
         ORBX_CUDA(cudaEventRecord(ex->evJoin, ex->stream2));
     }
     launch_fast_cells(s, P, F, B, ex->fastSmem);
@@ -372,6 +392,7 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
+    if (ex->mirror && !fork) ORBX_CUDA(mirror_pyramid(ex, s));
     launches += 4;
     ex->lastLaunches = launches;
     return ORBX_OK;
@@ -386,7 +407,7 @@ static int enqueue(orbx_extractor* ex, int B)
     ex->lastB = B;
     if (!ex->profile && graphsEnv && !ex->graphsOff && B <= GRAPH_MAX_BATCH) {
         orbx_extractor::GraphKey key;
-        key.B = B; key.form = ex->octForm; key.fma = ex->plan.fmaMode;
+        key.B = B; key.form = ex->octForm; key.fma = ex->plan.fmaMode; key.mirror = ex->mirror;
         key.lv0 = ex->bufs.lv0; key.pitch = ex->bufs.lv0Pitch; key.frame = ex->bufs.lv0Frame;
         if (ex->graphExec && key == ex->graphKey) {
             ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
@@ -574,6 +595,27 @@ int orbx_set_fma_mode(orbx_extractor* ex, int fma_mode)
     if (!ex) { set_error("null handle"); return ORBX_ERR_ARG; }
     ex->fmaMode = fma_mode ? 1 : 0;
     ex->plan.fmaMode = ex->fmaMode;
+    return ORBX_OK;
+}
+
+int orbx_set_pyramid_mirror(orbx_extractor* ex, int on)
+{
+    if (!ex) { set_error("null handle"); return ORBX_ERR_ARG; }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    if (on && !ex->h_pyr && ex->W) {
+        ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+        ORBX_CUDA(cudaMallocHost(&ex->h_pyr, ex->lv0Frame + ex->plan.pyrSlab));
+    }
+    ex->mirror = on != 0;
+    return ORBX_OK;
+}
+
+int orbx_pyramid_mirror(orbx_extractor* ex, int level, const uint8_t** ptr, size_t* pitch)
+{
+    if (!ex || !ptr || !pitch || level < 0 || level >= ex->nlevels) { set_error("orbx_pyramid_mirror: bad argument"); return ORBX_ERR_ARG; }
+    if (!ex->mirror || !ex->h_pyr || ex->lastB == 0) { set_error("orbx_pyramid_mirror: the mirror is off or no extraction has run"); return ORBX_ERR_STATE; }
+    if (level == 0) { *ptr = ex->h_pyr; *pitch = ex->lv0Pitch; }
+    else { *ptr = ex->h_pyr + ex->lv0Frame + ex->plan.lv[level].planeOff; *pitch = (size_t)ex->plan.lv[level].pitch; }
     return ORBX_OK;
 }
 

@@ -250,23 +250,59 @@ using namespace orbx;
 
 extern "C" {
 
+// The reference builds an ORBmatcher on the stack at every call site (Tracking.cc:742,907,1012,1329,1502,1541,
+// LocalMapping.cc:223,491, LoopClosing.cc:249,598): creating a stream and growing the device / page-locked arenas, then
+// cudaFree-ing them (which synchronises the device), would cost milliseconds per Tracking step.  Contexts are therefore
+// recycled: orbm_destroy parks a context (stream + arenas alive) in a per-thread free list and orbm_create hands a parked
+// context of the same device back out, so a stack-constructed matcher costs two vector operations.  Parked contexts are
+// really destroyed when their thread exits or when the list is full.
+namespace {
+constexpr int PARK_MAX = 16;
+
+void destroy_now(orbx_matcher* m)
+{
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    m->arena.release();
+    m->arena2.release();
+    cudaFree(m->d_partial);
+    cudaFree(m->d_tickets);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    cudaGetLastError();
+    delete m;
+}
+
+struct Parked {
+    std::vector<orbx_matcher*> free;
+    ~Parked() { for (orbx_matcher* m : free) destroy_now(m); }
+};
+thread_local Parked t_parked;
+}  // namespace
+
 int orbm_create(int device, orbx_matcher** out)
 {
     if (!out) { set_error("orbm_create: out is null"); return ORBX_ERR_ARG; }
     *out = nullptr;
+    if (device < 0) ORBX_CUDA(cudaGetDevice(&device));          // -1: the calling thread's current device
+    for (size_t i = 0; i < t_parked.free.size(); i++)
+        if (t_parked.free[i]->device == device) {
+            *out = t_parked.free[i];
+            t_parked.free.erase(t_parked.free.begin() + (long)i);
+            return ORBX_OK;
+        }
     int ndev = 0;
     ORBX_CUDA(cudaGetDeviceCount(&ndev));
-    if (device < 0 || device >= ndev) { set_error("orbm_create: device %d not present (%d CUDA devices)", device, ndev); return ORBX_ERR_CUDA; }
+    if (device >= ndev) { set_error("orbm_create: device %d not present (%d CUDA devices)", device, ndev); return ORBX_ERR_CUDA; }
     ORBX_CUDA(cudaSetDevice(device));
     orbx_matcher* m = new orbx_matcher;
     m->device = device;
-    cudaDeviceProp prop;
-    if (!cuda_ok(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties", __FILE__, __LINE__) ||
+    int sms = 0;
+    if (!cuda_ok(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "cudaDeviceGetAttribute", __FILE__, __LINE__) ||
         !cuda_ok(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking), "cudaStreamCreate", __FILE__, __LINE__)) {
         delete m;
         return ORBX_ERR_CUDA;
     }
-    m->smCount = prop.multiProcessorCount;
+    m->smCount = sms;
     m->arena.stream = m->stream;
     m->arena2.stream = m->stream;
     *out = m;
@@ -276,15 +312,18 @@ int orbm_create(int device, orbx_matcher** out)
 void orbm_destroy(orbx_matcher* m)
 {
     if (!m) return;
-    cudaSetDevice(m->device);
-    if (m->stream) cudaStreamSynchronize(m->stream);
-    m->arena.release();
-    m->arena2.release();
-    cudaFree(m->d_partial);
-    cudaFree(m->d_tickets);
-    if (m->stream) cudaStreamDestroy(m->stream);
-    delete m;
+    if ((int)t_parked.free.size() < PARK_MAX) { t_parked.free.push_back(m); return; }    // every entry point leaves the stream idle
+    destroy_now(m);
 }
+
+// really frees the calling thread's parked contexts (tests, and hosts that want the memory back)
+void orbm_trim(void)
+{
+    for (orbx_matcher* m : t_parked.free) destroy_now(m);
+    t_parked.free.clear();
+}
+
+int orbm_device(const orbx_matcher* m) { return m ? m->device : -1; }
 
 void* orbm_stream(orbx_matcher* m) { return m ? (void*)m->stream : nullptr; }
 int orbm_last_launches(const orbx_matcher* m) { return m ? m->lastLaunches : 0; }

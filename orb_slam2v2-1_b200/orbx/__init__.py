@@ -64,11 +64,15 @@ def lib():
         "orbx_level_size": (i, [vp, i, vp, vp]),
         "orbx_pyramid_level": (i, [vp, i, i, i, vp, sz]),
         "orbx_pyramid_device": (i, [vp, i, i, vp, vp]),
+        "orbx_set_pyramid_mirror": (i, [vp, i]),
+        "orbx_pyramid_mirror": (i, [vp, i, vp, vp]),
         "orbx_debug_blurred_level": (i, [vp, i, i, vp, sz]),
         "orbx_debug_candidates": (i, [vp, i, i, vp, i, vp]),
         "orbx_debug_level_count": (i, [vp, i, i, vp]),
         "orbm_create": (i, [i, vp]),
         "orbm_destroy": (None, [vp]),
+        "orbm_trim": (None, []),
+        "orbm_device": (i, [vp]),
         "orbm_stream": (vp, [vp]),
         "orbm_last_launches": (i, [vp]),
         "orbm_descriptor_distance": (i, [vp, vp, vp, i, vp]),
@@ -343,7 +347,8 @@ class ORBmatcher:
 
     TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30        # src/ORBmatcher.cc:37-39
 
-    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+    def __init__(self, nnratio=0.6, checkOri=True, device=-1):
+        """device: CUDA ordinal, -1 = the calling thread's current device (contexts are recycled by the library)."""
         self._L = lib()
         h = C.c_void_p()
         _check(self._L.orbm_create(device, C.byref(h)))
@@ -359,6 +364,9 @@ class ORBmatcher:
 
     def stream(self):
         return self._L.orbm_stream(self._h)
+
+    def device(self):
+        return self._L.orbm_device(self._h)
 
     def DescriptorDistance(self, a, b):
         """ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1649-1665); a, b: 32-byte rows or [n, 32] arrays."""

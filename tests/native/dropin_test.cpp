@@ -20,7 +20,7 @@ int main(int argc, char** argv)
     fclose(f);
     try {
         ORB_SLAM2::ORBextractor* ex = new ORB_SLAM2::ORBextractor(nf, 1.2f, 8, 20, 7);     // Tracking.cc:113-119
-        cv::Mat im(h, w, cv::CV_8UC1, img.data());
+        cv::Mat im(h, w, CV_8UC1, img.data());
         std::vector<cv::KeyPoint> keys;
         cv::Mat desc;
         (*ex)(im, cv::Mat(), keys, desc);                                                    // Frame.cc:247-253
