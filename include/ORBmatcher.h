@@ -1,15 +1,22 @@
 // ORBmatcher.h -- drop-in for the descriptor-level part of the reference's include/ORBmatcher.h
 // (kimwin2/ORB_SLAM2v2-1 include/ORBmatcher.h:37-102, src/ORBmatcher.cc) and of Frame::ComputeStereoMatches
 // (src/Frame.cc:481-655) over the C ABI of liborbx.so (include/orbx.h).  Same class name, constructor, constants and
-// return conventions.  The searches take a FrameView (the members of Frame/KeyFrame that the routines read) instead
-// of Frame&, because Frame drags the whole SLAM object graph (Map, MapPoint, ROS messages) into the translation
-// unit; INTEGRATION.md shows the three-line adapter from the reference's Frame.  Predicates that read map state
-// (isBad, Observations, epipolar checks) stay on the host side of the caller, as in SURVEY.md section 8(a) a15.
+// return conventions.  Two layers:
+//   * the tracking searches under the reference's own signatures -- SearchByProjection(Frame&, vpMapPoints, th),
+//     SearchByProjection(CurrentFrame, LastFrame, th, bMono), SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches),
+//     SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12), SearchForInitialization(Frame&, Frame&, ...) -- as member templates
+//     over the user's Frame / KeyFrame / MapPoint types (ORBmatcher_reference_api.inl), so the call sites in Tracking.cc and
+//     LoopClosing.cc compile unchanged while this repository stays free of the SLAM object graph (Map, ROS messages);
+//   * the same searches, and the LocalMapping / LoopClosing ones, over a FrameView + plain arrays (the members the routines
+//     read), which is what the templates call.  Predicates that read map state (isBad, Observations, epipolar checks) stay on
+//     the host side, as in SURVEY.md section 8(a) a15.
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
+#include <cstring>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <utility>
 #include <vector>
 #include "orbx.h"
@@ -30,7 +37,10 @@ struct FrameView {
 class ORBmatcher
 {
 public:
-    ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = 0) : mfNNratio(nnratio), mbCheckOrientation(checkOri), m_(nullptr)
+    // device: CUDA ordinal, -1 = the calling thread's current device.  Construction is cheap enough for the reference's habit
+    // of building a matcher on the stack per call (Tracking.cc:742,907,1012,...): the library recycles the context (stream,
+    // device and page-locked arenas) of the last matcher this thread destroyed.
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = -1) : mfNNratio(nnratio), mbCheckOrientation(checkOri), m_(nullptr)
     {
         if (orbm_create(device, &m_) != ORBX_OK) fail("orbm_create");
     }
@@ -38,14 +48,18 @@ public:
     ORBmatcher(const ORBmatcher&) = delete;
     ORBmatcher& operator=(const ORBmatcher&) = delete;
 
-    // Computes the Hamming distance between two ORB descriptors (ORBmatcher.cc:1649-1665).  One pair per call costs a
-    // kernel launch; DescriptorDistances() is the batched form for callers such as MapPoint::ComputeDistinctiveDescriptors.
+    // Computes the Hamming distance between two ORB descriptors (ORBmatcher.cc:1649-1665).  A single pair is 8 XOR + popcount
+    // on the host -- the reference calls this inline N^2 times (MapPoint.cc:286-296), where a kernel launch per pair would be
+    // ~10^3 x slower; the device forms are DescriptorDistances() (many pairs), SearchBruteForce() and
+    // ComputeDistinctiveDescriptors() (the whole MapPoint.cc:252-312 loop for a batch of points).
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b)
     {
-        int d = 0;
-        if (orbm_descriptor_distance(shared(), a.ptr<uint8_t>(0), b.ptr<uint8_t>(0), 1, &d) != ORBX_OK)
-            throw std::runtime_error(std::string("orbm_descriptor_distance: ") + orbx_last_error());
-        return d;
+        uint32_t pa[8], pb[8];
+        memcpy(pa, a.ptr<uint8_t>(0), 32);
+        memcpy(pb, b.ptr<uint8_t>(0), 32);
+        int dist = 0;
+        for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
+        return dist;
     }
     std::vector<int> DescriptorDistances(const cv::Mat& a, const cv::Mat& b)      // row i of a against row i of b
     {
@@ -70,6 +84,14 @@ public:
         for (size_t i = 0; i < k1.size(); i++) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }
         return n;
     }
+
+    // ---- the reference's own signatures (include/ORBmatcher.h:47-82 of the reference); definitions in ORBmatcher_reference_api.inl
+    template <class FrameT, class MapPointT> int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3);
+    template <class FrameT> int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono);
+    template <class KeyFrameT, class FrameT, class MapPointT> int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches);
+    template <class KeyFrameT, class MapPointT> int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12);
+    template <class FrameT, class = typename std::enable_if<!std::is_same<typename std::remove_cv<FrameT>::type, FrameView>::value>::type>
+    int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
 
     // Best / second-best scan of SearchByBoW's inner loop (ORBmatcher.cc:205-230) over whole descriptor sets, with the
     // acceptance test bestDist1 <= TH_LOW && bestDist1 < mfNNratio * bestDist2.  Returns the number accepted;
@@ -382,15 +404,6 @@ protected:
         }
         return o;
     }
-    static orbx_matcher* shared()
-    {
-        static thread_local struct Holder {
-            orbx_matcher* m = nullptr;
-            ~Holder() { orbm_destroy(m); }
-        } h;
-        if (!h.m && orbm_create(0, &h.m) != ORBX_OK) throw std::runtime_error(std::string("orbm_create: ") + orbx_last_error());
-        return h.m;
-    }
     void fail(const char* what) { throw std::runtime_error(std::string(what) + ": " + orbx_last_error()); }
 
     float mfNNratio;
@@ -399,5 +412,7 @@ protected:
 };
 
 }  // namespace ORB_SLAM2
+
+#include "ORBmatcher_reference_api.inl"
 
 #endif  // ORBMATCHER_H

@@ -27,6 +27,31 @@ def _build(tmp_path):
     return exe
 
 
+def _build_native(tmp_path, source, name, opencv_shaped=False):
+    """g++ one of tests/native/*.cpp against include/.  opencv_shaped: compile the ORBX_USE_OPENCV branch of the headers (what a
+    user of the reference builds) against an OpenCV-shaped core.hpp -- CV_8U as a macro, cv::_InputArray / _OutputArray classes,
+    MatStep -- for which oracle/ref_shim serves (this image has no OpenCV C++ headers)."""
+    if not os.path.exists(orbx.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    exe = str(tmp_path / name)
+    libdir = os.path.dirname(orbx.LIB_PATH)
+    cmd = ["g++", "-std=c++11", "-O1", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "tests", "native")]
+    if opencv_shaped:
+        cmd += ["-DORBX_USE_OPENCV", "-I", os.path.join(ROOT, "oracle", "ref_shim")]
+    subprocess.check_call(cmd + ["-o", exe, os.path.join(ROOT, "tests", "native", source), "-L", libdir, "-lorbx", "-Wl,-rpath," + libdir])
+    return exe
+
+
+@pytest.mark.parametrize("opencv_shaped", [False, True], ids=["bundled_shim", "opencv_shaped_headers"])
+@pytest.mark.parametrize("source", ["dropin_test.cpp", "reference_api_test.cpp"])
+def test_headers_compile_in_both_modes(tmp_path, source, opencv_shaped):
+    """include/ORBextractor.h and include/ORBmatcher.h -- with the reference's call lines of Tracking.cc:742-743, :907, :1112,
+    :598 and LoopClosing.cc:249 written verbatim in reference_api_test.cpp -- compile and link with the bundled cv shim and in
+    the ORBX_USE_OPENCV branch."""
+    _build_native(tmp_path, source, "t_" + source[:-4], opencv_shaped)
+
+
 def _has_gpu():
     import torch
     return torch.cuda.is_available()
@@ -108,3 +133,30 @@ def test_dropin_matches_oracle(tmp_path, w, h, nf, seed):
         idx = np.frombuffer(b, dtype=np.uint32, count=cnt, offset=p); p += 4 * cnt
         assert node == ofn[a] and np.array_equal(idx, ofi[ofo[a]:ofo[a + 1]])
     assert p == len(b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("opencv_shaped", [False, True], ids=["bundled_shim", "opencv_shaped_headers"])
+def test_reference_signatures_equal_frameview_path(tmp_path, opencv_shaped):
+    """SearchByProjection(Frame&, vpMapPoints, th), SearchByProjection(Current, Last, th, bMono), SearchByBoW x2 and
+    SearchForInitialization(Frame&, Frame&, ...) on stand-in SLAM types give what the FrameView overloads (checked against
+    the oracle in test_searches.py) give on the same inputs; the program exits non-zero on any difference."""
+    exe = _build_native(tmp_path, "reference_api_test.cpp", "refapi", opencv_shaped)
+    L, R = synth.stereo_rects(640, 480, 2100)[:2]
+    (tmp_path / "a.raw").write_bytes(L.tobytes())
+    (tmp_path / "b.raw").write_bytes(R.tobytes())
+    r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), "640", "480", "1000"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("ok"), (r.returncode, r.stdout, r.stderr[-2000:])
+
+
+@pytest.mark.gpu
+def test_dropin_opencv_shaped_build_matches_oracle(tmp_path):
+    """The ORBX_USE_OPENCV branch of the headers, run: same outputs as the bundled-shim build."""
+    exe = _build_native(tmp_path, "dropin_test.cpp", "dropin_cv", True)
+    img = synth.rects(640, 480, 1000)
+    (tmp_path / "in.raw").write_bytes(img.tobytes())
+    subprocess.check_call([exe, str(tmp_path / "in.raw"), "640", "480", "1000", str(tmp_path / "out.bin")])
+    b = (tmp_path / "out.bin").read_bytes()
+    n, = struct.unpack_from("<i", b, 0)
+    okps, odesc = O.OracleExtractor(1000, 1.2, 8, 20, 7)(img)
+    assert n == len(okps) and b[4:4 + 28 * n] == okps.tobytes() and b[4 + 28 * n:4 + 60 * n] == odesc.tobytes()
