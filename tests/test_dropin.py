@@ -142,7 +142,10 @@ def test_reference_signatures_equal_frameview_path(tmp_path, opencv_shaped):
     SearchForInitialization(Frame&, Frame&, ...) on stand-in SLAM types give what the FrameView overloads (checked against
     the oracle in test_searches.py) give on the same inputs; the program exits non-zero on any difference."""
     exe = _build_native(tmp_path, "reference_api_test.cpp", "refapi", opencv_shaped)
-    L, R = synth.stereo_rects(640, 480, 2100)[:2]
+    # two views of one scene: the second is the first moved by (3, 1) pixels with fresh noise, so every windowed search has work
+    L = synth.rects(640, 480, 2100)
+    rng = np.random.default_rng(2100)
+    R = np.clip(np.roll(L, (1, 3), axis=(0, 1)).astype(np.int16) + rng.integers(-3, 4, L.shape), 0, 255).astype(np.uint8)
     (tmp_path / "a.raw").write_bytes(L.tobytes())
     (tmp_path / "b.raw").write_bytes(R.tobytes())
     r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), "640", "480", "1000"], capture_output=True, text=True)
