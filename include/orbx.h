@@ -183,6 +183,20 @@ int orbm_match_ratio(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t
 int orbm_match_bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
                                  int* d_best_idx, int* d_best_dist, int* d_second_dist);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scan of orbm_match_bruteforce_device -- same
+ * kernel, same results -- with the kernel's scratch in a fixed file-scope device array instead of a context's grown buffers:
+ * no handle, and no cudaMalloc / cudaFree / allocating library call on any path.  Works on the calling thread's CURRENT device
+ * and enqueues on `stream` (a cudaStream_t, NULL = the default stream) without synchronising; inputs and outputs are device
+ * pointers as in orbm_match_bruteforce_device.
+ * Limits: nq <= 16384 queries and nt < 2^22 train rows; anything larger returns ORBX_ERR_ARG (use the handle-based entry).
+ * The array is 1 MiB + 4 KiB per GPU, held by every GPU that loads the library until the process exits.  All calls on a device
+ * SHARE it and it keeps the last call's contents (what must start at zero is cleared on `stream` by each call): two calls that
+ * overlap on the GPU -- different streams, or different threads without ordering -- race; order them on one stream or with
+ * events.  The first call on each device takes the array's address (cudaGetSymbolAddress): make it outside stream capture. */
+int orbm_match_bruteforce_device_noalloc(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
+                                         int* d_best_idx, int* d_best_dist, int* d_second_dist, void* stream);
+
 /* Candidate-list scan (the windowed / BoW-bucketed searches): query i scans train rows
  * cand_idx[cand_off[i] .. cand_off[i+1]) in that order.  second_idx = -1 when there is none.  HOST buffers. */
 int orbm_match_candidates(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt,

@@ -10,6 +10,7 @@
 #include "matcher_internal.cuh"
 #include <string.h>
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 namespace orbx {
@@ -358,6 +359,76 @@ int orbm_match_bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, co
     }
     ORBX_CUDA(cudaSetDevice(m->device));
     return bruteforce_device(m, d_q, nq, d_t, nt, 0, 0.f, d_best_idx, d_best_dist, d_second_dist, nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// orbm_match_bruteforce_device_noalloc: the same scan (k_bf_scan) for callers that may not call cudaMalloc (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid it).  The kernel's scratch -- per-segment (min1, min2) partials
+// and one ticket counter per query block -- lives in a file-scope device array of fixed size instead of the context's grown
+// buffers.  Every GPU that loads the library holds the array (1 MiB + 4 KiB) until exit.  In host code `g_noalloc_scratch`
+// is only a stand-in for the symbol: its device address is taken once per device with cudaGetSymbolAddress, with that
+// device current, and that pointer is what the kernel receives.
+constexpr int NOALLOC_MAX_QUERIES = 16384;                        // 128 query blocks
+constexpr int NOALLOC_PARTIALS = 131072;                          // uint2 entries: segments x queries of one call
+constexpr int NOALLOC_TICKETS = 1024;                             // >= NOALLOC_MAX_QUERIES / BF_THREADS
+constexpr size_t NOALLOC_BYTES = sizeof(uint2) * (size_t)NOALLOC_PARTIALS + sizeof(int) * (size_t)NOALLOC_TICKETS;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+namespace {
+struct NoAllocDevice { unsigned char* scratch = nullptr; int smCount = 0; };
+NoAllocDevice g_noalloc_dev[64];
+std::mutex g_noalloc_lock;
+}  // namespace
+
+int orbm_match_bruteforce_device_noalloc(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int* d_best_idx, int* d_best_dist,
+                                         int* d_second_dist, void* stream)
+{
+    if (nq < 0 || nt < 0 || (nq > 0 && (!d_q || !d_best_idx || !d_best_dist || !d_second_dist)) || (nt > 0 && !d_t) ||
+        ((uintptr_t)d_q & 15) || ((uintptr_t)d_t & 15)) {
+        set_error("orbm_match_bruteforce_device_noalloc: bad argument (descriptor pointers must be 16-byte aligned)");
+        return ORBX_ERR_ARG;
+    }
+    if (nq > NOALLOC_MAX_QUERIES || nt >= (int)KEY_POS_MASK) {
+        set_error("orbm_match_bruteforce_device_noalloc: %d queries x %d train rows is beyond the fixed scratch of this entry point "
+                  "(at most %d queries and %d train rows); use orbm_match_bruteforce_device", nq, nt, NOALLOC_MAX_QUERIES, (int)KEY_POS_MASK - 1);
+        return ORBX_ERR_ARG;
+    }
+    if (nq == 0) return ORBX_OK;
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("orbm_match_bruteforce_device_noalloc: device ordinal %d out of range", dev); return ORBX_ERR_ARG; }
+    NoAllocDevice nd;
+    {   // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> hold(g_noalloc_lock);
+        if (!g_noalloc_dev[dev].scratch) {
+            void* p = nullptr;
+            int sms = 0;
+            ORBX_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            ORBX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            if (!p || sms <= 0) { set_error("orbm_match_bruteforce_device_noalloc: no device address for the scratch array"); return ORBX_ERR_CUDA; }
+            g_noalloc_dev[dev].smCount = sms;
+            g_noalloc_dev[dev].scratch = (unsigned char*)p;
+        }
+        nd = g_noalloc_dev[dev];
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    uint2* partial = reinterpret_cast<uint2*>(nd.scratch);
+    int* tickets = reinterpret_cast<int*>(nd.scratch + sizeof(uint2) * (size_t)NOALLOC_PARTIALS);
+    // the same segmentation as bruteforce_device, with the segment count also bounded by the fixed partial array
+    const int qblocks = (nq + BF_THREADS - 1) / BF_THREADS;
+    int nseg = std::max(1, (4 * nd.smCount + qblocks - 1) / qblocks);
+    nseg = std::min(nseg, std::max(1, nt / 32));
+    nseg = std::min(nseg, std::max(1, NOALLOC_PARTIALS / nq));
+    const int segLen = nt > 0 ? (nt + nseg - 1) / nseg : 1;
+    nseg = nt > 0 ? (nt + segLen - 1) / segLen : 1;
+    // the array keeps the last call's contents: partials are written before they are read, the ticket counters must start at
+    // zero (an aborted call may have left them otherwise), so they are cleared on the caller's stream ahead of the kernel
+    ORBX_CUDA(cudaMemsetAsync(tickets, 0, sizeof(int) * (size_t)qblocks, s));
+    dim3 grd(qblocks, nseg);
+    k_bf_scan<<<grd, BF_THREADS, 0, s>>>((const uint4*)d_q, nq, (const uint4*)d_t, nt, segLen, partial, tickets, 0, 0.f, d_best_idx,
+                                         d_best_dist, d_second_dist, nullptr);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
 }
 
 static int bruteforce_host(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int th_low, float nnratio,

@@ -79,6 +79,7 @@ def lib():
         "orbm_match_bruteforce": (i, [vp, vp, i, vp, i, vp, vp, vp]),
         "orbm_match_ratio": (i, [vp, vp, i, vp, i, i, f, vp, vp, vp, vp]),
         "orbm_match_bruteforce_device": (i, [vp, vp, i, vp, i, vp, vp, vp]),
+        "orbm_match_bruteforce_device_noalloc": (i, [vp, i, vp, i, vp, vp, vp, vp]),
         "orbm_match_candidates": (i, [vp, vp, i, vp, i, vp, vp, vp, vp, vp, vp]),
         "orbm_candidate_distances": (i, [vp, vp, i, vp, i, vp, vp, vp]),
         "orbm_grid_candidates": (i, [vp, vp, i, f, f, f, f, vp, i, vp, i, i, vp, vp, vp, i]),
