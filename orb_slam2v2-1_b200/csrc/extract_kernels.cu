@@ -6,6 +6,7 @@
 // All arithmetic that decides a keypoint or a descriptor bit is integer or individually-rounded float
 // (__fmul_rn/__fadd_rn/__fdiv_rn): nvcc must not contract anything here.
 #include "extract_kernels.cuh"
+#include "tma.cuh"
 #include <algorithm>
 #include "sincosf_glibc.h"
 #include <float.h>
@@ -1021,8 +1022,21 @@ constexpr int DESC_PATCH_ROWS = 37, DESC_PATCH_WPITCH = 12;      // blurred foot
 __device__ __forceinline__ int round_magic_bits(float v) { return __float_as_int(__fadd_rn(v, 12582912.f)); }
 constexpr int MAGIC_BITS = 0x4B400000;
 
+// Shared memory of one warp in the TMA form.  A tiled TMA box must START on a 16-byte boundary of the row (an unaligned inner
+// coordinate raises "illegal instruction"; measured with tools/tma_probe.cu), so each box begins at x rounded down to 16 and is wide
+// enough for the slack: the 37-column descriptor footprint travels as 64 x 37, the 31-column orientation patch as 48 x 31.
+constexpr int DESC_BOX_BLUR_W = 64, DESC_BOX_IMG_W = 48;
+constexpr int DESC_BOX_BLUR_BYTES = DESC_BOX_BLUR_W * DESC_PATCH_ROWS, DESC_BOX_IMG_BYTES = DESC_BOX_IMG_W * 31;      // 2368, 1488
+constexpr int DESC_BOX_IMG_OFF = 2432, DESC_BOX_STRIDE = 2432 + 1536;                                                  // 128-byte multiples
+
+struct OrientMaps { LevelMaps img, blur; };
+
+// TMA = true: both patches of a keypoint arrive by one cp.async.bulk.tensor each (one lane issues them, completion on two
+// mbarriers), whatever their alignment; TMA = false: per-lane LDGSTS / LDG of aligned words, for a caller-owned level 0 whose base
+// or pitch is not a multiple of 16 bytes.
+template <bool TMA>
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const uint2* __restrict__ icTab,
-                                                                    const float4* __restrict__ patT)
+                                                                    const float4* __restrict__ patT, const __grid_constant__ OrientMaps M)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int g = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);      // keypoint index inside the frame
@@ -1047,10 +1061,25 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     // The 37 x 37 footprint of the descriptor (rotated pattern reach <= 18) on the BLURRED level goes to shared memory as
     // 11 aligned words per row, copied by LDGSTS while the orientation is computed: the 512 test bytes are then shared-memory
     // reads instead of scattered global byte loads (which had the kernel bound by L1 wavefronts).
-    __shared__ uint32_t s_patch[DESC_WARPS][DESC_PATCH_ROWS * DESC_PATCH_WPITCH];
+    __shared__ __align__(128) uint8_t s_box[TMA ? DESC_WARPS * DESC_BOX_STRIDE : 16];
+    __shared__ uint64_t s_bar[DESC_WARPS][2];
+    __shared__ uint32_t s_patch[TMA ? 1 : DESC_WARPS][TMA ? 1 : DESC_PATCH_ROWS * DESC_PATCH_WPITCH];
     const int bp = G.pitch;
-    const int px0 = cx - 18, pal = px0 & 3;
-    {
+    const int px0 = cx - 18, pal = px0 & (TMA ? 15 : 3);
+    const unsigned boxBase = (unsigned)__cvta_generic_to_shared(s_box) + (unsigned)((threadIdx.x >> 5) * DESC_BOX_STRIDE);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&s_bar[threadIdx.x >> 5][0]);
+    if constexpr (TMA) {
+        if (lane == 0) {
+            mbar_init(bar0, 1);
+            mbar_init(bar0 + 8, 1);
+            mbar_fence_init();
+            mbar_expect_tx(bar0, DESC_BOX_IMG_BYTES);
+            tma_load_box(boxBase + DESC_BOX_IMG_OFF, &M.img.m[l], (cx - HALF_PATCH) & ~15, cy - HALF_PATCH, f, bar0);
+            mbar_expect_tx(bar0 + 8, DESC_BOX_BLUR_BYTES);
+            tma_load_box(boxBase, &M.blur.m[l], px0 - pal, cy - 18, f, bar0 + 8);
+        }
+        __syncwarp();
+    } else {
         const uint8_t* src = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)(unsigned)((cy - 18) * bp + (px0 - pal));
         const unsigned sbase = (unsigned)__cvta_generic_to_shared(&s_patch[threadIdx.x >> 5][0]);
 #pragma unroll
@@ -1067,10 +1096,28 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     // IC_Angle: first-order moments over the radius-15 disc of the UNBLURRED level.  The 31 x 31 patch is read as aligned
     // 32-bit words (9 per row whatever the alignment of cx - 15): 279 (row, word) items spread over the 32 lanes, and every
     // item is two IDP.4A against host-built weight words (u resp. v inside the disc, 0 outside) selected by the alignment.
-    int pitch;
-    const uint8_t* img = level_plane(P, F, f, l, pitch);
     int m10 = 0, m01 = 0;
-    {
+    if constexpr (TMA) {
+        // the box starts at the 16-byte boundary at or below cx - 15: the patch is words (al >> 2) .. (al >> 2) + 8 of each 12-word
+        // row, weighted by the table of its byte alignment al & 3 -- the same 279 (row, word) items as the LDG form, as LDS.32
+        mbar_wait(bar0, 0);
+        const int al = (cx - HALF_PATCH) & 15;
+        const uint32_t* box = reinterpret_cast<const uint32_t*>(s_box + (threadIdx.x >> 5) * DESC_BOX_STRIDE + DESC_BOX_IMG_OFF) + (al >> 2);
+        const uint2* tab = icTab + (al & 3) * IC_ITEMS_PAD;
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            const int i = lane + 32 * k;
+            if (k < 8 || i < IC_ITEMS) {
+                const int row = (i * 57) >> 9, word = i - 9 * row;         // i / 9 for i < 288
+                const uint2 wt = __ldg(&tab[i]);
+                const unsigned px = box[row * (DESC_BOX_IMG_W / 4) + word];
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(px), "r"(wt.x));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(px), "r"(wt.y));
+            }
+        }
+    } else {
+        int pitch;
+        const uint8_t* img = level_plane(P, F, f, l, pitch);
         const int x0 = cx - HALF_PATCH, al = x0 & 3;
         const uint8_t* org = img + (size_t)(unsigned)((cy - HALF_PATCH) * pitch + (x0 - al));
         const uint2* tab = icTab + al * IC_ITEMS_PAD;
@@ -1099,11 +1146,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     orbx_sc::sincosf_glibc(__fmul_rn(angle, factorPI), &b, &a);       // a = cos, b = sin (:112-113)
     // shared-space byte address of the patch centre with both rounding biases folded in (32-bit arithmetic, wraps):
     // address = centre + (rbits - MAGIC) * pitch + (cbits - MAGIC)
-    constexpr unsigned PB = DESC_PATCH_WPITCH * 4;
-    const unsigned ctrb = (unsigned)__cvta_generic_to_shared(&s_patch[threadIdx.x >> 5][0]) + 18u * PB + 18u + (unsigned)pal -
+    constexpr unsigned PB = TMA ? DESC_BOX_BLUR_W : DESC_PATCH_WPITCH * 4;
+    const unsigned ctrb = (TMA ? boxBase : (unsigned)__cvta_generic_to_shared(&s_patch[threadIdx.x >> 5][0])) + 18u * PB + 18u + (unsigned)pal -
                           (unsigned)MAGIC_BITS * (PB + 1u);
-    asm volatile("cp.async.wait_all;" ::: "memory");
-    __syncwarp();
+    if constexpr (TMA) mbar_wait(bar0 + 8, 0);
+    else {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();
+    }
     unsigned val = 0;
 #pragma unroll
     for (int bit = 0; bit < 8; bit++) {
@@ -1145,10 +1195,19 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     }
 }
 
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B)
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B,
+                            const LevelMaps* imgMaps, const LevelMaps* blurMaps)
 {
     dim3 grd((P.totalNodes + DESC_WARPS - 1) / DESC_WARPS, B);
-    k_orient_describe<<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT);
+    OrientMaps M;
+    if (imgMaps && blurMaps) {
+        M.img = *imgMaps;
+        M.blur = *blurMaps;
+        k_orient_describe<true><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+    } else {
+        memset(&M, 0, sizeof M);
+        k_orient_describe<false><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ padded copy-out

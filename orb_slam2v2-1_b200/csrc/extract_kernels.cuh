@@ -1,6 +1,7 @@
 // extract_kernels.cuh -- launch interface of the ORB extraction kernels (extract_kernels.cu).
 #pragma once
 #include "orbx_common.cuh"
+#include "tma.cuh"
 
 namespace orbx {
 
@@ -37,7 +38,9 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B);
 // IC_Angle (:77-104) + computeOrbDescriptor (:108-147) + operator()'s assembly (:1095-1103)
-void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B);
+// imgMaps / blurMaps: TMA maps of the unblurred / blurred levels with boxes of 48 x 31 / 64 x 37 bytes (null: LDGSTS form)
+void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B,
+                            const LevelMaps* imgMaps, const LevelMaps* blurMaps);
 // padded (w+2b)x(h+2b) BORDER_REFLECT_101 copy of one plane into dst (row pitch dpitch)
 void launch_reflect_copy(cudaStream_t s, const uint8_t* src, int w, int h, int spitch, uint8_t* dst, int border, int dpitch);
 

@@ -29,6 +29,25 @@ bool cuda_ok(cudaError_t e, const char* what, const char* file, int line)
     return false;
 }
 
+bool tma_encode_planes(CUtensorMap* map, const void* base, int w, int h, int frames, size_t pitch, size_t frameStride, int boxW, int boxH)
+{
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                 const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static const EncodeFn encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult st;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &st) != cudaSuccess || st != cudaDriverEntryPointSuccess) fn = nullptr;
+        cudaGetLastError();
+        return (EncodeFn)fn;
+    }();
+    if (!encode || !tma_aligned(base, pitch, frameStride) || boxW > 256 || boxH > 256 || (boxW & 15) || frames < 1) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frameStride};
+    const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1u}, estr[3] = {1u, 1u, 1u};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static inline int round_half_even(float v) { return (int)lrintf(v); }      // cvRound
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -78,6 +97,14 @@ struct orbx_extractor {
     // lv0Frame + planeOff[l] with the device pitch; page-locked, filled by two copies that run beside FAST + quadtree
     bool mirror = false;
     uint8_t* h_pyr = nullptr;
+
+    // TMA maps (tma.cuh): unblurred levels with the 48 x 31 box of IC_Angle, blurred levels with the 64 x 37 descriptor box.
+    // Levels >= 1 and the blurred planes are the handle's own buffers (encoded once per shape); level 0 follows bufs.lv0.
+    LevelMaps mapsImg{}, mapsBlur{};
+    bool tmaShape = false, tmaLv0 = false;
+    const void* mapLv0 = nullptr;
+    unsigned long long mapLv0Pitch = 0, mapLv0Frame = 0;
+    int mapLv0B = 0;
 
     int lastB = 0;                     // frames of the last call (0 = none)
     int lastLaunches = 0;
@@ -340,6 +367,18 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     ORBX_CUDA(cudaMallocHost(&ex->h_in, ex->h_in_bytes));
     ORBX_CUDA(cudaMallocHost(&ex->h_out, ex->h_out_bytes));
     if (ex->mirror) ORBX_CUDA(cudaMallocHost(&ex->h_pyr, ex->lv0Frame + P.pyrSlab));
+    {   // tensor maps of the handle's own planes; any failure (old driver) leaves the LDGSTS kernels in charge
+        static const bool tmaEnv = !(getenv("ORBX_TMA") && atoi(getenv("ORBX_TMA")) == 0);
+        bool ok = tmaEnv && ex->nlevels <= TMA_LEVELS;
+        for (int l = 0; l < ex->nlevels && ok; l++) {
+            const LevelGeom& G = P.lv[l];
+            ok = tma_encode_planes(&ex->mapsBlur.m[l], F.blur + G.blurOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.blurSlab, 64, 37);
+            if (ok && l > 0) ok = tma_encode_planes(&ex->mapsImg.m[l], F.pyr + G.planeOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.pyrSlab, 48, 31);
+        }
+        ex->tmaShape = ok;
+        ex->tmaLv0 = false;
+        ex->mapLv0 = nullptr;
+    }
     ex->W = w; ex->H = h; ex->capB = cap;
     return ORBX_OK;
 }
@@ -390,7 +429,7 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
     if (fork) ORBX_CUDA(cudaStreamWaitEvent(s, ex->evJoin, 0));
     else launch_blur(s, P, F, B);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
-    launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B);
+    launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B, ex->tmaLv0 ? &ex->mapsImg : nullptr, ex->tmaLv0 ? &ex->mapsBlur : nullptr);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     if (ex->mirror && !fork) ORBX_CUDA(mirror_pyramid(ex, s));
     launches += 4;
@@ -400,14 +439,26 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
 
 // The whole extraction of B frames on the handle's stream: ComputePyramid -> cell FAST -> DistributeOctTree ->
 // GaussianBlur -> orientation + descriptors (operator(), ORBextractor.cc:1043-1105).
+// level-0 tensor maps follow the buffer the frames are in (the handle's own planes or the caller's device images)
+static void refresh_lv0_maps(orbx_extractor* ex, int B)
+{
+    const FrameBufs& F = ex->bufs;
+    if (!ex->tmaShape) { ex->tmaLv0 = false; return; }
+    const int frames = F.lv0 == ex->d_lv0 ? ex->capB : B;
+    if (ex->mapLv0 == F.lv0 && ex->mapLv0Pitch == F.lv0Pitch && ex->mapLv0Frame == F.lv0Frame && ex->mapLv0B >= B && ex->mapLv0B == frames) return;
+    ex->tmaLv0 = tma_encode_planes(&ex->mapsImg.m[0], F.lv0, ex->plan.lv[0].w, ex->plan.lv[0].h, frames, (size_t)F.lv0Pitch, (size_t)F.lv0Frame, 48, 31);
+    ex->mapLv0 = F.lv0; ex->mapLv0Pitch = F.lv0Pitch; ex->mapLv0Frame = F.lv0Frame; ex->mapLv0B = frames;
+}
+
 static int enqueue(orbx_extractor* ex, int B)
 {
+    refresh_lv0_maps(ex, B);
     static const bool graphsEnv = !(getenv("ORBX_GRAPHS") && atoi(getenv("ORBX_GRAPHS")) == 0);
     cudaStream_t s = ex->stream;
     ex->lastB = B;
     if (!ex->profile && graphsEnv && !ex->graphsOff && B <= GRAPH_MAX_BATCH) {
         orbx_extractor::GraphKey key;
-        key.B = B; key.form = ex->octForm; key.fma = ex->plan.fmaMode; key.mirror = ex->mirror;
+        key.B = B; key.form = ex->octForm; key.fma = ex->plan.fmaMode; key.mirror = ex->mirror + 2 * (int)ex->tmaLv0;
         key.lv0 = ex->bufs.lv0; key.pitch = ex->bufs.lv0Pitch; key.frame = ex->bufs.lv0Frame;
         if (ex->graphExec && key == ex->graphKey) {
             ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
