@@ -259,8 +259,9 @@ int fast_tile_pitch(const Plan& P)
 
 __device__ __forceinline__ unsigned swar_gt(unsigned a, unsigned K) { return ((a & 0x7F7F7F7Fu) + K) | a; }    // bit 7 of a byte: byte > t
 
-template <int TP>
-__device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F, int smemPerWarp, int f, int cell, uint8_t* smem)
+template <int TP, bool TMA>
+__device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F, int smemPerWarp, int f, int cell, uint8_t* smem,
+                                               const LevelMaps& M, uint64_t* bars)
 {
     constexpr int TPW = TP / 4;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -280,11 +281,24 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     const int iw = tw - 6, ih = th - 6;                   // detection zone: no corner within 3 px of the ROI edge
     const int dx0 = cu.z & 0xFF, scp = (cu.z >> 8) & 0xFF, dFirst = (cu.z >> 16) & 0xFF;
     uint8_t* tile = smem + (size_t)wid * smemPerWarp;
-    uint8_t* sc = tile + th * TP;                         // score map: (ih + 2) x scp, 1-px zero frame
+    // score map: (ih + 2) x scp, 1-px zero frame; behind the whole box in the TMA form (the box always has hCell + 6 rows)
+    uint8_t* sc = tile + (TMA ? G.hCell + 6 : th) * TP;
     const int scBytes = ((ih + 2) * scp + 15) & ~15;
     uint16_t* list = reinterpret_cast<uint16_t*>(sc + scBytes);
     const uint32_t* tileW = reinterpret_cast<const uint32_t*>(tile);
 
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&bars[wid]);
+    if constexpr (TMA) {
+        // the whole ROI as ONE box of TP x (hCell + 6) bytes from the 16-byte boundary at or below iniX (rows below the ROI of a
+        // bottom cell come along or are zero-filled outside the plane; nothing reads them)
+        if (lane == 0) {
+            mbar_init(bar, 1);
+            mbar_fence_init();
+            mbar_expect_tx(bar, (unsigned)((G.hCell + 6) * TP));
+            tma_load_box((unsigned)__cvta_generic_to_shared(tile), &M.m[l], iniX - dx0, iniY, f, bar);
+        }
+        __syncwarp();
+    } else {
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below.
@@ -322,6 +336,7 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             }
         }
     }
+    }
     // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih)
     const int zx0 = dx0 + 3, zx1 = zx0 + iw;
     // pre-filter work items: lane = (row zr0, 8-byte column zc) of a block of rpiZ zone rows
@@ -339,7 +354,8 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)(ct.w & 0xFFFF) * G.slotCap;
     const int scBias = 1 - zx0 - 2 * scp;                 // score-map index of tile pixel (row, col) = row * scp + col + scBias
     int total = 0;
-    asm volatile("cp.async.wait_all;" ::: "memory");
+    if constexpr (TMA) mbar_wait(bar, 0);
+    else asm volatile("cp.async.wait_all;" ::: "memory");
 
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? P.iniTh : P.minTh;
@@ -449,26 +465,37 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
 #ifndef FAST_MINB
 #define FAST_MINB 32
 #endif
-template <int TP>
-__global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp)
+template <int TP, bool TMA>
+__global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB) k_fast_cells(const Plan P, const FrameBufs F, int smemPerWarp,
+                                                                          const __grid_constant__ LevelMaps M)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
-    fast_cell_body<TP>(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem);
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t bars[FAST_WARPS];
+    fast_cell_body<TP, TMA>(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem, M, bars);
 }
 
-template <int TP>
-static void launch_fast_cells_tp(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
+template <int TP, bool TMA>
+static void launch_fast_cells_tp(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes, const LevelMaps& M)
 {
     static SmemOptIn optin;            // small levels can have cells of up to 61 x 61 pixels
-    optin.ensure(k_fast_cells<TP>, smemBytes);
+    optin.ensure(k_fast_cells<TP, TMA>, smemBytes);
     dim3 grd((P.totalCells + FAST_WARPS - 1) / FAST_WARPS, B);
-    k_fast_cells<TP><<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS));
+    k_fast_cells<TP, TMA><<<grd, FAST_WARPS * 32, smemBytes, s>>>(P, F, (int)(smemBytes / FAST_WARPS), M);
 }
 
-void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes)
+// maps: TMA maps of the unblurred levels with a box of fastPitch x (hCell + 6) bytes (null: LDGSTS staging)
+void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes, const LevelMaps* maps)
 {
-    if (P.fastPitch == 64) launch_fast_cells_tp<64>(s, P, F, B, smemBytes);
-    else launch_fast_cells_tp<128>(s, P, F, B, smemBytes);
+    LevelMaps M;
+    if (maps) M = *maps;
+    else memset(&M, 0, sizeof M);
+    if (P.fastPitch == 64) {
+        if (maps) launch_fast_cells_tp<64, true>(s, P, F, B, smemBytes, M);
+        else launch_fast_cells_tp<64, false>(s, P, F, B, smemBytes, M);
+    } else {
+        if (maps) launch_fast_cells_tp<128, true>(s, P, F, B, smemBytes, M);
+        else launch_fast_cells_tp<128, false>(s, P, F, B, smemBytes, M);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ quadtree

@@ -32,7 +32,7 @@ void launch_resize(cudaStream_t s, const uint8_t* src, int spitch, size_t sframe
                    size_t dframe, const void* xtab, const int4* ytab, int B, int sh);
 // xtab: one 32-byte record per group of 4 output columns (see build_resize_tables)
 // per-cell FAST-9/16 + NMS + ini/min retry, all levels and frames (ComputeKeyPointsOctTree cell loop, :789-829)
-void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes);
+void launch_fast_cells(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, size_t smemBytes, const LevelMaps* maps);
 // DistributeOctTree (:539-763), one CTA per (level, frame)
 cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int B, int capS, int sortCap, int form = 0);   // form: orbx_set_octree_form
 // GaussianBlur 7x7 sigma 2 of every level (:1085-1086)

@@ -100,7 +100,7 @@ struct orbx_extractor {
 
     // TMA maps (tma.cuh): unblurred levels with the 48 x 31 box of IC_Angle, blurred levels with the 64 x 37 descriptor box.
     // Levels >= 1 and the blurred planes are the handle's own buffers (encoded once per shape); level 0 follows bufs.lv0.
-    LevelMaps mapsImg{}, mapsBlur{};
+    LevelMaps mapsImg{}, mapsBlur{}, mapsFast{};      // mapsFast: unblurred levels with the FAST cell box, fastPitch x (hCell + 6)
     bool tmaShape = false, tmaLv0 = false;
     const void* mapLv0 = nullptr;
     unsigned long long mapLv0Pitch = 0, mapLv0Frame = 0;
@@ -373,7 +373,9 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
         for (int l = 0; l < ex->nlevels && ok; l++) {
             const LevelGeom& G = P.lv[l];
             ok = tma_encode_planes(&ex->mapsBlur.m[l], F.blur + G.blurOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.blurSlab, 64, 37);
-            if (ok && l > 0) ok = tma_encode_planes(&ex->mapsImg.m[l], F.pyr + G.planeOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.pyrSlab, 48, 31);
+            if (ok && l > 0)
+                ok = tma_encode_planes(&ex->mapsImg.m[l], F.pyr + G.planeOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.pyrSlab, 48, 31) &&
+                     tma_encode_planes(&ex->mapsFast.m[l], F.pyr + G.planeOff, G.w, G.h, cap, (size_t)G.pitch, (size_t)P.pyrSlab, P.fastPitch, G.hCell + 6);
         }
         ex->tmaShape = ok;
         ex->tmaLv0 = false;
@@ -422,7 +424,7 @@ static int launch_all(orbx_extractor* ex, int B, bool prof)
         if (ex->mirror) ORBX_CUDA(mirror_pyramid(ex, ex->stream2));      // the copy engine works while FAST + quadtree run
         ORBX_CUDA(cudaEventRecord(ex->evJoin, ex->stream2));
     }
-    launch_fast_cells(s, P, F, B, ex->fastSmem);
+    launch_fast_cells(s, P, F, B, ex->fastSmem, ex->tmaLv0 ? &ex->mapsFast : nullptr);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octForm));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
@@ -446,7 +448,9 @@ static void refresh_lv0_maps(orbx_extractor* ex, int B)
     if (!ex->tmaShape) { ex->tmaLv0 = false; return; }
     const int frames = F.lv0 == ex->d_lv0 ? ex->capB : B;
     if (ex->mapLv0 == F.lv0 && ex->mapLv0Pitch == F.lv0Pitch && ex->mapLv0Frame == F.lv0Frame && ex->mapLv0B >= B && ex->mapLv0B == frames) return;
-    ex->tmaLv0 = tma_encode_planes(&ex->mapsImg.m[0], F.lv0, ex->plan.lv[0].w, ex->plan.lv[0].h, frames, (size_t)F.lv0Pitch, (size_t)F.lv0Frame, 48, 31);
+    ex->tmaLv0 = tma_encode_planes(&ex->mapsImg.m[0], F.lv0, ex->plan.lv[0].w, ex->plan.lv[0].h, frames, (size_t)F.lv0Pitch, (size_t)F.lv0Frame, 48, 31) &&
+                 tma_encode_planes(&ex->mapsFast.m[0], F.lv0, ex->plan.lv[0].w, ex->plan.lv[0].h, frames, (size_t)F.lv0Pitch, (size_t)F.lv0Frame,
+                                   ex->plan.fastPitch, ex->plan.lv[0].hCell + 6);
     ex->mapLv0 = F.lv0; ex->mapLv0Pitch = F.lv0Pitch; ex->mapLv0Frame = F.lv0Frame; ex->mapLv0B = frames;
 }
 
