@@ -511,59 +511,99 @@ def e2e_leg(args, cfg, S):
         pinned.append((pa, base))
     chunk = min(args.e2e_chunk, B)
     nthreads = args.e2e_threads
-    workers = []
-    for _ in range(nthreads):
-        hs = [orbx.ORBextractor(*params(cfg), device=local, max_batch=chunk) for _ in sides]
-        for h, host in zip(hs, sides):
-            h.set_fma_mode(1)
-            h(host[0])                                                  # plans the shape; max_keypoints is exact afterwards
-        workers.append((hs, orbx.ORBmatcher(0.6, True, device=local) if stereo else None))
-    cap = workers[0][0][0].max_keypoints()
-    scapacity = max(cap, 64)
-    outs = []
-    for _ in range(nthreads):
-        per_side = []
-        for _ in sides:       # result arrays of the caller: page-locked and laid out with cap = the handle's per-frame capacity, so
-            pk = torch.zeros((chunk, cap, 28), dtype=torch.uint8).pin_memory()      # that the library copies straight into them
-            pd = torch.zeros((chunk, cap, 32), dtype=torch.uint8).pin_memory()
-            per_side.append((pk, pd, np.zeros(chunk, np.int32)))
-        outs.append((per_side, np.zeros((chunk, scapacity), np.float32), np.zeros((chunk, scapacity), np.float32), np.zeros(chunk, np.int32)))
-    chunks = [(c0, min(chunk, B - c0)) for c0 in range(0, B, chunk)]
+    # what the box can move: the same pinned frames copied to the device and nothing else, all ranks at once -> the e2e ceiling
+    dst = torch.empty((B, frame), dtype=torch.uint8, device="cuda")
+    src_t = [torch.from_numpy(np.frombuffer((C.c_uint8 * (B * frame)).from_address(base), dtype=np.uint8).reshape(B, frame)) for _, base in pinned]
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    c0e, c1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dst.copy_(src_t[0], non_blocking=True)
+    c0e.record()
+    for _ in range(8):
+        for t_ in src_t:
+            dst.copy_(t_, non_blocking=True)
+    c1e.record()
+    c1e.synchronize()
+    h2d_gbs = 8 * len(sides) * B * frame / (c0e.elapsed_time(c1e) / 1e3) / 1e9
+    del dst
     errors = []
+    if not stereo:
+        # the library's own driver (orbx_pool_*): this rank's GPU, `nthreads` lanes (host threads with their own handles) that take
+        # chunks of the batch in turn; results go straight into the caller's page-locked arrays at the frame's index
+        pool = orbx.ExtractorPool(*params(cfg), devices=[local], chunk=chunk, lanes=nthreads)
+        pool.set_fma_mode(1)
+        cap = pool.plan(W, H)
+        scapacity = cap
+        pk = torch.zeros((B, cap, 28), dtype=torch.uint8).pin_memory()
+        pd = torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory()
+        nn = np.zeros(B, np.int32)
+        ptrs = (C.c_void_p * B)(*[pinned[0][1] + i * frame for i in range(B)])
 
-    def worker(t, nsteps):
-        try:
-            torch.cuda.set_device(local)
-            hs, m = workers[t]
-            per_side, uR, dep, nm = outs[t]
+        def run(nsteps):
             for _ in range(nsteps):
-                for ci in range(t, len(chunks), nthreads):
-                    c0, cb = chunks[ci]
-                    for h, (_, base), (pk, pd, n) in zip(hs, pinned, per_side):
-                        ptrs = (C.c_void_p * cb)(*[base + (c0 + i) * frame for i in range(cb)])
-                        rc = L.orbx_extract_batch(h._h, ptrs, cb, W, H, P32, C.c_void_p(pk.data_ptr()), C.c_void_p(pd.data_ptr()), cap,
-                                                  n.ctypes.data_as(C.c_void_p))
-                        if rc != 0:
-                            raise RuntimeError(L.orbx_last_error().decode())
-                    if stereo:
+                rc = L.orbx_pool_extract_batch(pool._h, ptrs, B, W, H, P32, C.c_void_p(pk.data_ptr()), C.c_void_p(pd.data_ptr()), cap,
+                                               nn.ctypes.data_as(C.c_void_p))
+                if rc != 0:
+                    raise RuntimeError(L.orbx_last_error().decode())
+
+        run(1)
+        # the pool's results are the device-resident leg's: same frames, same bytes
+        resL = S["resL"]
+        for b in (0, B // 2, B - 1):
+            k = pk[b].numpy().view(orbx.KP_DTYPE).reshape(cap)[:nn[b]]
+            assert k.tobytes() == resL[b][0].tobytes() and np.array_equal(pd[b].numpy()[:nn[b]], resL[b][1]), "pool result differs (frame %d)" % b
+    else:
+        workers = []
+        for _ in range(nthreads):
+            hs = [orbx.ORBextractor(*params(cfg), device=local, max_batch=chunk) for _ in sides]
+            for h, host in zip(hs, sides):
+                h.set_fma_mode(1)
+                h(host[0])                                                  # plans the shape; max_keypoints is exact afterwards
+            workers.append((hs, orbx.ORBmatcher(0.6, True, device=local)))
+        cap = workers[0][0][0].max_keypoints()
+        scapacity = max(cap, 64)
+        outs = []
+        for _ in range(nthreads):
+            per_side = []
+            for _ in sides:   # result arrays of the caller: page-locked and laid out with cap = the handle's per-frame capacity, so
+                pk = torch.zeros((chunk, cap, 28), dtype=torch.uint8).pin_memory()      # that the library copies straight into them
+                pd = torch.zeros((chunk, cap, 32), dtype=torch.uint8).pin_memory()
+                per_side.append((pk, pd, np.zeros(chunk, np.int32)))
+            outs.append((per_side, np.zeros((chunk, scapacity), np.float32), np.zeros((chunk, scapacity), np.float32), np.zeros(chunk, np.int32)))
+        chunks = [(c0, min(chunk, B - c0)) for c0 in range(0, B, chunk)]
+
+        def worker(t, nsteps):
+            try:
+                torch.cuda.set_device(local)
+                hs, m = workers[t]
+                per_side, uR, dep, nm = outs[t]
+                for _ in range(nsteps):
+                    for ci in range(t, len(chunks), nthreads):
+                        c0, cb = chunks[ci]
+                        for h, (_, base), (pk, pd, n) in zip(hs, pinned, per_side):
+                            ptrs = (C.c_void_p * cb)(*[base + (c0 + i) * frame for i in range(cb)])
+                            rc = L.orbx_extract_batch(h._h, ptrs, cb, W, H, P32, C.c_void_p(pk.data_ptr()), C.c_void_p(pd.data_ptr()), cap,
+                                                      n.ctypes.data_as(C.c_void_p))
+                            if rc != 0:
+                                raise RuntimeError(L.orbx_last_error().decode())
                         rc = L.orbm_stereo_matches_batch(m._h, hs[0]._h, hs[1]._h, cfg["bf"], 0.0, cfg["fx"], uR.ctypes.data_as(C.c_void_p),
                                                          dep.ctypes.data_as(C.c_void_p), scapacity, nm.ctypes.data_as(C.c_void_p))
                         if rc != 0:
                             raise RuntimeError(L.orbx_last_error().decode())
-        except Exception as e:          # noqa: re-raised after join -- a dead worker would otherwise make e2e come out too high
-            errors.append(e)
+            except Exception as e:      # noqa: re-raised after join -- a dead worker would otherwise make e2e come out too high
+                errors.append(e)
 
-    def run(nsteps):
-        th = [threading.Thread(target=worker, args=(t, nsteps)) for t in range(nthreads)]
-        for x in th:
-            x.start()
-        for x in th:
-            x.join()
-        if errors:
-            raise errors[0]
+        def run(nsteps):
+            th = [threading.Thread(target=worker, args=(t, nsteps)) for t in range(nthreads)]
+            for x in th:
+                x.start()
+            for x in th:
+                x.join()
+            if errors:
+                raise errors[0]
 
-    run(1)
-    # the results in the caller's pinned arrays are the same bytes as the device-resident leg's (last chunk of worker 0 = chunk 0 or later)
+        run(1)
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
@@ -578,9 +618,15 @@ def e2e_leg(args, cfg, S):
     ns = len(sides)
     h2d = B * ns * ((H - 1) * P32 + W)
     d2h = B * ns * (cap * 60 + 4) + (B * (2 * 4 * scapacity + 4) if stereo else 0)
-    how = "orbx_extract_batch%s on pinned host frames into pinned host results, %d handle sets x %d-unit chunks on %d host threads" % (
-        " (left, right) + orbm_stereo_matches_batch" if stereo else "", nthreads, chunk, nthreads)
-    return B * world * args.steps / e2e_s, h2d, d2h, how
+    if stereo:
+        how = "orbx_extract_batch (left, right) + orbm_stereo_matches_batch on pinned host frames into pinned host results, %d handle sets x %d-pair chunks on %d host threads" % (nthreads, chunk, nthreads)
+    else:
+        how = "orbx_pool_extract_batch (the library's multi-GPU driver, this rank's GPU): pinned host frames in, pinned host results out, %d lanes x %d-frame chunks" % (nthreads, chunk)
+    value = B * world * args.steps / e2e_s
+    ceiling = {"h2d_GBps_this_rank": h2d_gbs, "e2e_h2d_GBps_this_rank": value / world * h2d / B / 1e9,
+               "frac": (value / world * h2d / B / 1e9) / h2d_gbs,
+               "note": "ceiling = the same pinned frames copied host-to-device and nothing else, all ranks at once; frac = input bytes/s of the e2e leg over it"}
+    return value, h2d, d2h, how, ceiling
 
 
 def match_leg(local):
@@ -615,7 +661,7 @@ def finish_ours(args, cfg, S):
     """e2e leg, matcher leg, roofline / cpu_baseline objects and the JSON line (rank 0)."""
     rank, world, local, dist, B = S["rank"], S["world"], S["local"], S["dist"], S["B"]
     value, acc = S["value"], S["acc"]
-    e2e_value, h2d, d2h, how = e2e_leg(args, cfg, S)
+    e2e_value, h2d, d2h, how, ceiling = e2e_leg(args, cfg, S)
     match = match_leg(local) if rank == 0 else {}
     if rank != 0:
         if dist is not None:
@@ -677,7 +723,7 @@ def finish_ours(args, cfg, S):
                    "l2": "inputs larger than L2 (%d MB per step)" % (B * W * H * (2 if cfg["stereo"] else 1) >> 20),
                    "keypoints_per_frame": S["nkp_mean"], "fma_mode": 1},
         "clocks": S["clk"], "gpu_launches": S["launches"], "parity": S["parity"], "parity_frames": min(args.parity_frames, B),
-        "e2e": {"value": e2e_value, "unit": unit_of(cfg), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "how": how, "numa": S["numa"]},
+        "e2e": {"value": e2e_value, "unit": unit_of(cfg), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "how": how, "numa": S["numa"], "ceiling": ceiling},
         "roofline": roofline, "cpu_baseline": cpu, "match": match,
     })
     if dist is not None:
@@ -694,13 +740,15 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="units per step per GPU (0 = the configuration's default)")
     ap.add_argument("--parity-frames", type=int, default=8, help="units each rank checks against the reference build before timing")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--e2e-threads", type=int, default=6, help="host threads (= handle sets) of the e2e leg")
+    ap.add_argument("--e2e-threads", type=int, default=0, help="host threads (= lanes / handle sets) of the e2e leg; 0 = min(8, max(3, host cores per rank))")
     ap.add_argument("--e2e-wc", type=int, default=0, help="1: e2e input frames in write-combined page-locked memory")
-    ap.add_argument("--e2e-chunk", type=int, default=64, help="units per orbx_extract_batch call in the e2e leg")
+    ap.add_argument("--e2e-chunk", type=int, default=32, help="units per chunk of the e2e leg")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
-    if args.config in (2, 4) and args.e2e_chunk == 64:
-        args.e2e_chunk = 16 if args.config == 4 else 32          # same bytes per chunk as 64 VGA frames
+    if args.config in (2, 4) and args.e2e_chunk == 32:
+        args.e2e_chunk = 8 if args.config == 4 else 16           # about the same bytes per chunk as 32 VGA frames
+    if args.e2e_threads <= 0:
+        args.e2e_threads = min(8, max(3, (os.cpu_count() or 4) // max(int(os.environ.get("WORLD_SIZE", "1")), 1)))
     quiet_stdout()
     if args.impl == "reference":
         run_reference(args, cfg)

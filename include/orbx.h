@@ -101,6 +101,26 @@ int orbx_extract_color_batch(orbx_extractor* ex, const uint8_t* const* imgs, int
 int orbx_extract_color_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, int w, int h, size_t pitch, size_t frame_stride,
                               int channels, int rgb);
 
+/* ---- Multi-GPU driver.  The reference extracts one image per thread (src/Frame.cc:78-81); frames are
+ * independent, so a pool shards a batch over GPUs with no collective: the batch is cut into chunks of `chunk` consecutive frames,
+ * chunk c goes to devices[c mod ndevices] (chunk = 1: frame i -> GPU i mod G), and every device runs `lanes` host threads, each with
+ * its own extractor handle (stream + workspace + page-locked staging buffer), so that copies and kernels of different chunks overlap.
+ * Results are written to the caller's arrays at the frame's own index: the output bytes are the same for every device count, chunk
+ * size and lane count.  devices = NULL or ndevices = 0: every visible GPU.  One pool call at a time per pool. */
+typedef struct orbx_pool orbx_pool;
+int orbx_pool_create(const int* devices, int ndevices, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                     int chunk, int lanes, orbx_pool** out);
+void orbx_pool_destroy(orbx_pool* pool);
+int orbx_pool_devices(const orbx_pool* pool);
+int orbx_pool_set_fma_mode(orbx_pool* pool, int fma_mode);
+/* Plans an image shape on every handle of the pool (allocates the workspaces once, outside any timed region) and returns the
+ * per-frame keypoint capacity for that shape: with cap equal to it and page-locked result arrays, orbx_pool_extract_batch copies
+ * straight into the caller's memory. */
+int orbx_pool_plan(orbx_pool* pool, int w, int h, int* max_keypoints);
+/* orbx_extract_batch over the pool: same arguments, same results, B unbounded.  Synchronous. */
+int orbx_pool_extract_batch(orbx_pool* pool, const uint8_t* const* imgs, int B, int w, int h, size_t stride,
+                            orbx_kp* kps, uint8_t* desc, int cap, int* n);
+
 /* Waits for the handle's stream and copies the results of the last orbx_extract_device call to HOST buffers laid out
  * as in orbx_extract_batch. */
 int orbx_fetch(orbx_extractor* ex, orbx_kp* kps, uint8_t* desc, int cap, int* n);

@@ -55,6 +55,12 @@ def lib():
         "orbx_extract_batch": (i, [vp, vp, i, i, i, sz, vp, vp, i, vp]),
         "orbx_extract_device": (i, [vp, vp, i, i, i, sz, sz]),
         "orbx_fetch": (i, [vp, vp, vp, i, vp]),
+        "orbx_pool_create": (i, [vp, i, i, f, i, i, i, i, i, vp]),
+        "orbx_pool_destroy": (None, [vp]),
+        "orbx_pool_devices": (i, [vp]),
+        "orbx_pool_set_fma_mode": (i, [vp, i]),
+        "orbx_pool_plan": (i, [vp, i, i, vp]),
+        "orbx_pool_extract_batch": (i, [vp, vp, i, i, i, sz, vp, vp, i, vp]),
         "orbx_results_device": (i, [vp, vp, vp, vp, vp]),
         "orbx_sync": (i, [vp]),
         "orbx_stream": (vp, [vp]),
@@ -341,6 +347,53 @@ class ORBextractor:
         n = C.c_int(0)
         _check(self._L.orbx_debug_level_count(self._h, frame, level, C.byref(n)))
         return n.value
+
+
+class ExtractorPool:
+    """orbx_pool_* (include/orbx.h): one process, every GPU -- a batch of frames sharded over devices in chunks, results in frame order."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, devices=None, chunk=64, lanes=2):
+        self._L = lib()
+        h = C.c_void_p()
+        if devices is None:
+            _check(self._L.orbx_pool_create(None, 0, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, chunk, lanes, C.byref(h)))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            _check(self._L.orbx_pool_create(arr, len(devices), nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, chunk, lanes, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbx_pool_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def devices(self):
+        return self._L.orbx_pool_devices(self._h)
+
+    def set_fma_mode(self, mode):
+        _check(self._L.orbx_pool_set_fma_mode(self._h, int(mode)))
+
+    def plan(self, w, h):
+        cap = C.c_int(0)
+        _check(self._L.orbx_pool_plan(self._h, w, h, C.byref(cap)))
+        return cap.value
+
+    def extract_batch(self, images):
+        """images: [B, H, W] uint8 array (or a sequence of equally-shaped 2-D arrays) -> list of (kps, desc), frame order."""
+        imgs = [_u8(im) for im in images]
+        B = len(imgs)
+        if B == 0:
+            return []
+        hh, ww = imgs[0].shape
+        cap = self.plan(ww, hh)
+        kps = np.zeros((B, cap), KP_DTYPE)
+        desc = np.zeros((B, cap, 32), np.uint8)
+        n = np.zeros(B, np.int32)
+        ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
+        _check(self._L.orbx_pool_extract_batch(self._h, ptrs, B, ww, hh, imgs[0].strides[0], _p(kps), _p(desc), cap, _p(n)))
+        return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
 
 
 class ORBmatcher:
