@@ -283,6 +283,38 @@ int orbm_search_by_bow(orbx_matcher* m, int variant, const orbx_kp* k1, const ui
                        const int* node2, const int* off2, const int* idx2, int nn2,
                        float nnratio, int checkOri, int* matches, int* nmatches);
 
+/* ---- A Frame that lives on the device.  The reference's Frame keeps mvKeysUn, mDescriptors and the
+ * 64 x 48 grid of AssignFeaturesToGrid (src/Frame.cc:230-245, 397-407) on the host and every windowed search walks them; here they are
+ * built once per frame in HBM -- the grid by a counting sort on the device that keeps insertion order -- and the searches below take
+ * the handle, so a search moves only the MapPoint side and is ONE launch (window enumeration in GetFeaturesInArea's order fused with
+ * the Hamming distances), one copy back and the greedy host replay.  At most 8192 keypoints per frame.  A frame belongs to the
+ * matcher's device. ---- */
+typedef struct orbm_frame orbm_frame;
+/* From host arrays: kps = mvKeysUn, desc = mDescriptors (n x 32), bounds = mnMinX, mnMaxX, mnMinY, mnMaxY. */
+int orbm_frame_create(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
+                      orbm_frame** out);
+/* Straight from the device results of frame `frame` of the extractor's last call, without a host round trip of the descriptors:
+ * Frame::UndistortKeyPoints (src/Frame.cc:419-449) runs on the device records (dist_coef = mDistCoef as floats; NULL or k1 == 0 leaves
+ * the keypoints as extracted, :421-425), then the grid is built.  orbm_frame_keypoints returns the (undistorted) keypoints. */
+int orbm_frame_from_extractor(orbx_matcher* m, orbx_extractor* ex, int frame, float fx, float fy, float cx, float cy, const float* dist_coef,
+                              int ndist, float minX, float maxX, float minY, float maxY, orbm_frame** out);
+void orbm_frame_destroy(orbm_frame* f);
+int orbm_frame_size(const orbm_frame* f);
+int orbm_frame_keypoints(const orbm_frame* f, orbx_kp* out);
+/* The device grid, for tests: cell_start = 64 * 48 + 1 ints over column-major cells (cell = ix * 48 + iy), entries = n feature indices. */
+int orbm_frame_grid(orbx_matcher* m, const orbm_frame* f, int* cell_start, int* entries);
+/* orbm_search_by_projection / orbm_search_by_projection_frame / orbm_search_for_initialization with the frame side resident on the
+ * device: same arguments without the frame's keypoints, descriptors and bounds; same results, index for index. */
+int orbm_search_by_projection_dev(orbx_matcher* m, const orbm_frame* f, const float* u_right, const uint8_t* occupied, const float* sf, int nlevels,
+                                  const float* proj_xy, const float* proj_xr, const int* level, const float* view_cos, const uint8_t* mp_desc,
+                                  const uint8_t* mp_has_obs, int nmp, float th, float nnratio, int* feature_match, int* nmatches);
+int orbm_search_by_projection_frame_dev(orbx_matcher* m, const orbm_frame* f, const float* u_right, const uint8_t* occupied, const float* sf,
+                                        int nlevels, const float* proj_xy, const float* proj_ur, const int* last_octave, const float* last_angle,
+                                        const uint8_t* mp_desc, const uint8_t* mp_has_obs, int nmp, float th, int mode, int checkOri,
+                                        int* feature_match, int* nmatches);
+int orbm_search_for_initialization_dev(orbx_matcher* m, const orbm_frame* f1, const orbm_frame* f2, float* prev_matched, int* matches12,
+                                       int windowSize, float nnratio, int checkOri, int* nmatches);
+
 /* ---- the LocalMapping / LoopClosing / relocalisation searches.  As above, the caller runs the reference's own skip tests
  * and projection (isBad, spAlreadyFound, depth sign, IsInImage, distance range, viewing angle, PredictScale) and passes, per
  * surviving MapPoint, the projection, the predicted level and GetDescriptor(). ---- */

@@ -88,6 +88,18 @@ static int undistort(orbx_matcher* m, const float* in, int n, int stride, const 
     return ORBX_OK;
 }
 
+// Frame::UndistortKeyPoints (src/Frame.cc:419-449) on keypoint records that already live on the device (orbm_frame_from_extractor):
+// in place; a camera without distortion (mDistCoef[0] == 0, :421-425) leaves them untouched.
+int undistort_keypoints_device(cudaStream_t s, orbx_kp* d_kps, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist)
+{
+    if (n <= 0 || !dist || ndist < 1 || dist[0] == 0.0f) return ORBX_OK;
+    Camera C;
+    if (!make_camera("orbm_frame_from_extractor", fx, fy, cx, cy, dist, ndist, C)) return ORBX_ERR_ARG;
+    k_undistort<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float*>(d_kps), n, 7, C, reinterpret_cast<float*>(d_kps));
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
 }  // namespace orbx
 
 using namespace orbx;

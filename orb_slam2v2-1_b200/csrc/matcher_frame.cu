@@ -219,6 +219,131 @@ void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, in
     else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
 }
 
+// Sequential replay of the greedy loop of SearchForInitialization (src/ORBmatcher.cc:427-483, :485-517): the vMatchedDistance skip
+// and the steals depend on visit order.  off / idx / dist: candidates of query q (feature qmap[q] of frame 1) in GetFeaturesInArea order.
+int replay_initialization(const orbx_kp* k1, int n1, const orbx_kp* k2, int n2, const std::vector<int>& qmap, const std::vector<int>& off,
+                          const std::vector<int>& idx, const std::vector<int>& dist, float nnratio, int checkOri, float* prev_matched,
+                          int* matches12)
+{
+    const int nq = (int)qmap.size();
+    int nm = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> matchedDist(n2, INT_MAX), m21(n2, -1);
+    for (int q = 0; q < nq; q++) {
+        const int i1 = qmap[q];
+        if (off[q + 1] == off[q]) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int c = off[q]; c < off[q + 1]; c++) {
+            const int i2 = idx[c], d = dist[c];
+            if (matchedDist[i2] <= d) continue;
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = i2; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        if (bestDist <= TH_LOW && bestDist < (float)bestDist2 * nnratio) {
+            if (m21[bestIdx2] >= 0) { matches12[m21[bestIdx2]] = -1; nm--; }
+            matches12[i1] = bestIdx2;
+            m21[bestIdx2] = i1;
+            matchedDist[bestIdx2] = bestDist;
+            nm++;
+            if (checkOri) {
+                float rot = k1[i1].angle - k2[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);       // factor = 1/HISTO_LENGTH as in the reference (:413), kept as is
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(i1);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int i1 : rotHist[i])
+                if (matches12[i1] >= 0) { matches12[i1] = -1; nm--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)          // update vbPrevMatched (:515-517)
+        if (matches12[i1] >= 0) { prev_matched[2 * i1] = k2[matches12[i1]].x; prev_matched[2 * i1 + 1] = k2[matches12[i1]].y; }
+    return nm;
+}
+
+// Sequential replay of SearchByProjection(Frame, MapPoints) (src/ORBmatcher.cc:50-126): occupancy changes as points are assigned.
+int replay_projection(const orbx_kp* kps, const float* u_right, const uint8_t* occupied_in, int n, const float* sf, const int* level,
+                      const std::vector<float>& rr, const float* proj_xr, const uint8_t* mp_has_obs, int nmp, float nnratio,
+                      const std::vector<int>& off, const std::vector<int>& idx, const std::vector<int>& dist, int* feature_match)
+{
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    int nm = 0;
+    for (int i = 0; i < nmp; i++) {
+        if (off[i + 1] == off[i]) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int c = off[i]; c < off[i + 1]; c++) {
+            const int j = idx[c];
+            if (occupied[j]) continue;
+            if (u_right[j] > 0) {
+                const float er = fabsf(proj_xr[i] - u_right[j]);
+                if (er > rr[i] * sf[level[i]]) continue;
+            }
+            const int d = dist[c];
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = kps[j].octave; bestIdx = j; }
+            else if (d < bestDist2) { bestLevel2 = kps[j].octave; bestDist2 = d; }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            feature_match[bestIdx] = i;
+            occupied[bestIdx] = mp_has_obs[i];
+            nm++;
+        }
+    }
+    return nm;
+}
+
+// Sequential replay of SearchByProjection(CurrentFrame, LastFrame) (src/ORBmatcher.cc:1385-1468).
+int replay_projection_frame(const orbx_kp* kps, const float* u_right, const uint8_t* occupied_in, int n, const std::vector<float>& qr,
+                            const float* proj_ur, const float* last_angle, const uint8_t* mp_has_obs, int nmp, int checkOri,
+                            const std::vector<int>& off, const std::vector<int>& idx, const std::vector<int>& dist, int* feature_match)
+{
+    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    int nm = 0;
+    for (int i = 0; i < nmp; i++) {
+        if (off[i + 1] == off[i]) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int c = off[i]; c < off[i + 1]; c++) {
+            const int i2 = idx[c];
+            if (occupied[i2]) continue;
+            if (u_right[i2] > 0) {
+                const float er = fabsf(proj_ur[i] - u_right[i2]);
+                if (er > qr[i]) continue;
+            }
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            feature_match[bestIdx2] = i;
+            occupied[bestIdx2] = mp_has_obs[i];
+            nm++;
+            if (checkOri) {
+                float rot = last_angle[i] - kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)roundf(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int j : rotHist[i]) { feature_match[j] = -1; nm--; }
+    }
+    return nm;
+}
+
 }  // namespace orbx
 
 extern "C" int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1, const uint8_t* d1, int n1,
@@ -292,47 +417,7 @@ extern "C" int orbm_search_for_initialization(orbx_matcher* m, const orbx_kp* k1
     }
     ORBX_CUDA(cudaStreamSynchronize(s));
 
-    // sequential replay of the greedy loop (:427-483): the vMatchedDistance skip and the steals depend on visit order
-    int nm = 0;
-    std::vector<int> rotHist[HISTO_LENGTH];
-    const float factor = 1.0f / HISTO_LENGTH;
-    std::vector<int> matchedDist(n2, INT_MAX), m21(n2, -1);
-    for (int q = 0; q < nq; q++) {
-        const int i1 = qmap[q];
-        if (off[q + 1] == off[q]) continue;
-        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
-        for (int c = off[q]; c < off[q + 1]; c++) {
-            const int i2 = idx[c], d = dist[c];
-            if (matchedDist[i2] <= d) continue;
-            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = i2; }
-            else if (d < bestDist2) bestDist2 = d;
-        }
-        if (bestDist <= TH_LOW && bestDist < (float)bestDist2 * nnratio) {
-            if (m21[bestIdx2] >= 0) { matches12[m21[bestIdx2]] = -1; nm--; }
-            matches12[i1] = bestIdx2;
-            m21[bestIdx2] = i1;
-            matchedDist[bestIdx2] = bestDist;
-            nm++;
-            if (checkOri) {
-                float rot = k1[i1].angle - k2[bestIdx2].angle;
-                if (rot < 0.0) rot += 360.0f;
-                int bin = (int)roundf(rot * factor);       // factor = 1/HISTO_LENGTH as in the reference (:413), kept as is
-                if (bin == HISTO_LENGTH) bin = 0;
-                rotHist[bin].push_back(i1);
-            }
-        }
-    }
-    if (checkOri) {
-        int ind1 = -1, ind2 = -1, ind3 = -1;
-        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-        for (int i = 0; i < HISTO_LENGTH; i++) {
-            if (i == ind1 || i == ind2 || i == ind3) continue;
-            for (int i1 : rotHist[i])
-                if (matches12[i1] >= 0) { matches12[i1] = -1; nm--; }
-        }
-    }
-    for (int i1 = 0; i1 < n1; i1++)          // update vbPrevMatched (:515-517)
-        if (matches12[i1] >= 0) { prev_matched[2 * i1] = k2[matches12[i1]].x; prev_matched[2 * i1 + 1] = k2[matches12[i1]].y; }
+    const int nm = replay_initialization(k1, n1, k2, n2, qmap, off, idx, dist, nnratio, checkOri, prev_matched, matches12);
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
 }
@@ -458,30 +543,7 @@ extern "C" int orbm_search_by_projection(orbx_matcher* m, const orbx_kp* kps, co
     std::vector<int> off, idx, dist;
     int rc = windowed_distances(m, kps, desc, n, minX, maxX, minY, maxY, proj_xy, qr.data(), qlev.data(), mp_desc, nmp, off, idx, dist);
     if (rc) return rc;
-    // sequential replay (:50-126): occupancy changes as points are assigned
-    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
-    int nm = 0;
-    for (int i = 0; i < nmp; i++) {
-        if (off[i + 1] == off[i]) continue;
-        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
-        for (int c = off[i]; c < off[i + 1]; c++) {
-            const int j = idx[c];
-            if (occupied[j]) continue;
-            if (u_right[j] > 0) {
-                const float er = fabsf(proj_xr[i] - u_right[j]);
-                if (er > rr[i] * sf[level[i]]) continue;
-            }
-            const int d = dist[c];
-            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = kps[j].octave; bestIdx = j; }
-            else if (d < bestDist2) { bestLevel2 = kps[j].octave; bestDist2 = d; }
-        }
-        if (bestDist <= TH_HIGH) {
-            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
-            feature_match[bestIdx] = i;
-            occupied[bestIdx] = mp_has_obs[i];
-            nm++;
-        }
-    }
+    const int nm = replay_projection(kps, u_right, occupied_in, n, sf, level, rr, proj_xr, mp_has_obs, nmp, nnratio, off, idx, dist, feature_match);
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
 }
@@ -514,42 +576,7 @@ extern "C" int orbm_search_by_projection_frame(orbx_matcher* m, const orbx_kp* k
     std::vector<int> off, idx, dist;
     int rc = windowed_distances(m, kps, desc, n, minX, maxX, minY, maxY, proj_xy, qr.data(), qlev.data(), mp_desc, nmp, off, idx, dist);
     if (rc) return rc;
-    std::vector<uint8_t> occupied(occupied_in, occupied_in + n);
-    std::vector<int> rotHist[HISTO_LENGTH];
-    const float factor = 1.0f / HISTO_LENGTH;
-    int nm = 0;
-    for (int i = 0; i < nmp; i++) {
-        if (off[i + 1] == off[i]) continue;
-        int bestDist = 256, bestIdx2 = -1;
-        for (int c = off[i]; c < off[i + 1]; c++) {
-            const int i2 = idx[c];
-            if (occupied[i2]) continue;
-            if (u_right[i2] > 0) {
-                const float er = fabsf(proj_ur[i] - u_right[i2]);
-                if (er > qr[i]) continue;
-            }
-            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
-        }
-        if (bestDist <= TH_HIGH) {
-            feature_match[bestIdx2] = i;
-            occupied[bestIdx2] = mp_has_obs[i];
-            nm++;
-            if (checkOri) {
-                float rot = last_angle[i] - kps[bestIdx2].angle;
-                if (rot < 0.0) rot += 360.0f;
-                int bin = (int)roundf(rot * factor);
-                if (bin == HISTO_LENGTH) bin = 0;
-                rotHist[bin].push_back(bestIdx2);
-            }
-        }
-    }
-    if (checkOri) {
-        int ind1 = -1, ind2 = -1, ind3 = -1;
-        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-        for (int i = 0; i < HISTO_LENGTH; i++)
-            if (i != ind1 && i != ind2 && i != ind3)
-                for (int j : rotHist[i]) { feature_match[j] = -1; nm--; }
-    }
+    const int nm = replay_projection_frame(kps, u_right, occupied_in, n, qr, proj_ur, last_angle, mp_has_obs, nmp, checkOri, off, idx, dist, feature_match);
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
 }

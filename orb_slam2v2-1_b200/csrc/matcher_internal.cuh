@@ -83,6 +83,7 @@ struct orbx_matcher {
     int* d_tickets = nullptr;      // brute force: arrivals per query block (k_bf_scan), zero between calls
     int ticketCap = 0;
     int lastLaunches = 0;
+    int windowSlots = 64;          // candidate slots per query of the device-frame searches: grows to what the last calls needed
 };
 
 namespace orbx {
@@ -104,11 +105,23 @@ __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, cons
 void build_grid_host(const orbx_kp* kps, int n, float minX, float maxX, float minY, float maxY, GridParams& gp,
                      std::vector<int>& start, std::vector<int>& entries);
 void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3);
+int replay_initialization(const orbx_kp* k1, int n1, const orbx_kp* k2, int n2, const std::vector<int>& qmap, const std::vector<int>& off,
+                          const std::vector<int>& idx, const std::vector<int>& dist, float nnratio, int checkOri, float* prev_matched,
+                          int* matches12);
+int replay_projection(const orbx_kp* kps, const float* u_right, const uint8_t* occupied_in, int n, const float* sf, const int* level,
+                      const std::vector<float>& rr, const float* proj_xr, const uint8_t* mp_has_obs, int nmp, float nnratio,
+                      const std::vector<int>& off, const std::vector<int>& idx, const std::vector<int>& dist, int* feature_match);
+int replay_projection_frame(const orbx_kp* kps, const float* u_right, const uint8_t* occupied_in, int n, const std::vector<float>& qr,
+                            const float* proj_ur, const float* last_angle, const uint8_t* mp_has_obs, int nmp, int checkOri,
+                            const std::vector<int>& off, const std::vector<int>& idx, const std::vector<int>& dist, int* feature_match);
 int windowed_distances(orbx_matcher* m, const orbx_kp* kps, const uint8_t* desc, int n, float minX, float maxX, float minY, float maxY,
                        const float* qxy, const float* qr, const int* qlev2, const uint8_t* qdesc, int nq,
                        std::vector<int>& off, std::vector<int>& idx, std::vector<int>& dist);
 int csr_distances(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, const std::vector<int>& off,
                   const std::vector<int>& idx, std::vector<int>& dist);
+
+// frame_glue.cu
+int undistort_keypoints_device(cudaStream_t s, orbx_kp* d_kps, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist);
 
 int bruteforce_device(orbx_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int th_low, float nnratio,
                       int* d_bi, int* d_bd, int* d_sd, uint8_t* d_acc);

@@ -78,6 +78,15 @@ def lib():
         "orbm_create": (i, [i, vp]),
         "orbm_destroy": (None, [vp]),
         "orbm_trim": (None, []),
+        "orbm_frame_create": (i, [vp, vp, vp, i, f, f, f, f, vp]),
+        "orbm_frame_from_extractor": (i, [vp, vp, i, f, f, f, f, vp, i, f, f, f, f, vp]),
+        "orbm_frame_destroy": (None, [vp]),
+        "orbm_frame_size": (i, [vp]),
+        "orbm_frame_keypoints": (i, [vp, vp]),
+        "orbm_frame_grid": (i, [vp, vp, vp, vp]),
+        "orbm_search_by_projection_dev": (i, [vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, i, f, f, vp, vp]),
+        "orbm_search_by_projection_frame_dev": (i, [vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, i, f, i, i, vp, vp]),
+        "orbm_search_for_initialization_dev": (i, [vp, vp, vp, vp, vp, i, f, i, vp]),
         "orbm_device": (i, [vp]),
         "orbm_stream": (vp, [vp]),
         "orbm_last_launches": (i, [vp]),
@@ -349,6 +358,47 @@ class ORBextractor:
         return n.value
 
 
+class DeviceFrame:
+    """orbm_frame (include/orbx.h): undistorted keypoints, descriptors and the 64 x 48 feature grid of a Frame, resident on the device."""
+
+    def __init__(self, matcher, kps=None, desc=None, bounds=None, extractor=None, frame=0, K4=None, dist_coef=None):
+        self._L = lib()
+        self._m = matcher
+        h = C.c_void_p()
+        b = [float(v) for v in bounds]
+        if extractor is None:
+            kps = np.ascontiguousarray(kps, KP_DTYPE)
+            desc = _u8(desc).reshape(-1, 32)
+            _check(self._L.orbm_frame_create(matcher._h, _p(kps), _p(desc), len(kps), *b, C.byref(h)))
+        else:
+            K4 = K4 if K4 is not None else (1.0, 1.0, 0.0, 0.0)
+            dc = None if dist_coef is None else np.ascontiguousarray(dist_coef, np.float32)
+            _check(self._L.orbm_frame_from_extractor(matcher._h, extractor._h, int(frame), *[float(v) for v in K4],
+                                                     None if dc is None else _p(dc), 0 if dc is None else len(dc), *b, C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbm_frame_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __len__(self):
+        return self._L.orbm_frame_size(self._h)
+
+    def keypoints(self):
+        k = np.zeros(max(len(self), 1), KP_DTYPE)
+        _check(self._L.orbm_frame_keypoints(self._h, _p(k)))
+        return k[:len(self)]
+
+    def grid(self):
+        cs = np.zeros(64 * 48 + 1, np.int32)
+        en = np.zeros(max(len(self), 1), np.int32)
+        _check(self._L.orbm_frame_grid(self._m._h, self._h, _p(cs), _p(en)))
+        return cs, en[:len(self)]
+
+
 class ExtractorPool:
     """orbx_pool_* (include/orbx.h): one process, every GPU -- a batch of frames sharded over devices in chunks, results in frame order."""
 
@@ -532,6 +582,38 @@ class ORBmatcher:
                                                        _p(last_angle), _p(mp_desc), _p(mp_has_obs), len(last_octave), float(th), int(mode),
                                                        int(self.mbCheckOrientation), _p(fm), C.byref(nm)))
         return nm.value, fm[:len(kps)]
+
+    # ---- the same three searches with the frame side resident on the device (DeviceFrame)
+    def SearchForInitializationDev(self, F1, F2, vbPrevMatched, windowSize=10):
+        prev = np.ascontiguousarray(vbPrevMatched, np.float32).copy()
+        m12 = np.zeros(max(len(F1), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_for_initialization_dev(self._h, F1._h, F2._h, _p(prev), _p(m12), windowSize, self.mfNNratio,
+                                                          int(self.mbCheckOrientation), C.byref(nm)))
+        return nm.value, m12[:len(F1)], prev
+
+    def SearchByProjectionDev(self, F, u_right, occupied, scale_factors, proj_xy, proj_xr, level, view_cos, mp_desc, mp_has_obs, th=1.0):
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        mp_desc = _u8(mp_desc).reshape(-1, 32)
+        u_right, sf, proj_xy, proj_xr, view_cos = f32(u_right), f32(scale_factors), f32(proj_xy).reshape(-1, 2), f32(proj_xr), f32(view_cos)
+        occupied, mp_has_obs, level = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(level, np.int32)
+        fm = np.zeros(max(len(F), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_by_projection_dev(self._h, F._h, _p(u_right), _p(occupied), _p(sf), len(sf), _p(proj_xy), _p(proj_xr), _p(level),
+                                                     _p(view_cos), _p(mp_desc), _p(mp_has_obs), len(level), float(th), self.mfNNratio, _p(fm), C.byref(nm)))
+        return nm.value, fm[:len(F)]
+
+    def SearchByProjectionFrameDev(self, F, u_right, occupied, scale_factors, proj_xy, proj_ur, last_octave, last_angle, mp_desc, mp_has_obs, th, mode=0):
+        f32 = lambda a: np.ascontiguousarray(a, np.float32)
+        mp_desc = _u8(mp_desc).reshape(-1, 32)
+        u_right, sf, proj_xy, proj_ur, last_angle = f32(u_right), f32(scale_factors), f32(proj_xy).reshape(-1, 2), f32(proj_ur), f32(last_angle)
+        occupied, mp_has_obs, last_octave = _u8(occupied), _u8(mp_has_obs), np.ascontiguousarray(last_octave, np.int32)
+        fm = np.zeros(max(len(F), 1), np.int32)
+        nm = C.c_int(0)
+        _check(self._L.orbm_search_by_projection_frame_dev(self._h, F._h, _p(u_right), _p(occupied), _p(sf), len(sf), _p(proj_xy), _p(proj_ur),
+                                                           _p(last_octave), _p(last_angle), _p(mp_desc), _p(mp_has_obs), len(last_octave), float(th),
+                                                           int(mode), int(self.mbCheckOrientation), _p(fm), C.byref(nm)))
+        return nm.value, fm[:len(F)]
 
     def SearchByBoW(self, k1, d1, valid1, fv1, k2, d2, fv2, valid2=None):
         """ORBmatcher::SearchByBoW (src/ORBmatcher.cc:159-288 when valid2 is None: key frame -> frame; :522-655 otherwise:

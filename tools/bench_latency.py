@@ -34,3 +34,24 @@ for (w, h, nf) in [(640, 480, 1000), (752, 480, 1200), (1241, 376, 2000), (1920,
     print(json.dumps({"config": "%dx%d nf=%d, one frame per call" % (w, h, nf), "gpu_ms_median": float(np.median(ts)) * 1e3,
                       "gpu_ms_p99": float(np.percentile(ts, 99)) * 1e3, "cpu_1_thread_ms_median": float(np.median(tc)) * 1e3,
                       "launches": ex.last_launches(), "keypoints": int(len(k))}), flush=True)
+
+# ---- the C++ classes themselves (include/ORBextractor.h, include/ORBmatcher.h), used the way the reference uses them: tools/latency_cpp.cpp
+import subprocess, tempfile
+tmp = tempfile.mkdtemp()
+exe = os.path.join(tmp, "latency_cpp")
+libdir = os.path.dirname(orbx.LIB_PATH)
+subprocess.check_call(["g++", "-std=c++11", "-O2", "-I", os.path.join(ROOT, "include"), "-o", exe, os.path.join(ROOT, "tools", "latency_cpp.cpp"),
+                       "-L", libdir, "-lorbx", "-Wl,-rpath," + libdir])
+for (w, h, nf) in [(640, 480, 1000), (640, 480, 2000)]:
+    a = synth.rects(w, h, 1000)
+    rng = np.random.default_rng(1000)
+    b = np.clip(np.roll(a, 3, axis=1).astype(np.int16) + rng.integers(-3, 4, a.shape), 0, 255).astype(np.uint8)
+    open(os.path.join(tmp, "a.raw"), "wb").write(a.tobytes())
+    open(os.path.join(tmp, "b.raw"), "wb").write(b.tobytes())
+    out = subprocess.run([exe, os.path.join(tmp, "a.raw"), os.path.join(tmp, "b.raw"), str(w), str(h), str(nf)], capture_output=True, text=True)
+    if out.returncode != 0:
+        raise SystemExit("latency_cpp failed: " + out.stderr[-2000:])
+    for ln in out.stdout.splitlines():
+        d = json.loads(ln)
+        d["config"] = "C++ classes, %dx%d nf=%d" % (w, h, nf)
+        print(json.dumps(d), flush=True)

@@ -50,6 +50,11 @@ def tracking_searches():
     tc, (on, om12, _) = timed(lambda: O.search_for_initialization(k1, d1, k2, d2, bounds, prev, 100, 0.9, True), 5)
     assert n == on and np.array_equal(m12, om12)
     line("SearchForInitialization", "calls/s", 1, tg, tc, features=(len(k1), len(k2)), matches=int(n))
+    # the same with both frames resident on the device (orbm_frame; built once per frame, here from host arrays)
+    tb, (F1, F2) = timed(lambda: (orbx.DeviceFrame(mi, k1, d1, bounds), orbx.DeviceFrame(mi, k2, d2, bounds)), 20)
+    tg, (n, m12, _) = timed(lambda: mi.SearchForInitializationDev(F1, F2, prev, 100), 50)
+    assert n == on and np.array_equal(m12, om12)
+    line("SearchForInitialization, device frames", "calls/s", 1, tg, tc, features=(len(k1), len(k2)), matches=int(n), frame_build_ms=tb * 1e3 / 2)
 
     s = scenes.projection_scene(1000)
     a = (s["kps"], s["desc"], s["u_right"], s["occupied"], scenes.BOUNDS, scenes.SF, s["proj_xy"], s["proj_xr"], s["level"])
@@ -58,11 +63,21 @@ def tracking_searches():
     tc, (on, ofm) = timed(lambda: O.search_by_projection(*a, s["view_cos"], s["mp_desc"], s["mp_has_obs"], 3.0, 0.8), 10)
     assert n == on and np.array_equal(fm, ofm)
     line("SearchByProjection(Frame, MapPoints)", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n))
+    tb, F = timed(lambda: orbx.DeviceFrame(mp, s["kps"], s["desc"], scenes.BOUNDS), 20)
+    tg, (n, fm) = timed(lambda: mp.SearchByProjectionDev(F, s["u_right"], s["occupied"], scenes.SF, s["proj_xy"], s["proj_xr"], s["level"], s["view_cos"],
+                                                         s["mp_desc"], s["mp_has_obs"], 3.0), 100)
+    assert n == on and np.array_equal(fm, ofm)
+    line("SearchByProjection(Frame, MapPoints), device frame", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n),
+         frame_build_ms=tb * 1e3)
     mf = orbx.ORBmatcher(0.9, True)
     tg, (n, fm) = timed(lambda: mf.SearchByProjectionFrame(*a, s["angle"], s["mp_desc"], s["mp_has_obs"], 15.0, 0), 50)
     tc, (on, ofm) = timed(lambda: O.search_by_projection_frame(*a, s["angle"], s["mp_desc"], s["mp_has_obs"], 15.0, 0, True), 10)
     assert n == on and np.array_equal(fm, ofm)
     line("SearchByProjection(CurrentFrame, LastFrame)", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n))
+    tg, (n, fm) = timed(lambda: mf.SearchByProjectionFrameDev(F, s["u_right"], s["occupied"], scenes.SF, s["proj_xy"], s["proj_xr"], s["level"], s["angle"],
+                                                              s["mp_desc"], s["mp_has_obs"], 15.0, 0), 100)
+    assert n == on and np.array_equal(fm, ofm)
+    line("SearchByProjection(CurrentFrame, LastFrame), device frame", "calls/s", 1, tg, tc, points=len(s["level"]), features=len(s["kps"]), matches=int(n))
 
     b = scenes.bow_scene(2000)
     mb = orbx.ORBmatcher(0.7, True)
