@@ -34,6 +34,40 @@ struct FrameView {
     float minX, maxX, minY, maxY;
 };
 
+class ORBmatcher;
+
+// A Frame that lives on the device (orbm_frame, include/orbx.h): mvKeysUn, mDescriptors and the 64 x 48 grid of
+// Frame::AssignFeaturesToGrid (src/Frame.cc:230-245) built once per frame in HBM, so that the windowed searches of one Tracking step
+// (SearchByProjection x2, SearchForInitialization) move only the MapPoint side.  Build it once per frame, next to Frame's own grid.
+class DeviceFrame
+{
+public:
+    // from the host members of a Frame: keysUn = mvKeysUn, descriptors = mDescriptors, bounds = mnMinX, mnMaxX, mnMinY, mnMaxY
+    DeviceFrame(ORBmatcher& matcher, const std::vector<cv::KeyPoint>& keysUn, const cv::Mat& descriptors, float minX, float maxX, float minY, float maxY);
+    // straight from the device results of the extractor's last call (no descriptor round trip); Frame::UndistortKeyPoints
+    // (src/Frame.cc:419-449) runs on the device when distCoef (mDistCoef as floats) is given and distCoef[0] != 0
+    DeviceFrame(ORBmatcher& matcher, ORBextractor& extractor, const float K4[4], const std::vector<float>& distCoef, float minX, float maxX, float minY,
+                float maxY, int frame = 0);
+    ~DeviceFrame() { orbm_frame_destroy(f_); }
+    DeviceFrame(const DeviceFrame&) = delete;
+    DeviceFrame& operator=(const DeviceFrame&) = delete;
+    int size() const { return orbm_frame_size(f_); }
+    std::vector<cv::KeyPoint> keypoints() const            // mvKeysUn as the device holds it
+    {
+        std::vector<orbx_kp> k(size());
+        if (orbm_frame_keypoints(f_, k.data()) != ORBX_OK) throw std::runtime_error(std::string("orbm_frame_keypoints: ") + orbx_last_error());
+        std::vector<cv::KeyPoint> out(k.size());
+        for (size_t i = 0; i < k.size(); i++) {
+            out[i].pt.x = k[i].x; out[i].pt.y = k[i].y; out[i].size = k[i].size; out[i].angle = k[i].angle;
+            out[i].response = k[i].response; out[i].octave = k[i].octave; out[i].class_id = k[i].class_id;
+        }
+        return out;
+    }
+    orbm_frame* handle() const { return f_; }
+private:
+    orbm_frame* f_ = nullptr;
+};
+
 class ORBmatcher
 {
 public:
@@ -90,8 +124,25 @@ public:
     template <class FrameT> int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono);
     template <class KeyFrameT, class FrameT, class MapPointT> int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches);
     template <class KeyFrameT, class MapPointT> int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12);
-    template <class FrameT, class = typename std::enable_if<!std::is_same<typename std::remove_cv<FrameT>::type, FrameView>::value>::type>
+    template <class FrameT, class = typename std::enable_if<!std::is_same<typename std::remove_cv<FrameT>::type, FrameView>::value &&
+                                                            !std::is_same<typename std::remove_cv<FrameT>::type, DeviceFrame>::value>::type>
     int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
+
+    // ---- the same searches against a DeviceFrame (definitions after the class)
+    int SearchForInitialization(const DeviceFrame& F1, const DeviceFrame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                int windowSize = 10)
+    {
+        std::vector<float> prev(2 * vbPrevMatched.size());
+        for (size_t i = 0; i < vbPrevMatched.size(); i++) { prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+        vnMatches12.assign(F1.size(), -1);
+        int n = 0;
+        if (orbm_search_for_initialization_dev(m_, F1.handle(), F2.handle(), prev.data(), vnMatches12.data(), windowSize, mfNNratio, mbCheckOrientation,
+                                               &n) != ORBX_OK)
+            fail("orbm_search_for_initialization_dev");
+        for (size_t i = 0; i < vbPrevMatched.size(); i++) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }
+        return n;
+    }
+    orbx_matcher* handle() const { return m_; }
 
     // Best / second-best scan of SearchByBoW's inner loop (ORBmatcher.cc:205-230) over whole descriptor sets, with the
     // acceptance test bestDist1 <= TH_LOW && bestDist1 < mfNNratio * bestDist2.  Returns the number accepted;
@@ -169,6 +220,29 @@ public:
                                             P.viewCosOrAngle.data(), P.descriptors.data(), P.hasObservations.data(), (int)P.level.size(), th, mode,
                                             mbCheckOrientation, vnMatch.data(), &n) != ORBX_OK)
             fail("orbm_search_by_projection_frame");
+        return n;
+    }
+
+    int SearchByProjection(const DeviceFrame& F, const FrameState& S, const ProjectedPoints& P, std::vector<int>& vnMatch, const float th = 3)
+    {
+        vnMatch.assign(F.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection_dev(m_, F.handle(), S.uRight->data(), S.occupied->data(), S.scaleFactors->data(), (int)S.scaleFactors->size(),
+                                          P.xy.data(), P.xr.data(), P.level.data(), P.viewCosOrAngle.data(), P.descriptors.data(), P.hasObservations.data(),
+                                          (int)P.level.size(), th, mfNNratio, vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection_dev");
+        return n;
+    }
+    int SearchByProjection(const DeviceFrame& CurrentFrame, const FrameState& S, const ProjectedPoints& P, std::vector<int>& vnMatch, const float th,
+                           const int mode)
+    {
+        vnMatch.assign(CurrentFrame.size(), -1);
+        int n = 0;
+        if (orbm_search_by_projection_frame_dev(m_, CurrentFrame.handle(), S.uRight->data(), S.occupied->data(), S.scaleFactors->data(),
+                                                (int)S.scaleFactors->size(), P.xy.data(), P.xr.data(), P.level.data(), P.viewCosOrAngle.data(),
+                                                P.descriptors.data(), P.hasObservations.data(), (int)P.level.size(), th, mode, mbCheckOrientation,
+                                                vnMatch.data(), &n) != ORBX_OK)
+            fail("orbm_search_by_projection_frame_dev");
         return n;
     }
 
@@ -410,6 +484,26 @@ protected:
     bool mbCheckOrientation;
     orbx_matcher* m_;
 };
+
+inline DeviceFrame::DeviceFrame(ORBmatcher& matcher, const std::vector<cv::KeyPoint>& keysUn, const cv::Mat& descriptors, float minX, float maxX,
+                                float minY, float maxY)
+{
+    std::vector<orbx_kp> k(keysUn.size());
+    for (size_t i = 0; i < k.size(); i++) {
+        k[i].x = keysUn[i].pt.x; k[i].y = keysUn[i].pt.y; k[i].size = keysUn[i].size; k[i].angle = keysUn[i].angle;
+        k[i].response = keysUn[i].response; k[i].octave = keysUn[i].octave; k[i].class_id = keysUn[i].class_id;
+    }
+    if (orbm_frame_create(matcher.handle(), k.data(), k.empty() ? nullptr : descriptors.ptr<uint8_t>(0), (int)k.size(), minX, maxX, minY, maxY, &f_) != ORBX_OK)
+        throw std::runtime_error(std::string("orbm_frame_create: ") + orbx_last_error());
+}
+
+inline DeviceFrame::DeviceFrame(ORBmatcher& matcher, ORBextractor& extractor, const float K4[4], const std::vector<float>& distCoef, float minX,
+                                float maxX, float minY, float maxY, int frame)
+{
+    if (orbm_frame_from_extractor(matcher.handle(), extractor.handle(), frame, K4[0], K4[1], K4[2], K4[3], distCoef.empty() ? nullptr : distCoef.data(),
+                                  (int)distCoef.size(), minX, maxX, minY, maxY, &f_) != ORBX_OK)
+        throw std::runtime_error(std::string("orbm_frame_from_extractor: ") + orbx_last_error());
+}
 
 }  // namespace ORB_SLAM2
 

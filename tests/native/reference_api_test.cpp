@@ -206,6 +206,24 @@ static int run(int, char** argv)
         CHECK(n2 == nmatches && ini2 == mvIniMatches, "SearchForInitialization: matches");
         for (size_t i = 0; i < prev2.size(); i++) CHECK(prev2[i].x == mvbPrevMatched[i].x && prev2[i].y == mvbPrevMatched[i].y, "SearchForInitialization: vbPrevMatched");
     }
+    // ---- the same searches against frames resident on the device (DeviceFrame): equal to the host-array path
+    {
+        ORBmatcher matcher(0.9, true);
+        const float K4[4] = {mLastFrame.fx, mLastFrame.fy, mLastFrame.cx, mLastFrame.cy};
+        DeviceFrame dLast(matcher, mLastFrame.mvKeysUn, mLastFrame.mDescriptors, 0.f, (float)w, 0.f, (float)h);
+        DeviceFrame dCur(matcher, ex, K4, std::vector<float>(), 0.f, (float)w, 0.f, (float)h);      // `ex` extracted the current frame last
+        CHECK(dCur.size() == mCurrentFrame.N, "DeviceFrame from the extractor: size");
+        std::vector<cv::KeyPoint> back = dCur.keypoints();
+        for (int i = 0; i < mCurrentFrame.N; i++) CHECK(back[i].pt.x == mCurrentFrame.mvKeysUn[i].pt.x && back[i].octave == mCurrentFrame.mvKeysUn[i].octave, "DeviceFrame keypoints");
+        std::vector<cv::Point2f> p1(mLastFrame.mvKeysUn.size()), p2;
+        for (size_t i = 0; i < p1.size(); i++) p1[i] = mLastFrame.mvKeysUn[i].pt;
+        p2 = p1;
+        std::vector<int> a, b;
+        FrameView V1 = {&mLastFrame.mvKeysUn, &mLastFrame.mDescriptors, 0.f, (float)w, 0.f, (float)h};
+        FrameView V2 = {&mCurrentFrame.mvKeysUn, &mCurrentFrame.mDescriptors, 0.f, (float)w, 0.f, (float)h};
+        const int n1 = matcher.SearchForInitialization(V1, V2, p1, a, 100), n2 = matcher.SearchForInitialization(dLast, dCur, p2, b, 100);
+        CHECK(n1 == n2 && a == b, "SearchForInitialization(DeviceFrame) equals the FrameView search");
+    }
     CHECK(nA > 50 && nB[0] > 50 && nB[2] > 50 && nC > 20 && nD > 20 && nE > 20, "every search finds matches on the synthetic pair");
     // static DescriptorDistance (MapPoint.cc:286-296 calls it N^2 times): host popcount, equal to the device pairs
     {
