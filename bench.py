@@ -352,13 +352,17 @@ def pin_to_gpu_numa_node(local):
 
 
 def parity_gate(cfg, hostL, hostR, resL, resR, stereo_out, frames):
+    frames = min(frames, len(resL))
     """Before any number is taken: this rank's first `frames` units must equal the reference build byte for byte (keypoints,
     descriptors; stereo: uRight / depth of the first two pairs).  The CUDA path runs with fma_mode 1 = the reference's own flags."""
     import numpy as np
     _, kind = _checker()
     exL = _cpu_extractor(cfg, 1)            # monotone node allocator: the definition the quadtree kernel is held to
     exR = _cpu_extractor(cfg, 1) if cfg["stereo"] else None
-    for b in range(frames):
+    B = len(resL)
+    # half of the checked units from the start of the batch, half from its end (a large batch runs as two halves on two streams)
+    picks = list(range((frames + 1) // 2)) + list(range(B - frames // 2, B))
+    for b in picks:
         if cfg["stereo"] and b < 2:
             kl, dl, kr, dr, n, uR, dep = cpu_unit(cfg, exL, exR, hostL[b], hostR[b])
             nm, guR, gdep = stereo_out

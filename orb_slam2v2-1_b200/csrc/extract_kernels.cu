@@ -471,7 +471,7 @@ __global__ void __launch_bounds__(FAST_WARPS * 32, FAST_MINB) k_fast_cells(const
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t bars[FAST_WARPS];
-    fast_cell_body<TP, TMA>(P, F, smemPerWarp, blockIdx.y, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem, M, bars);
+    fast_cell_body<TP, TMA>(P, F, smemPerWarp, blockIdx.y + F.frame0, blockIdx.x * FAST_WARPS + (threadIdx.x >> 5), smem, M, bars);
 }
 
 template <int TP, bool TMA>
@@ -576,7 +576,7 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
     __shared__ int wsum[33];
     __shared__ int s_k, s_nexp, s_m;
     constexpr int T = CFG::THREADS;
-    const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int l = blockIdx.x, f = blockIdx.y + F.frame0, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const LevelGeom& G = P.lv[l];
 
     short4* rA = reinterpret_cast<short4*>(smraw);
@@ -1007,7 +1007,7 @@ __device__ __forceinline__ void blur_tile_body(const Plan& P, const FrameBufs& F
 
 __global__ void __launch_bounds__(BLUR_WARPS * 32, BLUR_MINB) k_blur(const Plan P, const FrameBufs F)
 {
-    blur_tile_body(P, F, blockIdx.y, blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5));
+    blur_tile_body(P, F, blockIdx.y + F.frame0, blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5));
 }
 
 void launch_blur(cudaStream_t s, const Plan& P, const FrameBufs& F, int B)
@@ -1065,7 +1065,7 @@ template <bool TMA>
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan P, const FrameBufs F, const uint2* __restrict__ icTab,
                                                                     const float4* __restrict__ patT, const __grid_constant__ OrientMaps M)
 {
-    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int f = blockIdx.y + F.frame0, lane = threadIdx.x & 31;
     const int g = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);      // keypoint index inside the frame
     // levels are concatenated in ascending order (:1103): lane i holds the count of level i, a warp scan finds the level
     const int myc = lane < P.nlevels ? F.levelCount[(size_t)f * MAX_LEVELS + lane] : 0;

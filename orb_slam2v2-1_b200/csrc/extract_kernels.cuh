@@ -21,6 +21,7 @@ struct FrameBufs {
     uint8_t* desc;                 // B x totalNodes x 32
     int* counts;                   // B
     const uint4* cellTab;          // 2 x totalCells (per shape, shared by all frames): FAST cell geometry, see fast_cell_record
+    int frame0;                    // first frame of this launch: a large batch runs as two halves on two streams (orbx_extractor.cu)
 };
 
 struct UMaxTable { int v[16]; };

@@ -397,46 +397,67 @@ static cudaError_t mirror_pyramid(orbx_extractor* ex, cudaStream_t s)
     return e;
 }
 
-// The 11 kernel launches of one call, in stream order.
-static int launch_all(orbx_extractor* ex, int B, bool prof)
+// The kernel launches of one call.  Up to GRAPH_MAX_BATCH frames: 11 launches, the blur on the second stream beside FAST + quadtree.
+// From SPLIT_MIN_PIXELS on: the batch runs as two halves, one per stream, so that the tail of every kernel of one half (SMs
+// draining) is filled by the other half's kernels (measured: 262 k -> 273 k frames/s at 512 VGA frames); 22 launches.
+constexpr size_t SPLIT_MIN_PIXELS = (size_t)128 * 640 * 480;      // level-0 pixels of a call from which the split pays (and at least 16 frames)
+
+static int launch_chain(orbx_extractor* ex, cudaStream_t s, int f0, int nb, bool prof, bool forkBlur)
 {
     const Plan& P = ex->plan;
-    const FrameBufs& F = ex->bufs;
-    cudaStream_t s = ex->stream;
-    int launches = 0;
+    FrameBufs F = ex->bufs;
+    F.frame0 = f0;
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     for (int l = 1; l < ex->nlevels; l++) {
         const uint8_t* src = l == 1 ? F.lv0 : F.pyr + P.lv[l - 1].planeOff;
         const int spitch = l == 1 ? (int)F.lv0Pitch : P.lv[l - 1].pitch;
         const size_t sframe = l == 1 ? (size_t)F.lv0Frame : (size_t)P.pyrSlab;
-        launch_resize(s, src, spitch, sframe, F.pyr + P.lv[l].planeOff, P.lv[l].w, P.lv[l].h, P.lv[l].pitch, P.pyrSlab,
-                      ex->d_xtab + ex->xtabOff[l], ex->d_ytab + ex->ytabOff[l], B, P.lv[l - 1].h);
-        launches++;
+        launch_resize(s, src + (size_t)f0 * sframe, spitch, sframe, F.pyr + P.lv[l].planeOff + (size_t)f0 * P.pyrSlab, P.lv[l].w, P.lv[l].h, P.lv[l].pitch,
+                      P.pyrSlab, ex->d_xtab + ex->xtabOff[l], ex->d_ytab + ex->ytabOff[l], nb, P.lv[l - 1].h);
     }
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     // a few frames leave most of the GPU idle: the blur (which needs the pyramid only) runs on a second stream beside
     // FAST + quadtree and joins before the descriptors; inside a captured graph this becomes a fork / join of nodes
-    const bool fork = !prof && B <= GRAPH_MAX_BATCH && ex->stream2 != nullptr;
-    if (fork) {
+    if (forkBlur) {
         ORBX_CUDA(cudaEventRecord(ex->evFork, s));
         ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->evFork, 0));
-        launch_blur(ex->stream2, P, F, B);
+        launch_blur(ex->stream2, P, F, nb);
         if (ex->mirror) ORBX_CUDA(mirror_pyramid(ex, ex->stream2));      // the copy engine works while FAST + quadtree run
         ORBX_CUDA(cudaEventRecord(ex->evJoin, ex->stream2));
     }
-    launch_fast_cells(s, P, F, B, ex->fastSmem, ex->tmaLv0 ? &ex->mapsFast : nullptr);
+    launch_fast_cells(s, P, F, nb, ex->fastSmem, ex->tmaLv0 ? &ex->mapsFast : nullptr);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
-    ORBX_CUDA(launch_octree(s, P, F, B, ex->capS, ex->sortCap, ex->octForm));
+    ORBX_CUDA(launch_octree(s, P, F, nb, ex->capS, ex->sortCap, ex->octForm));
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
-    if (fork) ORBX_CUDA(cudaStreamWaitEvent(s, ex->evJoin, 0));
-    else launch_blur(s, P, F, B);
+    if (forkBlur) ORBX_CUDA(cudaStreamWaitEvent(s, ex->evJoin, 0));
+    else launch_blur(s, P, F, nb);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
-    launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, B, ex->tmaLv0 ? &ex->mapsImg : nullptr, ex->tmaLv0 ? &ex->mapsBlur : nullptr);
+    launch_orient_describe(s, P, F, ex->d_icTab, ex->d_patT, nb, ex->tmaLv0 ? &ex->mapsImg : nullptr, ex->tmaLv0 ? &ex->mapsBlur : nullptr);
     if (prof) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
-    if (ex->mirror && !fork) ORBX_CUDA(mirror_pyramid(ex, s));
-    launches += 4;
-    ex->lastLaunches = launches;
+    if (ex->mirror && !forkBlur && f0 == 0) ORBX_CUDA(mirror_pyramid(ex, s));
     return ORBX_OK;
+}
+
+static int launch_all(orbx_extractor* ex, int B, bool prof)
+{
+    static const bool splitEnv = !(getenv("ORBX_SPLIT") && atoi(getenv("ORBX_SPLIT")) == 0);
+    cudaStream_t s = ex->stream;
+    const int perChain = (ex->nlevels - 1) + 4;
+    if (!prof && splitEnv && B >= 16 && (size_t)B * ex->W * ex->H >= SPLIT_MIN_PIXELS && ex->stream2 != nullptr) {
+        const int h1 = B / 2;
+        ORBX_CUDA(cudaEventRecord(ex->evFork, s));
+        ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->evFork, 0));
+        int rc = launch_chain(ex, s, 0, h1, false, false);
+        if (!rc) rc = launch_chain(ex, ex->stream2, h1, B - h1, false, false);
+        if (rc) return rc;
+        ORBX_CUDA(cudaEventRecord(ex->evJoin, ex->stream2));
+        ORBX_CUDA(cudaStreamWaitEvent(s, ex->evJoin, 0));
+        ex->lastLaunches = 2 * perChain;
+        return ORBX_OK;
+    }
+    const int rc = launch_chain(ex, s, 0, B, prof, !prof && B <= GRAPH_MAX_BATCH && ex->stream2 != nullptr);
+    ex->lastLaunches = perChain;
+    return rc;
 }
 
 // The whole extraction of B frames on the handle's stream: ComputePyramid -> cell FAST -> DistributeOctTree ->

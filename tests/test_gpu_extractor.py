@@ -216,3 +216,21 @@ def test_batch_call_on_page_locked_arrays_from_the_library():
         assert n[b] == len(ok) and kps[b, :n[b]].tobytes() == ok.tobytes() and np.array_equal(de.array[b, :n[b]], od)
     for a in (fin, kp, de):
         a.free()
+
+
+def test_large_batch_runs_as_two_halves_on_two_streams():
+    """From 128 VGA frames' worth of pixels on, a call is split over the handle's two streams (orbx_extractor.cu, launch_all): every
+    frame of both halves, odd batch size included, must still equal the oracle."""
+    distinct = [synth.rects(640, 480, 60 + i) for i in range(5)]
+    oe = O.OracleExtractor(500, 1.2, 8, 20, 7)
+    want = [oe(f) for f in distinct]
+    ex = orbx.ORBextractor(500, 1.2, 8, 20, 7, max_batch=131)
+    for B in (131, 128):
+        got = ex.extract_batch([distinct[i % 5] for i in range(B)])
+        assert ex.last_launches() == 22
+        for i, (k, d) in enumerate(got):
+            assert k.tobytes() == want[i % 5][0].tobytes() and np.array_equal(d, want[i % 5][1]), (B, i)
+    got = ex.extract_batch(distinct)            # a small batch afterwards on the same handle: one chain again
+    assert ex.last_launches() == 11
+    for i, (k, d) in enumerate(got):
+        assert k.tobytes() == want[i][0].tobytes() and np.array_equal(d, want[i][1])
