@@ -4,8 +4,19 @@
                                                  and gpurun_out/TAG_launches_b512.csv (ncu launch list of bench.py --steps 2)
   -> profiles/TAG_ncu_full_summary.txt, profiles/TAG_traffic.json (DRAM bytes and warp instructions per frame and kernel),
      profiles/TAG_launches_b512.csv"""
-import collections, csv, io, json, os, re, subprocess, sys
+import collections, csv, hashlib, io, json, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def kernel_source_sha16():
+    """The stamp bench.py compares (same files, same order): counters are only quoted for the kernel sources they were taken on."""
+    h = hashlib.sha256()
+    for f in ("extract_kernels.cu", "extract_kernels.cuh", "orbx_extractor.cu"):
+        h.update(open(os.path.join(ROOT, "orb_slam2v2-1_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+
 tag, note = sys.argv[1], sys.argv[2]
 rep = os.path.join(ROOT, "gpurun_out", tag + "_full.ncu-rep")
 table = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_table.py"), rep], capture_output=True, text=True).stdout
@@ -24,6 +35,7 @@ for row in r[2:]:
     acc[k] += float(row[ri].replace(",", "")) * mul[r[1][ri]] + float(row[wi].replace(",", "")) * mul[r[1][wi]]
     inst[k] += float(row[ii].replace(",", ""))
 json.dump({"source": "profiles/%s_ncu_full_summary.txt (ncu --set full --clock-control none, tools/profile_once.py 512)" % tag,
+           "kernel_source_sha16": kernel_source_sha16(), "config": 0,
            "frames_per_launch": 512, "shape": "640x480 nf=1000",
            "dram_bytes_per_frame": {k: int(round(v / 512)) for k, v in acc.items()},
            "warp_instructions_per_frame": {k: int(round(v / 512)) for k, v in inst.items()}},
@@ -33,7 +45,7 @@ hdr = [i for i, x in enumerate(rows) if x and x[0] == "ID"][0]
 h = rows[hdr]
 ki, vi, gi, bi = h.index("Kernel Name"), h.index("Metric Value"), h.index("Grid Size"), h.index("Block Size")
 out = ["# ncu --metrics gpu__time_duration.sum --clock-control none -c 400: python bench.py --steps 2 --warmup 1 --no-cpu "
-       "(512 frames per launch; per-launch times are cold-cache and serialised)", "id,kernel,grid,block,ns"]
+       "(512 frames per step as two halves of 256 on two streams; per-launch times are cold-cache and serialised)", "id,kernel,grid,block,ns"]
 share = collections.defaultdict(float)
 for n, x in enumerate(rows[hdr + 1:]):
     if len(x) <= vi:
@@ -41,8 +53,7 @@ for n, x in enumerate(rows[hdr + 1:]):
     name = re.sub(r"^void ", "", x[ki]).split("(")[0].replace("orbx::", "")
     ns = int(float(x[vi].replace(",", "")))
     out.append("%d,%s,(%s),(%s),%d" % (n, name, x[gi].strip("()").replace(", ", "x"), x[bi].strip("()").replace(", ", "x"), ns))
-    if "512" in x[gi]:
-        share[name.split("<")[0]] += ns
+    share[name.split("<")[0]] += ns
 open(os.path.join(ROOT, "profiles", tag + "_launches_b512.csv"), "w").write("\n".join(out) + "\n")
 tot = sum(v for k, v in share.items() if k in names)
 print(table)

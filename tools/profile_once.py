@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """One warm-up extraction plus one profiled extraction of B synthetic 640x480 frames (for ncu):
-ncu --set full --import-source on --clock-control none --launch-skip 11 --launch-count 11 -o gpurun_out/x python tools/profile_once.py [B]"""
+ncu --set full --import-source on --clock-control none --launch-skip 22 --launch-count 22 -o gpurun_out/x python tools/profile_once.py [B]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "orb_slam2v2-1_b200"))
