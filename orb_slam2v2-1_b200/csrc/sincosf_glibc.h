@@ -5,8 +5,8 @@
 // bit-exact descriptor needs the same algorithm, not CUDA's cosf/sinf: glibc's is the ARM optimized-routines
 // design -- argument reduction and a degree-7/8 polynomial, all in double, rounded once to float.  The
 // coefficient table below was read out of this image's libm.so.6 (__sincosf_table); every double operation is
-// individually rounded (no FMA).  tests/test_sincosf.py checks this header, compiled for the host, against the
-// running glibc over all 1 086 953 882 floats in [0, 6.3]: 0 mismatches for both functions.
+// individually rounded (no FMA).  tests/native/sincosf_check.cpp (run by tests/test_abi.py::
+// test_sincosf_restatement_matches_glibc) checks this header, compiled for the host, against the running glibc over all 1 086 953 882 floats in [0, 6.3]: 0 mismatches for both functions.
 //
 // ORBX_HD functions: usable from device code (with __dmul_rn/__dadd_rn so nvcc cannot contract) and from
 // host code (compile with -ffp-contract=off).
