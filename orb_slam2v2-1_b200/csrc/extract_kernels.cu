@@ -164,10 +164,10 @@ constexpr int FAST_WARPS = FAST_WARPS_N;
 
 // raw = max over the 16 arcs of 9 contiguous ring pixels of min(ring - centre) resp. min(centre - ring)
 // (OpenCV cornerScore<16>; corner iff raw > threshold, response = raw - 1).  min/max commute with the subtraction of the
-// centre, so the arcs are evaluated on the raw ring values.  E[j] = (ring[j], ring[j+8]) as s16x2 for j = 0..15 (indices
-// mod 16; built with IMADs, i.e. on the FMA pipe): the arc starting at k is the low half of min(E[k..k+8]) and the arc
-// starting at k+8 its high half.  Nine-element minima from shared triples T[j] = min3(E[j..j+2]) and
-// W[k] = min3(T[k], T[k+3], T[k+6]), all 3-input VIMNMX3.
+// centre, so the arcs are evaluated on the raw ring values, and max over an arc = 255 - min over the arc of (255 - ring), so ONE
+// max-of-min network serves both polarities: E[j] = (ring[j], 255 - ring[j]) as s16x2 (one IMAD per ring pixel, i.e. on the FMA
+// pipe), nine-element minima from shared triples T[j] = min3(E[j..j+2]) and W[k] = min3(T[k], T[k+3], T[k+6]) (indices mod 16),
+// then the maximum of the 16 W -- 40 three-input VIMNMX3 per pixel (the kernel binds on the ALU pipe, where they run).
 __device__ __forceinline__ unsigned vmin3s2(unsigned a, unsigned b, unsigned c) { return __vmins2(__vmins2(a, b), c); }
 __device__ __forceinline__ unsigned vmax3s2(unsigned a, unsigned b, unsigned c) { return __vmaxs2(__vmaxs2(a, b), c); }
 
@@ -182,18 +182,17 @@ __device__ __forceinline__ int fast_raw_score(const uint8_t* c)
     r[12] = c[-3]; r[13] = c[pitch - 3]; r[14] = c[2 * pitch - 2]; r[15] = c[3 * pitch - 1];
     unsigned E[16];
 #pragma unroll
-    for (int j = 0; j < 16; j++) E[j] = r[(j + 8) & 15] * 65536u + r[j];
-    unsigned Tn[14], Tx[14];
+    for (int j = 0; j < 16; j++) E[j] = r[j] * 0xFFFF0001u + 0x00FF0000u;          // r + ((255 - r) << 16): no borrow, r <= 255
+    unsigned T[16], W[16];
 #pragma unroll
-    for (int j = 0; j < 14; j++) { Tn[j] = vmin3s2(E[j], E[j + 1], E[j + 2]); Tx[j] = vmax3s2(E[j], E[j + 1], E[j + 2]); }
-    unsigned Wn[8], Wx[8];
+    for (int j = 0; j < 16; j++) T[j] = vmin3s2(E[j], E[(j + 1) & 15], E[(j + 2) & 15]);
 #pragma unroll
-    for (int k = 0; k < 8; k++) { Wn[k] = vmin3s2(Tn[k], Tn[k + 3], Tn[k + 6]); Wx[k] = vmax3s2(Tx[k], Tx[k + 3], Tx[k + 6]); }
-    // bright: max over arcs of the arc minimum; dark: min over arcs of the arc maximum
-    const unsigned bright = vmax3s2(vmax3s2(Wn[0], Wn[1], Wn[2]), vmax3s2(Wn[3], Wn[4], Wn[5]), __vmaxs2(Wn[6], Wn[7]));
-    const unsigned dark = vmin3s2(vmin3s2(Wx[0], Wx[1], Wx[2]), vmin3s2(Wx[3], Wx[4], Wx[5]), __vmins2(Wx[6], Wx[7]));
-    const int b = max((int)(bright & 0xFFFF), (int)(bright >> 16)) - v;
-    const int d = v - min((int)(dark & 0xFFFF), (int)(dark >> 16));
+    for (int k = 0; k < 16; k++) W[k] = vmin3s2(T[k], T[(k + 3) & 15], T[(k + 6) & 15]);
+    const unsigned m = vmax3s2(vmax3s2(vmax3s2(W[0], W[1], W[2]), vmax3s2(W[3], W[4], W[5]), vmax3s2(W[6], W[7], W[8])),
+                               vmax3s2(vmax3s2(W[9], W[10], W[11]), vmax3s2(W[12], W[13], W[14]), W[15]), W[15]);
+    // low half: max over arcs of the arc minimum (bright); high half: 255 - (min over arcs of the arc maximum) (dark)
+    const int b = (int)(m & 0xFFFF) - v;
+    const int d = v - 255 + (int)(m >> 16);
     return max(b, d);
 }
 
