@@ -209,7 +209,7 @@ size_t fast_smem_bytes(const Plan& P)
 {
     int m = 0;
     for (int l = 0; l < P.nlevels; l++) m = max(m, fast_warp_smem(P.lv[l].wCell, P.lv[l].hCell, P.fastPitch));
-    return (size_t)m * FAST_WARPS;
+    return (size_t)((m + 127) & ~127) * FAST_WARPS;        // every warp's tile starts on a 128-byte boundary (TMA destination)
 }
 
 // Cell table (two uint4 per cell, per image shape; built by fast_cell_record on the host):
