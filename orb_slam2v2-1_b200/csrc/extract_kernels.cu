@@ -506,15 +506,19 @@ struct OctSmall { static constexpr int THREADS = 128, MINB = 10, KEYS = 1536; };
 struct OctLarge { static constexpr int THREADS = 256, MINB = 4, KEYS = 4096; };
 struct OctHuge { static constexpr int THREADS = 512, MINB = 2, KEYS = 4096; };
 
-// in-place exclusive scan of a[0..n) by the whole CTA; returns the total.  wsum: 33 ints of shared memory.
-template <int T>                       // compile-time: the per-thread chunk is a shift, not an integer division
-__device__ int block_exclusive_scan(int* a, int n, int* wsum)
+// Exclusive scan of val(0..n) by the whole CTA: out[i] = sum of val(j), j < i; returns the total.  A thread owns a run of
+// consecutive elements; every warp scans the warp totals itself, so there are two barriers: one inside and one at the end
+// (which publishes out[] and frees wsum for the next scan).  val is evaluated twice per element and must not read out[].
+// wsum: T / 32 ints of shared memory.
+template <int T, class V>                       // T compile-time: the per-thread run is a shift, not an integer division
+__device__ int block_exclusive_scan(int n, int* out, int* wsum, V val)
 {
+    constexpr int NW = T >> 5;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + T - 1) / T;
     const int b = min(tid * per, n), e = min(b + per, n);
     int s = 0;
-    for (int i = b; i < e; i++) s += a[i];
+    for (int i = b; i < e; i++) s += val(i);
     int inc = s;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -523,21 +527,16 @@ __device__ int block_exclusive_scan(int* a, int n, int* wsum)
     }
     if (lane == 31) wsum[wid] = inc;
     __syncthreads();
-    if (wid == 0) {
-        const int v = lane < (T >> 5) ? wsum[lane] : 0;
-        int vi = v;
+    const int v = lane < NW ? wsum[lane] : 0;
+    int vi = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
-            if (lane >= o) vi += t;
-        }
-        wsum[lane] = vi - v;
-        if (lane == 31) wsum[32] = vi;
+    for (int o = 1; o < NW; o <<= 1) {
+        const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
+        if (lane >= o) vi += t;
     }
-    __syncthreads();
-    int off = wsum[wid] + inc - s;
-    for (int i = b; i < e; i++) { const int t = a[i]; a[i] = off; off += t; }
-    const int total = wsum[32];
+    const int total = __shfl_sync(0xFFFFFFFFu, vi, NW - 1);
+    int off = __shfl_sync(0xFFFFFFFFu, vi - v, wid) + inc - s;
+    for (int i = b; i < e; i++) { const int t = val(i); out[i] = off; off += t; }
     __syncthreads();
     return total;
 }
@@ -552,14 +551,19 @@ static bool octree_large(const Plan& P, int B, int capS)
     return capS > thr || (long long)B * P.nlevels < 1000;
 }
 
+// bytes of the per-node arrays of k_octree (the candidate arrays follow them)
+__host__ __device__ inline size_t octree_node_bytes(int capS, int sortCap)
+{
+    return ((size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 2 + 8) + (size_t)sortCap * 4 + 15) & ~(size_t)15;
+}
+
 // shared memory of the larger form (the limit check at plan time); launch_octree sizes the launch itself
 size_t octree_smem_bytes(int capS, int sortCap, int keysCap)
 {
     const int OCT_KEYS_SMEM = keysCap > 0 ? keysCap : OctLarge::KEYS;
-    // rectA, rectB (short4) | cntA, cntB | cc[4] | chBeg | tmp | skey[sortCap] | rankOf, mapS (u16) | childPos[4] (u16)
+    // rectA, rectB (short4) | cntA, cntB | cc[4] | chBeg | tmp | skey[sortCap] | rankOf[2], mapS (u16) | childPos[4] (u16)
     // ... | keys (u32) and node positions (u16) of up to OCT_KEYS_SMEM candidates
-    const size_t nodes = ((size_t)capS * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 2 + 2 + 8) + (size_t)sortCap * 4 + 15) & ~(size_t)15;
-    return nodes + (size_t)OCT_KEYS_SMEM * 6 + 64;
+    return octree_node_bytes(capS, sortCap) + (size_t)OCT_KEYS_SMEM * 6 + 64;
 }
 
 // DistributeOctTree.  The reference keeps nodes in a std::list built with push_front; a pass over the list splits
@@ -572,8 +576,8 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
 {
     constexpr int OCT_KEYS_SMEM = CFG::KEYS;
     extern __shared__ __align__(16) uint8_t smraw[];
-    __shared__ int wsum[33];
-    __shared__ int s_k, s_nexp, s_m;
+    __shared__ int wsum[32];
+    __shared__ int s_k[2], s_nexp[2], s_m;      // [pass parity]: a pass never resets what a slower warp of the previous pass still reads
     constexpr int T = CFG::THREADS;
     const int l = blockIdx.x, f = blockIdx.y + F.frame0, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const LevelGeom& G = P.lv[l];
@@ -586,8 +590,8 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
     int* chBeg = cc + 4 * capS;            // creation index of a rank's first child
     int* tmp = chBeg + capS;
     uint32_t* skey = reinterpret_cast<uint32_t*>(tmp + capS);   // processing order (positions) / sort keys
-    uint16_t* rankOf = reinterpret_cast<uint16_t*>(skey + sortCap);
-    uint16_t* mapS = rankOf + capS;
+    uint16_t* rankOf2 = reinterpret_cast<uint16_t*>(skey + sortCap);      // processing rank of a list position, per pass parity
+    uint16_t* mapS = rankOf2 + 2 * capS;
     uint16_t* childPos = mapS + capS;
 
     const int ncell = G.nCols * G.nRows;
@@ -595,7 +599,7 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
     const uint32_t* slots = F.slots + (size_t)f * P.slotSlab + G.slotOff;
     uint32_t* keys = F.keys + (size_t)f * P.keySlab + G.keyOff;
     uint16_t* knode = F.knode + (size_t)f * P.keySlab + G.keyOff;
-    uint32_t* keysS = reinterpret_cast<uint32_t*>(smraw + ((((size_t)capS * 56 + (size_t)sortCap * 4) + 15) & ~(size_t)15));
+    uint32_t* keysS = reinterpret_cast<uint32_t*>(smraw + octree_node_bytes(capS, sortCap));
     uint16_t* knodeS = reinterpret_cast<uint16_t*>(keysS + OCT_KEYS_SMEM);
     uint32_t* outKeys = F.levelKeys + (size_t)f * P.totalNodes + G.nodeBase;
     int* outCount = F.levelCount + (size_t)f * MAX_LEVELS + l;
@@ -619,21 +623,19 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
     }
     if (lane == 31) wsum[wid] = inc;
     __syncthreads();
-    if (wid == 0) {
-        const int v = lane < (T >> 5) ? wsum[lane] : 0;
+    int n, at;
+    {   // every warp scans the warp totals itself
+        constexpr int NW = T >> 5;
+        const int v = lane < NW ? wsum[lane] : 0;
         int vi = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
+        for (int o = 1; o < NW; o <<= 1) {
             const int t = __shfl_up_sync(0xFFFFFFFFu, vi, o);
             if (lane >= o) vi += t;
         }
-        wsum[lane] = vi - v;
-        if (lane == 31) wsum[32] = vi;
+        n = __shfl_sync(0xFFFFFFFFu, vi, NW - 1);
+        at = __shfl_sync(0xFFFFFFFFu, vi - v, wid) + inc - mine;
     }
-    __syncthreads();
-    const int n = wsum[32];
-    int at = wsum[wid] + inc - mine;
-    __syncthreads();            // wsum is reused by the scans below
     if (n == 0) {
         if (tid == 0) *outCount = 0;
         return;
@@ -660,37 +662,53 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
                 }
         }
     }
-    if (nIni == 1 && tid == 0) rootCnt[0] = n;
-    __syncthreads();
-    if (tid == 0) {
-        int m0 = 0;
-        for (int i = 0; i < nIni; i++) {
-            if (rootCnt[i] > 0) {           // empty roots are erased (:574-585)
-                rA[m0] = make_short4((short)(int)__fmul_rn(G.hX, (float)i), (short)(int)__fmul_rn(G.hX, (float)(i + 1)),
-                                     (short)0, (short)(G.maxBY - MIN_BORDER));
-                cA[m0] = rootCnt[i];
-                tmp[i] = m0++;
-            }
+    int m;
+    if (nIni == 1) {                        // one root (every shape up to 1.5 : 1): it holds all n > 0 candidates
+        if (tid == 0) {
+            rA[0] = make_short4((short)0, (short)(int)G.hX, (short)0, (short)(G.maxBY - MIN_BORDER));
+            cA[0] = n;
         }
-        s_m = m0;
+        m = 1;
+        __syncthreads();                    // wsum (the setup scan above) is reused by the scans below
+    } else {
+        __syncthreads();
+        if (wid == 0) {                     // empty roots are erased (:574-585): a ballot per 32 roots ranks the others
+            int m0 = 0;
+            for (int i0 = 0; i0 < nIni; i0 += 32) {
+                const int i = i0 + lane;
+                const int rc = i < nIni ? rootCnt[i] : 0;
+                const unsigned live = __ballot_sync(0xFFFFFFFFu, rc > 0);
+                if (rc > 0) {
+                    const int q = m0 + __popc(live & ((1u << lane) - 1));
+                    rA[q] = make_short4((short)(int)__fmul_rn(G.hX, (float)i), (short)(int)__fmul_rn(G.hX, (float)(i + 1)),
+                                        (short)0, (short)(G.maxBY - MIN_BORDER));
+                    cA[q] = rc;
+                    tmp[i] = q;
+                }
+                m0 += __popc(live);
+            }
+            if (lane == 0) s_m = m0;
+        }
+        __syncthreads();
+        // the candidates were written in runs of cells, one run per thread: this pass and every later one index them tid, tid + T, ...
+        for (int i = tid; i < n; i += T) knode[i] = (uint16_t)tmp[knode[i]];
+        m = s_m;
+        __syncthreads();                    // tmp is the output of the first scan below
     }
-    __syncthreads();
-    for (int i = tid; i < n; i += T) knode[i] = (uint16_t)tmp[knode[i]];
-    int m = s_m;
     const int N = G.quota;
     bool lf = false;
-    __syncthreads();
 
-    for (;;) {
+    // Barriers per pass: 9 (10 in the largest-first phase, plus the sort's).  knode[i] is only ever touched by thread i mod T.
+    for (int pass = 0;; pass++) {
+        const int par = pass & 1;
+        uint16_t* rankOf = rankOf2 + par * capS;
         // ---- processing order P: all expandable nodes (more than one key)
-        for (int p = tid; p < m; p += T) { tmp[p] = cA[p] > 1; rankOf[p] = 0xFFFF; }
-        if (tid == 0) { s_k = 0x7FFFFFFF; s_nexp = 0; }
-        __syncthreads();
-        const int np = block_exclusive_scan<T>(tmp, m, wsum);
+        if (tid == 0) { s_k[par] = 0x7FFFFFFF; s_nexp[par] = 0; }
+        const int np = block_exclusive_scan<T>(m, tmp, wsum, [&](int p) { rankOf[p] = 0xFFFF; return (int)(cA[p] > 1); });
         if (np == 0) break;                                   // nothing to split: list size cannot change
         if (!lf) {
-            for (int p = tid; p < m; p += T) if (cA[p] > 1) skey[tmp[p]] = (uint32_t)p;      // list order (:606)
-            __syncthreads();
+            for (int p = tid; p < m; p += T)
+                if (cA[p] > 1) { skey[tmp[p]] = (uint32_t)p; rankOf[p] = (uint16_t)tmp[p]; }      // list order (:606)
         } else {
             int sp = 1;
             while (sp < np) sp <<= 1;
@@ -709,10 +727,12 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
                     }
                 }
             __syncthreads();
-            for (int r = tid; r < np; r += T) skey[r] = 4095u - (skey[r] & 4095u);
-            __syncthreads();
+            for (int r = tid; r < np; r += T) {               // thread r alone reads and writes skey[r]
+                const uint32_t pos = 4095u - (skey[r] & 4095u);
+                skey[r] = pos;
+                rankOf[pos] = (uint16_t)r;
+            }
         }
-        for (int r = tid; r < np; r += T) rankOf[skey[r]] = (uint16_t)r;
         for (int i = tid; i < 4 * np; i += T) cc[i] = 0;
         __syncthreads();
 
@@ -738,25 +758,22 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
         __syncthreads();
 
         // ---- children per rank, creation indices, early stop of the largest-first phase (:730-731)
-        for (int r = tid; r < np; r += T)
-            chBeg[r] = (cc[4 * r] > 0) + (cc[4 * r + 1] > 0) + (cc[4 * r + 2] > 0) + (cc[4 * r + 3] > 0);
-        __syncthreads();
-        const int totalCh = block_exclusive_scan<T>(chBeg, np, wsum);
+        const int totalCh = block_exclusive_scan<T>(np, chBeg, wsum, [&](int r) {
+            return (int)(cc[4 * r] > 0) + (int)(cc[4 * r + 1] > 0) + (int)(cc[4 * r + 2] > 0) + (int)(cc[4 * r + 3] > 0);
+        });
         int k = np;
         if (lf) {
             for (int r = tid; r < np; r += T) {
                 const int end = (r + 1 < np) ? chBeg[r + 1] : totalCh;
-                if (m + end - (r + 1) >= N) atomicMin(&s_k, r);
+                if (m + end - (r + 1) >= N) atomicMin(&s_k[par], r);
             }
             __syncthreads();
-            if (s_k != 0x7FFFFFFF) k = s_k + 1;
+            if (s_k[par] != 0x7FFFFFFF) k = s_k[par] + 1;
         }
         const int C = (k == np) ? totalCh : chBeg[k];
 
         // ---- new list = reverse(children) ++ unsplit nodes
-        for (int p = tid; p < m; p += T) tmp[p] = (int)rankOf[p] >= k;
-        __syncthreads();
-        block_exclusive_scan<T>(tmp, m, wsum);
+        block_exclusive_scan<T>(m, tmp, wsum, [&](int p) { return (int)((int)rankOf[p] >= k); });
         for (int p = tid; p < m; p += T)
             if ((int)rankOf[p] >= k) {
                 const int q = C + tmp[p];
@@ -784,7 +801,7 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
                 }
             }
         }
-        if (nexp) atomicAdd(&s_nexp, nexp);
+        if (nexp) atomicAdd(&s_nexp[par], nexp);
         __syncthreads();
         for (int i = tid; i < n; i += T) {
             const int kn = knode[i];
@@ -794,13 +811,15 @@ __global__ void __launch_bounds__(CFG::THREADS, CFG::MINB) k_octree(const Plan P
         }
         const int m2 = C + (m - k);
         const bool done = (m2 >= N) || (m2 == m);
-        if (!done && !lf && m2 + 3 * s_nexp > N) lf = true;
+        if (!done && !lf && m2 + 3 * s_nexp[par] > N) lf = true;
         { short4* t = rA; rA = rB; rB = t; }
         { int* t = cA; cA = cB; cB = t; }
         m = m2;
-        __syncthreads();
         if (done) break;
+        // no barrier here: the next pass writes the other rankOf / s_k / s_nexp, tmp, skey and cc, none of which the loop above
+        // reads, and the arrays it reads first (cA, rA) were complete at the barrier before that loop
     }
+    __syncthreads();
 
     // ---- best key of every node: highest response, first in candidate order (:742-760)
     unsigned* best = reinterpret_cast<unsigned*>(tmp);
