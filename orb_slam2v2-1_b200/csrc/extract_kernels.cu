@@ -1178,11 +1178,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
             }
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, o);
-        m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, o);
-    }
+    m10 = __reduce_add_sync(0xFFFFFFFFu, m10);             // REDUX.SUM: one instruction instead of five shuffle + add steps
+    m01 = __reduce_add_sync(0xFFFFFFFFu, m01);
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
     // rBRIEF on the blurred level: lane = descriptor byte, 8 test pairs each
