@@ -1237,15 +1237,184 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     }
 }
 
+// The same operator with 32 keypoints per warp (TMA form only).  Everything that is one value per keypoint -- the level
+// look-up, fastAtan2, the double-precision sincosf restatement (85 of the 614 warp instructions per keypoint of the kernel
+// above), the 28-byte record -- runs once per WARP with lane k working for keypoint k; the two warp-cooperative parts, the
+// moments (lane = patch words) and the descriptor (lane = descriptor byte), loop over the 32 keypoints with the next
+// keypoint's box already in flight (two buffers per warp, two mbarriers per loop) and the 8 float4 pattern entries of the
+// lane held in registers for all of them.
+#ifndef OD32_WARPS_N
+#define OD32_WARPS_N 8
+#endif
+#ifndef OD32_MINB
+#define OD32_MINB 3
+#endif
+constexpr int OD32_WARPS = OD32_WARPS_N;
+constexpr int OD32_BUF = 2432;            // one buffer takes either box (blurred 64 x 37 = 2368 B, unblurred 48 x 31 = 1488 B)
+
+__global__ void __launch_bounds__(OD32_WARPS * 32, OD32_MINB) k_orient_describe32(const Plan P, const FrameBufs F, const uint2* __restrict__ icTab,
+                                                                         const float4* __restrict__ patT,
+                                                                         const __grid_constant__ OrientMaps M)
+{
+    constexpr unsigned FULL = 0xFFFFFFFFu;
+    const int f = blockIdx.y + F.frame0, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int g0 = (blockIdx.x * OD32_WARPS + wrp) * 32;               // first keypoint of this warp inside the frame
+    // levels are concatenated in ascending order (:1103): lane i holds the count of level i
+    const int myc = lane < P.nlevels ? F.levelCount[(size_t)f * MAX_LEVELS + lane] : 0;
+    int inc = myc;
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) {
+        const int t = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += t;
+    }
+    const int total = __shfl_sync(FULL, inc, 15);
+    if (g0 == 0 && lane == 0) F.counts[f] = total;
+    if (g0 >= total) return;
+    const int cnt = min(32, total - g0), g = g0 + lane;
+    const bool valid = lane < cnt;
+
+    // ---- lane k: level, key and centre of keypoint g0 + k
+    int l = 0, idx = 0, nodeBase = 0, scaledPatch = 0;
+    float scale = 1.f;
+#pragma unroll
+    for (int j = 0; j < MAX_LEVELS; j++) {
+        if (j < P.nlevels) {
+            const int hi = __shfl_sync(FULL, inc, j), lo = hi - __shfl_sync(FULL, myc, j);
+            if (g >= lo && g < hi) { l = j; idx = g - lo; nodeBase = P.lv[j].nodeBase; scaledPatch = P.lv[j].scaledPatch; scale = P.lv[j].scale; }
+        }
+    }
+    const uint32_t key = valid ? F.levelKeys[(size_t)f * P.totalNodes + nodeBase + idx] : 0u;
+    const int cxl = key_x(key) + MIN_BORDER, cyl = key_y(key) + MIN_BORDER;      // level coordinates (:841-842)
+    const unsigned packed = (unsigned)cxl | ((unsigned)cyl << 13) | ((unsigned)l << 26);
+
+    __shared__ __align__(128) uint8_t s_buf[OD32_WARPS * 2 * OD32_BUF];
+    __shared__ uint64_t s_bar[OD32_WARPS][4];
+    const unsigned bufBase = (unsigned)__cvta_generic_to_shared(s_buf) + (unsigned)(wrp * 2 * OD32_BUF);
+    const unsigned barA = (unsigned)__cvta_generic_to_shared(&s_bar[wrp][0]), barC = barA + 16;
+    if (lane == 0) {
+        mbar_init(barA, 1);
+        mbar_init(barA + 8, 1);
+        mbar_init(barC, 1);
+        mbar_init(barC + 8, 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+
+    // ---- IC_Angle moments, one keypoint after the other: the unblurred 31 x 31 patch arrives as a 48 x 31 box from the
+    // 16-byte boundary at or below cx - 15 (279 (row, word) items over the 32 lanes, two IDP.4A each, weights by alignment)
+    if (lane == 0) {
+        mbar_expect_tx(barA, DESC_BOX_IMG_BYTES);
+        tma_load_box(bufBase, &M.img.m[l], (cxl - HALF_PATCH) & ~15, cyl - HALF_PATCH, f, barA);
+    }
+    int my10 = 0, my01 = 0;
+    for (int k = 0; k < cnt; k++) {
+        const unsigned pk = __shfl_sync(FULL, packed, k), pn = __shfl_sync(FULL, packed, (k + 1) & 31);
+        if (lane == 0 && k + 1 < cnt) {          // the buffer of keypoint k - 1: every lane passed that iteration's REDUX
+            const unsigned bn = barA + 8u * ((k + 1) & 1);
+            mbar_expect_tx(bn, DESC_BOX_IMG_BYTES);
+            tma_load_box(bufBase + (unsigned)(((k + 1) & 1) * OD32_BUF), &M.img.m[pn >> 26], (int)((pn & 0x1FFFu) - HALF_PATCH) & ~15,
+                         (int)((pn >> 13) & 0x1FFFu) - HALF_PATCH, f, bn);
+        }
+        mbar_wait(barA + 8u * (k & 1), (k >> 1) & 1);
+        const int al = ((int)(pk & 0x1FFFu) - HALF_PATCH) & 15;
+        const uint32_t* box = reinterpret_cast<const uint32_t*>(s_buf + (wrp * 2 + (k & 1)) * OD32_BUF) + (al >> 2);
+        const uint2* tab = icTab + (al & 3) * IC_ITEMS_PAD;
+        int m10 = 0, m01 = 0;
+#pragma unroll
+        for (int it = 0; it < 9; it++) {
+            const int i = lane + 32 * it;
+            if (it < 8 || i < IC_ITEMS) {
+                const int row = (i * 57) >> 9, word = i - 9 * row;         // i / 9 for i < 288
+                const uint2 wt = __ldg(&tab[i]);
+                const unsigned px = box[row * (DESC_BOX_IMG_W / 4) + word];
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(px), "r"(wt.x));
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m01) : "r"(px), "r"(wt.y));
+            }
+        }
+        m10 = __reduce_add_sync(FULL, m10);
+        m01 = __reduce_add_sync(FULL, m01);
+        if (lane == k) { my10 = m10; my01 = m01; }
+    }
+
+    // ---- lane k: orientation, rotation and the record of keypoint k
+    const float angle = fast_atan2_deg((float)my01, (float)my10);
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float ca, sb;
+    orbx_sc::sincosf_glibc(__fmul_rn(angle, factorPI), &sb, &ca);      // ca = cos, sb = sin (:112-113)
+    if (valid) {
+        unsigned* rec = reinterpret_cast<unsigned*>(F.kps + ((size_t)f * P.totalNodes + g));
+        rec[0] = __float_as_uint(l ? __fmul_rn((float)cxl, scale) : (float)cxl);      // pt *= mvScaleFactor[level] for level != 0 (:1095-1101)
+        rec[1] = __float_as_uint(l ? __fmul_rn((float)cyl, scale) : (float)cyl);
+        rec[2] = __float_as_uint((float)scaledPatch);
+        rec[3] = __float_as_uint(angle);
+        rec[4] = __float_as_uint((float)key_r(key));
+        rec[5] = (unsigned)l;
+        rec[6] = 0xFFFFFFFFu;                                                          // class_id = -1
+    }
+
+    // ---- rBRIEF on the blurred level, one keypoint after the other: lane = descriptor byte, its 8 test pairs in registers
+    float4 pt[8];
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) pt[bit] = __ldg(&patT[bit * 32 + lane]);
+    if (lane == 0) {                             // every lane passed the last REDUX above: both buffers are free
+        mbar_expect_tx(barC, DESC_BOX_BLUR_BYTES);
+        tma_load_box(bufBase, &M.blur.m[l], (cxl - 18) & ~15, cyl - 18, f, barC);
+    }
+    const bool fma = P.fmaMode != 0;
+    uint8_t* dout = F.desc + ((size_t)f * P.totalNodes + g0) * 32 + lane;
+    for (int k = 0; k < cnt; k++) {
+        const unsigned pk = __shfl_sync(FULL, packed, k), pn = __shfl_sync(FULL, packed, (k + 1) & 31);
+        const float a = __shfl_sync(FULL, ca, k), b = __shfl_sync(FULL, sb, k);
+        if (lane == 0 && k + 1 < cnt) {          // the buffer of keypoint k - 1: freed by the __syncwarp that ended its iteration
+            const unsigned bn = barC + 8u * ((k + 1) & 1);
+            mbar_expect_tx(bn, DESC_BOX_BLUR_BYTES);
+            tma_load_box(bufBase + (unsigned)(((k + 1) & 1) * OD32_BUF), &M.blur.m[pn >> 26], (int)((pn & 0x1FFFu) - 18) & ~15,
+                         (int)((pn >> 13) & 0x1FFFu) - 18, f, bn);
+        }
+        // shared-space byte address of the patch centre with both rounding biases folded in (32-bit arithmetic, wraps):
+        // address = centre + (rbits - MAGIC) * pitch + (cbits - MAGIC)
+        const unsigned pal = ((pk & 0x1FFFu) - 18u) & 15u;
+        const unsigned ctrb = bufBase + (unsigned)((k & 1) * OD32_BUF) + 18u * DESC_BOX_BLUR_W + 18u + pal - (unsigned)MAGIC_BITS * (DESC_BOX_BLUR_W + 1u);
+        mbar_wait(barC + 8u * (k & 1), (k >> 1) & 1);
+        unsigned val = 0;
+#pragma unroll
+        for (int bit = 0; bit < 8; bit++) {
+            int r0, c0, r1, c1;
+            if (fma) {     // contracted form g++ -O3 -march=native emits for x*b + y*a and x*a - y*b
+                r0 = round_magic_bits(__fmaf_rn(pt[bit].x, b, __fmul_rn(pt[bit].y, a)));
+                c0 = round_magic_bits(__fmaf_rn(pt[bit].x, a, -__fmul_rn(pt[bit].y, b)));
+                r1 = round_magic_bits(__fmaf_rn(pt[bit].z, b, __fmul_rn(pt[bit].w, a)));
+                c1 = round_magic_bits(__fmaf_rn(pt[bit].z, a, -__fmul_rn(pt[bit].w, b)));
+            } else {
+                r0 = round_magic_bits(__fadd_rn(__fmul_rn(pt[bit].x, b), __fmul_rn(pt[bit].y, a)));
+                c0 = round_magic_bits(__fsub_rn(__fmul_rn(pt[bit].x, a), __fmul_rn(pt[bit].y, b)));
+                r1 = round_magic_bits(__fadd_rn(__fmul_rn(pt[bit].z, b), __fmul_rn(pt[bit].w, a)));
+                c1 = round_magic_bits(__fsub_rn(__fmul_rn(pt[bit].z, a), __fmul_rn(pt[bit].w, b)));
+            }
+            unsigned t0, t1;
+            asm("ld.shared.u8 %0, [%1];" : "=r"(t0) : "r"(ctrb + (unsigned)r0 * DESC_BOX_BLUR_W + (unsigned)c0));
+            asm("ld.shared.u8 %0, [%1];" : "=r"(t1) : "r"(ctrb + (unsigned)r1 * DESC_BOX_BLUR_W + (unsigned)c1));
+            val |= (unsigned)(t0 < t1) << bit;
+        }
+        dout[(size_t)k * 32] = (uint8_t)val;
+        __syncwarp();
+    }
+}
+
 void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, const uint2* icTab, const float4* patT, int B,
                             const LevelMaps* imgMaps, const LevelMaps* blurMaps)
 {
     dim3 grd((P.totalNodes + DESC_WARPS - 1) / DESC_WARPS, B);
     OrientMaps M;
     if (imgMaps && blurMaps) {
+        static const bool perWarp32 = !(getenv("ORBX_ORIENT32") && atoi(getenv("ORBX_ORIENT32")) == 0);      // A/B switch
         M.img = *imgMaps;
         M.blur = *blurMaps;
-        k_orient_describe<true><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+        if (perWarp32) {
+            dim3 g32((P.totalNodes + OD32_WARPS * 32 - 1) / (OD32_WARPS * 32), B);
+            k_orient_describe32<<<g32, OD32_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+        } else
+            k_orient_describe<true><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
     } else {
         memset(&M, 0, sizeof M);
         k_orient_describe<false><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
