@@ -212,33 +212,46 @@ size_t fast_smem_bytes(const Plan& P)
     return (size_t)((m + 127) & ~127) * FAST_WARPS;        // every warp's tile starts on a 128-byte boundary (TMA destination)
 }
 
-// Cell table (two uint4 per cell, per image shape; built by fast_cell_record on the host):
-//   a = {iniX | iniY << 16, tw | th << 16 (0 = skipped cell), level | xoff << 4 | yoff << 16, cell index inside the level}
-//   b = {recipS | rpiS << 20 | nq << 26, recipZ | rpiZ << 20 | nd << 26, dx0 | scp << 8 | dFirst << 16, 0}
-// nq = 16-byte pieces per tile row, rpiS = 32 / nq tile rows staged per warp iteration; nd = 8-byte columns that cover the
-// detection zone, rpiZ = 32 / nd zone rows filtered per warp iteration; recip* = 65536 / n + 1 (lane / n by multiply-shift);
-// dx0 = iniX - tile origin, scp = pitch of the score map, dFirst = first 8-byte column of the zone.
-void fast_cell_record(const LevelGeom& G, int level, int i, int j, uint4* rec)
+// Cell table (FAST_CELL_REC uint4 per cell, per image shape; built by fast_cell_record on the host).  Everything a warp needs
+// that does not depend on the frame or the lane is a ready-made word here, so the kernel's set-up is loads, not arithmetic:
+//   r0 = {tile origin x (iniX rounded down to 16) | iniY << 16, iw | ih << 16 (detection zone; 0 = skipped cell), level | th << 8,
+//         slot index of the cell's output inside a frame's slot array}
+//   r1 = {offset of the score map | offset of the survivor list << 16 (bytes from the warp's tile), scBytes | scp << 16, scBias,
+//         ceil(ih / rpiZ)}
+//   r2 = {recipZ | rpiZ << 20 | nd << 26, recipS | rpiS << 20 | nq << 26, xoff - dx0, dFirst | yoff << 8}
+//   r3 = {bit-7 mask of the zone bytes in the FIRST 8-byte column (two words), the same for the LAST column (two words)}
+// nq = 16-byte pieces per tile row, rpiS = 32 / nq tile rows staged per warp iteration (LDGSTS form); nd = 8-byte columns that
+// cover the detection zone, rpiZ = 32 / nd zone rows filtered per warp iteration; recip* = 65536 / n + 1 (lane / n by
+// multiply-shift); dx0 = iniX - tile origin, scp = pitch of the score map ((ih + 2) x scp bytes, 1-px zero frame), scBias: score-map
+// index of tile pixel (row, col) = row * scp + col + scBias; dFirst = first 8-byte column of the zone.
+void fast_cell_record(const LevelGeom& G, int level, int i, int j, int tp, uint4* rec)
 {
     const int iniX = MIN_BORDER + j * G.wCell, iniY = MIN_BORDER + i * G.hCell;
     const int maxX = min(iniX + G.wCell + 6, G.maxBX), maxY = min(iniY + G.hCell + 6, G.maxBY);
     const int tw = maxX - iniX, th = maxY - iniY;
     const bool skip = iniX >= G.maxBX - 6 || iniY >= G.maxBY - 3 || tw < 7 || th < 7;
-    uint4 a, b = make_uint4(0, 0, 0, 0);
-    a.x = (unsigned)iniX | ((unsigned)iniY << 16);
-    a.y = skip ? 0u : ((unsigned)tw | ((unsigned)th << 16));
-    a.z = (unsigned)level | ((unsigned)(j * G.wCell) << 4) | ((unsigned)(i * G.hCell) << 16);
-    a.w = (unsigned)(i * G.nCols + j);
-    if (!skip) {
-        const int dx0 = iniX & 15, nq = (dx0 + tw + 15) >> 4, rpiS = 32 / nq;
-        const int zx0 = dx0 + 3, zx1 = zx0 + tw - 6, dFirst = zx0 >> 3, nd = ((zx1 - 1) >> 3) - dFirst + 1, rpiZ = 32 / nd;
-        const int scp = (tw - 6 + 2 + 3) & ~3;
-        b.x = (unsigned)(65536 / nq + 1) | ((unsigned)rpiS << 20) | ((unsigned)nq << 26);      // recip <= 65537: 17 bits
-        b.y = (unsigned)(65536 / nd + 1) | ((unsigned)rpiZ << 20) | ((unsigned)nd << 26);
-        b.z = (unsigned)dx0 | ((unsigned)scp << 8) | ((unsigned)dFirst << 16);
-    }
-    rec[0] = a;
-    rec[1] = b;
+    for (int k = 0; k < FAST_CELL_REC; k++) rec[k] = make_uint4(0, 0, 0, 0);
+    if (skip) return;
+    const int dx0 = iniX & 15, nq = (dx0 + tw + 15) >> 4, rpiS = 32 / nq;
+    const int iw = tw - 6, ih = th - 6;
+    const int zx0 = dx0 + 3, zx1 = zx0 + iw, dFirst = zx0 >> 3, nd = ((zx1 - 1) >> 3) - dFirst + 1, rpiZ = 32 / nd;
+    const int scp = (iw + 2 + 3) & ~3, scBytes = ((ih + 2) * scp + 15) & ~15;
+    const int scOff = (G.hCell + 6) * tp;                       // the tile always has room for hCell + 6 rows (fast_warp_smem)
+    auto zone_mask = [&](int col) {                             // bytes of 8-byte column `col` that lie inside [zx0, zx1)
+        const int lo = min(max(zx0 - 8 * col, 0), 8), hi = min(max(zx1 - 8 * col, 0), 8);
+        unsigned long long m = 0;
+        for (int b = lo; b < hi; b++) m |= 0x80ull << (8 * b);
+        return m;
+    };
+    const unsigned long long mf = zone_mask(dFirst), ml = zone_mask(dFirst + nd - 1);
+    rec[0] = make_uint4((unsigned)(iniX - dx0) | ((unsigned)iniY << 16), (unsigned)iw | ((unsigned)ih << 16), (unsigned)level | ((unsigned)th << 8),
+                        (unsigned)(G.slotOff + (unsigned long long)(i * G.nCols + j) * G.slotCap));
+    rec[1] = make_uint4((unsigned)scOff | ((unsigned)(scOff + scBytes) << 16), (unsigned)scBytes | ((unsigned)scp << 16),
+                        (unsigned)(1 - zx0 - 2 * scp), (unsigned)((ih + rpiZ - 1) / rpiZ));
+    rec[2] = make_uint4((unsigned)(65536 / nd + 1) | ((unsigned)rpiZ << 20) | ((unsigned)nd << 26),       // recip <= 65537: 17 bits
+                        (unsigned)(65536 / nq + 1) | ((unsigned)rpiS << 20) | ((unsigned)nq << 26), (unsigned)(j * G.wCell - dx0),
+                        (unsigned)dFirst | ((unsigned)(i * G.hCell) << 8));
+    rec[3] = make_uint4((unsigned)mf, (unsigned)(mf >> 32), (unsigned)ml, (unsigned)(ml >> 32));
 }
 
 // tile pitch that fits every cell of the plan: 64 bytes unless a cell row (from its 16-byte-aligned origin) is longer
@@ -266,24 +279,23 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (cell >= P.totalCells) return;
     const unsigned FULL = 0xFFFFFFFFu, ltmask = (1u << lane) - 1;
-    const uint4 ct = __ldg(&F.cellTab[2 * cell]);
+    const uint4* rec = F.cellTab + (size_t)FAST_CELL_REC * cell;
+    const uint4 r0 = __ldg(&rec[0]);
     int* cntOut = F.cellCount + (size_t)f * P.totalCells + cell;
-    if (ct.y == 0) {                                      // skipped cell / ROI too small for cv::FAST
+    if (r0.y == 0) {                                      // skipped cell / ROI too small for cv::FAST
         if (lane == 0) *cntOut = 0;
         return;
     }
-    const uint4 cu = __ldg(&F.cellTab[2 * cell + 1]);
-    // cell ROI (ORBextractor.cc:791-806): [iniX, iniX + tw) x [iniY, iniY + th), overlap of 6 px with the next cell
-    const int iniX = ct.x & 0xFFFF, iniY = ct.x >> 16, tw = ct.y & 0xFFFF, th = ct.y >> 16;
-    const int l = ct.z & 15, xoff = (ct.z >> 4) & 0xFFF, yoff = ct.z >> 16;
-    const LevelGeom& G = P.lv[l];
-    const int iw = tw - 6, ih = th - 6;                   // detection zone: no corner within 3 px of the ROI edge
-    const int dx0 = cu.z & 0xFF, scp = (cu.z >> 8) & 0xFF, dFirst = (cu.z >> 16) & 0xFF;
+    const uint4 r1 = __ldg(&rec[1]), r2 = __ldg(&rec[2]), r3 = __ldg(&rec[3]);
+    // cell ROI (ORBextractor.cc:791-806): [iniX, iniX + tw) x [iniY, iniY + th), overlap of 6 px with the next cell; detection zone
+    // iw x ih: no corner within 3 px of the ROI edge
+    const int tileX = r0.x & 0xFFFF, iniY = r0.x >> 16, ih = r0.y >> 16;
+    const int l = r0.z & 0xFF;
+    const int scp = r1.y >> 16, scBytes = r1.y & 0xFFFF, scBias = (int)r1.z, zIters = (int)r1.w;
+    const int xAdj = (int)r2.z, dFirst = r2.w & 0xFF, yoff = r2.w >> 8;
     uint8_t* tile = smem + (size_t)wid * smemPerWarp;
-    // score map: (ih + 2) x scp, 1-px zero frame; behind the whole box in the TMA form (the box always has hCell + 6 rows)
-    uint8_t* sc = tile + (TMA ? G.hCell + 6 : th) * TP;
-    const int scBytes = ((ih + 2) * scp + 15) & ~15;
-    uint16_t* list = reinterpret_cast<uint16_t*>(sc + scBytes);
+    uint8_t* sc = tile + (r1.x & 0xFFFF);                 // score map, behind the hCell + 6 rows of the tile
+    uint16_t* list = reinterpret_cast<uint16_t*>(tile + (r1.x >> 16));
     const uint32_t* tileW = reinterpret_cast<const uint32_t*>(tile);
 
     const unsigned bar = (unsigned)__cvta_generic_to_shared(&bars[wid]);
@@ -293,8 +305,8 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         if (lane == 0) {
             mbar_init(bar, 1);
             mbar_fence_init();
-            mbar_expect_tx(bar, (unsigned)((G.hCell + 6) * TP));
-            tma_load_box((unsigned)__cvta_generic_to_shared(tile), &M.m[l], iniX - dx0, iniY, f, bar);
+            mbar_expect_tx(bar, r1.x & 0xFFFFu);           // (hCell + 6) * TP bytes: the box ends where the score map begins
+            tma_load_box((unsigned)__cvta_generic_to_shared(tile), &M.m[l], tileX, iniY, f, bar);
         }
         __syncwarp();
     } else {
@@ -302,11 +314,11 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     {   // global -> shared without a register round trip (LDGSTS); completion is awaited after the set-up below.
         // lane = (row r0, 16-byte piece q0) of a block of rpiS whole tile rows: no index arithmetic inside the loop
-        const int nq = cu.x >> 26, rpiS = (cu.x >> 20) & 0x3F;
-        const int r0 = (int)(((unsigned)lane * (cu.x & 0xFFFFFu)) >> 16), q0 = lane - r0 * nq;
-        if (r0 < rpiS) {
-            const uint8_t* p = img + (size_t)(iniY + r0) * pitch + (iniX - dx0) + 16 * q0;
-            unsigned sdst = (unsigned)__cvta_generic_to_shared(tile) + (unsigned)(r0 * TP + 16 * q0);
+        const int nq = r2.y >> 26, rpiS = (r2.y >> 20) & 0x3F, th = r0.z >> 8;
+        const int sr0 = (int)(((unsigned)lane * (r2.y & 0xFFFFFu)) >> 16), q0 = lane - sr0 * nq;
+        if (sr0 < rpiS) {
+            const uint8_t* p = img + (size_t)(iniY + sr0) * pitch + tileX + 16 * q0;
+            unsigned sdst = (unsigned)__cvta_generic_to_shared(tile) + (unsigned)(sr0 * TP + 16 * q0);
             const size_t pstep = (size_t)rpiS * pitch;
             const unsigned sstep = (unsigned)(rpiS * TP);
             // level 0 may be the caller's device image, only 4-byte aligned: same layout from 4-byte copies
@@ -317,16 +329,16 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
                 constexpr int FLAT = 5;
 #pragma unroll
                 for (int it = 0; it < FLAT; it++)
-                    if (r0 + it * rpiS < th)
+                    if (sr0 + it * rpiS < th)
                         asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst + (unsigned)it * sstep), "l"(p + (size_t)it * pstep));
-                if (r0 + FLAT * rpiS < th) {
+                if (sr0 + FLAT * rpiS < th) {
                     p += FLAT * pstep;
                     sdst += FLAT * sstep;
-                    for (int r = r0 + FLAT * rpiS; r < th; r += rpiS, p += pstep, sdst += sstep)
+                    for (int r = sr0 + FLAT * rpiS; r < th; r += rpiS, p += pstep, sdst += sstep)
                         asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(p));
                 }
             } else {
-                for (int r = r0; r < th; r += rpiS, p += pstep, sdst += sstep) {
+                for (int r = sr0; r < th; r += rpiS, p += pstep, sdst += sstep) {
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst), "l"(p));
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 4), "l"(p + 4));
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 8), "l"(p + 8));
@@ -336,22 +348,14 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         }
     }
     }
-    // zone in tile coordinates: columns [zx0, zx1), rows [3, 3 + ih)
-    const int zx0 = dx0 + 3, zx1 = zx0 + iw;
-    // pre-filter work items: lane = (row zr0, 8-byte column zc) of a block of rpiZ zone rows
-    const int nd = cu.y >> 26, rpiZ = (cu.y >> 20) & 0x3F;
-    const int zr0 = (int)(((unsigned)lane * (cu.y & 0xFFFFFu)) >> 16), zc = lane - zr0 * nd;
+    // pre-filter work items: lane = (row zr0, 8-byte column zc) of a block of rpiZ zone rows (zone: tile rows [3, 3 + ih))
+    const int nd = r2.x >> 26, rpiZ = (r2.x >> 20) & 0x3F;
+    const int zr0 = (int)(((unsigned)lane * (r2.x & 0xFFFFFu)) >> 16), zc = lane - zr0 * nd;
     const bool zactive = zr0 < rpiZ;
-    const int bc = 8 * (dFirst + zc);                     // tile column of the item's first pixel
-    unsigned zm0 = 0, zm1 = 0;                            // bytes of the item that lie inside the zone
-    if (zactive) {
-        const int lo = min(max(zx0 - bc, 0), 8), hi = min(max(zx1 - bc, 0), 8);
-        const unsigned long long m = (hi >= 8 ? ~0ull : ((1ull << (8 * hi)) - 1)) & ~(lo >= 8 ? ~0ull : ((1ull << (8 * lo)) - 1));
-        zm0 = (unsigned)m & 0x80808080u;
-        zm1 = (unsigned)(m >> 32) & 0x80808080u;
-    }
-    uint32_t* out = F.slots + (size_t)f * P.slotSlab + G.slotOff + (size_t)(ct.w & 0xFFFF) * G.slotCap;
-    const int scBias = 1 - zx0 - 2 * scp;                 // score-map index of tile pixel (row, col) = row * scp + col + scBias
+    // bytes of the item that lie inside the zone: only the first and the last column are partial
+    const unsigned zm0 = zactive ? (zc == 0 ? r3.x : 0x80808080u) & (zc == nd - 1 ? r3.z : 0x80808080u) : 0u;
+    const unsigned zm1 = zactive ? (zc == 0 ? r3.y : 0x80808080u) & (zc == nd - 1 ? r3.w : 0x80808080u) : 0u;
+    uint32_t* out = F.slots + (size_t)f * P.slotSlab + r0.w;
     int total = 0;
     if constexpr (TMA) mbar_wait(bar, 0);
     else asm volatile("cp.async.wait_all;" ::: "memory");
@@ -369,8 +373,9 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
         {
             const uint32_t* w = tileW + (3 + zr0) * TPW + 2 * (dFirst + zc);
             uint8_t* mk = sc + zr0 * rmb + zc;
-            if (zactive)
-                for (int row0 = zr0; row0 < ih; row0 += rpiZ, w += rpiZ * TPW, mk += rpiZ * rmb) {
+            // zIters = ceil(ih / rpiZ) from the table: a warp-uniform trip count (no division by rpiZ for the unroller)
+            for (int it = 0, row0 = zr0; it < zIters; it++, row0 += rpiZ, w += rpiZ * TPW, mk += rpiZ * rmb)
+                if (zactive && row0 < ih) {
                     const uint2 C = *reinterpret_cast<const uint2*>(w);
                     const uint2 U = *reinterpret_cast<const uint2*>(w - 3 * TPW), D = *reinterpret_cast<const uint2*>(w + 3 * TPW);
                     const unsigned Lw = w[-1], Rw = w[2];
@@ -451,7 +456,7 @@ __device__ __forceinline__ void fast_cell_body(const Plan& P, const FrameBufs& F
             const unsigned kb = __ballot_sync(FULL, keep);
             if (keep) {
                 // coordinates relative to (minBorderX, minBorderY): ROI-relative + j*wCell (ORBextractor.cc:822-823)
-                const int x = (int)(e & (TP - 1)) - dx0 + xoff, y = (int)(e / TP) + yoff;
+                const int x = (int)(e & (TP - 1)) + xAdj, y = (int)(e / TP) + yoff;
                 out[total + __popc(kb & ltmask)] = pack_key(x, y, v - 1);
             }
             total += __popc(kb);

@@ -20,7 +20,7 @@ struct FrameBufs {
     orbx_kp* kps;                  // B x totalNodes
     uint8_t* desc;                 // B x totalNodes x 32
     int* counts;                   // B
-    const uint4* cellTab;          // 2 x totalCells (per shape, shared by all frames): FAST cell geometry, see fast_cell_record
+    const uint4* cellTab;          // FAST_CELL_REC x totalCells (per shape, shared by all frames): FAST cell geometry, see fast_cell_record
     int frame0;                    // first frame of this launch: a large batch runs as two halves on two streams (orbx_extractor.cu)
 };
 
@@ -51,7 +51,8 @@ void launch_gray(cudaStream_t s, const uint8_t* src, size_t spitch, size_t sfram
 
 size_t fast_smem_bytes(const Plan& P);
 int fast_tile_pitch(const Plan& P);                                       // 64 or 128; 0 = a cell is too wide
-void fast_cell_record(const LevelGeom& G, int level, int i, int j, uint4* rec);   // the two table entries of cell (i, j)
+constexpr int FAST_CELL_REC = 4;   // uint4 per cell of the FAST cell table
+void fast_cell_record(const LevelGeom& G, int level, int i, int j, int tp, uint4* rec);   // the table entries of cell (i, j); tp = fast_tile_pitch
 size_t octree_smem_bytes(int capS, int sortCap, int keysCap = 0);   // keysCap 0: the larger of the two kernel forms
 
 }  // namespace orbx

@@ -330,7 +330,7 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     const size_t oSlots = take(sizeof(uint32_t) * P.slotSlab * cap), oKeys = take(sizeof(uint32_t) * P.keySlab * cap);
     const size_t oKnode = take(sizeof(uint16_t) * P.keySlab * cap);
     const size_t oLK = take(sizeof(uint32_t) * P.totalNodes * cap), oLC = take(sizeof(int) * MAX_LEVELS * cap);
-    const size_t oCT = take(sizeof(uint4) * 2 * P.totalCells);
+    const size_t oCT = take(sizeof(uint4) * FAST_CELL_REC * P.totalCells);
     // outputs contiguous: counts | kps | desc  (one D2H copy)
     const size_t oOut = off;
     const size_t oCounts = take(sizeof(int) * cap), oKps = take(sizeof(orbx_kp) * P.totalNodes * cap);
@@ -351,11 +351,11 @@ static int ensure_shape(orbx_extractor* ex, int w, int h, int B)
     F.counts = (int*)(base + oCounts);
     F.cellTab = (const uint4*)(base + oCT);
     {   // FAST cell table (ComputeKeyPointsOctTree :789-806)
-        std::vector<uint4> tab(2 * (size_t)P.totalCells);
+        std::vector<uint4> tab(FAST_CELL_REC * (size_t)P.totalCells);
         for (int l = 0; l < ex->nlevels; l++) {
             const LevelGeom& G = P.lv[l];
             for (int i = 0; i < G.nRows; i++)
-                for (int j = 0; j < G.nCols; j++) fast_cell_record(G, l, i, j, &tab[2 * (size_t)(G.cellBase + i * G.nCols + j)]);
+                for (int j = 0; j < G.nCols; j++) fast_cell_record(G, l, i, j, P.fastPitch, &tab[FAST_CELL_REC * (size_t)(G.cellBase + i * G.nCols + j)]);
         }
         ORBX_CUDA(cudaMemcpyAsync(base + oCT, tab.data(), sizeof(uint4) * tab.size(), cudaMemcpyHostToDevice, ex->stream));
         ORBX_CUDA(cudaStreamSynchronize(ex->stream));
