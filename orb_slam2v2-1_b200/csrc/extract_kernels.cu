@@ -879,7 +879,6 @@ cudaError_t launch_octree(cudaStream_t s, const Plan& P, const FrameBufs& F, int
 //   vertical:   out(y) = 18 h(y-3) + 34 h(y-2) + 48 h(y-1) + 56 h(y) + 48 h(y+1) + 34 h(y+2) + 18 h(y+3) + 32768
 //                      = IDP.2A(P(y-2),(18,34)) + IDP.2A(P(y),(48,56)) + IDP.2A(P(y+2),(48,34)) + IDP.2A(P(y+3),(0,18)),
 //               and the result byte is bits 16..23 of the accumulator (one PRMT tree packs the 4 pixels).
-constexpr int BLUR_COLS = 128;       // output columns per warp: 32 lanes x 4
 constexpr int BLUR_ROWS = 60;        // rows per strip (+ 6 halo rows = 11 blocks of 6)
 constexpr int BLUR_WARPS = 8;
 #ifndef BLUR_MINB
@@ -1005,6 +1004,9 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ img, int 
 #undef BLUR_ROW
 }
 
+// A warp takes 32 consecutive (strip, word) items of a level, word fastest: every lane works whatever the level width (128-column
+// tiles left 11 % of the lanes idle over the pyramid of a 640 x 480 frame); a warp whose lanes straddle two strips, or touch a
+// border, takes the general form of the strip loop.
 __device__ __forceinline__ void blur_tile_body(const Plan& P, const FrameBufs& F, int f, int tile)
 {
     const int lane = threadIdx.x & 31;
@@ -1012,18 +1014,20 @@ __device__ __forceinline__ void blur_tile_body(const Plan& P, const FrameBufs& F
     int l = 0;
     while (l + 1 < P.nlevels && tile >= P.lv[l + 1].blurTileBase) ++l;
     const LevelGeom& G = P.lv[l];
-    const int t = tile - G.blurTileBase;
-    const int ty = t / G.blurTilesX, tx = t - ty * G.blurTilesX;
-    const int w = G.w, h = G.h;
-    const int x = tx * BLUR_COLS + lane * 4;            // first of this lane's 4 columns
-    if (x >= w) return;                                 // no warp-wide operation below: idle lanes leave
-    const int y0 = ty * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
+    const int w = G.w, h = G.h, nw = G.blurTilesX;
+    const int item = (tile - G.blurTileBase) * 32 + lane;
+    const bool active = item < nw * ((h + BLUR_ROWS - 1) / BLUR_ROWS);
+    const int strip = item / nw, x = (item - strip * nw) * 4;                  // first of this lane's 4 columns
+    const int y0 = strip * BLUR_ROWS, y1 = min(y0 + BLUR_ROWS, h);
+    // warp-uniform choice of the strip loop: all lanes interior in y / no lane on the left or right image border
+    const bool interior = __all_sync(0xFFFFFFFFu, !active || (y0 >= 3 && y1 + 3 <= h));
+    const bool plain = __all_sync(0xFFFFFFFFu, !active || (x > 0 && x + 8 <= w));
+    if (!active) return;                                                        // no warp-wide operation below
     int pitch;
     const uint8_t* img = level_plane(P, F, f, l, pitch);
     const BlurEdge E = blur_edge(x, w);
     uint8_t* dst = F.blur + (size_t)f * P.blurSlab + G.blurOff + (size_t)(unsigned)y0 * (unsigned)G.pitch + x;
-    const bool plain = tx > 0 && tx * BLUR_COLS + 31 * 4 + 8 <= w;                                    // warp-uniform, like the next test
-    if (y0 >= 3 && y1 + 3 <= h) {
+    if (interior) {
         if (plain) blur_strip<true, true>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
         else blur_strip<true, false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);
     } else blur_strip<false, false>(img, pitch, h, x, y0, y1, E, dst, G.pitch);

@@ -42,8 +42,8 @@ struct LevelGeom {
     int nIni;             // root nodes of DistributeOctTree (:543)
     int nodeCap;          // capacity of the node list / per-level keypoint output
     int nodeBase;         // first output slot of this level in the per-frame level-key array
-    int blurTileBase;     // first blur tile of this level
-    int blurTilesX;
+    int blurTileBase;     // first blur warp of this level
+    int blurTilesX;       // words (4 columns) per row of the level: the blur's work items are (60-row strip, word) pairs, 32 per warp
     int scaledPatch;      // (int)(31 * mvScaleFactor[level]) (:845)
     float hX;             // root node width (:545)
     float scale;          // mvScaleFactor[level]

@@ -196,9 +196,10 @@ static int build_plan(orbx_extractor* ex, int w, int h)
         capS = std::max(capS, std::max(G.quota + 4, 4 * G.nIni) + 4);
         G.nodeBase = nodes;
         nodes += G.nodeCap;
-        G.blurTilesX = (G.w + 127) / 128;        // k_blur: 128 output columns x 60 rows per warp
+        // k_blur: a lane owns one word (4 columns) of one 60-row strip; the (strip, word) items of a level are dealt to warps 32 at a time
+        G.blurTilesX = (G.w + 3) / 4;            // words per row
         G.blurTileBase = tiles;
-        tiles += G.blurTilesX * ((G.h + 59) / 60);
+        tiles += (G.blurTilesX * ((G.h + 59) / 60) + 31) / 32;
         G.scaledPatch = (int)(31 * ex->mvScaleFactor[l]);            // PATCH_SIZE*mvScaleFactor[level] (:845)
         G.scale = ex->mvScaleFactor[l];
         G.planeOff = pyr;
