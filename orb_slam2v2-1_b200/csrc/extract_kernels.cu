@@ -1249,10 +1249,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
     }
 }
 
-// The same operator with 32 keypoints per warp (TMA form only).  Everything that is one value per keypoint -- the level
+// The same operator with KPW (16) keypoints per warp (TMA form only).  Everything that is one value per keypoint -- the level
 // look-up, fastAtan2, the double-precision sincosf restatement (85 of the 614 warp instructions per keypoint of the kernel
 // above), the 28-byte record -- runs once per WARP with lane k working for keypoint k; the two warp-cooperative parts, the
-// moments (lane = patch words) and the descriptor (lane = descriptor byte), loop over the 32 keypoints with the next
+// moments (lane = patch words) and the descriptor (lane = descriptor byte), loop over the KPW keypoints with the next
 // keypoint's box already in flight (two buffers per warp, two mbarriers per loop) and the 8 float4 pattern entries of the
 // lane held in registers for all of them.
 #ifndef OD32_WARPS_N
@@ -1264,13 +1264,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const Plan 
 constexpr int OD32_WARPS = OD32_WARPS_N;
 constexpr int OD32_BUF = 2432;            // one buffer takes either box (blurred 64 x 37 = 2368 B, unblurred 48 x 31 = 1488 B)
 
+template <int KPW>                        // keypoints per warp (lanes >= KPW idle in the per-keypoint part): 16 by default, see launch_orient_describe
 __global__ void __launch_bounds__(OD32_WARPS * 32, OD32_MINB) k_orient_describe32(const Plan P, const FrameBufs F, const uint2* __restrict__ icTab,
                                                                          const float4* __restrict__ patT,
                                                                          const __grid_constant__ OrientMaps M)
 {
     constexpr unsigned FULL = 0xFFFFFFFFu;
     const int f = blockIdx.y + F.frame0, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    const int g0 = (blockIdx.x * OD32_WARPS + wrp) * 32;               // first keypoint of this warp inside the frame
+    const int g0 = (blockIdx.x * OD32_WARPS + wrp) * KPW;              // first keypoint of this warp inside the frame
     // levels are concatenated in ascending order (:1103): lane i holds the count of level i
     const int myc = lane < P.nlevels ? F.levelCount[(size_t)f * MAX_LEVELS + lane] : 0;
     int inc = myc;
@@ -1282,7 +1283,7 @@ __global__ void __launch_bounds__(OD32_WARPS * 32, OD32_MINB) k_orient_describe3
     const int total = __shfl_sync(FULL, inc, 15);
     if (g0 == 0 && lane == 0) F.counts[f] = total;
     if (g0 >= total) return;
-    const int cnt = min(32, total - g0), g = g0 + lane;
+    const int cnt = min(KPW, total - g0), g = g0 + lane;
     const bool valid = lane < cnt;
 
     // ---- lane k: level, key and centre of keypoint g0 + k
@@ -1422,9 +1423,17 @@ void launch_orient_describe(cudaStream_t s, const Plan& P, const FrameBufs& F, c
         static const bool perWarp32 = !(getenv("ORBX_ORIENT32") && atoi(getenv("ORBX_ORIENT32")) == 0);      // A/B switch
         M.img = *imgMaps;
         M.blur = *blurMaps;
-        if (perWarp32) {
-            dim3 g32((P.totalNodes + OD32_WARPS * 32 - 1) / (OD32_WARPS * 32), B);
-            k_orient_describe32<<<g32, OD32_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+        // Measured (orientation + descriptors, ms): 16 keypoints per warp is the best or tied from ~40 VGA frames per launch up
+        // (48 frames 0.042, 256 frames 0.165, 64 1080p frames 0.182 -- against 0.047 / 0.204 / 0.246 for one keypoint per warp and
+        // 0.052 / 0.180 / 0.234 for 32); below that a warp's serial run of keypoints is the critical path of the launch and the
+        // one-keypoint-per-warp form wins (one frame per call: 0.009 against 0.040 ms with 32 keypoints per warp)
+        static const int kpwEnv = getenv("ORBX_ORIENT_KPW") ? atoi(getenv("ORBX_ORIENT_KPW")) : 0;      // tuning override: 1 / 8 / 16 / 32
+        const int kpw = kpwEnv ? kpwEnv : ((long long)B * P.totalNodes >= 36000 ? 16 : 1);
+        if (perWarp32 && kpw > 1) {
+            dim3 g32((P.totalNodes + OD32_WARPS * kpw - 1) / (OD32_WARPS * kpw), B);
+            if (kpw == 32) k_orient_describe32<32><<<g32, OD32_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+            else if (kpw == 16) k_orient_describe32<16><<<g32, OD32_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
+            else k_orient_describe32<8><<<g32, OD32_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
         } else
             k_orient_describe<true><<<grd, DESC_WARPS * 32, 0, s>>>(P, F, icTab, patT, M);
     } else {
