@@ -53,7 +53,7 @@ for n, x in enumerate(rows[hdr + 1:]):
     name = re.sub(r"^void ", "", x[ki]).split("(")[0].replace("orbx::", "")
     ns = int(float(x[vi].replace(",", "")))
     out.append("%d,%s,(%s),(%s),%d" % (n, name, x[gi].strip("()").replace(", ", "x"), x[bi].strip("()").replace(", ", "x"), ns))
-    share[name.split("<")[0]] += ns
+    share[name.split("<")[0].replace("k_orient_describe32", "k_orient_describe")] += ns
 open(os.path.join(ROOT, "profiles", tag + "_launches_b512.csv"), "w").write("\n".join(out) + "\n")
 tot = sum(v for k, v in share.items() if k in names)
 print(table)
