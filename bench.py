@@ -412,7 +412,8 @@ def run_ours(args, cfg):
     dL, dR = make_inputs(cfg, nd, cfg["seed"] + 1000 * rank)       # units are independent: every rank has its own
     hostL = np.ascontiguousarray(np.tile(dL, (B // nd + 1, 1, 1))[:B])
     hostR = np.ascontiguousarray(np.tile(dR, (B // nd + 1, 1, 1))[:B]) if stereo else None
-    pitch = (W + 3) & ~3                                           # the device entry point wants 4-byte aligned rows
+    pitch = (W + 15) & ~15                                         # rows on 16-byte boundaries: what a caller who keeps frames in HBM would do (the TMA
+                                                                   # staging needs it; 4-byte aligned rows are accepted and take the LDGSTS kernels)
     devL = padded_device(hostL, pitch)                             # B x H x pitch u8, resident in HBM, larger than L2
     devR = padded_device(hostR, pitch) if stereo else None
     exL = orbx.ORBextractor(*params(cfg), device=local, max_batch=B)
