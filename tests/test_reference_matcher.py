@@ -1,0 +1,72 @@
+"""The product's ORBmatcher against the UNMODIFIED reference src/ORBmatcher.cc (oracle/_ref/libmatcher_ref.so: the reference's file
+compiled where it lies over the cv shim and stand-in Frame / KeyFrame / MapPoint objects, oracle/ref_shim/slam) on the same objects.
+CPU leg: the library is built and exports every entry point of matcher_ref.h, and the test program compiles against it.
+GPU leg: tests/native/reference_matcher_test.cpp runs every search both ways and exits non-zero on any difference."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "orb_slam2v2-1_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+REFLIB = os.path.join(ROOT, "oracle", "_ref", "libmatcher_ref.so")
+
+
+def _reflib():
+    """oracle/_ref/libmatcher_ref.so: built here from /root/reference when that exists, else the prebuilt file that travelled."""
+    if os.path.isdir("/root/reference"):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "_ref"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(REFLIB):
+        pytest.skip("oracle/_ref/libmatcher_ref.so is not built and /root/reference is absent")
+    return REFLIB
+
+
+def _build(tmp_path):
+    import orbx
+    _reflib()
+    if not os.path.exists(orbx.LIB_PATH):
+        sys.path.insert(0, ROOT)
+        import __graft_entry__ as g
+        g.build()
+    exe = str(tmp_path / "refmatch")
+    libdir, refdir = os.path.dirname(orbx.LIB_PATH), os.path.dirname(REFLIB)
+    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-Werror", "-DORBX_USE_OPENCV", "-I", os.path.join(ROOT, "include"),
+                           "-I", os.path.join(ROOT, "oracle", "ref_shim"), "-I", os.path.join(ROOT, "oracle", "ref_shim", "slam"),
+                           "-o", exe, os.path.join(ROOT, "tests", "native", "reference_matcher_test.cpp"),
+                           "-L", libdir, "-lorbx", "-Wl,-rpath," + libdir, "-L", refdir, "-lmatcher_ref", "-Wl,-rpath," + refdir])
+    return exe
+
+
+def test_reference_matcher_library_exports_every_entry_point(tmp_path):
+    lib = _reflib()
+    syms = subprocess.run(["nm", "-DC", lib], capture_output=True, text=True, check=True).stdout
+    for name in ("refm::SearchByProjection(float, bool, ORB_SLAM2_REF::Frame&, std::vector", "refm::SearchByProjection(float, bool, ORB_SLAM2_REF::Frame&, ORB_SLAM2_REF::Frame const&",
+                 "refm::SearchByProjection(float, bool, ORB_SLAM2_REF::Frame&, ORB_SLAM2_REF::KeyFrame*", "refm::SearchByProjection(float, bool, ORB_SLAM2_REF::KeyFrame*, cv::Mat",
+                 "refm::SearchByBoW(float, bool, ORB_SLAM2_REF::KeyFrame*, ORB_SLAM2_REF::Frame&", "refm::SearchByBoW(float, bool, ORB_SLAM2_REF::KeyFrame*, ORB_SLAM2_REF::KeyFrame*",
+                 "refm::SearchForInitialization", "refm::SearchForTriangulation", "refm::SearchBySim3", "refm::Fuse(float, bool, ORB_SLAM2_REF::KeyFrame*, std::vector",
+                 "refm::Fuse(float, bool, ORB_SLAM2_REF::KeyFrame*, cv::Mat", "refm::DescriptorDistance",
+                 # the reference's own class, under the renamed namespace
+                 "ORB_SLAM2_REF::ORBmatcher::SearchByBoW", "ORB_SLAM2_REF::ORBmatcher::ComputeThreeMaxima", "ORB_SLAM2_REF::ORBmatcher::DescriptorDistance"):
+        assert name in syms, name
+    _build(tmp_path)        # the test program compiles and links against it
+
+
+def _views(tmp_path, w, h, seed, dx, dy):
+    from orbx import synth
+    a = synth.rects(w, h, seed)
+    rng = np.random.default_rng(seed)
+    b = np.clip(np.roll(a, (dy, dx), axis=(0, 1)).astype(np.int16) + rng.integers(-3, 4, a.shape), 0, 255).astype(np.uint8)
+    (tmp_path / "a.raw").write_bytes(a.tobytes())
+    (tmp_path / "b.raw").write_bytes(b.tobytes())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy", [(640, 480, 1000, 2100, 3, 1), (752, 480, 1200, 2200, -4, 2), (640, 480, 2000, 2300, 2, -3)])
+def test_searches_equal_the_reference_matcher(tmp_path, w, h, nf, seed, dx, dy):
+    exe = _build(tmp_path)
+    _views(tmp_path, w, h, seed, dx, dy)
+    r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.rstrip().endswith("ok"), (r.returncode, r.stdout[-3000:], r.stderr[-3000:])
