@@ -112,6 +112,279 @@ static bool same_points(const std::vector<MapPoint*>& a, const std::vector<MapPo
 }
 static int assigned(const std::vector<MapPoint*>& v) { int n = 0; for (size_t i = 0; i < v.size(); i++) n += v[i] != NULL; return n; }
 
+// ---- two identical universes of objects for the searches that MUTATE map points and key frames (Fuse): one for the reference, one
+// for the product.  World = camera of view A; view B is the same scene from a camera moved by the image shift at depth Z0.
+struct Universe {
+    Frame FA, FB;
+    std::vector<MapPoint> pa, pb;
+    KeyFrame KA, KB;
+    void build(const Frame& FA0, const Frame& FB0, int w, int h, float dx, float dy)
+    {
+        FA = FA0; FB = FB0;
+        FA.mTcw = pose(0, 0, 0);
+        FB.mTcw = pose(dx * Z0 / FX, dy * Z0 / FY, 0);
+        make_points(pa, FA, Z0);
+        make_points(pb, FB, Z0);
+        for (size_t i = 0; i < pb.size(); i++)           // B's points from B's camera into the world: X_w = X_c - t (R = I)
+            if (FB.mvpMapPoints[i])
+                for (int k = 0; k < 2; k++) pb[i].mWorldPos.at<float>(k) -= FB.mTcw.at<float>(k, 3);
+        fill_keyframe(KA, FA, w, h);
+        fill_keyframe(KB, FB, w, h);
+        for (size_t i = 0; i < pa.size(); i++) if (FA.mvpMapPoints[i]) pa[i].mObservations[&KA] = i;
+        for (size_t i = 0; i < pb.size(); i++) if (FB.mvpMapPoints[i]) pb[i].mObservations[&KB] = i;
+    }
+    int id(const MapPoint* p) const
+    {
+        if (!p) return -1;
+        if (!pa.empty() && p >= &pa[0] && p <= &pa[pa.size() - 1]) return (int)(p - &pa[0]);
+        if (!pb.empty() && p >= &pb[0] && p <= &pb[pb.size() - 1]) return (1 << 20) + (int)(p - &pb[0]);
+        return -2;
+    }
+    std::vector<int> ids(const std::vector<MapPoint*>& v) const { std::vector<int> o(v.size()); for (size_t i = 0; i < v.size(); i++) o[i] = id(v[i]); return o; }
+    // everything Fuse can change
+    std::vector<int> state() const
+    {
+        std::vector<int> o = ids(KA.mvpMapPoints), b = ids(KB.mvpMapPoints);
+        o.insert(o.end(), b.begin(), b.end());
+        for (int set = 0; set < 2; set++) {
+            const std::vector<MapPoint>& v = set ? pb : pa;
+            for (size_t i = 0; i < v.size(); i++) {
+                o.push_back(v[i].bad); o.push_back(v[i].nObs); o.push_back(id(v[i].mpReplaced));
+                o.push_back(v[i].mObservations.count(const_cast<KeyFrame*>(&KA)) ? (int)v[i].mObservations.find(const_cast<KeyFrame*>(&KA))->second : -1);
+                o.push_back(v[i].mObservations.count(const_cast<KeyFrame*>(&KB)) ? (int)v[i].mObservations.find(const_cast<KeyFrame*>(&KB))->second : -1);
+            }
+        }
+        return o;
+    }
+};
+
+static ORB_SLAM2::FrameView view_of(const KeyFrame& K)
+{
+    ORB_SLAM2::FrameView v = {&K.mvKeysUn, &K.mDescriptors, (float)K.mnMinX, (float)K.mnMaxX, (float)K.mnMinY, (float)K.mnMaxY};
+    return v;
+}
+
+// What a caller does before handing points to the array forms: the reference's own projection and skip tests,
+// written with the same cv::Mat expressions as ORBmatcher.cc:850-889 / :1011-1056 / :321-362.  Returns false where the reference `continue`s.
+static bool project_into_keyframe(KeyFrame* pKF, const cv::Mat& Rcw, const cv::Mat& tcw, const cv::Mat& Ow, MapPoint* pMP, bool oneOverZdouble,
+                                  float& u, float& v, float& invz, int& level)
+{
+    cv::Mat p3Dw = pMP->GetWorldPos();
+    cv::Mat p3Dc = Rcw * p3Dw + tcw;
+    if (p3Dc.at<float>(2) < 0.0f) return false;
+    invz = oneOverZdouble ? (float)(1.0 / p3Dc.at<float>(2)) : 1 / p3Dc.at<float>(2);          // `1.0/z` (:1022) resp. `1/z` (:861, :330)
+    const float x = p3Dc.at<float>(0) * invz, y = p3Dc.at<float>(1) * invz;
+    u = pKF->fx * x + pKF->cx;
+    v = pKF->fy * y + pKF->cy;
+    if (!pKF->IsInImage(u, v)) return false;
+    const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+    cv::Mat PO = p3Dw - Ow;
+    const float dist3D = cv::norm(PO);
+    if (dist3D < minDistance || dist3D > maxDistance) return false;
+    cv::Mat Pn = pMP->GetNormal();
+    if (PO.dot(Pn) < 0.5 * dist3D) return false;
+    level = pMP->PredictScale(dist3D, pKF);
+    return true;
+}
+
+static void push_point(ORB_SLAM2::ORBmatcher::ProjectedPoints& P, float u, float v, float ur, int level, float angle, MapPoint* pMP)
+{
+    P.xy.push_back(u); P.xy.push_back(v); P.xr.push_back(ur); P.level.push_back(level); P.viewCosOrAngle.push_back(angle);
+    const cv::Mat d = pMP->GetDescriptor();
+    P.descriptors.insert(P.descriptors.end(), d.ptr<uint8_t>(0), d.ptr<uint8_t>(0) + 32);
+    P.hasObservations.push_back(pMP->Observations() > 0);
+}
+
+static cv::Mat sim3(const cv::Mat& T, float s)          // [s R | s t; 0 1]
+{
+    cv::Mat S = T.clone();
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 4; c++) S.at<float>(r, c) *= s;
+    return S;
+}
+
+static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, float dx, float dy, float nn, bool checkOri, ORB_SLAM2::ORBmatcher& mine)
+{
+    typedef ORB_SLAM2::ORBmatcher::ProjectedPoints Projected;
+    // ---- Fuse(pKF, vpMapPoints, th)  (ORBmatcher.cc:827-977, LocalMapping::SearchInNeighbors)
+    {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        std::vector<MapPoint*> vr = R.FA.mvpMapPoints, vm = M.FA.mvpMapPoints;          // A's points (with NULLs and bad ones) into key frame B
+        const float th = 3.f;
+        const int nr = refm::Fuse(nn, checkOri, &R.KB, vr, th);
+        KeyFrame* pKF = &M.KB;
+        cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();
+        Projected P;
+        std::vector<int> who;
+        for (size_t i = 0; i < vm.size(); i++) {
+            MapPoint* pMP = vm[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            float u, v, invz; int level;
+            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, false, u, v, invz, level)) continue;
+            push_point(P, u, v, u - pKF->mbf * invz, level, 0.f, pMP);
+            who.push_back((int)i);
+        }
+        std::vector<int> best;
+        mine.Fuse(view_of(*pKF), pKF->mvuRight, pKF->mvScaleFactors, pKF->mvInvLevelSigma2, P, best, th);
+        int nm = 0;
+        for (size_t j = 0; j < best.size(); j++) {          // :940-957
+            if (best[j] < 0) continue;
+            MapPoint* pMP = vm[who[j]];
+            MapPoint* pMPinKF = pKF->GetMapPoint(best[j]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) {
+                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                    else pMPinKF->Replace(pMP);
+                }
+            } else {
+                pMP->AddObservation(pKF, best[j]);
+                pKF->AddMapPoint(pMP, best[j]);
+            }
+            nm++;
+        }
+        CHECK(nr == nm && R.state() == M.state(), "Fuse(KeyFrame, MapPoints)");
+        printf("Fuse(KF, MPs): %d fused of %d projected\n", nr, (int)who.size());
+        CHECK(nr > (int)vr.size() / 10, "Fuse(KeyFrame, MapPoints): too few fused");
+    }
+    // ---- Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)  (:979-1102, LoopClosing::SearchAndFuse)
+    {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        std::vector<MapPoint*> vr, vm;
+        for (size_t i = 0; i < R.pa.size(); i++) if (R.FA.mvpMapPoints[i]) { vr.push_back(&R.pa[i]); vm.push_back(&M.pa[i]); }
+        const float th = 4.f;
+        std::vector<MapPoint*> repR(vr.size(), static_cast<MapPoint*>(NULL)), repM(vm.size(), static_cast<MapPoint*>(NULL));
+        const int nr = refm::Fuse(nn, checkOri, &R.KB, sim3(R.KB.Tcw, 1.25f), vr, th, repR);
+        KeyFrame* pKF = &M.KB;
+        cv::Mat Scw = sim3(M.KB.Tcw, 1.25f);
+        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);                              // :988-992
+        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+        cv::Mat Rcw = sRcw / scw;
+        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+        cv::Mat Ow = -Rcw.t() * tcw;
+        const std::set<MapPoint*> found = pKF->GetMapPoints();
+        Projected P;
+        std::vector<int> who;
+        for (size_t i = 0; i < vm.size(); i++) {
+            MapPoint* pMP = vm[i];
+            if (pMP->isBad() || found.count(pMP)) continue;
+            float u, v, invz; int level;
+            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, true, u, v, invz, level)) continue;
+            push_point(P, u, v, -1.f, level, 0.f, pMP);
+            who.push_back((int)i);
+        }
+        std::vector<int> best;
+        mine.Fuse(view_of(*pKF), pKF->mvScaleFactors, P, best, th);
+        int nm = 0;
+        for (size_t j = 0; j < best.size(); j++) {          // :1083-1095
+            if (best[j] < 0) continue;
+            MapPoint* pMP = vm[who[j]];
+            MapPoint* pMPinKF = pKF->GetMapPoint(best[j]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) repM[who[j]] = pMPinKF;
+            } else {
+                pMP->AddObservation(pKF, best[j]);
+                pKF->AddMapPoint(pMP, best[j]);
+            }
+            nm++;
+        }
+        CHECK(nr == nm && R.state() == M.state() && R.ids(repR) == M.ids(repM), "Fuse(KeyFrame, Scw, MapPoints)");
+        printf("Fuse(KF, Scw, MPs): %d fused of %d projected\n", nr, (int)who.size());
+        CHECK(nr > (int)vr.size() / 10, "Fuse(KeyFrame, Scw, MapPoints): too few fused");
+    }
+    // ---- SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)  (:290-403, LoopClosing::ComputeSim3)
+    {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        std::vector<MapPoint*> vr, vm;
+        for (size_t i = 0; i < R.pa.size(); i++) if (R.FA.mvpMapPoints[i]) { vr.push_back(&R.pa[i]); vm.push_back(&M.pa[i]); }
+        // already matched: every sixth feature of B holds its own point, and a few of A's points are among them
+        std::vector<MapPoint*> mr(R.KB.N, static_cast<MapPoint*>(NULL)), mm(M.KB.N, static_cast<MapPoint*>(NULL));
+        for (int i = 0; i < R.KB.N; i += 6) { mr[i] = R.KB.mvpMapPoints[i]; mm[i] = M.KB.mvpMapPoints[i]; }
+        for (size_t i = 1; i < vr.size() && 7 * i + 1 < mr.size(); i += 9) { mr[7 * i + 1] = vr[i]; mm[7 * i + 1] = vm[i]; }
+        const int th = 10;
+        const int nr = refm::SearchByProjection(nn, checkOri, &R.KB, sim3(R.KB.Tcw, 0.8f), vr, mr, th);
+        KeyFrame* pKF = &M.KB;
+        cv::Mat Scw = sim3(M.KB.Tcw, 0.8f);
+        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);                              // :299-303
+        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+        cv::Mat Rcw = sRcw / scw;
+        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+        cv::Mat Ow = -Rcw.t() * tcw;
+        std::set<MapPoint*> found(mm.begin(), mm.end());
+        found.erase(static_cast<MapPoint*>(NULL));
+        Projected P;
+        std::vector<int> who;
+        for (size_t i = 0; i < vm.size(); i++) {
+            MapPoint* pMP = vm[i];
+            if (pMP->isBad() || found.count(pMP)) continue;
+            float u, v, invz; int level;
+            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, false, u, v, invz, level)) continue;
+            push_point(P, u, v, -1.f, level, 0.f, pMP);
+            who.push_back((int)i);
+        }
+        std::vector<uint8_t> vbMatched(mm.size());
+        for (size_t j = 0; j < mm.size(); j++) vbMatched[j] = mm[j] != NULL;
+        std::vector<int> vnMatch;
+        const int nm = mine.SearchByProjection(view_of(*pKF), vbMatched, pKF->mvScaleFactors, P, vnMatch, th);
+        for (size_t j = 0; j < vnMatch.size(); j++) if (vnMatch[j] >= 0) mm[j] = vm[who[vnMatch[j]]];       // :396
+        CHECK(nr == nm && R.ids(mr) == M.ids(mm), "SearchByProjection(KeyFrame, Scw, MapPoints)");
+        printf("SearchByProjection(KF, Scw, MPs): %d matches of %d projected\n", nr, (int)who.size());
+        CHECK(nr > (int)vr.size() / 10, "SearchByProjection(KeyFrame, Scw, MapPoints): too few matches");
+    }
+    // ---- SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)  (:1474-1601, Tracking::Relocalization)
+    for (int variant = 0; variant < 2; variant++) {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        std::set<MapPoint*> foundR, foundM;
+        for (size_t i = 0; i < R.pa.size(); i += 5) if (R.FA.mvpMapPoints[i]) { foundR.insert(&R.pa[i]); foundM.insert(&M.pa[i]); }
+        // the current frame keeps a third of its own points (occupied slots), the rest is free
+        for (int i = 0; i < R.FB.N; i++) if (i % 3) { R.FB.mvpMapPoints[i] = NULL; M.FB.mvpMapPoints[i] = NULL; }
+        const float th = variant ? 3.f : 10.f;
+        const int ORBdist = variant ? 64 : 100;
+        const int nr = refm::SearchByProjection(nn, checkOri, R.FB, &R.KA, foundR, th, ORBdist);
+        Frame& F = M.FB;
+        KeyFrame* pKF = &M.KA;
+        const cv::Mat Rcw = F.mTcw.rowRange(0, 3).colRange(0, 3);                      // :1478-1480
+        const cv::Mat tcw = F.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat Ow = -Rcw.t() * tcw;
+        const std::vector<MapPoint*> vpMPs = pKF->GetMapPointMatches();
+        Projected P;
+        std::vector<int> who;
+        for (size_t i = 0; i < vpMPs.size(); i++) {
+            MapPoint* pMP = vpMPs[i];
+            if (!pMP || pMP->isBad() || foundM.count(pMP)) continue;
+            cv::Mat x3Dw = pMP->GetWorldPos();                                         // :1499-1531
+            cv::Mat x3Dc = Rcw * x3Dw + tcw;
+            const float xc = x3Dc.at<float>(0), yc = x3Dc.at<float>(1);
+            const float invzc = 1.0 / x3Dc.at<float>(2);
+            const float u = F.fx * xc * invzc + F.cx, v = F.fy * yc * invzc + F.cy;
+            if (u < F.mnMinX || u > F.mnMaxX) continue;
+            if (v < F.mnMinY || v > F.mnMaxY) continue;
+            cv::Mat PO = x3Dw - Ow;
+            float dist3D = cv::norm(PO);
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            push_point(P, u, v, -1.f, pMP->PredictScale(dist3D, &F), pKF->mvKeysUn[i].angle, pMP);
+            who.push_back((int)i);
+        }
+        std::vector<uint8_t> occupied(F.N);
+        for (int j = 0; j < F.N; j++) occupied[j] = F.mvpMapPoints[j] != NULL;
+        std::vector<int> vnMatch;
+        ORB_SLAM2::FrameView fv = {&F.mvKeysUn, &F.mDescriptors, Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY};
+        const int nm = mine.SearchByProjection(fv, occupied, F.mvScaleFactors, P, vnMatch, th, ORBdist);
+        for (size_t j = 0; j < vnMatch.size(); j++) if (vnMatch[j] >= 0) F.mvpMapPoints[j] = vpMPs[who[vnMatch[j]]];       // :1551
+        CHECK(nr == nm && R.ids(R.FB.mvpMapPoints) == M.ids(M.FB.mvpMapPoints), "SearchByProjection(Frame, KeyFrame)");
+        printf("SearchByProjection(F, KF) variant %d: %d matches of %d projected\n", variant, nr, (int)who.size());
+        CHECK(nr > R.FA.N / 12, "SearchByProjection(Frame, KeyFrame): too few matches");
+    }
+}
+
+
 static int run(char** argv)
 {
     const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
@@ -214,6 +487,7 @@ static int run(char** argv)
             printf("SearchForInitialization checkOri %d: %d matches\n", co, nr);
             CHECK(nr > FA.N / 20, "SearchForInitialization: too few matches");
         }
+        map_side_searches(FA, FBbare, w, h, dx, dy, nn, checkOri, mine);
     }
     // ---- DescriptorDistance (:1649-1665)
     for (int i = 0; i + 1 < FA.N; i += 7)
