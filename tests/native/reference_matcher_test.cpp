@@ -385,6 +385,129 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
 }
 
 
+// one direction of SearchBySim3's flattening (ORBmatcher.cc:1145-1183 resp. :1225-1263): one entry per feature of the source key frame,
+// level -1 where the reference skips it
+static void project_sim3(KeyFrame* src, KeyFrame* dst, const std::vector<MapPoint*>& vpSrc, const std::vector<bool>& matched, const cv::Mat& Rsw,
+                         const cv::Mat& tsw, const cv::Mat& sRds, const cv::Mat& tds, ORB_SLAM2::ORBmatcher::ProjectedPoints& P)
+{
+    const std::vector<uint8_t> none(32, 0);
+    for (size_t i = 0; i < vpSrc.size(); i++) {
+        MapPoint* pMP = vpSrc[i];
+        float u = 0, v = 0;
+        int level = -1;
+        if (pMP && !matched[i] && !pMP->isBad()) {
+            cv::Mat p3Dw = pMP->GetWorldPos();
+            cv::Mat p3Dcs = Rsw * p3Dw + tsw;
+            cv::Mat p3Dcd = sRds * p3Dcs + tds;
+            if (!(p3Dcd.at<float>(2) < 0.0)) {
+                const float invz = 1.0 / p3Dcd.at<float>(2);
+                const float x = p3Dcd.at<float>(0) * invz, y = p3Dcd.at<float>(1) * invz;
+                u = src->fx * x + src->cx;                                       // the reference takes fx .. cy from pKF1 for both directions (:1107-1110)
+                v = src->fy * y + src->cy;
+                if (dst->IsInImage(u, v)) {
+                    const float dist3D = cv::norm(p3Dcd);
+                    if (!(dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance())) level = pMP->PredictScale(dist3D, dst);
+                }
+            }
+        }
+        P.xy.push_back(u); P.xy.push_back(v); P.xr.push_back(-1.f); P.level.push_back(level); P.viewCosOrAngle.push_back(0.f);
+        if (level >= 0) {
+            const cv::Mat d = pMP->GetDescriptor();
+            P.descriptors.insert(P.descriptors.end(), d.ptr<uint8_t>(0), d.ptr<uint8_t>(0) + 32);
+        } else
+            P.descriptors.insert(P.descriptors.end(), none.begin(), none.end());
+        P.hasObservations.push_back(1);
+    }
+}
+
+static void loop_and_triangulation_searches(const Frame& FA0, const Frame& FB0, int w, int h, float dx, float dy, float nn, bool checkOri,
+                                            ORB_SLAM2::ORBmatcher& mine)
+{
+    typedef ORB_SLAM2::ORBmatcher::ProjectedPoints Projected;
+    // ---- SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th)  (ORBmatcher.cc:1104-1328, LoopClosing::ComputeSim3)
+    for (int variant = 0; variant < 2; variant++) {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        const float s12 = 1.f, th = variant ? 7.5f : 10.f;
+        cv::Mat R12(3, 3, CV_32F), t12(3, 1, CV_32F);                    // camera 2 -> camera 1: p1 = s12 R12 p2 + t12 = p2 + (t1w - t2w)
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) R12.at<float>(r, c) = r == c ? 1.f : 0.f;
+        for (int k = 0; k < 3; k++) t12.at<float>(k) = R.KA.Tcw.at<float>(k, 3) - R.KB.Tcw.at<float>(k, 3);
+        if (variant) t12.at<float>(0) += 0.004f;
+        std::vector<MapPoint*> mr(R.KA.N, static_cast<MapPoint*>(NULL)), mm(M.KA.N, static_cast<MapPoint*>(NULL));
+        for (int i = 2; i < R.KA.N && i < R.KB.N; i += 10)                // a few pairs known beforehand
+            if (R.KB.mvpMapPoints[i]) { mr[i] = R.KB.mvpMapPoints[i]; mm[i] = M.KB.mvpMapPoints[i]; }
+        const int nr = refm::SearchBySim3(nn, checkOri, &R.KA, &R.KB, mr, s12, R12, t12, th);
+        KeyFrame *pKF1 = &M.KA, *pKF2 = &M.KB;
+        cv::Mat R1w = pKF1->GetRotation(), t1w = pKF1->GetTranslation(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();      // :1113-1123
+        cv::Mat sR12 = s12 * R12;
+        cv::Mat sR21 = (1.0 / s12) * R12.t();
+        cv::Mat t21 = -sR21 * t12;
+        const std::vector<MapPoint*> vp1 = pKF1->GetMapPointMatches(), vp2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vp1.size(), N2 = (int)vp2.size();
+        std::vector<bool> already1(N1, false), already2(N2, false);
+        for (int i = 0; i < N1; i++)
+            if (mm[i]) {
+                already1[i] = true;
+                const int idx2 = mm[i]->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) already2[idx2] = true;
+            }
+        Projected P12, P21;
+        project_sim3(pKF1, pKF2, vp1, already1, R1w, t1w, sR21, t21, P12);
+        project_sim3(pKF1, pKF1, vp2, already2, R2w, t2w, sR12, t12, P21);          // fx .. cy of pKF1, image bounds of pKF1 (:1233-1240)
+        std::vector<int> m12;
+        const int nm = mine.SearchBySim3(view_of(*pKF1), view_of(*pKF2), pKF2->mvScaleFactors, P12, P21, m12, th);
+        for (int i1 = 0; i1 < N1; i1++) if (m12[i1] >= 0) mm[i1] = vp2[m12[i1]];   // :1318
+        CHECK(nr == nm && R.ids(mr) == M.ids(mm), "SearchBySim3");
+        printf("SearchBySim3 variant %d: %d found\n", variant, nr);
+        CHECK(nr > R.KA.N / 12, "SearchBySim3: too few found");
+    }
+    // ---- SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo)  (:657-825, LocalMapping::CreateNewMapPoints)
+    for (int onlyStereo = 0; onlyStereo < 2; onlyStereo++) {
+        Universe R, M;
+        R.build(FA0, FB0, w, h, dx, dy);
+        M.build(FA0, FB0, w, h, dx, dy);
+        // only features WITHOUT a map point take part: free two thirds of them in both key frames
+        for (int i = 0; i < R.KA.N; i++) if (i % 3) { R.KA.mvpMapPoints[i] = NULL; M.KA.mvpMapPoints[i] = NULL; }
+        for (int i = 0; i < R.KB.N; i++) if (i % 3 != 1) { R.KB.mvpMapPoints[i] = NULL; M.KB.mvpMapPoints[i] = NULL; }
+        // fundamental matrix of a translation t = C2 - C1 between identical cameras: F12 = K^-T [t]x K^-1
+        const float tx = R.KB.Tcw.at<float>(0, 3), ty = R.KB.Tcw.at<float>(1, 3), tz = 0.02f;
+        for (int u = 0; u < 2; u++) { Universe& U = u ? M : R; U.KB.Tcw.at<float>(2, 3) = tz; }
+        cv::Mat F12(3, 3, CV_32F);
+        {
+            const double ifx = 1.0 / FX, ify = 1.0 / FY, cx = w * 0.5, cy = h * 0.5;
+            const double Kinv[3][3] = {{ifx, 0, -cx * ifx}, {0, ify, -cy * ify}, {0, 0, 1}};
+            const double tX[3][3] = {{0, -tz, ty}, {tz, 0, -tx}, {-ty, tx, 0}};
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 3; c++) {
+                    double a = 0;
+                    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) a += Kinv[i][r] * tX[i][j] * Kinv[j][c];
+                    F12.at<float>(r, c) = (float)a;
+                }
+        }
+        std::vector<std::pair<size_t, size_t> > pr, pm;
+        const int nr = refm::SearchForTriangulation(nn, checkOri, &R.KA, &R.KB, F12, pr, onlyStereo != 0);
+        KeyFrame *pKF1 = &M.KA, *pKF2 = &M.KB;
+        cv::Mat Cw = pKF1->GetCameraCenter();                                         // :664-672
+        cv::Mat R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+        cv::Mat C2 = R2w * Cw + t2w;
+        const float invz = 1.0f / C2.at<float>(2);
+        const float ex = pKF2->fx * C2.at<float>(0) * invz + pKF2->cx, ey = pKF2->fy * C2.at<float>(1) * invz + pKF2->cy;
+        std::vector<uint8_t> has1(pKF1->N), has2(pKF2->N);
+        for (int i = 0; i < pKF1->N; i++) has1[i] = pKF1->GetMapPoint(i) != NULL;
+        for (int i = 0; i < pKF2->N; i++) has2[i] = pKF2->GetMapPoint(i) != NULL;
+        const ORB_SLAM2::ORBmatcher::FeatureVectorCSR fv1 = ORB_SLAM2::ORBmatcher::FeatureVectorCSR::from(pKF1->mFeatVec),
+                                                      fv2 = ORB_SLAM2::ORBmatcher::FeatureVectorCSR::from(pKF2->mFeatVec);
+        ORB_SLAM2::ORBmatcher::KeyFrameState S1 = {&has1, &pKF1->mvuRight, &fv1}, S2 = {&has2, &pKF2->mvuRight, &fv2};
+        const int nm = mine.SearchForTriangulation(view_of(*pKF1), S1, view_of(*pKF2), S2, F12, ex, ey, pKF2->mvScaleFactors, pKF2->mvLevelSigma2, pm,
+                                                   onlyStereo != 0);
+        CHECK(nr == nm && pr == pm, "SearchForTriangulation");
+        printf("SearchForTriangulation onlyStereo %d: %d pairs\n", onlyStereo, nr);
+        if (!onlyStereo) CHECK(nr > R.KA.N / 20, "SearchForTriangulation: too few pairs");
+    }
+}
+
+
 static int run(char** argv)
 {
     const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
@@ -488,6 +611,7 @@ static int run(char** argv)
             CHECK(nr > FA.N / 20, "SearchForInitialization: too few matches");
         }
         map_side_searches(FA, FBbare, w, h, dx, dy, nn, checkOri, mine);
+        loop_and_triangulation_searches(FA, FBbare, w, h, dx, dy, nn, checkOri, mine);
     }
     // ---- DescriptorDistance (:1649-1665)
     for (int i = 0; i + 1 < FA.N; i += 7)
