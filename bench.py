@@ -540,16 +540,30 @@ def e2e_leg(args, cfg, S):
         pool.set_fma_mode(1)
         cap = pool.plan(W, H)
         scapacity = cap
-        pk = torch.zeros((B, cap, 28), dtype=torch.uint8).pin_memory()
-        pd = torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory()
-        nn = np.zeros(B, np.int32)
+        # two steps in flight (orbx_pool_submit_batch / orbx_pool_wait), each with its own result arrays: the lanes go from the last
+        # chunks of one step to the first of the next without the fill / drain gap of a synchronous call per step -- what the stereo
+        # leg's worker threads do by themselves.  Every step's H2D, kernels and D2H lie inside the timed region.
+        DEPTH = 2
+        outs_ = [(torch.zeros((B, cap, 28), dtype=torch.uint8).pin_memory(), torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory(),
+                  np.zeros(B, np.int32)) for _ in range(DEPTH)]
+        pk, pd, nn = outs_[0]
         ptrs = (C.c_void_p * B)(*[pinned[0][1] + i * frame for i in range(B)])
 
         def run(nsteps):
-            for _ in range(nsteps):
-                rc = L.orbx_pool_extract_batch(pool._h, ptrs, B, W, H, P32, C.c_void_p(pk.data_ptr()), C.c_void_p(pd.data_ptr()), cap,
-                                               nn.ctypes.data_as(C.c_void_p))
+            tickets = []
+            for s_ in range(nsteps):
+                if len(tickets) == DEPTH:
+                    if L.orbx_pool_wait(pool._h, tickets.pop(0)) != 0:
+                        raise RuntimeError(L.orbx_last_error().decode())
+                k_, d_, n_ = outs_[s_ % DEPTH]
+                t_ = C.c_ulonglong(0)
+                rc = L.orbx_pool_submit_batch(pool._h, ptrs, B, W, H, P32, C.c_void_p(k_.data_ptr()), C.c_void_p(d_.data_ptr()), cap,
+                                              n_.ctypes.data_as(C.c_void_p), C.byref(t_))
                 if rc != 0:
+                    raise RuntimeError(L.orbx_last_error().decode())
+                tickets.append(t_.value)
+            for t_ in tickets:
+                if L.orbx_pool_wait(pool._h, t_) != 0:
                     raise RuntimeError(L.orbx_last_error().decode())
 
         run(1)
@@ -626,7 +640,7 @@ def e2e_leg(args, cfg, S):
     if stereo:
         how = "orbx_extract_batch (left, right) + orbm_stereo_matches_batch on pinned host frames into pinned host results, %d handle sets x %d-pair chunks on %d host threads" % (nthreads, chunk, nthreads)
     else:
-        how = "orbx_pool_extract_batch (the library's multi-GPU driver, this rank's GPU): pinned host frames in, pinned host results out, %d lanes x %d-frame chunks" % (nthreads, chunk)
+        how = "orbx_pool_submit_batch / orbx_pool_wait (the library's multi-GPU driver, this rank's GPU; two steps in flight): pinned host frames in, pinned host results out, %d lanes x %d-frame chunks" % (nthreads, chunk)
     value = B * world * args.steps / e2e_s
     ceiling = {"h2d_GBps_this_rank": h2d_gbs, "e2e_h2d_GBps_this_rank": value / world * h2d / B / 1e9,
                "frac": (value / world * h2d / B / 1e9) / h2d_gbs,

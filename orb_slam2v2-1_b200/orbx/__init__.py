@@ -61,6 +61,8 @@ def lib():
         "orbx_pool_set_fma_mode": (i, [vp, i]),
         "orbx_pool_plan": (i, [vp, i, i, vp]),
         "orbx_pool_extract_batch": (i, [vp, vp, i, i, i, sz, vp, vp, i, vp]),
+        "orbx_pool_submit_batch": (i, [vp, vp, i, i, i, sz, vp, vp, i, vp, vp]),
+        "orbx_pool_wait": (i, [vp, C.c_ulonglong]),
         "orbx_results_device": (i, [vp, vp, vp, vp, vp]),
         "orbx_sync": (i, [vp]),
         "orbx_stream": (vp, [vp]),
@@ -444,6 +446,32 @@ class ExtractorPool:
         ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
         _check(self._L.orbx_pool_extract_batch(self._h, ptrs, B, ww, hh, imgs[0].strides[0], _p(kps), _p(desc), cap, _p(n)))
         return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
+
+    def submit(self, images):
+        """orbx_pool_submit_batch: queue a batch and return a ticket object; several may be in flight.  wait(ticket) -> results."""
+        imgs = [_u8(im) for im in images]
+        B = len(imgs)
+        if B == 0:
+            return None
+        hh, ww = imgs[0].shape
+        cap = self._caps.get((ww, hh)) if hasattr(self, "_caps") else None
+        if cap is None:
+            cap = self.plan(ww, hh)                 # planning waits for the batches in flight
+            self.__dict__.setdefault("_caps", {})[(ww, hh)] = cap
+        kps = np.zeros((B, cap), KP_DTYPE)
+        desc = np.zeros((B, cap, 32), np.uint8)
+        n = np.zeros(B, np.int32)
+        ptrs = (C.c_void_p * B)(*[im.ctypes.data for im in imgs])
+        t = C.c_ulonglong(0)
+        _check(self._L.orbx_pool_submit_batch(self._h, ptrs, B, ww, hh, imgs[0].strides[0], _p(kps), _p(desc), cap, _p(n), C.byref(t)))
+        return (t.value, imgs, kps, desc, n)        # the ticket keeps the frames and the result arrays alive
+
+    def wait(self, ticket):
+        if ticket is None:
+            return []
+        t, _imgs, kps, desc, n = ticket
+        _check(self._L.orbx_pool_wait(self._h, t))
+        return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(len(n))]
 
 
 class ORBmatcher:

@@ -73,3 +73,25 @@ def test_pool_reports_errors_of_its_workers():
     with pytest.raises(orbx.OrbxError):
         orbx.ExtractorPool(500, devices=[0, 0])
     pool.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunk,lanes", [(2, 3), (5, 2)])
+def test_pool_batches_in_flight_equal_synchronous_calls(chunk, lanes):
+    """orbx_pool_submit_batch / orbx_pool_wait: several batches queued at once (different sizes, one with a frame without keypoints, one
+    empty), waited for out of order -- every batch gets what a synchronous call gives, and an unknown ticket is an error."""
+    oe = O.OracleExtractor(500, 1.2, 8, 20, 7)
+    batches = [_frames(7, seed=60), _frames(3, seed=80) + [synth.flat(320, 240)], [], _frames(11, seed=100)]
+    pool = orbx.ExtractorPool(500, 1.2, 8, 20, 7, devices=[0], chunk=chunk, lanes=lanes)
+    for _ in range(2):
+        tickets = [pool.submit(b) for b in batches]
+        for i in (3, 0, 2, 1):
+            got = pool.wait(tickets[i])
+            assert len(got) == len(batches[i])
+            for (k, d), f in zip(got, batches[i]):
+                ok, od = oe(f)
+                assert k.tobytes() == ok.tobytes() and np.array_equal(d, od)
+    assert orbx.lib().orbx_pool_wait(pool._h, 12345) == orbx.ERR_ARG
+    sync = pool.extract_batch(batches[0])                    # the synchronous form still works afterwards
+    assert len(sync) == 7
+    pool.close()
