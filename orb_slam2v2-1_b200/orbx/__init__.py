@@ -413,6 +413,7 @@ class ExtractorPool:
             arr = (C.c_int * len(devices))(*devices)
             _check(self._L.orbx_pool_create(arr, len(devices), nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, chunk, lanes, C.byref(h)))
         self._h = h
+        self._caps = {}                             # per-frame keypoint capacity of the shapes planned so far
 
     def close(self):
         if getattr(self, "_h", None):
@@ -454,10 +455,9 @@ class ExtractorPool:
         if B == 0:
             return None
         hh, ww = imgs[0].shape
-        cap = self._caps.get((ww, hh)) if hasattr(self, "_caps") else None
+        cap = self._caps.get((ww, hh))
         if cap is None:
-            cap = self.plan(ww, hh)                 # planning waits for the batches in flight
-            self.__dict__.setdefault("_caps", {})[(ww, hh)] = cap
+            cap = self._caps[(ww, hh)] = self.plan(ww, hh)          # planning waits for the batches in flight
         kps = np.zeros((B, cap), KP_DTYPE)
         desc = np.zeros((B, cap, 32), np.uint8)
         n = np.zeros(B, np.int32)
