@@ -1,7 +1,9 @@
 """The product's ORBmatcher against the UNMODIFIED reference src/ORBmatcher.cc (oracle/_ref/libmatcher_ref.so: the reference's file
 compiled where it lies over the cv shim and stand-in Frame / KeyFrame / MapPoint objects, oracle/ref_shim/slam) on the same objects.
-CPU leg: the library is built and exports every entry point of matcher_ref.h, and the test program compiles against it.
-GPU leg: tests/native/reference_matcher_test.cpp runs every search both ways and exits non-zero on any difference."""
+GPU leg: tests/native/reference_matcher_test.cpp runs every search both ways and exits non-zero on any difference.
+CPU leg: the same program linked against tests/native/orbx_on_oracle.cpp -- the 21 C-ABI entry points it needs, implemented by the CPU
+oracle (test infrastructure, never shipped) -- instead of liborbx.so: the headers' flattening code and the oracle's searches against the
+reference's own matcher, without a GPU.  With the GPU suite's CUDA == oracle tests this closes the triangle."""
 import os
 import subprocess
 import sys
@@ -24,19 +26,27 @@ def _reflib():
     return REFLIB
 
 
-def _build(tmp_path):
+def _build(tmp_path, on_oracle=False):
     import orbx
     _reflib()
     if not os.path.exists(orbx.LIB_PATH):
         sys.path.insert(0, ROOT)
         import __graft_entry__ as g
         g.build()
-    exe = str(tmp_path / "refmatch")
-    libdir, refdir = os.path.dirname(orbx.LIB_PATH), os.path.dirname(REFLIB)
+    exe = str(tmp_path / ("refmatch_cpu" if on_oracle else "refmatch"))
+    libdir, refdir, oradir = os.path.dirname(orbx.LIB_PATH), os.path.dirname(REFLIB), os.path.join(ROOT, "oracle")
+    if on_oracle:       # the C ABI the headers call, served by the CPU oracle
+        import oracle_py  # noqa: builds oracle/liborb_oracle.so when it is missing
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-fPIC", "-shared", "-I", os.path.join(ROOT, "include"), "-I", oradir,
+                               "-o", str(tmp_path / "liborbx_on_oracle.so"), os.path.join(ROOT, "tests", "native", "orbx_on_oracle.cpp"),
+                               "-L", oradir, "-lorb_oracle", "-Wl,-rpath," + oradir])
+        link = ["-L", str(tmp_path), "-lorbx_on_oracle", "-Wl,-rpath," + str(tmp_path)]
+    else:
+        link = ["-L", libdir, "-lorbx", "-Wl,-rpath," + libdir]
     subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-Werror", "-DORBX_USE_OPENCV", "-I", os.path.join(ROOT, "include"),
                            "-I", os.path.join(ROOT, "oracle", "ref_shim"), "-I", os.path.join(ROOT, "oracle", "ref_shim", "slam"),
-                           "-o", exe, os.path.join(ROOT, "tests", "native", "reference_matcher_test.cpp"),
-                           "-L", libdir, "-lorbx", "-Wl,-rpath," + libdir, "-L", refdir, "-lmatcher_ref", "-Wl,-rpath," + refdir])
+                           "-o", exe, os.path.join(ROOT, "tests", "native", "reference_matcher_test.cpp")] + link +
+                          ["-L", refdir, "-lmatcher_ref", "-Wl,-rpath," + refdir])
     return exe
 
 
@@ -63,8 +73,21 @@ def _views(tmp_path, w, h, seed, dx, dy):
     (tmp_path / "b.raw").write_bytes(b.tobytes())
 
 
+SCENES = [(640, 480, 1000, 2100, 3, 1), (752, 480, 1200, 2200, -4, 2), (640, 480, 2000, 2300, 2, -3)]
+
+
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy", SCENES + [(400, 300, 500, 2400, 5, 4)])
+def test_oracle_searches_equal_the_reference_matcher_on_cpu(tmp_path, w, h, nf, seed, dx, dy):
+    """All eleven searches: the drop-in headers over the CPU oracle against the unmodified reference ORBmatcher.cc, same objects."""
+    exe = _build(tmp_path, on_oracle=True)
+    _views(tmp_path, w, h, seed, dx, dy)
+    r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.rstrip().endswith("ok"), (r.returncode, r.stdout[-3000:], r.stderr[-3000:])
+    assert r.stdout.count("SearchBySim3") == 4 and r.stdout.count("Fuse(KF, MPs)") == 2
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("w,h,nf,seed,dx,dy", [(640, 480, 1000, 2100, 3, 1), (752, 480, 1200, 2200, -4, 2), (640, 480, 2000, 2300, 2, -3)])
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy", SCENES)
 def test_searches_equal_the_reference_matcher(tmp_path, w, h, nf, seed, dx, dy):
     exe = _build(tmp_path)
     _views(tmp_path, w, h, seed, dx, dy)
