@@ -111,7 +111,7 @@ int orbx_extract_color_device(orbx_extractor* ex, const uint8_t* d_imgs, int B, 
 typedef struct orbx_pool orbx_pool;
 int orbx_pool_create(const int* devices, int ndevices, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
                      int chunk, int lanes, orbx_pool** out);
-void orbx_pool_destroy(orbx_pool* pool);
+void orbx_pool_destroy(orbx_pool* pool);      /* lets the batches in flight run to their end first */
 int orbx_pool_devices(const orbx_pool* pool);
 int orbx_pool_set_fma_mode(orbx_pool* pool, int fma_mode);
 /* Plans an image shape on every handle of the pool (allocates the workspaces once, outside any timed region) and returns the

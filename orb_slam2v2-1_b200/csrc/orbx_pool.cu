@@ -194,7 +194,8 @@ void orbx_pool_destroy(orbx_pool* p)
 {
     if (!p) return;
     {
-        std::lock_guard<std::mutex> lk(p->mu);
+        std::unique_lock<std::mutex> lk(p->mu);
+        p->cvDone.wait(lk, [&] { return p->queue.empty() && p->planPending == 0; });      // batches still in flight run to their end first
         p->quit = true;
     }
     p->cvWork.notify_all();
