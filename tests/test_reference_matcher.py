@@ -64,9 +64,9 @@ def test_reference_matcher_library_exports_every_entry_point(tmp_path):
     _build(tmp_path)        # the test program compiles and links against it
 
 
-def _views(tmp_path, w, h, seed, dx, dy):
+def _views(tmp_path, w, h, seed, dx, dy, kind="rects"):
     from orbx import synth
-    a = synth.rects(w, h, seed)
+    a = getattr(synth, kind)(w, h, seed)
     rng = np.random.default_rng(seed)
     b = np.clip(np.roll(a, (dy, dx), axis=(0, 1)).astype(np.int16) + rng.integers(-3, 4, a.shape), 0, 255).astype(np.uint8)
     (tmp_path / "a.raw").write_bytes(a.tobytes())
@@ -76,12 +76,18 @@ def _views(tmp_path, w, h, seed, dx, dy):
 SCENES = [(640, 480, 1000, 2100, 3, 1), (752, 480, 1200, 2200, -4, 2), (640, 480, 2000, 2300, 2, -3)]
 
 
-@pytest.mark.parametrize("w,h,nf,seed,dx,dy", SCENES + [(400, 300, 500, 2400, 5, 4)])
-def test_oracle_searches_equal_the_reference_matcher_on_cpu(tmp_path, w, h, nf, seed, dx, dy):
+@pytest.fixture(scope="module")
+def cpu_exe(tmp_path_factory):
+    return _build(tmp_path_factory.mktemp("refmatch_cpu"), on_oracle=True)
+
+
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy,kind", [s + ("rects",) for s in SCENES] +
+                         [(400, 300, 500, 2400, 5, 4, "rects"), (640, 480, 1000, 2500, 2, 2, "texture"), (512, 384, 800, 2600, -3, -2, "texture"),
+                          (752, 480, 1500, 2700, 6, 0, "rects"), (640, 480, 3000, 2800, 1, 1, "texture")])
+def test_oracle_searches_equal_the_reference_matcher_on_cpu(tmp_path, cpu_exe, w, h, nf, seed, dx, dy, kind):
     """All eleven searches: the drop-in headers over the CPU oracle against the unmodified reference ORBmatcher.cc, same objects."""
-    exe = _build(tmp_path, on_oracle=True)
-    _views(tmp_path, w, h, seed, dx, dy)
-    r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
+    _views(tmp_path, w, h, seed, dx, dy, kind)
+    r = subprocess.run([cpu_exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.rstrip().endswith("ok"), (r.returncode, r.stdout[-3000:], r.stderr[-3000:])
     assert r.stdout.count("SearchBySim3") == 4 and r.stdout.count("Fuse(KF, MPs)") == 2
 
