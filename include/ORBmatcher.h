@@ -18,6 +18,7 @@
 #include <string>
 #include <type_traits>
 #include <utility>
+#include <set>
 #include <vector>
 #include "orbx.h"
 #include "orbx_cv_shim.h"
@@ -127,6 +128,23 @@ public:
     template <class FrameT, class = typename std::enable_if<!std::is_same<typename std::remove_cv<FrameT>::type, FrameView>::value &&
                                                             !std::is_same<typename std::remove_cv<FrameT>::type, DeviceFrame>::value>::type>
     int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10);
+#ifdef ORBX_USE_OPENCV
+    // The LocalMapping / LoopClosing / relocalisation searches under the reference's signatures (include/ORBmatcher.h:56-82 there; call
+    // sites Tracking.cc:1597,1611, LocalMapping.cc:276,497,522, LoopClosing.cc:333,385,608).  They project with the same cv::Mat
+    // expressions as the reference (so the floats are OpenCV's own) and therefore exist only in builds against OpenCV.
+    template <class FrameT, class KeyFrameT, class MapPointT>
+    int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th, const int ORBdist);
+    template <class KeyFrameT, class MapPointT>
+    int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th);
+    template <class KeyFrameT>
+    int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo);
+    template <class KeyFrameT, class MapPointT>
+    int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12, const cv::Mat& R12, const cv::Mat& t12,
+                     const float th);
+    template <class KeyFrameT, class MapPointT> int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0);
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, float th, std::vector<MapPointT*>& vpReplacePoint);
+#endif
 
     // ---- the same searches against a DeviceFrame (definitions after the class)
     int SearchForInitialization(const DeviceFrame& F1, const DeviceFrame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,

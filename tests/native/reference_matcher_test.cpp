@@ -158,43 +158,6 @@ struct Universe {
     }
 };
 
-static ORB_SLAM2::FrameView view_of(const KeyFrame& K)
-{
-    ORB_SLAM2::FrameView v = {&K.mvKeysUn, &K.mDescriptors, (float)K.mnMinX, (float)K.mnMaxX, (float)K.mnMinY, (float)K.mnMaxY};
-    return v;
-}
-
-// What a caller does before handing points to the array forms: the reference's own projection and skip tests,
-// written with the same cv::Mat expressions as ORBmatcher.cc:850-889 / :1011-1056 / :321-362.  Returns false where the reference `continue`s.
-static bool project_into_keyframe(KeyFrame* pKF, const cv::Mat& Rcw, const cv::Mat& tcw, const cv::Mat& Ow, MapPoint* pMP, bool oneOverZdouble,
-                                  float& u, float& v, float& invz, int& level)
-{
-    cv::Mat p3Dw = pMP->GetWorldPos();
-    cv::Mat p3Dc = Rcw * p3Dw + tcw;
-    if (p3Dc.at<float>(2) < 0.0f) return false;
-    invz = oneOverZdouble ? (float)(1.0 / p3Dc.at<float>(2)) : 1 / p3Dc.at<float>(2);          // `1.0/z` (:1022) resp. `1/z` (:861, :330)
-    const float x = p3Dc.at<float>(0) * invz, y = p3Dc.at<float>(1) * invz;
-    u = pKF->fx * x + pKF->cx;
-    v = pKF->fy * y + pKF->cy;
-    if (!pKF->IsInImage(u, v)) return false;
-    const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
-    cv::Mat PO = p3Dw - Ow;
-    const float dist3D = cv::norm(PO);
-    if (dist3D < minDistance || dist3D > maxDistance) return false;
-    cv::Mat Pn = pMP->GetNormal();
-    if (PO.dot(Pn) < 0.5 * dist3D) return false;
-    level = pMP->PredictScale(dist3D, pKF);
-    return true;
-}
-
-static void push_point(ORB_SLAM2::ORBmatcher::ProjectedPoints& P, float u, float v, float ur, int level, float angle, MapPoint* pMP)
-{
-    P.xy.push_back(u); P.xy.push_back(v); P.xr.push_back(ur); P.level.push_back(level); P.viewCosOrAngle.push_back(angle);
-    const cv::Mat d = pMP->GetDescriptor();
-    P.descriptors.insert(P.descriptors.end(), d.ptr<uint8_t>(0), d.ptr<uint8_t>(0) + 32);
-    P.hasObservations.push_back(pMP->Observations() > 0);
-}
-
 static cv::Mat sim3(const cv::Mat& T, float s)          // [s R | s t; 0 1]
 {
     cv::Mat S = T.clone();
@@ -204,7 +167,6 @@ static cv::Mat sim3(const cv::Mat& T, float s)          // [s R | s t; 0 1]
 
 static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, float dx, float dy, float nn, bool checkOri, ORB_SLAM2::ORBmatcher& mine)
 {
-    typedef ORB_SLAM2::ORBmatcher::ProjectedPoints Projected;
     // ---- Fuse(pKF, vpMapPoints, th)  (ORBmatcher.cc:827-977, LocalMapping::SearchInNeighbors)
     {
         Universe R, M;
@@ -213,39 +175,9 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
         std::vector<MapPoint*> vr = R.FA.mvpMapPoints, vm = M.FA.mvpMapPoints;          // A's points (with NULLs and bad ones) into key frame B
         const float th = 3.f;
         const int nr = refm::Fuse(nn, checkOri, &R.KB, vr, th);
-        KeyFrame* pKF = &M.KB;
-        cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();
-        Projected P;
-        std::vector<int> who;
-        for (size_t i = 0; i < vm.size(); i++) {
-            MapPoint* pMP = vm[i];
-            if (!pMP) continue;
-            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
-            float u, v, invz; int level;
-            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, false, u, v, invz, level)) continue;
-            push_point(P, u, v, u - pKF->mbf * invz, level, 0.f, pMP);
-            who.push_back((int)i);
-        }
-        std::vector<int> best;
-        mine.Fuse(view_of(*pKF), pKF->mvuRight, pKF->mvScaleFactors, pKF->mvInvLevelSigma2, P, best, th);
-        int nm = 0;
-        for (size_t j = 0; j < best.size(); j++) {          // :940-957
-            if (best[j] < 0) continue;
-            MapPoint* pMP = vm[who[j]];
-            MapPoint* pMPinKF = pKF->GetMapPoint(best[j]);
-            if (pMPinKF) {
-                if (!pMPinKF->isBad()) {
-                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
-                    else pMPinKF->Replace(pMP);
-                }
-            } else {
-                pMP->AddObservation(pKF, best[j]);
-                pKF->AddMapPoint(pMP, best[j]);
-            }
-            nm++;
-        }
+        const int nm = mine.Fuse(&M.KB, vm, th);                          // as at LocalMapping.cc:497 matcher.Fuse(pKFi,vpMapPointMatches) / :522
         CHECK(nr == nm && R.state() == M.state(), "Fuse(KeyFrame, MapPoints)");
-        printf("Fuse(KF, MPs): %d fused of %d projected\n", nr, (int)who.size());
+        printf("Fuse(KF, MPs): %d fused of %d candidates\n", nr, (int)vr.size());
         CHECK(nr > (int)vr.size() / 10, "Fuse(KeyFrame, MapPoints): too few fused");
     }
     // ---- Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)  (:979-1102, LoopClosing::SearchAndFuse)
@@ -258,41 +190,9 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
         const float th = 4.f;
         std::vector<MapPoint*> repR(vr.size(), static_cast<MapPoint*>(NULL)), repM(vm.size(), static_cast<MapPoint*>(NULL));
         const int nr = refm::Fuse(nn, checkOri, &R.KB, sim3(R.KB.Tcw, 1.25f), vr, th, repR);
-        KeyFrame* pKF = &M.KB;
-        cv::Mat Scw = sim3(M.KB.Tcw, 1.25f);
-        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);                              // :988-992
-        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
-        cv::Mat Rcw = sRcw / scw;
-        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
-        cv::Mat Ow = -Rcw.t() * tcw;
-        const std::set<MapPoint*> found = pKF->GetMapPoints();
-        Projected P;
-        std::vector<int> who;
-        for (size_t i = 0; i < vm.size(); i++) {
-            MapPoint* pMP = vm[i];
-            if (pMP->isBad() || found.count(pMP)) continue;
-            float u, v, invz; int level;
-            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, true, u, v, invz, level)) continue;
-            push_point(P, u, v, -1.f, level, 0.f, pMP);
-            who.push_back((int)i);
-        }
-        std::vector<int> best;
-        mine.Fuse(view_of(*pKF), pKF->mvScaleFactors, P, best, th);
-        int nm = 0;
-        for (size_t j = 0; j < best.size(); j++) {          // :1083-1095
-            if (best[j] < 0) continue;
-            MapPoint* pMP = vm[who[j]];
-            MapPoint* pMPinKF = pKF->GetMapPoint(best[j]);
-            if (pMPinKF) {
-                if (!pMPinKF->isBad()) repM[who[j]] = pMPinKF;
-            } else {
-                pMP->AddObservation(pKF, best[j]);
-                pKF->AddMapPoint(pMP, best[j]);
-            }
-            nm++;
-        }
+        const int nm = mine.Fuse(&M.KB, sim3(M.KB.Tcw, 1.25f), vm, th, repM);   // as at LoopClosing.cc:608 matcher.Fuse(pKF,cvScw,mvpLoopMapPoints,4,vpReplacePoints)
         CHECK(nr == nm && R.state() == M.state() && R.ids(repR) == M.ids(repM), "Fuse(KeyFrame, Scw, MapPoints)");
-        printf("Fuse(KF, Scw, MPs): %d fused of %d projected\n", nr, (int)who.size());
+        printf("Fuse(KF, Scw, MPs): %d fused of %d candidates\n", nr, (int)vr.size());
         CHECK(nr > (int)vr.size() / 10, "Fuse(KeyFrame, Scw, MapPoints): too few fused");
     }
     // ---- SearchByProjection(pKF, Scw, vpPoints, vpMatched, th)  (:290-403, LoopClosing::ComputeSim3)
@@ -308,32 +208,9 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
         for (size_t i = 1; i < vr.size() && 7 * i + 1 < mr.size(); i += 9) { mr[7 * i + 1] = vr[i]; mm[7 * i + 1] = vm[i]; }
         const int th = 10;
         const int nr = refm::SearchByProjection(nn, checkOri, &R.KB, sim3(R.KB.Tcw, 0.8f), vr, mr, th);
-        KeyFrame* pKF = &M.KB;
-        cv::Mat Scw = sim3(M.KB.Tcw, 0.8f);
-        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);                              // :299-303
-        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
-        cv::Mat Rcw = sRcw / scw;
-        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
-        cv::Mat Ow = -Rcw.t() * tcw;
-        std::set<MapPoint*> found(mm.begin(), mm.end());
-        found.erase(static_cast<MapPoint*>(NULL));
-        Projected P;
-        std::vector<int> who;
-        for (size_t i = 0; i < vm.size(); i++) {
-            MapPoint* pMP = vm[i];
-            if (pMP->isBad() || found.count(pMP)) continue;
-            float u, v, invz; int level;
-            if (!project_into_keyframe(pKF, Rcw, tcw, Ow, pMP, false, u, v, invz, level)) continue;
-            push_point(P, u, v, -1.f, level, 0.f, pMP);
-            who.push_back((int)i);
-        }
-        std::vector<uint8_t> vbMatched(mm.size());
-        for (size_t j = 0; j < mm.size(); j++) vbMatched[j] = mm[j] != NULL;
-        std::vector<int> vnMatch;
-        const int nm = mine.SearchByProjection(view_of(*pKF), vbMatched, pKF->mvScaleFactors, P, vnMatch, th);
-        for (size_t j = 0; j < vnMatch.size(); j++) if (vnMatch[j] >= 0) mm[j] = vm[who[vnMatch[j]]];       // :396
+        const int nm = mine.SearchByProjection(&M.KB, sim3(M.KB.Tcw, 0.8f), vm, mm, th);   // as at LoopClosing.cc:385 matcher.SearchByProjection(mpCurrentKF, mScw, mvpLoopMapPoints, mvpCurrentMatchedPoints,10)
         CHECK(nr == nm && R.ids(mr) == M.ids(mm), "SearchByProjection(KeyFrame, Scw, MapPoints)");
-        printf("SearchByProjection(KF, Scw, MPs): %d matches of %d projected\n", nr, (int)who.size());
+        printf("SearchByProjection(KF, Scw, MPs): %d matches of %d candidates\n", nr, (int)vr.size());
         CHECK(nr > (int)vr.size() / 10, "SearchByProjection(KeyFrame, Scw, MapPoints): too few matches");
     }
     // ---- SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)  (:1474-1601, Tracking::Relocalization)
@@ -348,82 +225,17 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
         const float th = variant ? 3.f : 10.f;
         const int ORBdist = variant ? 64 : 100;
         const int nr = refm::SearchByProjection(nn, checkOri, R.FB, &R.KA, foundR, th, ORBdist);
-        Frame& F = M.FB;
-        KeyFrame* pKF = &M.KA;
-        const cv::Mat Rcw = F.mTcw.rowRange(0, 3).colRange(0, 3);                      // :1478-1480
-        const cv::Mat tcw = F.mTcw.rowRange(0, 3).col(3);
-        const cv::Mat Ow = -Rcw.t() * tcw;
-        const std::vector<MapPoint*> vpMPs = pKF->GetMapPointMatches();
-        Projected P;
-        std::vector<int> who;
-        for (size_t i = 0; i < vpMPs.size(); i++) {
-            MapPoint* pMP = vpMPs[i];
-            if (!pMP || pMP->isBad() || foundM.count(pMP)) continue;
-            cv::Mat x3Dw = pMP->GetWorldPos();                                         // :1499-1531
-            cv::Mat x3Dc = Rcw * x3Dw + tcw;
-            const float xc = x3Dc.at<float>(0), yc = x3Dc.at<float>(1);
-            const float invzc = 1.0 / x3Dc.at<float>(2);
-            const float u = F.fx * xc * invzc + F.cx, v = F.fy * yc * invzc + F.cy;
-            if (u < F.mnMinX || u > F.mnMaxX) continue;
-            if (v < F.mnMinY || v > F.mnMaxY) continue;
-            cv::Mat PO = x3Dw - Ow;
-            float dist3D = cv::norm(PO);
-            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
-            push_point(P, u, v, -1.f, pMP->PredictScale(dist3D, &F), pKF->mvKeysUn[i].angle, pMP);
-            who.push_back((int)i);
-        }
-        std::vector<uint8_t> occupied(F.N);
-        for (int j = 0; j < F.N; j++) occupied[j] = F.mvpMapPoints[j] != NULL;
-        std::vector<int> vnMatch;
-        ORB_SLAM2::FrameView fv = {&F.mvKeysUn, &F.mDescriptors, Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY};
-        const int nm = mine.SearchByProjection(fv, occupied, F.mvScaleFactors, P, vnMatch, th, ORBdist);
-        for (size_t j = 0; j < vnMatch.size(); j++) if (vnMatch[j] >= 0) F.mvpMapPoints[j] = vpMPs[who[vnMatch[j]]];       // :1551
+        const int nm = mine.SearchByProjection(M.FB, &M.KA, foundM, th, ORBdist);   // as at Tracking.cc:1597 matcher2.SearchByProjection(mCurrentFrame,vpCandidateKFs[i],sFound,10,100) / :1611 (..,3,64)
         CHECK(nr == nm && R.ids(R.FB.mvpMapPoints) == M.ids(M.FB.mvpMapPoints), "SearchByProjection(Frame, KeyFrame)");
-        printf("SearchByProjection(F, KF) variant %d: %d matches of %d projected\n", variant, nr, (int)who.size());
+        printf("SearchByProjection(F, KF) variant %d: %d matches\n", variant, nr);
         CHECK(nr > R.FA.N / 12, "SearchByProjection(Frame, KeyFrame): too few matches");
     }
 }
 
 
-// one direction of SearchBySim3's flattening (ORBmatcher.cc:1145-1183 resp. :1225-1263): one entry per feature of the source key frame,
-// level -1 where the reference skips it
-static void project_sim3(KeyFrame* src, KeyFrame* dst, const std::vector<MapPoint*>& vpSrc, const std::vector<bool>& matched, const cv::Mat& Rsw,
-                         const cv::Mat& tsw, const cv::Mat& sRds, const cv::Mat& tds, ORB_SLAM2::ORBmatcher::ProjectedPoints& P)
-{
-    const std::vector<uint8_t> none(32, 0);
-    for (size_t i = 0; i < vpSrc.size(); i++) {
-        MapPoint* pMP = vpSrc[i];
-        float u = 0, v = 0;
-        int level = -1;
-        if (pMP && !matched[i] && !pMP->isBad()) {
-            cv::Mat p3Dw = pMP->GetWorldPos();
-            cv::Mat p3Dcs = Rsw * p3Dw + tsw;
-            cv::Mat p3Dcd = sRds * p3Dcs + tds;
-            if (!(p3Dcd.at<float>(2) < 0.0)) {
-                const float invz = 1.0 / p3Dcd.at<float>(2);
-                const float x = p3Dcd.at<float>(0) * invz, y = p3Dcd.at<float>(1) * invz;
-                u = src->fx * x + src->cx;                                       // the reference takes fx .. cy from pKF1 for both directions (:1107-1110)
-                v = src->fy * y + src->cy;
-                if (dst->IsInImage(u, v)) {
-                    const float dist3D = cv::norm(p3Dcd);
-                    if (!(dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance())) level = pMP->PredictScale(dist3D, dst);
-                }
-            }
-        }
-        P.xy.push_back(u); P.xy.push_back(v); P.xr.push_back(-1.f); P.level.push_back(level); P.viewCosOrAngle.push_back(0.f);
-        if (level >= 0) {
-            const cv::Mat d = pMP->GetDescriptor();
-            P.descriptors.insert(P.descriptors.end(), d.ptr<uint8_t>(0), d.ptr<uint8_t>(0) + 32);
-        } else
-            P.descriptors.insert(P.descriptors.end(), none.begin(), none.end());
-        P.hasObservations.push_back(1);
-    }
-}
-
 static void loop_and_triangulation_searches(const Frame& FA0, const Frame& FB0, int w, int h, float dx, float dy, float nn, bool checkOri,
                                             ORB_SLAM2::ORBmatcher& mine)
 {
-    typedef ORB_SLAM2::ORBmatcher::ProjectedPoints Projected;
     // ---- SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th)  (ORBmatcher.cc:1104-1328, LoopClosing::ComputeSim3)
     for (int variant = 0; variant < 2; variant++) {
         Universe R, M;
@@ -438,26 +250,7 @@ static void loop_and_triangulation_searches(const Frame& FA0, const Frame& FB0, 
         for (int i = 2; i < R.KA.N && i < R.KB.N; i += 10)                // a few pairs known beforehand
             if (R.KB.mvpMapPoints[i]) { mr[i] = R.KB.mvpMapPoints[i]; mm[i] = M.KB.mvpMapPoints[i]; }
         const int nr = refm::SearchBySim3(nn, checkOri, &R.KA, &R.KB, mr, s12, R12, t12, th);
-        KeyFrame *pKF1 = &M.KA, *pKF2 = &M.KB;
-        cv::Mat R1w = pKF1->GetRotation(), t1w = pKF1->GetTranslation(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();      // :1113-1123
-        cv::Mat sR12 = s12 * R12;
-        cv::Mat sR21 = (1.0 / s12) * R12.t();
-        cv::Mat t21 = -sR21 * t12;
-        const std::vector<MapPoint*> vp1 = pKF1->GetMapPointMatches(), vp2 = pKF2->GetMapPointMatches();
-        const int N1 = (int)vp1.size(), N2 = (int)vp2.size();
-        std::vector<bool> already1(N1, false), already2(N2, false);
-        for (int i = 0; i < N1; i++)
-            if (mm[i]) {
-                already1[i] = true;
-                const int idx2 = mm[i]->GetIndexInKeyFrame(pKF2);
-                if (idx2 >= 0 && idx2 < N2) already2[idx2] = true;
-            }
-        Projected P12, P21;
-        project_sim3(pKF1, pKF2, vp1, already1, R1w, t1w, sR21, t21, P12);
-        project_sim3(pKF1, pKF1, vp2, already2, R2w, t2w, sR12, t12, P21);          // fx .. cy of pKF1, image bounds of pKF1 (:1233-1240)
-        std::vector<int> m12;
-        const int nm = mine.SearchBySim3(view_of(*pKF1), view_of(*pKF2), pKF2->mvScaleFactors, P12, P21, m12, th);
-        for (int i1 = 0; i1 < N1; i1++) if (m12[i1] >= 0) mm[i1] = vp2[m12[i1]];   // :1318
+        const int nm = mine.SearchBySim3(&M.KA, &M.KB, mm, s12, R12, t12, th);   // as at LoopClosing.cc:333 matcher.SearchBySim3(mpCurrentKF,pKF,vpMapPointMatches,s,R,t,7.5)
         CHECK(nr == nm && R.ids(mr) == M.ids(mm), "SearchBySim3");
         printf("SearchBySim3 variant %d: %d found\n", variant, nr);
         CHECK(nr > R.KA.N / 12, "SearchBySim3: too few found");
@@ -487,20 +280,7 @@ static void loop_and_triangulation_searches(const Frame& FA0, const Frame& FB0, 
         }
         std::vector<std::pair<size_t, size_t> > pr, pm;
         const int nr = refm::SearchForTriangulation(nn, checkOri, &R.KA, &R.KB, F12, pr, onlyStereo != 0);
-        KeyFrame *pKF1 = &M.KA, *pKF2 = &M.KB;
-        cv::Mat Cw = pKF1->GetCameraCenter();                                         // :664-672
-        cv::Mat R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
-        cv::Mat C2 = R2w * Cw + t2w;
-        const float invz = 1.0f / C2.at<float>(2);
-        const float ex = pKF2->fx * C2.at<float>(0) * invz + pKF2->cx, ey = pKF2->fy * C2.at<float>(1) * invz + pKF2->cy;
-        std::vector<uint8_t> has1(pKF1->N), has2(pKF2->N);
-        for (int i = 0; i < pKF1->N; i++) has1[i] = pKF1->GetMapPoint(i) != NULL;
-        for (int i = 0; i < pKF2->N; i++) has2[i] = pKF2->GetMapPoint(i) != NULL;
-        const ORB_SLAM2::ORBmatcher::FeatureVectorCSR fv1 = ORB_SLAM2::ORBmatcher::FeatureVectorCSR::from(pKF1->mFeatVec),
-                                                      fv2 = ORB_SLAM2::ORBmatcher::FeatureVectorCSR::from(pKF2->mFeatVec);
-        ORB_SLAM2::ORBmatcher::KeyFrameState S1 = {&has1, &pKF1->mvuRight, &fv1}, S2 = {&has2, &pKF2->mvuRight, &fv2};
-        const int nm = mine.SearchForTriangulation(view_of(*pKF1), S1, view_of(*pKF2), S2, F12, ex, ey, pKF2->mvScaleFactors, pKF2->mvLevelSigma2, pm,
-                                                   onlyStereo != 0);
+        const int nm = mine.SearchForTriangulation(&M.KA, &M.KB, F12, pm, onlyStereo != 0);   // as at LocalMapping.cc:276 matcher.SearchForTriangulation(mpCurrentKeyFrame,pKF2,F12,vMatchedIndices,false)
         CHECK(nr == nm && pr == pm, "SearchForTriangulation");
         printf("SearchForTriangulation onlyStereo %d: %d pairs\n", onlyStereo, nr);
         if (!onlyStereo) CHECK(nr > R.KA.N / 20, "SearchForTriangulation: too few pairs");
