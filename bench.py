@@ -311,7 +311,7 @@ def run_reference(args, cfg):
     _, kind = _checker()
     for _ in range(args.warmup):
         cpu_reference_throughput(cfg, left, right, 1.0, threads)
-    per_step = max(2.0, min(10.0, 60.0 / max(args.steps, 1)))
+    per_step = max(0.5, min(10.0, 60.0 / max(args.steps, 1)))          # about a minute of CPU work whatever K is
     vals, n = [], 0
     for _ in range(args.steps):
         v, cnt = cpu_reference_throughput(cfg, left, right, per_step, threads)
@@ -752,7 +752,7 @@ def finish_ours(args, cfg, S):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)        # 100 x 1.7 ms: a timed region of ~0.17 s at config 0
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=0, choices=sorted(CONFIGS), help="BASELINE.json configs index (default 0: the metric's)")
