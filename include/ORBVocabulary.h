@@ -46,6 +46,8 @@ public:
         while (std::getline(f, s)) {
             std::stringstream sn(s);
             int pid, leaf;
+            // an empty (last) line is skipped.  The reference turns it into one more child of the root whose leaf flag, weight and
+            // descriptor are never written (TemplatedVocabulary.h:1394-1431 after a failed extraction; tests/test_reference_frame.py)
             if (!(sn >> pid >> leaf)) continue;
             parent.push_back(pid);
             for (int i = 0; i < 32; i++) { int b = 0; sn >> b; desc.push_back((uint8_t)b); }               // FORB::fromString

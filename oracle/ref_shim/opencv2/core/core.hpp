@@ -18,6 +18,12 @@
 #include <algorithm>
 #include <stdexcept>
 #include <initializer_list>
+#include <limits.h>
+#include <float.h>
+#include <string>
+#include <sstream>
+#include <fstream>
+#include <iostream>
 
 typedef unsigned char uchar;
 typedef unsigned short ushort;
@@ -114,7 +120,7 @@ struct MatStep {
 // Mat::zeros / Mat::eye return an expression in OpenCV; ASSIGNING one to an existing Mat of the same size and type
 // fills that Mat's buffer in place instead of rebinding it.  The reference relies on this at ORBextractor.cc:1037
 // (`descriptors = Mat::zeros(...)` on a row range of the output matrix).
-struct MatExpr { int rows, cols, type; bool eye; };
+struct MatExpr { int rows, cols, type; bool eye; float fill; };     // fill: value of every element (Mat::ones, scaled), 0 for zeros / eye
 
 // Dense 2-D single-channel matrix with OpenCV's sharing semantics: copies and ROIs alias one
 // reference-counted buffer; clone() is deep.
@@ -203,13 +209,27 @@ public:
         dst.create(rows, cols, type());
         for (int y = 0; y < rows; y++) memmove(dst.data + (size_t)y * dst.step.p[0], data + (size_t)y * step.p[0], (size_t)cols * elemSize());
     }
-    static MatExpr zeros(int r, int c, int type) { MatExpr e = {r, c, type, false}; return e; }
-    static MatExpr eye(int r, int c, int type) { MatExpr e = {r, c, type, true}; return e; }
+    // into an existing view of the same size and type (OpenCV: copyTo(OutputArray) on a temporary header, Frame.cc:279-280)
+    void copyTo(const Mat& dst) const
+    {
+        if (dst.rows != rows || dst.cols != cols || dst.type() != type()) throw std::runtime_error("cv shim: copyTo into a view of another size");
+        for (int y = 0; y < rows; y++) memmove(dst.data + (size_t)y * dst.step.p[0], data + (size_t)y * step.p[0], (size_t)cols * elemSize());
+    }
+    // The shim's Mat has one channel: an N x 2 CV_32F matrix and its N x 1 two-channel view (Frame.cc:436, :438) are the same bytes,
+    // and undistortPoints below reads either as N points.
+    Mat reshape(int) const { return *this; }
+    static MatExpr zeros(int r, int c, int type) { MatExpr e = {r, c, type, false, 0.f}; return e; }
+    static MatExpr eye(int r, int c, int type) { MatExpr e = {r, c, type, true, 0.f}; return e; }
+    static MatExpr ones(int r, int c, int type) { MatExpr e = {r, c, type, false, 1.f}; return e; }
     Mat(const MatExpr& e) : Mat() { *this = e; }
     Mat& operator=(const MatExpr& e)
     {
         create(e.rows, e.cols, e.type);         // keeps the buffer when size and type already match
         for (int y = 0; y < rows; y++) memset(data + (size_t)y * step.p[0], 0, (size_t)cols * elemSize());
+        if (e.fill != 0.f) {
+            if (depth() != CV_32F) throw std::runtime_error("cv shim: Mat::ones is CV_32F only");
+            for (int y = 0; y < rows; y++) for (int x = 0; x < cols; x++) at<float>(y, x) = e.fill;
+        }
         if (e.eye)
             for (int i = 0; i < std::min(rows, cols); i++) {
                 if (depth() == CV_32F) at<float>(i, i) = 1.f; else if (depth() == CV_64F) at<double>(i, i) = 1.0; else at<uchar>(i, i) = 1;
@@ -303,6 +323,36 @@ void copyMakeBorder(InputArray src, OutputArray dst, int top, int bottom, int le
 void resize(InputArray src, OutputArray dst, Size dsize, double fx = 0, double fy = 0, int interpolation = INTER_LINEAR);
 void GaussianBlur(InputArray src, OutputArray dst, Size ksize, double sigmaX, double sigmaY = 0, int borderType = BORDER_DEFAULT);
 void FAST(InputArray image, std::vector<KeyPoint>& keypoints, int threshold, bool nonmaxSuppression = true);
+
+// cv::undistortPoints(src, dst, K, dist, R = noArray(), P = K): oracle/orb_primitives.cpp's restatement (pinned to cv2 by
+// tests/test_oracle_vs_cv2.py); src / dst: N x 2 CV_32F (see Mat::reshape), K 3 x 3 CV_32F, dist 4 or 5 x 1 (or 1 x 4 / 5) CV_32F
+void undistortPoints(InputArray src, OutputArray dst, InputArray cameraMatrix, InputArray distCoeffs, InputArray R = noArray(), InputArray P = noArray());
+
+// YAML / XML storage: not provided.  DBoW2's TemplatedVocabulary declares virtual save / load over it; this build loads vocabularies
+// with loadFromTextFile only, so every operation here throws.
+class FileNode {
+public:
+    FileNode operator[](const std::string&) const { return fail(); }
+    FileNode operator[](const char*) const { return fail(); }
+    FileNode operator[](int) const { return fail(); }
+    size_t size() const { fail(); return 0; }
+    operator int() const { fail(); return 0; }
+    operator float() const { fail(); return 0; }
+    operator double() const { fail(); return 0; }
+    operator std::string() const { fail(); return std::string(); }
+private:
+    static FileNode fail() { throw std::runtime_error("cv shim: FileStorage not provided"); }
+};
+class FileStorage {
+public:
+    enum { READ = 0, WRITE = 1 };
+    FileStorage(const std::string&, int) {}
+    bool isOpened() const { return false; }
+    void release() {}
+    FileNode operator[](const std::string&) const { throw std::runtime_error("cv shim: FileStorage not provided"); }
+    FileNode operator[](const char*) const { throw std::runtime_error("cv shim: FileStorage not provided"); }
+};
+template <typename T> static inline FileStorage& operator<<(FileStorage&, const T&) { throw std::runtime_error("cv shim: FileStorage not provided"); }
 
 class KeyPointsFilter {
 public:

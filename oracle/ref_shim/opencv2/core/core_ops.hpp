@@ -30,6 +30,10 @@ static inline Mat operator-(const Mat& a) { return shim::map(a, [](float p) { re
 static inline Mat operator*(const Mat& a, double s) { return shim::map(a, [s](float p) { return (float)(p * s); }); }
 static inline Mat operator*(double s, const Mat& a) { return a * s; }
 static inline Mat operator/(const Mat& a, double s) { return shim::map(a, [s](float p) { return (float)(p / s); }); }
+static inline MatExpr operator*(double s, const MatExpr& e) { MatExpr r = e; r.fill = (float)(e.fill * s); return r; }     // s * Mat::ones(...)
+static inline MatExpr operator*(const MatExpr& e, double s) { return s * e; }
+static inline Mat operator-(const Mat& a, const MatExpr& e) { return a - Mat(e); }
+static inline Mat operator+(const Mat& a, const MatExpr& e) { return a + Mat(e); }
 static inline Mat operator*(const Mat& a, const Mat& b)
 {
     shim::need32f(a); shim::need32f(b);
@@ -84,6 +88,19 @@ static inline double norm(const Mat& a, int normType = NORM_L2)
     for (int y = 0; y < a.rows; y++)
         for (int x = 0; x < a.cols; x++) {
             const double v = a.at<float>(y, x);
+            if (normType == NORM_L1) s += std::fabs(v); else if (normType == NORM_INF) s = std::max(s, std::fabs(v)); else s += v * v;
+        }
+    return normType == NORM_L2 ? std::sqrt(s) : s;
+}
+// norm(a, b, type) = norm(a - b, type), CV_32F, accumulated in double (normDiffL1_32f and friends)
+static inline double norm(const Mat& a, const Mat& b, int normType = NORM_L2)
+{
+    shim::need32f(a); shim::need32f(b);
+    if (a.rows != b.rows || a.cols != b.cols) throw std::runtime_error("cv shim: norm size mismatch");
+    double s = 0;
+    for (int y = 0; y < a.rows; y++)
+        for (int x = 0; x < a.cols; x++) {
+            const double v = (double)a.at<float>(y, x) - (double)b.at<float>(y, x);
             if (normType == NORM_L1) s += std::fabs(v); else if (normType == NORM_INF) s = std::max(s, std::fabs(v)); else s += v * v;
         }
     return normType == NORM_L2 ? std::sqrt(s) : s;

@@ -9,16 +9,24 @@
 // `#define ORB_SLAM2 ORB_SLAM2_REF` so that the reference's ORBmatcher cannot collide with the product's class of the same name.
 #ifndef ORBX_SLAM_OBJECTS_H
 #define ORBX_SLAM_OBJECTS_H
+// With ORBX_REAL_FRAME (the build of the reference's src/Frame.cc, ref_shim/frame/) only MapPoint and KeyFrame are stood in: Frame is the
+// reference's own class and DBoW2's vendored headers are the real ones.
 #define MAPPOINT_H
 #define KEYFRAME_H
+#ifndef ORBX_REAL_FRAME
 #define FRAME_H
+#endif
 #include <cmath>
 #include <map>
 #include <mutex>
 #include <set>
 #include <vector>
 #include <opencv2/core/core.hpp>
+#ifdef ORBX_REAL_FRAME
+#include <Thirdparty/DBoW2/DBoW2/FeatureVector.h>      // found on the include path only: the reference's vendored DBoW2
+#else
 #include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
+#endif
 
 #define FRAME_GRID_ROWS 48
 #define FRAME_GRID_COLS 64
@@ -140,6 +148,7 @@ public:
     FeatureGrid grid;
 };
 
+#ifndef ORBX_REAL_FRAME
 class Frame
 {
 public:
@@ -166,18 +175,25 @@ public:
     FeatureGrid grid;
 };
 
+#endif
+
 inline int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF)
 {
     const float ratio = mfMaxDistance / currentDist;
     const int n = (int)ceil(log(ratio) / pKF->mfLogScaleFactor);
     return n < 0 ? 0 : (n >= pKF->mnScaleLevels ? pKF->mnScaleLevels - 1 : n);
 }
-inline int MapPoint::PredictScale(const float& currentDist, Frame* pF)
-{
-    const float ratio = mfMaxDistance / currentDist;
-    const int n = (int)ceil(log(ratio) / pF->mfLogScaleFactor);
-    return n < 0 ? 0 : (n >= pF->mnScaleLevels ? pF->mnScaleLevels - 1 : n);
-}
+// MapPoint.cc:414-429; with ORBX_REAL_FRAME this text is compiled after the reference's Frame.h (ref_shim/frame/Frame.h)
+#define ORBX_PREDICT_SCALE_FRAME \
+    inline int MapPoint::PredictScale(const float& currentDist, Frame* pF) \
+    { \
+        const float ratio = mfMaxDistance / currentDist; \
+        const int n = (int)ceil(log(ratio) / pF->mfLogScaleFactor); \
+        return n < 0 ? 0 : (n >= pF->mnScaleLevels ? pF->mnScaleLevels - 1 : n); \
+    }
+#ifndef ORBX_REAL_FRAME
+ORBX_PREDICT_SCALE_FRAME
+#endif
 
 }  // namespace ORB_SLAM2
 #endif
