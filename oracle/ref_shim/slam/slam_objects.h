@@ -10,7 +10,8 @@
 #ifndef ORBX_SLAM_OBJECTS_H
 #define ORBX_SLAM_OBJECTS_H
 // With ORBX_REAL_FRAME (the build of the reference's src/Frame.cc, ref_shim/frame/) only MapPoint and KeyFrame are stood in: Frame is the
-// reference's own class and DBoW2's vendored headers are the real ones.
+// reference's own class and DBoW2's vendored headers are the real ones.  With ORBX_REAL_MAPPOINT (the build of src/MapPoint.cc,
+// ref_shim/mappoint/) MapPoint is the reference's own class, already defined when this file is read, and KeyFrame / Frame are stood in.
 #define MAPPOINT_H
 #define KEYFRAME_H
 #ifndef ORBX_REAL_FRAME
@@ -37,6 +38,7 @@ namespace ORB_SLAM2
 class KeyFrame;
 class Frame;
 
+#ifndef ORBX_REAL_MAPPOINT
 class MapPoint
 {
 public:
@@ -73,6 +75,8 @@ public:
     std::map<KeyFrame*, size_t> mObservations;
     MapPoint* mpReplaced;
 };
+
+#endif  // ORBX_REAL_MAPPOINT
 
 // the 64 x 48 bucket grid over the undistorted keypoints: Frame::AssignFeaturesToGrid / PosInGrid (Frame.cc:230-245, :397-407),
 // KeyFrame copies it (KeyFrame.cc:41-58)
@@ -113,9 +117,13 @@ struct FeatureGrid {
 class KeyFrame
 {
 public:
-    KeyFrame() : mnId(0), N(0), fx(0), fy(0), cx(0), cy(0), invfx(0), invfy(0), mbf(0), mb(0), mThDepth(0), mnScaleLevels(8), mfScaleFactor(1.2f),
+    KeyFrame() : mnId(0), mnFrameId(0), bad(false), N(0), fx(0), fy(0), cx(0), cy(0), invfx(0), invfy(0), mbf(0), mb(0), mThDepth(0), mnScaleLevels(8), mfScaleFactor(1.2f),
                  mfLogScaleFactor(std::log(1.2f)), mnMinX(0), mnMinY(0), mnMaxX(0), mnMaxY(0) {}
-    long unsigned int mnId;
+    long unsigned int mnId, mnFrameId;
+    bool bad;
+    bool isBad() { return bad; }                                                // KeyFrame.cc:563-567
+    void EraseMapPointMatch(const size_t& idx) { mvpMapPoints[idx] = static_cast<MapPoint*>(NULL); }          // KeyFrame.cc:213-217
+    void ReplaceMapPointMatch(const size_t& idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }                  // KeyFrame.cc:228-231
     int N;
     float fx, fy, cx, cy, invfx, invfy, mbf, mb, mThDepth;
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
@@ -152,7 +160,10 @@ public:
 class Frame
 {
 public:
-    Frame() : N(0), mbf(0), mb(0), mThDepth(0), mnScaleLevels(8), mfScaleFactor(1.2f), mfLogScaleFactor(std::log(1.2f)) {}
+    Frame() : mnId(0), N(0), mbf(0), mb(0), mThDepth(0), mnScaleLevels(8), mfScaleFactor(1.2f), mfLogScaleFactor(std::log(1.2f)) {}
+    long unsigned int mnId;
+    cv::Mat GetCameraCenter() { return mOw.clone(); }                            // Frame.h:68-70
+    cv::Mat mOw;
     int N;
     static float fx, fy, cx, cy, invfx, invfy;
     float mbf, mb, mThDepth;
@@ -177,12 +188,14 @@ public:
 
 #endif
 
+#ifndef ORBX_REAL_MAPPOINT
 inline int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF)
 {
     const float ratio = mfMaxDistance / currentDist;
     const int n = (int)ceil(log(ratio) / pKF->mfLogScaleFactor);
     return n < 0 ? 0 : (n >= pKF->mnScaleLevels ? pKF->mnScaleLevels - 1 : n);
 }
+#endif
 // MapPoint.cc:414-429; with ORBX_REAL_FRAME this text is compiled after the reference's Frame.h (ref_shim/frame/Frame.h)
 #define ORBX_PREDICT_SCALE_FRAME \
     inline int MapPoint::PredictScale(const float& currentDist, Frame* pF) \
@@ -191,7 +204,7 @@ inline int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF)
         const int n = (int)ceil(log(ratio) / pF->mfLogScaleFactor); \
         return n < 0 ? 0 : (n >= pF->mnScaleLevels ? pF->mnScaleLevels - 1 : n); \
     }
-#ifndef ORBX_REAL_FRAME
+#if !defined(ORBX_REAL_FRAME) && !defined(ORBX_REAL_MAPPOINT)
 ORBX_PREDICT_SCALE_FRAME
 #endif
 
