@@ -12,8 +12,8 @@ configuration: 0 (default, the one the metric names) = 640x480 / 1000 features, 
   match  : brute-force Hamming Mpairs/s (10000x10000 and 2000x2000, SearchByBoW-shaped scan), device resident.
   roofline / cpu_baseline: see DESIGN.md section "Measurement".
 `--impl reference` times the reference's own CPU code on the host cores: oracle/_ref, the unmodified src/ORBextractor.cc compiled
-over a cv shim (kind "reference"); Frame::ComputeStereoMatches, which cannot be compiled here (ROS headers), comes from the oracle
-port.  Same metric, config and workload string as the CUDA arm.
+over a cv shim (kind "reference"); the stereo configurations run the reference's own Frame per pair (oracle/_ref/libframe_ref.so: the
+unmodified src/Frame.cc with ExtractORB on both images and ComputeStereoMatches).  Same metric, config and workload string as the CUDA arm.
 """
 import argparse
 import hashlib
@@ -197,9 +197,22 @@ def _cpu_extractor(cfg, allocator):
     return mod.OracleExtractor(*params(cfg), tie_mode=0, fma_mode=1)
 
 
+def _stereo_pipeline(cfg):
+    """The reference's own Frame for one rectified pair (oracle/_ref/libframe_ref.so: unmodified Frame.cc + ORBextractor.cc + ORBmatcher.cc):
+    extraction of both images, grid, ComputeStereoMatches; None where that library is not built (then cpu_unit's port is used)."""
+    _, kind = _checker()
+    if kind != "reference":
+        return None
+    import ref_frame_py as RF
+    if not RF.available():
+        return None
+    return RF.RefStereoPipeline([cfg["fx"], cfg["fx"], cfg["W"] * 0.5, cfg["H"] * 0.5], cfg["bf"], 35.0, *params(cfg))
+
+
 def cpu_unit(cfg, exL, exR, left, right):
     """One unit of the workload on the CPU, as the reference runs it: operator() on the image (stereo: on both, then
-    Frame::ComputeStereoMatches on the two mvImagePyramids -- from the oracle port, the reference's Frame.cc needs ROS headers)."""
+    Frame::ComputeStereoMatches on the two mvImagePyramids -- the oracle's port of it, which tests/test_reference_frame.py holds equal to
+    the reference's; the timed legs use the reference's own Frame instead when libframe_ref.so is there, see _stereo_pipeline)."""
     kl, dl = exL(left)
     if not cfg["stereo"]:
         return kl, dl
@@ -221,11 +234,16 @@ def cpu_reference_throughput(cfg, left, right, seconds_budget, threads):
 
     def worker(t):
         try:
-            exL = _cpu_extractor(cfg, 0)
-            exR = _cpu_extractor(cfg, 0) if cfg["stereo"] else None
+            pipe = _stereo_pipeline(cfg) if cfg["stereo"] else None
+            if pipe is None:
+                exL = _cpu_extractor(cfg, 0)
+                exR = _cpu_extractor(cfg, 0) if cfg["stereo"] else None
             i = t
             while time.perf_counter() < stop_at[0]:
-                cpu_unit(cfg, exL, exR, left[i % len(left)], right[i % len(left)] if cfg["stereo"] else None)
+                if pipe is not None:
+                    pipe.run(left[i % len(left)], right[i % len(left)])
+                else:
+                    cpu_unit(cfg, exL, exR, left[i % len(left)], right[i % len(left)] if cfg["stereo"] else None)
                 done[t] += 1
                 i += threads
         except Exception as e:          # noqa: a dead worker must not turn into a silently higher or lower number
@@ -291,7 +309,8 @@ def cpu_baseline_object(cfg, left, right, seconds, with_single=True):
     what = ("unmodified reference src/ORBextractor.cc (oracle/_ref, g++ -O3 -march=x86-64-v3, cv primitives = the cv2-pinned scalar shim)"
             if kind == "reference" else "scalar C++ port of the reference (oracle/)")
     if cfg["stereo"]:
-        what += " + Frame::ComputeStereoMatches from the oracle port"
+        what += (" inside the unmodified reference src/Frame.cc (constructor + ExtractORB(1, right) + ComputeStereoMatches, libframe_ref.so)"
+                 if _stereo_pipeline(cfg) is not None else " + Frame::ComputeStereoMatches from the oracle port")
     out = {"value": v, "unit": unit_of(cfg), "cores": threads, "kind": kind,
            "sample": "%d %s in %.0f s, one extractor instance%s and one unit per thread; %s" %
                      (cnt, "pairs" if cfg["stereo"] else "frames", seconds, " pair" if cfg["stereo"] else "", what)}
@@ -320,6 +339,8 @@ def run_reference(args, cfg):
     value = sum(vals) / len(vals)
     sample = "%d steps of %.1f s, %d units in total, one reference extractor%s + one unit per thread" % (
         args.steps, per_step, n, " pair" if cfg["stereo"] else "")
+    if cfg["stereo"] and _stereo_pipeline(cfg) is not None:
+        sample += "; each pair through the unmodified reference src/Frame.cc (constructor + ExtractORB(1, right) + ComputeStereoMatches)"
     emit({
         "impl": "reference", "metric": metric_of(cfg), "value": value, "unit": unit_of(cfg), "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -2,7 +2,8 @@
 src/ORBextractor.cc and the vendored Thirdparty/DBoW2, compiled where they lie over oracle/ref_shim/; entry points:
 oracle/ref_shim/frame_ref_api.cpp).
 
-TEST INFRASTRUCTURE, NOT PRODUCT: only tests/ may import this module.  The library is built by `make -C oracle _ref` in the container that
+TEST INFRASTRUCTURE, NOT PRODUCT: only tests/ and the cpu_baseline / --impl reference legs of bench.py (stereo configurations) may import
+this module.  The library is built by `make -C oracle _ref` in the container that
 holds /root/reference; the GPU box receives the built file with the snapshot.
 """
 import ctypes as C
@@ -64,6 +65,11 @@ def lib():
         L.reff_voc_transform.argtypes = [vp, vp, i, i, vp, vp, vp, vp, vp, vp]
         L.reff_voc_score.restype = d
         L.reff_voc_score.argtypes = [vp, vp, vp, i, vp, vp, i]
+        L.reff_stereo_create.restype = vp
+        L.reff_stereo_create.argtypes = [i, f, i, i, i, vp, f, f]
+        L.reff_stereo_destroy.argtypes = [vp]
+        L.reff_stereo_run.restype = i
+        L.reff_stereo_run.argtypes = [vp, vp, vp, i, i, vp]
         _lib = L
     return _lib
 
@@ -103,6 +109,28 @@ class RefVocabulary:
         ia, va = np.ascontiguousarray(a[0], np.int32), np.ascontiguousarray(a[1], np.float64)
         ib, vb = np.ascontiguousarray(b[0], np.int32), np.ascontiguousarray(b[1], np.float64)
         return self.L.reff_voc_score(self.h, _p(ia), _p(va), len(ia), _p(ib), _p(vb), len(ib))
+
+
+class RefStereoPipeline:
+    """Two reference extractors kept across pairs; run(left, right) builds the reference Frame of one rectified pair (extraction of both
+    images, grid, ComputeStereoMatches) and returns (N, features with a stereo match).  The timed CPU baseline of the stereo configurations."""
+
+    def __init__(self, K4, bf, thDepth=35.0, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniTh=20, minTh=7):
+        self.L = lib()
+        K4 = np.ascontiguousarray(K4, np.float32)
+        self.h = self.L.reff_stereo_create(nfeatures, scaleFactor, nlevels, iniTh, minTh, _p(K4), bf, thDepth)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.reff_stereo_destroy(self.h)
+            self.h = None
+
+    def run(self, left, right):
+        left, right = np.ascontiguousarray(left, np.uint8), np.ascontiguousarray(right, np.uint8)
+        counts = np.zeros(2, np.int32)
+        if self.L.reff_stereo_run(self.h, _p(left), _p(right), left.shape[1], left.shape[0], _p(counts)) != 0:
+            raise RuntimeError("the reference Frame threw")
+        return int(counts[0]), int(counts[1])
 
 
 class RefFrame:

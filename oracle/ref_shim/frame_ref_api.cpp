@@ -163,6 +163,44 @@ int reff_frame_unproject_stereo(reff_frame* f, int i, float* xyz)
     return 1;
 }
 
+// ---- one stereo unit after another with the extractors kept, as Tracking keeps them (Tracking.cc:88-95): the timed CPU baseline of the
+// stereo configurations.  Per pair: Frame(imLeft, ...) [ExtractORB(0), UndistortKeyPoints, bounds, AssignFeaturesToGrid], ExtractORB(1, imRight),
+// ComputeStereoMatches(); the Frame is destroyed before returning.  counts2 = (N, features with a stereo match).
+struct reff_stereo_pipeline {
+    std::unique_ptr<ORBextractor> left, right;
+    cv::Mat K, dist;
+    float bf, thDepth;
+};
+reff_stereo_pipeline* reff_stereo_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, const float* K4, float bf, float thDepth)
+{
+    std::unique_ptr<reff_stereo_pipeline> p(new reff_stereo_pipeline);
+    p->left.reset(new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh));
+    p->right.reset(new ORBextractor(nfeatures, scaleFactor, nlevels, iniTh, minTh));
+    p->K = cv::Mat::eye(3, 3, CV_32F);
+    p->K.at<float>(0, 0) = K4[0]; p->K.at<float>(1, 1) = K4[1]; p->K.at<float>(0, 2) = K4[2]; p->K.at<float>(1, 2) = K4[3];
+    p->dist = cv::Mat::zeros(4, 1, CV_32F);                                  // stereo input is rectified (Frame.h:150-152)
+    p->bf = bf; p->thDepth = thDepth;
+    return p.release();
+}
+void reff_stereo_destroy(reff_stereo_pipeline* p) { delete p; }
+int reff_stereo_run(reff_stereo_pipeline* p, const uint8_t* im_left, const uint8_t* im_right, int w, int h, int* counts2)
+{
+    try {
+        cv::Mat imL(h, w, CV_8UC1, const_cast<uint8_t*>(im_left)), imR(h, w, CV_8UC1, const_cast<uint8_t*>(im_right));
+        Frame F(imL, 0.0, p->left.get(), static_cast<ORBVocabulary*>(NULL), p->K, p->dist, p->bf, p->thDepth);
+        F.mpORBextractorRight = p->right.get();
+        F.ExtractORB(1, imR);
+        F.ComputeStereoMatches();
+        int matched = 0;
+        for (int i = 0; i < F.N; i++) matched += F.mvuRight[i] >= 0;
+        counts2[0] = F.N; counts2[1] = matched;
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "reff_stereo_run: %s\n", e.what());
+        return -1;
+    }
+}
+
 // ---- the vendored DBoW2 vocabulary (ORBVocabulary = TemplatedVocabulary<FORB::TDescriptor, FORB>), loaded with the reference's own
 // loadFromTextFile (TemplatedVocabulary.h:1351-1436)
 reff_voc* reff_voc_load_text(const char* path)

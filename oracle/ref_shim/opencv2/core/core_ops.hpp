@@ -12,14 +12,22 @@ template <class F> static inline Mat zip(const Mat& a, const Mat& b, F f)
     need32f(a); need32f(b);
     if (a.rows != b.rows || a.cols != b.cols) throw std::runtime_error("cv shim: size mismatch");
     Mat r(a.rows, a.cols, CV_32F);
-    for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) r.at<float>(y, x) = f(a.at<float>(y, x), b.at<float>(y, x));
+    for (int y = 0; y < a.rows; y++) {
+        const float *pa = a.ptr<float>(y), *pb = b.ptr<float>(y);
+        float* pr = r.ptr<float>(y);
+        for (int x = 0; x < a.cols; x++) pr[x] = f(pa[x], pb[x]);
+    }
     return r;
 }
 template <class F> static inline Mat map(const Mat& a, F f)
 {
     need32f(a);
     Mat r(a.rows, a.cols, CV_32F);
-    for (int y = 0; y < a.rows; y++) for (int x = 0; x < a.cols; x++) r.at<float>(y, x) = f(a.at<float>(y, x));
+    for (int y = 0; y < a.rows; y++) {
+        const float* pa = a.ptr<float>(y);
+        float* pr = r.ptr<float>(y);
+        for (int x = 0; x < a.cols; x++) pr[x] = f(pa[x]);
+    }
     return r;
 }
 } // namespace shim
@@ -32,8 +40,19 @@ static inline Mat operator*(double s, const Mat& a) { return a * s; }
 static inline Mat operator/(const Mat& a, double s) { return shim::map(a, [s](float p) { return (float)(p / s); }); }
 static inline MatExpr operator*(double s, const MatExpr& e) { MatExpr r = e; r.fill = (float)(e.fill * s); return r; }     // s * Mat::ones(...)
 static inline MatExpr operator*(const MatExpr& e, double s) { return s * e; }
-static inline Mat operator-(const Mat& a, const MatExpr& e) { return a - Mat(e); }
-static inline Mat operator+(const Mat& a, const MatExpr& e) { return a + Mat(e); }
+// a -/+ (s * Mat::ones): per element a -/+ fill in float, what the evaluated expression gives (the constant matrix is not materialised)
+static inline Mat operator-(const Mat& a, const MatExpr& e)
+{
+    if (e.eye || a.rows != e.rows || a.cols != e.cols) return a - Mat(e);
+    const float c = e.fill;
+    return shim::map(a, [c](float p) { return p - c; });
+}
+static inline Mat operator+(const Mat& a, const MatExpr& e)
+{
+    if (e.eye || a.rows != e.rows || a.cols != e.cols) return a + Mat(e);
+    const float c = e.fill;
+    return shim::map(a, [c](float p) { return p + c; });
+}
 static inline Mat operator*(const Mat& a, const Mat& b)
 {
     shim::need32f(a); shim::need32f(b);
@@ -68,6 +87,15 @@ inline Mat Mat::inv() const { throw std::runtime_error("cv shim: Mat::inv not pr
 inline void Mat::convertTo(Mat& dst, int rtype) const
 {
     Mat r(rows, cols, rtype & 7);
+    if (depth() == CV_8U && (rtype & 7) == CV_32F) {        // the one conversion on a hot path (Frame.cc:579, :596): no per-element dispatch
+        for (int y = 0; y < rows; y++) {
+            const uchar* s = ptr<uchar>(y);
+            float* d = r.ptr<float>(y);
+            for (int x = 0; x < cols; x++) d[x] = (float)s[x];
+        }
+        dst = r;
+        return;
+    }
     for (int y = 0; y < rows; y++)
         for (int x = 0; x < cols; x++) {
             double v = depth() == CV_8U ? (double)at<uchar>(y, x) : depth() == CV_32F ? (double)at<float>(y, x)
@@ -98,11 +126,13 @@ static inline double norm(const Mat& a, const Mat& b, int normType = NORM_L2)
     shim::need32f(a); shim::need32f(b);
     if (a.rows != b.rows || a.cols != b.cols) throw std::runtime_error("cv shim: norm size mismatch");
     double s = 0;
-    for (int y = 0; y < a.rows; y++)
+    for (int y = 0; y < a.rows; y++) {
+        const float *pa = a.ptr<float>(y), *pb = b.ptr<float>(y);
         for (int x = 0; x < a.cols; x++) {
-            const double v = (double)a.at<float>(y, x) - (double)b.at<float>(y, x);
+            const double v = (double)pa[x] - (double)pb[x];
             if (normType == NORM_L1) s += std::fabs(v); else if (normType == NORM_INF) s = std::max(s, std::fabs(v)); else s += v * v;
         }
+    }
     return normType == NORM_L2 ? std::sqrt(s) : s;
 }
 

@@ -52,6 +52,18 @@ def test_compute_stereo_matches_without_right_keypoints_or_matches():
     assert n == 0 and uR.tobytes() == F.u_right.tobytes() and dep.tobytes() == F.depth_out.tobytes()
 
 
+def test_stereo_pipeline_of_the_cpu_baseline():
+    """bench.py's stereo CPU legs: extractors kept, one reference Frame per pair.  Which of several equally sized quadtree nodes is split
+    first depends on heap addresses, so the counts are bounded, not pinned."""
+    w, h = 752, 480
+    left, right = synth.stereo_rects(w, h, 1001)[:2]
+    p = RF.RefStereoPipeline([435.2, 435.2, w * 0.5, h * 0.5], 47.9, nfeatures=1200)
+    F = RF.RefFrame("stereo", left, [435.2, 435.2, w * 0.5, h * 0.5], np.zeros(4), bf=47.9, im_right=right, nfeatures=1200)
+    for _ in range(2):
+        n, matched = p.run(left, right)
+        assert abs(n - F.N) <= 12 and abs(matched - int((F.u_right >= 0).sum())) <= 25 and matched > 100
+
+
 # ---------------------------------------------------------------------------------------------- undistortion, bounds, RGB-D
 CAMERAS = [("tum1", (517.3, 516.5, 318.6, 255.3), (0.2624, -0.9531, -0.0054, 0.0026, 1.1633)),
            ("tum2", (520.9, 521.0, 325.1, 249.7), (0.2312, -0.7849, -0.0033, -0.0001, 0.9172)),
