@@ -271,6 +271,9 @@ template <class KeyFrameT, class MapPointT> int ORBmatcher::Fuse(KeyFrameT* pKF,
     for (size_t j = 0; j < best.size(); j++) {                             // :937-958, in the reference's visiting order
         if (best[j] < 0) continue;
         MapPointT* pMP = vpMapPoints[who[j]];
+        // the reference evaluates :851-852 when it reaches the point, i.e. after the Replace / AddObservation calls of the points before
+        // it (a point listed twice, or one that an earlier iteration replaced): evaluated again here, at the same moment
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
         MapPointT* pMPinKF = pKF->GetMapPoint(best[j]);
         if (pMPinKF) {
             if (!pMPinKF->isBad()) {

@@ -173,6 +173,7 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
         R.build(FA0, FB0, w, h, dx, dy);
         M.build(FA0, FB0, w, h, dx, dy);
         std::vector<MapPoint*> vr = R.FA.mvpMapPoints, vm = M.FA.mvpMapPoints;          // A's points (with NULLs and bad ones) into key frame B
+        for (size_t i = 0; i < R.FA.mvpMapPoints.size(); i += 7) { vr.push_back(R.FA.mvpMapPoints[i]); vm.push_back(M.FA.mvpMapPoints[i]); }   // some listed twice
         const float th = 3.f;
         const int nr = refm::Fuse(nn, checkOri, &R.KB, vr, th);
         const int nm = mine.Fuse(&M.KB, vm, th);                          // as at LocalMapping.cc:497 matcher.Fuse(pKFi,vpMapPointMatches) / :522
