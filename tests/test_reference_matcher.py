@@ -99,3 +99,55 @@ def test_searches_equal_the_reference_matcher(tmp_path, w, h, nf, seed, dx, dy):
     _views(tmp_path, w, h, seed, dx, dy)
     r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.rstrip().endswith("ok"), (r.returncode, r.stdout[-3000:], r.stderr[-3000:])
+
+
+# ---- the same comparison on the reference's REAL objects: tests/native/reference_objects_test.cpp compiles the product's drop-in ORBmatcher
+# against the reference's own Frame.h / KeyFrame.h / MapPoint.h / ORBmatcher.h and links the reference's own object code
+# (oracle/_ref/libslam_ref.so: unmodified Frame.cc, KeyFrame.cc, MapPoint.cc, ORBmatcher.cc, ORBextractor.cc, DBoW2).  Compiling it needs the
+# reference tree, so the GPU leg runs the executable `make -C oracle _ref_tests` built where that tree exists.
+REAL_EXE = os.path.join(ROOT, "oracle", "_ref", "reference_objects_test")
+REF_TREE = os.environ.get("ORB_REFERENCE_ROOT", "/root/reference")
+
+
+@pytest.fixture(scope="module")
+def real_cpu_exe(tmp_path_factory):
+    if not os.path.isdir(os.path.join(REF_TREE, "include")):
+        pytest.skip("the reference tree is not here: its headers are needed to compile this test")
+    tmp = tmp_path_factory.mktemp("refobjects_cpu")
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "_ref/libslam_ref.so"], stdout=subprocess.DEVNULL)
+    import oracle_py  # noqa: builds oracle/liborb_oracle.so when it is missing
+    oradir, shim = os.path.join(ROOT, "oracle"), os.path.join(ROOT, "oracle", "ref_shim")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-fPIC", "-shared", "-I", os.path.join(ROOT, "include"), "-I", oradir,
+                           "-o", str(tmp / "liborbx_on_oracle.so"), os.path.join(ROOT, "tests", "native", "orbx_on_oracle.cpp"),
+                           "-L", oradir, "-lorb_oracle", "-Wl,-rpath," + oradir])
+    exe = str(tmp / "refobjects_cpu")
+    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-DORBX_USE_OPENCV", "-Wno-overloaded-virtual", "-I", os.path.join(shim, "slam_full"), "-I", shim,
+                           "-I", os.path.join(REF_TREE, "include"), "-I", REF_TREE, "-o", exe, os.path.join(ROOT, "tests", "native", "reference_objects_test.cpp"),
+                           "-L", str(tmp), "-lorbx_on_oracle", "-Wl,-rpath," + str(tmp), "-L", os.path.join(oradir, "_ref"), "-lslam_ref",
+                           "-Wl,-rpath," + os.path.join(oradir, "_ref")])
+    return exe
+
+
+def _run_real(exe, tmp_path, w, h, nf, seed, dx, dy, kind="rects"):
+    _views(tmp_path, w, h, seed, dx, dy, kind)
+    r = subprocess.run([exe, str(tmp_path / "a.raw"), str(tmp_path / "b.raw"), str(w), str(h), str(nf), str(dx), str(dy)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.rstrip().endswith("ok"), (r.returncode, r.stdout[-3000:], r.stderr[-3000:])
+    assert r.stdout.count("SearchBySim3") == 4 and r.stdout.count("Fuse(KF, MPs)") == 2 and r.stdout.count("SearchForTriangulation") == 4
+
+
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy,kind", [s + ("rects",) for s in SCENES] +
+                         [(400, 300, 500, 2400, 5, 4, "rects"), (640, 480, 1000, 2500, 2, 2, "texture"), (752, 480, 1500, 2700, 6, 0, "rects")])
+def test_drop_in_headers_on_the_reference_s_real_objects_cpu(tmp_path, real_cpu_exe, w, h, nf, seed, dx, dy, kind):
+    """All eleven searches, the product's ORBmatcher (over the CPU oracle's C ABI) and the reference's, same call lines, on real
+    ORB_SLAM2 Frame / KeyFrame / MapPoint objects."""
+    _run_real(real_cpu_exe, tmp_path, w, h, nf, seed, dx, dy, kind)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,nf,seed,dx,dy", SCENES)
+def test_drop_in_headers_on_the_reference_s_real_objects(tmp_path, w, h, nf, seed, dx, dy):
+    if os.path.isdir(os.path.join(REF_TREE, "include")):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "_ref_tests"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(REAL_EXE):
+        pytest.skip("oracle/_ref/reference_objects_test was not built (make -C oracle _ref_tests needs the reference tree)")
+    _run_real(REAL_EXE, tmp_path, w, h, nf, seed, dx, dy)
