@@ -15,7 +15,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 REF_ROOT = os.environ.get("ORB_REFERENCE_ROOT", "/root/reference")
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 PATH = os.path.join(_HERE, "_ref", "libframe_ref.so")
-_lib = None
+# The same C interface over the reference's Frame.cc compiled against THIS REPOSITORY'S ORBextractor.h / ORBmatcher.h (oracle/Makefile, _ref_tests):
+# liborbx.so behind it (GPU), or the C ABI served by the CPU oracle.
+DROPIN_PATH = os.path.join(_HERE, "_ref", "libframe_dropin.so")
+DROPIN_CPU_PATH = os.path.join(_HERE, "_ref", "libframe_dropin_cpu.so")
+_libs = {}
 
 
 def available():
@@ -24,12 +28,19 @@ def available():
     return os.path.exists(PATH)
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        if not available():
+def dropin_available(cpu):
+    path = DROPIN_CPU_PATH if cpu else DROPIN_PATH
+    if os.path.exists(os.path.join(REF_ROOT, "src", "Frame.cc")) and (cpu or os.path.exists(os.path.join(_HERE, "..", "orb_slam2v2-1_b200", "orbx", "liborbx.so"))):
+        subprocess.check_call(["make", "-C", _HERE, "liborb_oracle.so", "_ref/" + os.path.basename(path), "REF=" + REF_ROOT], stdout=subprocess.DEVNULL)
+    return os.path.exists(path)
+
+
+def lib(path=None):
+    path = path or PATH
+    if path not in _libs:
+        if path == PATH and not available():
             raise RuntimeError("oracle/_ref/libframe_ref.so is missing and /root/reference is not here to build it")
-        L = C.CDLL(PATH)
+        L = C.CDLL(path)
         vp, i, f, d = C.c_void_p, C.c_int, C.c_float, C.c_double
         L.reff_frame_create.restype = vp
         L.reff_frame_create.argtypes = [i, vp, vp, vp, i, i, i, f, i, i, i, vp, vp, i, f, f, vp]
@@ -51,7 +62,8 @@ def lib():
         L.reff_frame_grid_cell.argtypes = [vp, i, i, vp, i]
         L.reff_frame_pos_in_grid.restype = i
         L.reff_frame_pos_in_grid.argtypes = [vp, f, f, vp, vp]
-        L.reff_frame_is_in_frustum.argtypes = [vp, vp, vp, vp, vp, vp, i, f, vp]
+        if hasattr(L, "reff_frame_is_in_frustum"):
+            L.reff_frame_is_in_frustum.argtypes = [vp, vp, vp, vp, vp, vp, i, f, vp]
         L.reff_frame_unproject_stereo.restype = i
         L.reff_frame_unproject_stereo.argtypes = [vp, i, vp]
         L.reff_voc_load_text.restype = vp
@@ -70,8 +82,8 @@ def lib():
         L.reff_stereo_destroy.argtypes = [vp]
         L.reff_stereo_run.restype = i
         L.reff_stereo_run.argtypes = [vp, vp, vp, i, i, vp]
-        _lib = L
-    return _lib
+        _libs[path] = L
+    return _libs[path]
 
 
 def _p(a):
@@ -81,8 +93,8 @@ def _p(a):
 class RefVocabulary:
     """ORBVocabulary of the reference (DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) loaded with its own loadFromTextFile."""
 
-    def __init__(self, path):
-        self.L = lib()
+    def __init__(self, path, libpath=None):
+        self.L = lib(libpath)
         self.h = self.L.reff_voc_load_text(os.fsencode(path))
         if not self.h:
             raise RuntimeError("loadFromTextFile failed: " + path)
@@ -115,8 +127,8 @@ class RefStereoPipeline:
     """Two reference extractors kept across pairs; run(left, right) builds the reference Frame of one rectified pair (extraction of both
     images, grid, ComputeStereoMatches) and returns (N, features with a stereo match).  The timed CPU baseline of the stereo configurations."""
 
-    def __init__(self, K4, bf, thDepth=35.0, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniTh=20, minTh=7):
-        self.L = lib()
+    def __init__(self, K4, bf, thDepth=35.0, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniTh=20, minTh=7, libpath=None):
+        self.L = lib(libpath)
         K4 = np.ascontiguousarray(K4, np.float32)
         self.h = self.L.reff_stereo_create(nfeatures, scaleFactor, nlevels, iniTh, minTh, _p(K4), bf, thDepth)
 
@@ -138,8 +150,8 @@ class RefFrame:
     ExtractORB(1, right) + ComputeStereoMatches(), see frame_ref_api.cpp on why), "rgbd" (Frame.cc:119)."""
 
     def __init__(self, kind, im, K4, dist, bf, thDepth=35.0, im_right=None, depth=None, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniTh=20, minTh=7,
-                 voc=None):
-        self.L = lib()
+                 voc=None, libpath=None):
+        self.L = lib(libpath)
         self.im = np.ascontiguousarray(im, np.uint8)
         self.im_right = None if im_right is None else np.ascontiguousarray(im_right, np.uint8)
         self.depth = None if depth is None else np.ascontiguousarray(depth, np.float32)

@@ -3,7 +3,8 @@
 // oracle/_ref/libframe_ref.so = /root/reference/src/Frame.cc, src/ORBmatcher.cc, src/ORBextractor.cc and the vendored
 // Thirdparty/DBoW2 (BowVector.cpp, FeatureVector.cpp, ScoringObject.cpp, FORB.cpp, TemplatedVocabulary.h, DUtils/Random.cpp), each compiled
 // where it lies (never copied), over the cv shim (ref_shim/opencv2) and the stand-in MapPoint / KeyFrame (ref_shim/slam/slam_objects.h),
-// namespace renamed to ORB_SLAM2_REFF.  This file only builds Frames through the reference's own constructors, calls the reference's own
+// namespace renamed to ORB_SLAM2_REFF.  (The same file also builds oracle/_ref/libframe_dropin.so, where ORBextractor and ORBmatcher are THIS
+// REPOSITORY'S drop-in headers instead of the reference's: see ref_shim/dropin/prelude_dropin.h.)  This file only builds Frames through the reference's own constructors, calls the reference's own
 // member functions and copies members out; what Frame computes -- UndistortKeyPoints, ComputeImageBounds, AssignFeaturesToGrid,
 // GetFeaturesInArea, ComputeStereoMatches, ComputeStereoFromRGBD, isInFrustum, ComputeBoW, UnprojectStereo -- is the reference's code.
 //
@@ -134,6 +135,7 @@ int reff_frame_pos_in_grid(const reff_frame* f, float x, float y, int* posX, int
     kp.pt.x = x; kp.pt.y = y;
     return f->F->PosInGrid(kp, *posX, *posY) ? 1 : 0;
 }
+#ifndef ORBX_FRAME_API_REAL_MAPPOINT     // fills the stand-in MapPoint's fields directly; left out where MapPoint is the reference's own class (libframe_dropin.so)
 // Frame::SetPose + isInFrustum (Frame.cc:255-340) for n MapPoints (world position, normal, distance range each).
 // out: n x 6 floats = (returned bool, mTrackProjX, mTrackProjY, mTrackProjXR, mnTrackScaleLevel, mTrackViewCos)
 void reff_frame_is_in_frustum(reff_frame* f, const float* Tcw16, const float* pos, const float* normal, const float* min_dist, const float* max_dist, int n,
@@ -154,6 +156,7 @@ void reff_frame_is_in_frustum(reff_frame* f, const float* Tcw16, const float* po
         o[0] = in ? 1.f : 0.f; o[1] = mp.mTrackProjX; o[2] = mp.mTrackProjY; o[3] = mp.mTrackProjXR; o[4] = (float)mp.mnTrackScaleLevel; o[5] = mp.mTrackViewCos;
     }
 }
+#endif
 // Frame::UnprojectStereo (Frame.cc:681-696) under the pose set by the last reff_frame_is_in_frustum: 3 floats, returns 0 where the reference returns an empty Mat
 int reff_frame_unproject_stereo(reff_frame* f, int i, float* xyz)
 {

@@ -236,3 +236,76 @@ def test_vocabulary_text_file_with_a_trailing_newline(tmp_path):
     _write_voc(b, voc, trailing_newline=True)
     assert RF.RefVocabulary(a).size() == 1000
     assert RF.RefVocabulary(b).size() in (1000, 1001)
+
+
+# ---------------------------------------------------------------------------------------------- the swap itself
+# oracle/_ref/libframe_dropin*.so: the reference's UNMODIFIED Frame.cc / KeyFrame.cc / MapPoint.cc compiled against THIS REPOSITORY'S
+# include/ORBextractor.h and include/ORBmatcher.h in place of the reference's headers (oracle/ref_shim/dropin/prelude_dropin.h) -- no
+# ORBextractor.cc, no ORBmatcher.cc of the reference inside.  The reference's own Frame constructor then drives the product's extractor
+# (operator(), GetLevels() .. GetInverseScaleSigmaSquares()), and the reference's own ComputeStereoMatches reads the product's mvImagePyramid.
+STEREO_SHAPES = [(640, 480, 1000, 520.0, 40.0, 1000), (752, 480, 1200, 435.2, 47.9, 1001), (1241, 376, 2000, 718.9, 386.1, 1002)]
+
+
+def _check_dropin_stereo_frame(libpath, w, h, nf, fx, bf, seed, keys_of):
+    left, right = synth.stereo_rects(w, h, seed)[:2]
+    F = RF.RefFrame("stereo", left, _K(w, h, fx, fx), np.zeros(4), bf=bf, im_right=right, nfeatures=nf, libpath=libpath)
+    (kl, dl), (kr, dr) = keys_of(left), keys_of(right)
+    assert F.keys.tobytes() == kl.tobytes() and F.desc.tobytes() == dl.tobytes()                # Frame::ExtractORB(0, .) ran the product's operator()
+    assert F.keys_right.tobytes() == kr.tobytes() and F.desc_right.tobytes() == dr.tobytes()
+    assert F.keys_un.tobytes() == F.keys.tobytes() and F.bounds.tolist() == [0.0, float(w), 0.0, float(h)]
+    oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
+    sf = oe.scale_tables()
+    assert F.sf.tobytes() == sf[0].tobytes() and F.isf.tobytes() == sf[1].tobytes() and F.sigma2.tobytes() == sf[2].tobytes() and F.isigma2.tobytes() == sf[3].tobytes()
+    # the reference's ComputeStereoMatches over the product's mvImagePyramid == the oracle over the same views
+    n, uR, dep = O.stereo_matches(F.keys, F.desc, F.keys_right, F.desc_right, F.pyramid(0), F.pyramid(1), F.sf, F.isf, bf, float(np.float32(bf) / F.mb))
+    assert uR.tobytes() == F.u_right.tobytes() and dep.tobytes() == F.depth_out.tobytes() and n > 40
+    # ... and the product's mvImagePyramid views are the oracle's pyramid levels
+    oe(left)
+    for l, lv in enumerate(F.pyramid(0)):
+        assert np.array_equal(lv, oe.level_padded(l)[19:-19, 19:-19]), l
+    # the grid the reference built over the product's keypoints
+    total = sum(len(F.grid_cell(c, r)) for c in range(64) for r in range(48))
+    assert total == F.N - sum(not F.pos_in_grid(float(k["x"]), float(k["y"]))[0] for k in F.keys_un)
+    return F, n, uR, dep
+
+
+@pytest.mark.parametrize("w,h,nf,fx,bf,seed", STEREO_SHAPES)
+def test_reference_frame_built_on_the_drop_in_extractor_cpu(w, h, nf, fx, bf, seed):
+    if not RF.dropin_available(cpu=True):
+        pytest.skip("oracle/_ref/libframe_dropin_cpu.so is not built and the reference tree is not here")
+    oe = O.OracleExtractor(nf, 1.2, 8, 20, 7)
+    _check_dropin_stereo_frame(RF.DROPIN_CPU_PATH, w, h, nf, fx, bf, seed, lambda im: oe(im))
+
+
+def test_reference_rgbd_frame_built_on_the_drop_in_extractor_cpu():
+    if not RF.dropin_available(cpu=True):
+        pytest.skip("oracle/_ref/libframe_dropin_cpu.so is not built and the reference tree is not here")
+    name, K4, dist = CAMERAS[0]
+    w, h, bf = 640, 480, 40.0
+    im = synth.rects(w, h, 1500)
+    depth = np.random.default_rng(6).uniform(0.4, 9.0, (h, w)).astype(np.float32)
+    F = RF.RefFrame("rgbd", im, K4, dist, bf=bf, depth=depth, libpath=RF.DROPIN_CPU_PATH)
+    k, d = O.OracleExtractor(1000, 1.2, 8, 20, 7)(im)
+    assert F.keys.tobytes() == k.tobytes() and F.desc.tobytes() == d.tobytes()
+    K4f = [np.float32(v) for v in K4]
+    assert O.undistort_keypoints(F.keys, K4f, dist).tobytes() == F.keys_un.tobytes()
+    uR, dep = O.stereo_from_rgbd(F.keys, F.keys_un, depth, bf)
+    assert uR.tobytes() == F.u_right.tobytes() and dep.tobytes() == F.depth_out.tobytes()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("w,h,nf,fx,bf,seed", STEREO_SHAPES)
+def test_reference_frame_built_on_the_cuda_extractor(w, h, nf, fx, bf, seed):
+    """The reference's Frame constructor and ComputeStereoMatches (its own CPU code) around the CUDA extractor, through the drop-in header;
+    the stereo association it computes equals the product's own CUDA ComputeStereoMatches on the same frame."""
+    if not RF.dropin_available(cpu=False):
+        pytest.skip("oracle/_ref/libframe_dropin.so was not built (make -C oracle _ref_tests needs the reference tree)")
+    import orbx
+    exL, exR = orbx.ORBextractor(nf, 1.2, 8, 20, 7), orbx.ORBextractor(nf, 1.2, 8, 20, 7)
+    left, right = synth.stereo_rects(w, h, seed)[:2]
+    F, n, uR, dep = _check_dropin_stereo_frame(RF.DROPIN_PATH, w, h, nf, fx, bf, seed, lambda im: orbx.ORBextractor(nf, 1.2, 8, 20, 7)(im))
+    kl, dl = exL(left)
+    kr, dr = exR(right)
+    m = orbx.ORBmatcher()
+    n2, uR2, dep2 = m.ComputeStereoMatches(exL, exR, kl, dl, kr, dr, bf, float(np.float32(bf) / F.mb))
+    assert n2 == n and uR2.tobytes() == uR.tobytes() and dep2.tobytes() == dep.tobytes()
