@@ -150,6 +150,7 @@ void orbo_stereo_from_rgbd(const orbo_kp* kps, const orbo_kp* kps_un, int n, con
 typedef struct orbo_vocabulary orbo_vocabulary;
 orbo_vocabulary* orbo_voc_create(int k, int L, int scoring, int weighting, const int* parent, const uint8_t* desc, const double* weight, int nnodes);
 void orbo_voc_destroy(orbo_vocabulary* v);
+int orbo_voc_size(const orbo_vocabulary* v);
 void orbo_voc_transform_raw(const orbo_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id, double* weight, int* node_id);
 int orbo_voc_transform(const orbo_vocabulary* voc, const uint8_t* desc, int n, int levelsup, int* bow_id, double* bow_val,
                        int* fv_node, int* fv_off, int* fv_idx, int* nfv);

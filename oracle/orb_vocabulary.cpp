@@ -39,6 +39,13 @@ orbo_vocabulary* orbo_voc_create(int k, int L, int scoring, int weighting, const
     return v;
 }
 void orbo_voc_destroy(orbo_vocabulary* v) { delete v; }
+// TemplatedVocabulary::size() (:838-842): the number of words
+int orbo_voc_size(const orbo_vocabulary* v)
+{
+    int n = 0;
+    for (size_t i = 1; i < v->word_id.size(); i++) n += v->word_id[i] >= 0;
+    return n;
+}
 
 // transform(feature, word_id, weight, nid, levelsup) (:1231-1270)
 void orbo_voc_transform_raw(const orbo_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id, double* weight, int* node_id)

@@ -75,8 +75,9 @@ def lib(path=None):
         L.reff_frame_compute_bow.argtypes = [vp] * 7
         L.reff_voc_transform.restype = i
         L.reff_voc_transform.argtypes = [vp, vp, i, i, vp, vp, vp, vp, vp, vp]
-        L.reff_voc_score.restype = d
-        L.reff_voc_score.argtypes = [vp, vp, vp, i, vp, vp, i]
+        if hasattr(L, "reff_voc_score"):
+            L.reff_voc_score.restype = d
+            L.reff_voc_score.argtypes = [vp, vp, vp, i, vp, vp, i]
         L.reff_stereo_create.restype = vp
         L.reff_stereo_create.argtypes = [i, f, i, i, i, vp, f, f]
         L.reff_stereo_destroy.argtypes = [vp]

@@ -260,6 +260,7 @@ int reff_voc_transform(reff_voc* v, const uint8_t* desc, int n, int levelsup, in
     *n_fv = nn;
     return nb;
 }
+#ifndef ORBX_FRAME_API_REAL_MAPPOINT     // the drop-in ORBVocabulary leaves scoring two vectors to DBoW2 (include/ORBVocabulary.h)
 // DBoW2's score between two BowVectors with the vocabulary's scoring object (TemplatedVocabulary::score, used by KeyFrameDatabase)
 double reff_voc_score(reff_voc* v, const int* id1, const double* val1, int n1, const int* id2, const double* val2, int n2)
 {
@@ -268,5 +269,6 @@ double reff_voc_score(reff_voc* v, const int* id1, const double* val1, int n1, c
     for (int i = 0; i < n2; i++) b[(DBoW2::WordId)id2[i]] = val2[i];
     return v->voc.score(a, b);
 }
+#endif
 
 }  // extern "C"

@@ -1,4 +1,4 @@
-// orbx_on_oracle.cpp -- TEST INFRASTRUCTURE, never shipped: the 21 entry points of include/orbx.h that the drop-in headers call in
+// orbx_on_oracle.cpp -- TEST INFRASTRUCTURE, never shipped: the entry points of include/orbx.h that the drop-in headers call in
 // tests/native/reference_matcher_test.cpp, implemented by the CPU oracle (oracle/orb_oracle.h).  Linked INSTEAD of liborbx.so it lets
 // that test run without a GPU: the headers' flattening code (include/ORBmatcher.h, ORBmatcher_reference_api.inl) and the oracle's
 // searches against the UNMODIFIED reference src/ORBmatcher.cc.  The product never sees this file (no CPU fallback exists in liborbx.so).
@@ -146,6 +146,21 @@ int orbm_search_for_triangulation(orbx_matcher*, const orbx_kp* k1, const uint8_
 {
     *nmatches = orbo_search_for_triangulation(K(k1), d1, n1, has1, ur1, node1, off1, idx1, nn1, K(k2), d2, n2, has2, ur2, node2, off2, idx2, nn2, F12, ex, ey,
                                               sf2, sig2, nlevels, onlyStereo, checkOri, m12);
+    return ORBX_OK;
+}
+
+// ---- ORBVocabulary (include/ORBVocabulary.h)
+int orbv_create(int, int k, int L, int scoring, int weighting, const int* parent, const uint8_t* desc, const double* weight, int nnodes, orbx_vocabulary** out)
+{
+    *out = reinterpret_cast<orbx_vocabulary*>(orbo_voc_create(k, L, scoring, weighting, parent, desc, weight, nnodes));
+    return *out ? ORBX_OK : ORBX_ERR_ARG;
+}
+void orbv_destroy(orbx_vocabulary* v) { if (v) orbo_voc_destroy(reinterpret_cast<orbo_vocabulary*>(v)); }
+int orbv_size(const orbx_vocabulary* v) { return v ? orbo_voc_size(reinterpret_cast<const orbo_vocabulary*>(v)) : 0; }
+int orbv_transform(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* bow_id, double* bow_val, int* nbow, int* fv_node, int* fv_off,
+                   int* fv_idx, int* nfv)
+{
+    *nbow = orbo_voc_transform(reinterpret_cast<const orbo_vocabulary*>(v), desc, n, levelsup, bow_id, bow_val, fv_node, fv_off, fv_idx, nfv);
     return ORBX_OK;
 }
 

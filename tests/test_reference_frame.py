@@ -309,3 +309,42 @@ def test_reference_frame_built_on_the_cuda_extractor(w, h, nf, fx, bf, seed):
     m = orbx.ORBmatcher()
     n2, uR2, dep2 = m.ComputeStereoMatches(exL, exR, kl, dl, kr, dr, bf, float(np.float32(bf) / F.mb))
     assert n2 == n and uR2.tobytes() == uR.tobytes() and dep2.tobytes() == dep.tobytes()
+
+
+def _check_dropin_bow(libpath, tmp_path):
+    """Frame::ComputeBoW of the reference (Frame.cc:410-417) calling the drop-in ORBVocabulary::transform with its own DBoW2 members."""
+    (k1, d1), _ = scenes.frames(1002)
+    voc = scenes.synthetic_vocabulary(7, 10, 5, shallow_leaf_prob=0.0, desc_pool=d1)
+    path = str(tmp_path / "voc.txt")
+    _write_voc(path, voc, trailing_newline=True)                                                # as saveToTextFile leaves it
+    pv = RF.RefVocabulary(path, libpath=libpath)                                                # the drop-in loadFromTextFile
+    assert pv.size() == int((np.bincount(voc[2][1:], minlength=len(voc[2])) == 0).sum())
+    w, h = 640, 480
+    F = RF.RefFrame("mono", synth.rects(w, h, 1400), _K(w, h), np.zeros(4), bf=40.0, voc=pv, libpath=libpath)
+    (b, v), fv = F.compute_bow()
+    (ob, ovv), ofv = O.OracleVocabulary(*voc).transform(F.desc, 4)
+    assert np.array_equal(b, ob) and v.tobytes() == ovv.tobytes() and len(b) > 300
+    for x, y in zip(fv, ofv):
+        assert np.array_equal(x, y)
+    return F, (b, v), fv, path
+
+
+def test_reference_frame_compute_bow_on_the_drop_in_vocabulary_cpu(tmp_path):
+    if not RF.dropin_available(cpu=True):
+        pytest.skip("oracle/_ref/libframe_dropin_cpu.so is not built and the reference tree is not here")
+    F, bow, fv, path = _check_dropin_bow(RF.DROPIN_CPU_PATH, tmp_path)
+    # the same frame through the reference's own DBoW2 (libframe_ref.so): identical vectors
+    _write_voc(path, scenes.synthetic_vocabulary(7, 10, 5, shallow_leaf_prob=0.0, desc_pool=scenes.frames(1002)[0][1]))
+    F2 = RF.RefFrame("mono", synth.rects(640, 480, 1400), _K(640, 480), np.zeros(4), bf=40.0, voc=RF.RefVocabulary(path))
+    if F2.desc.tobytes() == F.desc.tobytes():                   # the reference extractor's tie-breaks follow the heap; usually the same set here
+        (b2, v2), fv2 = F2.compute_bow()
+        assert np.array_equal(bow[0], b2) and bow[1].tobytes() == v2.tobytes()
+        for x, y in zip(fv, fv2):
+            assert np.array_equal(x, y)
+
+
+@pytest.mark.gpu
+def test_reference_frame_compute_bow_on_the_cuda_vocabulary(tmp_path):
+    if not RF.dropin_available(cpu=False):
+        pytest.skip("oracle/_ref/libframe_dropin.so was not built (make -C oracle _ref_tests needs the reference tree)")
+    _check_dropin_bow(RF.DROPIN_PATH, tmp_path)
