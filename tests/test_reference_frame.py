@@ -61,7 +61,7 @@ def test_stereo_pipeline_of_the_cpu_baseline():
     F = RF.RefFrame("stereo", left, [435.2, 435.2, w * 0.5, h * 0.5], np.zeros(4), bf=47.9, im_right=right, nfeatures=1200)
     for _ in range(2):
         n, matched = p.run(left, right)
-        assert abs(n - F.N) <= 12 and abs(matched - int((F.u_right >= 0).sum())) <= 25 and matched > 100
+        assert abs(n - F.N) <= 40 and abs(matched - int((F.u_right >= 0).sum())) <= 60 and matched > 100
 
 
 # ---------------------------------------------------------------------------------------------- undistortion, bounds, RGB-D
