@@ -75,9 +75,12 @@ def lib(path=None):
         L.reff_frame_compute_bow.argtypes = [vp] * 7
         L.reff_voc_transform.restype = i
         L.reff_voc_transform.argtypes = [vp, vp, i, i, vp, vp, vp, vp, vp, vp]
-        if hasattr(L, "reff_voc_score"):
-            L.reff_voc_score.restype = d
-            L.reff_voc_score.argtypes = [vp, vp, vp, i, vp, vp, i]
+        L.reff_voc_score.restype = d
+        L.reff_voc_score.argtypes = [vp, vp, vp, i, vp, vp, i]
+        L.reff_voc_load_binary.restype = vp
+        L.reff_voc_load_binary.argtypes = [C.c_char_p]
+        if hasattr(L, "reff_voc_save_binary"):
+            L.reff_voc_save_binary.argtypes = [vp, C.c_char_p]
         L.reff_stereo_create.restype = vp
         L.reff_stereo_create.argtypes = [i, f, i, i, i, vp, f, f]
         L.reff_stereo_destroy.argtypes = [vp]
@@ -94,11 +97,15 @@ def _p(a):
 class RefVocabulary:
     """ORBVocabulary of the reference (DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>) loaded with its own loadFromTextFile."""
 
-    def __init__(self, path, libpath=None):
+    def __init__(self, path, libpath=None, binary=False):
         self.L = lib(libpath)
-        self.h = self.L.reff_voc_load_text(os.fsencode(path))
+        self.h = (self.L.reff_voc_load_binary if binary else self.L.reff_voc_load_text)(os.fsencode(path))
         if not self.h:
-            raise RuntimeError("loadFromTextFile failed: " + path)
+            raise RuntimeError("loadFrom%sFile failed: %s" % ("Binary" if binary else "Text", path))
+
+    def save_binary(self, path):
+        """DBoW2's saveToBinaryFile (the reference build only)."""
+        self.L.reff_voc_save_binary(self.h, os.fsencode(path))
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -260,7 +260,6 @@ int reff_voc_transform(reff_voc* v, const uint8_t* desc, int n, int levelsup, in
     *n_fv = nn;
     return nb;
 }
-#ifndef ORBX_FRAME_API_REAL_MAPPOINT     // the drop-in ORBVocabulary leaves scoring two vectors to DBoW2 (include/ORBVocabulary.h)
 // DBoW2's score between two BowVectors with the vocabulary's scoring object (TemplatedVocabulary::score, used by KeyFrameDatabase)
 double reff_voc_score(reff_voc* v, const int* id1, const double* val1, int n1, const int* id2, const double* val2, int n2)
 {
@@ -269,6 +268,19 @@ double reff_voc_score(reff_voc* v, const int* id1, const double* val1, int n1, c
     for (int i = 0; i < n2; i++) b[(DBoW2::WordId)id2[i]] = val2[i];
     return v->voc.score(a, b);
 }
+// loadFromBinaryFile (TemplatedVocabulary.h:1467-1511; System.cc:84)
+reff_voc* reff_voc_load_binary(const char* path)
+{
+    std::unique_ptr<reff_voc> v(new reff_voc);
+    try {
+        if (!v->voc.loadFromBinaryFile(path)) return NULL;
+    } catch (...) {
+        return NULL;
+    }
+    return v.release();
+}
+#ifndef ORBX_FRAME_API_REAL_MAPPOINT     // DBoW2 only: the drop-in vocabulary reads this format, it does not write it
+void reff_voc_save_binary(reff_voc* v, const char* path) { v->voc.saveToBinaryFile(path); }
 #endif
 
 }  // extern "C"

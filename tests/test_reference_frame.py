@@ -348,3 +348,43 @@ def test_reference_frame_compute_bow_on_the_cuda_vocabulary(tmp_path):
     if not RF.dropin_available(cpu=False):
         pytest.skip("oracle/_ref/libframe_dropin.so was not built (make -C oracle _ref_tests needs the reference tree)")
     _check_dropin_bow(RF.DROPIN_PATH, tmp_path)
+
+
+@pytest.mark.parametrize("scoring", [0, 1, 2, 3, 4, 5])
+def test_drop_in_vocabulary_score_and_binary_file_are_dbow2(tmp_path, scoring):
+    """score(v1, v2) (ScoringObject.cpp) and loadFromBinaryFile (TemplatedVocabulary.h:1467-1511) of include/ORBVocabulary.h against the
+    vendored DBoW2: the binary file is written by DBoW2's own saveToBinaryFile."""
+    if not RF.dropin_available(cpu=True):
+        pytest.skip("oracle/_ref/libframe_dropin_cpu.so is not built and the reference tree is not here")
+    (k1, d1), (k2, d2) = scenes.frames(1003)
+    voc = scenes.synthetic_vocabulary(11, 10, 4, shallow_leaf_prob=0.0, desc_pool=d1)
+    txt, binf = str(tmp_path / "voc.txt"), str(tmp_path / "voc.bin")
+    _write_voc(txt, voc, scoring, 0)
+    dbow = RF.RefVocabulary(txt)
+    dbow.save_binary(binf)
+    mine_txt = RF.RefVocabulary(txt, libpath=RF.DROPIN_CPU_PATH)
+    mine_bin = RF.RefVocabulary(binf, libpath=RF.DROPIN_CPU_PATH, binary=True)
+    dbow_bin = RF.RefVocabulary(binf, binary=True)
+    nwords = int((np.bincount(voc[2][1:], minlength=len(voc[2])) == 0).sum())
+    assert mine_txt.size() == mine_bin.size() == dbow.size() == nwords
+    assert dbow_bin.size() in (nwords, nwords + 1)           # DBoW2's reader files the last record twice (see include/ORBVocabulary.h)
+    # the binary format keeps the weights as float
+    k, L, parent, desc, weight = voc
+    ov32 = O.OracleVocabulary(k, L, parent, desc, weight.astype(np.float32).astype(np.float64), scoring, 0)
+    for feats in (d1, d2):
+        (b, v), fv = mine_bin.transform(feats, 4)
+        (rb, rv), rfv = dbow_bin.transform(feats, 4)
+        (ob, ovv), ofv = ov32.transform(feats, 4)
+        assert np.array_equal(b, ob) and v.tobytes() == ovv.tobytes() and np.array_equal(b, rb) and v.tobytes() == rv.tobytes()
+        for x, y, z in zip(fv, ofv, rfv):
+            assert np.array_equal(x, y) and np.array_equal(x, z)
+    # scores: the two frames against each other and themselves, both ways, and against an empty vector
+    va, vb = dbow.transform(d1, 4)[0], dbow.transform(d2, 4)[0]
+    empty = (np.zeros(0, np.int32), np.zeros(0, np.float64))
+    sub = (va[0][::3], va[1][::3])
+    seen = set()
+    for x, y in [(va, vb), (vb, va), (va, va), (va, sub), (sub, vb), (va, empty), (empty, vb)]:
+        r, m = dbow.score(x, y), mine_txt.score(x, y)
+        assert np.float64(r).tobytes() == np.float64(m).tobytes(), (scoring, r, m)
+        seen.add(round(r, 6))
+    assert len(seen) >= 3
