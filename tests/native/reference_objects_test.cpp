@@ -161,9 +161,9 @@ struct World {
                 o.push_back(p->isBad()); o.push_back(p->Observations()); o.push_back(id(p->GetReplaced()));
                 o.push_back(p->GetIndexInKeyFrame(KA)); o.push_back(p->GetIndexInKeyFrame(KB)); o.push_back(p->GetFound());
                 const cv::Mat d = p->GetDescriptor();                              // Replace recomputes it (MapPoint.cc:222)
-                int hsh = 0;
-                for (int k = 0; k < 32; k++) hsh = hsh * 31 + d.ptr<uint8_t>(0)[k];
-                o.push_back(hsh);
+                unsigned hsh = 0;
+                for (int k = 0; k < 32; k++) hsh = hsh * 31u + d.ptr<uint8_t>(0)[k];
+                o.push_back((int)(hsh & 0x7FFFFFFFu));
             }
         }
         return o;
