@@ -31,6 +31,7 @@ template <class FrameT> inline std::vector<uint8_t> occupied_with_observations(c
     for (size_t j = 0; j < o.size(); j++) o[j] = (F.mvpMapPoints[j] && F.mvpMapPoints[j]->Observations() > 0) ? 1 : 0;
     return o;
 }
+// For builds WITHOUT OpenCV (with it the templates below write the reference's cv::Mat expressions themselves).
 // Rows 0..2 of a 4x4 CV_32F pose, evaluated the way cv::Mat expressions evaluate them for 3x3 * 3x1 products:
 // A*b + c runs through gemm's small-matrix path (float products summed left to right, then (float)(t*1.0 + c*1.0) in double);
 // -A.t()*b runs through the general path (double accumulation, scaled by -1, rounded once).
@@ -93,10 +94,21 @@ int ORBmatcher::SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpM
 template <class FrameT>
 int ORBmatcher::SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono)
 {
+#ifdef ORBX_USE_OPENCV
+    // with OpenCV the reference's own expressions (:1340-1348, :1362-1363), so that every float is what the installed OpenCV makes of them
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat twc = -Rcw.t() * tcw;
+    const cv::Mat Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat tlcM = Rlw * twc + tlw;
+    const float tlc[3] = {tlcM.template at<float>(0), tlcM.template at<float>(1), tlcM.template at<float>(2)};
+#else
     const detail::Pose34 Tcw(CurrentFrame.mTcw), Tlw(LastFrame.mTcw);
     float twc[3], tlc[3];
     Tcw.centre(twc);                                                   // :1343
     Tlw.apply(twc, tlc);                                               // :1348
+#endif
     const bool bForward = tlc[2] > CurrentFrame.mb && !bMono;          // :1350-1351
     const bool bBackward = -tlc[2] > CurrentFrame.mb && !bMono;
     ProjectedPoints P;
@@ -107,9 +119,14 @@ int ORBmatcher::SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame
         if (!pMP) continue;
         if (LastFrame.mvbOutlier[i]) continue;
         const cv::Mat x3Dw = pMP->GetWorldPos();                       // 3x1 CV_32F
+#ifdef ORBX_USE_OPENCV
+        const cv::Mat x3DcM = Rcw * x3Dw + tcw;                        // :1363
+        const float x3Dc[3] = {x3DcM.template at<float>(0), x3DcM.template at<float>(1), x3DcM.template at<float>(2)};
+#else
         const float xw[3] = {x3Dw.at<float>(0, 0), x3Dw.at<float>(1, 0), x3Dw.at<float>(2, 0)};
         float x3Dc[3];
         Tcw.apply(xw, x3Dc);                                           // :1363
+#endif
         const float xc = x3Dc[0];
         const float yc = x3Dc[1];
         const float invzc = 1.0 / x3Dc[2];

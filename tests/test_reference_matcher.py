@@ -15,6 +15,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "orb_slam2v2-1_b200"))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 REFLIB = os.path.join(ROOT, "oracle", "_ref", "libmatcher_ref.so")
+# The test programs are compiled the way the reference's tree is (CMakeLists.txt:26-27: -O3 -march=native; x86-64-v3 here as for oracle/_ref): the
+# drop-in templates hold the reference's float expressions (fx*xc*invzc+cx, u-mbf*invzc ...), and whether g++ contracts them into fma must be the
+# same on both sides, as it is when a maintainer compiles the swapped header inside the reference's own build.  (Found by
+# tools/fuzz_reference_objects.py: at -O1 without FMA, 5 of 80 random scenes differed in one or two window-boundary cases.)
+REF_FLAGS = ["-O3", "-march=x86-64-v3"]
 
 
 def _reflib():
@@ -43,7 +48,7 @@ def _build(tmp_path, on_oracle=False):
         link = ["-L", str(tmp_path), "-lorbx_on_oracle", "-Wl,-rpath," + str(tmp_path)]
     else:
         link = ["-L", libdir, "-lorbx", "-Wl,-rpath," + libdir]
-    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-Werror", "-DORBX_USE_OPENCV", "-I", os.path.join(ROOT, "include"),
+    subprocess.check_call(["g++", "-std=c++11"] + REF_FLAGS + ["-Wall", "-Werror", "-DORBX_USE_OPENCV", "-I", os.path.join(ROOT, "include"),
                            "-I", os.path.join(ROOT, "oracle", "ref_shim"), "-I", os.path.join(ROOT, "oracle", "ref_shim", "slam"),
                            "-o", exe, os.path.join(ROOT, "tests", "native", "reference_matcher_test.cpp")] + link +
                           ["-L", refdir, "-lmatcher_ref", "-Wl,-rpath," + refdir])
@@ -121,7 +126,7 @@ def real_cpu_exe(tmp_path_factory):
                            "-o", str(tmp / "liborbx_on_oracle.so"), os.path.join(ROOT, "tests", "native", "orbx_on_oracle.cpp"),
                            "-L", oradir, "-lorb_oracle", "-Wl,-rpath," + oradir])
     exe = str(tmp / "refobjects_cpu")
-    subprocess.check_call(["g++", "-std=c++11", "-O1", "-Wall", "-DORBX_USE_OPENCV", "-Wno-overloaded-virtual", "-I", os.path.join(shim, "slam_full"), "-I", shim,
+    subprocess.check_call(["g++", "-std=c++11"] + REF_FLAGS + ["-Wall", "-DORBX_USE_OPENCV", "-Wno-overloaded-virtual", "-I", os.path.join(shim, "slam_full"), "-I", shim,
                            "-I", os.path.join(REF_TREE, "include"), "-I", REF_TREE, "-o", exe, os.path.join(ROOT, "tests", "native", "reference_objects_test.cpp"),
                            "-L", str(tmp), "-lorbx_on_oracle", "-Wl,-rpath," + str(tmp), "-L", os.path.join(oradir, "_ref"), "-lslam_ref",
                            "-Wl,-rpath," + os.path.join(oradir, "_ref")])
