@@ -156,3 +156,13 @@ def test_drop_in_headers_on_the_reference_s_real_objects(tmp_path, w, h, nf, see
     if not os.path.exists(REAL_EXE):
         pytest.skip("oracle/_ref/reference_objects_test was not built (make -C oracle _ref_tests needs the reference tree)")
     _run_real(REAL_EXE, tmp_path, w, h, nf, seed, dx, dy)
+
+
+@pytest.mark.gpu
+def test_drop_in_headers_on_real_objects_random_scenes():
+    """tools/fuzz_reference_objects.py with a fixed seed: six random scenes (kinds, sizes, feature counts 300-3000, shifts) through the CUDA
+    searches, on the reference's real objects (profiles/r02_fuzz_reference_objects_gpu.log holds this very run)."""
+    if not os.path.exists(REAL_EXE):
+        pytest.skip("oracle/_ref/reference_objects_test was not built (make -C oracle _ref_tests needs the reference tree)")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_reference_objects.py"), REAL_EXE, "6", "31"], capture_output=True, text=True)
+    assert r.returncode == 0 and "6 runs, 0 with a difference" in r.stdout, (r.stdout[-2000:], r.stderr[-2000:])
