@@ -1,6 +1,10 @@
 // core_ops.hpp -- CV SHIM FOR THE REFERENCE BUILD (test infrastructure, not product): the few CV_32F
 // matrix operations the reference's ORBmatcher.cc writes (products, sums, transposes, scalar scaling,
-// dot, L2 norm).  Evaluated eagerly; products, dot and norm accumulate in double like OpenCV's float paths.
+// dot, L2 norm).  Evaluated eagerly; products, dot and norm accumulate in double and round once.  Real OpenCV evaluates lazily: `A*b + c`
+// with a 3 x 3 A is ONE gemm whose small-matrix path sums float products and then forms (float)(t*1.0 + c*1.0) in double, so a projection
+// can differ from this shim's in the last bit.  That does not enter any comparison: wherever the reference's sources and the drop-in headers
+// are held against each other, both are compiled over this same algebra (and in a real build both sit on the same OpenCV) -- the drop-in
+// templates write the reference's own cv::Mat expressions (include/ORBmatcher_reference_api.inl).
 #pragma once
 
 namespace cv {
