@@ -1,6 +1,6 @@
 // ORBmatcher_reference_api.inl -- the searches of include/ORBmatcher.h under the REFERENCE'S OWN SIGNATURES
-// (kimwin2/ORB_SLAM2v2-1 include/ORBmatcher.h:47-82), so that call sites such as Tracking.cc:742-743, :907-911, :1012-1016,
-// :1336, LoopClosing.cc:249 compile unchanged.  Frame / KeyFrame / MapPoint are template parameters: this repository does not
+// (kimwin2/ORB_SLAM2v2-1 include/ORBmatcher.h:47-82), so that call sites such as Tracking.cc:742-743, :907-910, :1012-1034,
+// :1329-1336, :1502-1522, LoopClosing.cc:249-275 compile unchanged.  Frame / KeyFrame / MapPoint are template parameters: this repository does not
 // pull the SLAM object graph (Map, ROS messages) into the translation unit; the user's own headers supply the types.  Each
 // overload runs the reference's host-side skip tests while flattening the objects into the arrays of the FrameView overloads,
 // calls those (device windows + Hamming, host replay of the order-dependent bookkeeping), and writes the results back the way
@@ -62,7 +62,7 @@ struct Pose34 {
 };
 }  // namespace detail
 
-// ORBmatcher.cc:45-129 -- TrackLocalMap (call site Tracking.cc:1112-1116: matcher.SearchByProjection(mCurrentFrame, mvpLocalMapPoints, th))
+// ORBmatcher.cc:45-129 -- TrackLocalMap (call site Tracking.cc:1329-1336: matcher.SearchByProjection(mCurrentFrame, mvpLocalMapPoints, th))
 template <class FrameT, class MapPointT>
 int ORBmatcher::SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th)
 {
@@ -90,7 +90,7 @@ int ORBmatcher::SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpM
     return nmatches;
 }
 
-// ORBmatcher.cc:1330-1472 -- TrackWithMotionModel (call site Tracking.cc:907: matcher.SearchByProjection(mCurrentFrame, mLastFrame, th, mSensor == System::MONOCULAR))
+// ORBmatcher.cc:1330-1472 -- TrackWithMotionModel (call sites Tracking.cc:1028, :1034: matcher.SearchByProjection(mCurrentFrame, mLastFrame, th, mSensor == System::MONOCULAR))
 template <class FrameT>
 int ORBmatcher::SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono)
 {
@@ -154,7 +154,7 @@ int ORBmatcher::SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame
     return nmatches;
 }
 
-// ORBmatcher.cc:159-288 -- TrackReferenceKeyFrame / Relocalization (call sites Tracking.cc:742-743, :1329-1336)
+// ORBmatcher.cc:159-288 -- TrackReferenceKeyFrame / Relocalization (call sites Tracking.cc:907-910, :1502-1522)
 template <class KeyFrameT, class FrameT, class MapPointT>
 int ORBmatcher::SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches)
 {
@@ -173,7 +173,7 @@ int ORBmatcher::SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& 
     return nmatches;
 }
 
-// ORBmatcher.cc:522-655 -- loop closing (call site LoopClosing.cc:249)
+// ORBmatcher.cc:522-655 -- loop closing (call site LoopClosing.cc:249-275)
 template <class KeyFrameT, class MapPointT>
 int ORBmatcher::SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12)
 {
@@ -190,7 +190,7 @@ int ORBmatcher::SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPoi
     return nmatches;
 }
 
-// ORBmatcher.cc:405-520 -- monocular initialisation (call site Tracking.cc:598)
+// ORBmatcher.cc:405-520 -- monocular initialisation (call site Tracking.cc:742-743)
 template <class FrameT, class>
 int ORBmatcher::SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
                                         int windowSize)

@@ -78,8 +78,10 @@ public:
     long unsigned int mnId, mnFrameId;
     double mTimeStamp;
     float mfGridElementWidthInv, mfGridElementHeightInv;
-    long unsigned int mnTrackReferenceForFrame, mnFuseTargetForKF, mnBALocalForKF, mnBAFixedForKF, mnLoopQuery, mnRelocQuery;
-    int mnLoopWords, mnRelocWords;
+    long unsigned int mnTrackReferenceForFrame, mnFuseTargetForKF, mnBALocalForKF, mnBAFixedForKF, mnLoopQuery;
+    int mnLoopWords;
+    long unsigned int mnRelocQuery;
+    int mnRelocWords;
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<float> mvuRight, mvDepth;
     cv::Mat mDescriptors;

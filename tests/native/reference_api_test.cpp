@@ -87,7 +87,7 @@ static int run(int, char** argv)
     }
     const std::vector<MapPoint*> none(mCurrentFrame.N, static_cast<MapPoint*>(NULL));
 
-    // ---- Tracking.cc:1112-1116 (SearchLocalPoints): ORBmatcher matcher(0.8); matcher.SearchByProjection(mCurrentFrame, mvpLocalMapPoints, th);
+    // ---- Tracking.cc:1329-1336 (SearchLocalPoints): ORBmatcher matcher(0.8); matcher.SearchByProjection(mCurrentFrame, mvpLocalMapPoints, th);
     int nA = 0;
     {
         ORBmatcher matcher(0.8);
@@ -116,7 +116,7 @@ static int run(int, char** argv)
             CHECK(mCurrentFrame.mvpMapPoints[j] == (vn[j] >= 0 ? who[vn[j]] : static_cast<MapPoint*>(NULL)), "SearchByProjection(Frame, MapPoints): F.mvpMapPoints");
     }
 
-    // ---- Tracking.cc:905-911 (TrackWithMotionModel): ORBmatcher matcher(0.9,true); fill(NULL); matcher.SearchByProjection(mCurrentFrame,mLastFrame,th,mono)
+    // ---- Tracking.cc:1012-1028 (TrackWithMotionModel): ORBmatcher matcher(0.9,true); fill(NULL); matcher.SearchByProjection(mCurrentFrame,mLastFrame,th,mono)
     int nB[3] = {0, 0, 0};
     for (int k = 0; k < 3; k++) {
         ORBmatcher matcher(0.9, true);
@@ -139,7 +139,7 @@ static int run(int, char** argv)
     }
     CHECK(nB[0] != nB[2] || nB[1] != nB[2], "forward / backward level windows differ from the monocular one");
 
-    // ---- Tracking.cc:742-743 (TrackReferenceKeyFrame): ORBmatcher matcher(0.7,true); vector<MapPoint*> vpMapPointMatches;
+    // ---- Tracking.cc:907-910 (TrackReferenceKeyFrame): ORBmatcher matcher(0.7,true); vector<MapPoint*> vpMapPointMatches;
     //      int nmatches = matcher.SearchByBoW(mpReferenceKF,mCurrentFrame,vpMapPointMatches);
     KeyFrame kfA, kfB;
     KeyFrame* mpReferenceKF = &kfA;
@@ -163,7 +163,7 @@ static int run(int, char** argv)
             CHECK(vpMapPointMatches[j] == (vn[j] >= 0 ? kfA.mvpMapPoints[vn[j]] : static_cast<MapPoint*>(NULL)), "SearchByBoW(KF, F): vpMapPointMatches");
     }
 
-    // ---- LoopClosing.cc:249: int nmatches = matcher.SearchByBoW(mpCurrentKF,pKF,vvpMapPointMatches[i]);
+    // ---- LoopClosing.cc:275: int nmatches = matcher.SearchByBoW(mpCurrentKF,pKF,vvpMapPointMatches[i]);
     std::vector<MapPoint> storeB(mCurrentFrame.N);
     kfB.N = mCurrentFrame.N; kfB.mvKeysUn = mCurrentFrame.mvKeysUn; kfB.mDescriptors = mCurrentFrame.mDescriptors; kfB.mFeatVec = mCurrentFrame.mFeatVec;
     kfB.mnMaxX = w; kfB.mnMaxY = h;
@@ -188,7 +188,7 @@ static int run(int, char** argv)
             CHECK(vvpMapPointMatches[i][k] == (vn[k] >= 0 ? kfB.mvpMapPoints[vn[k]] : static_cast<MapPoint*>(NULL)), "SearchByBoW(KF, KF): vpMatches12");
     }
 
-    // ---- Tracking.cc:596-598 (MonocularInitialization): ORBmatcher matcher(0.9,true);
+    // ---- Tracking.cc:742-743 (MonocularInitialization): ORBmatcher matcher(0.9,true);
     //      int nmatches = matcher.SearchForInitialization(mInitialFrame,mCurrentFrame,mvbPrevMatched,mvIniMatches,100);
     int nE = 0;
     {

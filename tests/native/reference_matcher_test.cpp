@@ -311,7 +311,7 @@ static int run(char** argv)
         const float nn = co ? 0.9f : 0.7f;
         ORB_SLAM2::ORBmatcher mine(nn, checkOri);
 
-        // ---- SearchByProjection(Frame&, vpMapPoints, th)  (ORBmatcher.cc:45-129, Tracking.cc:1112-1116)
+        // ---- SearchByProjection(Frame&, vpMapPoints, th)  (ORBmatcher.cc:45-129, Tracking.cc:1329-1336)
         {
             std::vector<MapPoint*> local;
             for (int i = 0; i < FA.N; i++) {
@@ -335,7 +335,7 @@ static int run(char** argv)
                 CHECK(nr > FA.N / 8, "SearchByProjection(Frame, MapPoints): too few matches for a meaningful comparison");
             }
         }
-        // ---- SearchByProjection(CurrentFrame, LastFrame, th, bMono)  (:1330-1472, Tracking.cc:907)
+        // ---- SearchByProjection(CurrentFrame, LastFrame, th, bMono)  (:1330-1472, Tracking.cc:1012-1034)
         for (int variant = 0; variant < 4; variant++) {
             // the image shift as a camera translation at the common depth Z0; variants 2 / 3 add motion along z (forward / backward)
             const float tz = variant == 2 ? -0.3f : (variant == 3 ? 0.3f : 0.f);
@@ -354,7 +354,7 @@ static int run(char** argv)
             printf("SearchByProjection(Cur, Last) checkOri %d variant %d: %d matches, %d slots\n", co, variant, nr, assigned(R.mvpMapPoints));
             if (variant < 2) CHECK(nr > FA.N / 8, "SearchByProjection(CurrentFrame, LastFrame): too few matches");
         }
-        // ---- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (:159-288, Tracking.cc:742-743)
+        // ---- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (:159-288, Tracking.cc:907-910)
         KeyFrame KA, KB;
         fill_keyframe(KA, FA, w, h);
         fill_keyframe(KB, FB, w, h);
@@ -367,7 +367,7 @@ static int run(char** argv)
             printf("SearchByBoW(KF, F) checkOri %d: %d matches\n", co, nr);
             CHECK(nr > FA.N / 10, "SearchByBoW(KeyFrame, Frame): too few matches");
         }
-        // ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (:522-655, LoopClosing.cc:249)
+        // ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (:522-655, LoopClosing.cc:249-275)
         {
             std::vector<MapPoint*> vr, vm;
             const int nr = refm::SearchByBoW(nn, checkOri, &KA, &KB, vr);
@@ -376,7 +376,7 @@ static int run(char** argv)
             printf("SearchByBoW(KF, KF) checkOri %d: %d matches\n", co, nr);
             CHECK(nr > FA.N / 10, "SearchByBoW(KeyFrame, KeyFrame): too few matches");
         }
-        // ---- SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)  (:405-520, Tracking.cc:598)
+        // ---- SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)  (:405-520, Tracking.cc:742-743)
         {
             std::vector<cv::Point2f> pr(FA.N), pm;
             for (int i = 0; i < FA.N; i++) pr[i] = FA.mvKeysUn[i].pt;

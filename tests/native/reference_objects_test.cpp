@@ -180,7 +180,7 @@ static cv::Mat sim3(const cv::Mat& T, float s)          // [s R | s t; 0 1]
 static void tracking_searches(World& W, const Frame& FBbare, float dx, float dy, ref::ORBmatcher& theirs, ORB_SLAM2::ORBmatcher& mine, int co)
 {
     const Frame& FA = W.FA;
-    // ---- SearchByProjection(Frame&, vpMapPoints, th)  (ORBmatcher.cc:45-129, Tracking.cc:1112-1116)
+    // ---- SearchByProjection(Frame&, vpMapPoints, th)  (ORBmatcher.cc:45-129, Tracking.cc:1329-1336)
     {
         std::vector<MapPoint*> local;
         for (int i = 0; i < FA.N; i++) {
@@ -204,7 +204,7 @@ static void tracking_searches(World& W, const Frame& FBbare, float dx, float dy,
             CHECK(nr > FA.N / 8, "SearchByProjection(Frame, MapPoints): too few matches for a meaningful comparison");
         }
     }
-    // ---- SearchByProjection(CurrentFrame, LastFrame, th, bMono)  (:1330-1472, Tracking.cc:907)
+    // ---- SearchByProjection(CurrentFrame, LastFrame, th, bMono)  (:1330-1472, Tracking.cc:1012-1034)
     for (int variant = 0; variant < 4; variant++) {
         const float tz = variant == 2 ? -0.3f : (variant == 3 ? 0.3f : 0.f);       // variants 2 / 3: motion along z (forward / backward)
         const bool bMono = variant == 1;
@@ -221,7 +221,7 @@ static void tracking_searches(World& W, const Frame& FBbare, float dx, float dy,
         printf("SearchByProjection(Cur, Last) checkOri %d variant %d: %d matches, %d slots\n", co, variant, nr, assigned(R.mvpMapPoints));
         if (variant < 2) CHECK(nr > FA.N / 8, "SearchByProjection(CurrentFrame, LastFrame): too few matches");
     }
-    // ---- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (:159-288, Tracking.cc:742-743)
+    // ---- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)  (:159-288, Tracking.cc:907-910)
     {
         Frame R = FBbare, M = FBbare;
         std::vector<MapPoint*> vr, vm;
@@ -231,7 +231,7 @@ static void tracking_searches(World& W, const Frame& FBbare, float dx, float dy,
         printf("SearchByBoW(KF, F) checkOri %d: %d matches\n", co, nr);
         CHECK(nr > FA.N / 10, "SearchByBoW(KeyFrame, Frame): too few matches");
     }
-    // ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (:522-655, LoopClosing.cc:249)
+    // ---- SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)  (:522-655, LoopClosing.cc:249-275)
     {
         std::vector<MapPoint*> vr, vm;
         const int nr = theirs.SearchByBoW(W.KA, W.KB, vr);
@@ -240,7 +240,7 @@ static void tracking_searches(World& W, const Frame& FBbare, float dx, float dy,
         printf("SearchByBoW(KF, KF) checkOri %d: %d matches\n", co, nr);
         CHECK(nr > FA.N / 10, "SearchByBoW(KeyFrame, KeyFrame): too few matches");
     }
-    // ---- SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)  (:405-520, Tracking.cc:598)
+    // ---- SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)  (:405-520, Tracking.cc:742-743)
     {
         std::vector<cv::Point2f> pr(FA.N), pm;
         for (int i = 0; i < FA.N; i++) pr[i] = FA.mvKeysUn[i].pt;
@@ -382,8 +382,74 @@ static void map_side_searches(const Frame& FA0, const Frame& FB0, int w, int h, 
     }
 }
 
+// The reference's own call lines, verbatim (argument types included: `int th`, integer literals, a `float` scale), against the product's class:
+// compiled, never run.  Overload resolution must pick the reference-signature templates.
+static void call_sites_compile(Frame& mCurrentFrame, Frame& mLastFrame, Frame& mInitialFrame, KeyFrame* mpReferenceKF, KeyFrame* mpCurrentKF, KeyFrame* pKF,
+                               KeyFrame* pKF2, KeyFrame* mpCurrentKeyFrame, KeyFrame* pKFi, std::vector<MapPoint*>& mvpLocalMapPoints,
+                               std::vector<KeyFrame*>& vpCandidateKFs, bool bMonocular)
+{
+    std::vector<MapPoint*> vpMapPointMatches, vpFuseCandidates, mvpLoopMapPoints, mvpCurrentMatchedPoints, vpReplacePoints;
+    std::vector<std::vector<MapPoint*> > vvpMapPointMatches(1);
+    std::vector<cv::Point2f> mvbPrevMatched;
+    std::vector<int> mvIniMatches;
+    std::vector<std::pair<size_t, size_t> > vMatchedIndices;
+    std::set<MapPoint*> sFound;
+    cv::Mat F12, mScw, cvScw, R, t;
+    const float s = 1.f;
+    int i = 0;
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.9,true);                                                                                    // Tracking.cc:742
+        int nmatches = matcher.SearchForInitialization(mInitialFrame,mCurrentFrame,mvbPrevMatched,mvIniMatches,100);                // :743
+        (void)nmatches;
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.7,true);                                                                                    // :907
+        int nmatches = matcher.SearchByBoW(mpReferenceKF,mCurrentFrame,vpMapPointMatches);                                          // :910
+        (void)nmatches;
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.9,true);                                                                                    // :1012
+        int th = 15;                                                                                                                // :1023-1027
+        int nmatches = matcher.SearchByProjection(mCurrentFrame,mLastFrame,th,bMonocular);                                          // :1028
+        nmatches = matcher.SearchByProjection(mCurrentFrame,mLastFrame,2*th,bMonocular);                                            // :1034
+        (void)nmatches;
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.8);                                                                                         // :1329
+        int th = 1;                                                                                                                 // :1330
+        matcher.SearchByProjection(mCurrentFrame,mvpLocalMapPoints,th);                                                             // :1336
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher2(0.9,true);                                                                                   // :1541
+        int nadditional =matcher2.SearchByProjection(mCurrentFrame,vpCandidateKFs[i],sFound,10,100);                                // :1597
+        nadditional =matcher2.SearchByProjection(mCurrentFrame,vpCandidateKFs[i],sFound,3,64);                                      // :1611
+        (void)nadditional;
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.6,false);                                                                                   // LocalMapping.cc:223
+        matcher.SearchForTriangulation(mpCurrentKeyFrame,pKF2,F12,vMatchedIndices,false);                                           // :276
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher;                                                                                              // :491
+        matcher.Fuse(pKFi,vpMapPointMatches);                                                                                       // :497
+        matcher.Fuse(mpCurrentKeyFrame,vpFuseCandidates);                                                                           // :522
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.75,true);                                                                                   // LoopClosing.cc:249
+        int nmatches = matcher.SearchByBoW(mpCurrentKF,pKF,vvpMapPointMatches[i]);                                                  // :275
+        (void)nmatches;
+        matcher.SearchBySim3(mpCurrentKF,pKF,vpMapPointMatches,s,R,t,7.5);                                                          // :333
+        matcher.SearchByProjection(mpCurrentKF, mScw, mvpLoopMapPoints, mvpCurrentMatchedPoints,10);                                // :385
+    }
+    {
+        ORB_SLAM2::ORBmatcher matcher(0.8);                                                                                         // :598
+        matcher.Fuse(pKF,cvScw,mvpLoopMapPoints,4,vpReplacePoints);                                                                 // :608
+    }
+}
+
 static int run(char** argv)
 {
+    (void)&call_sites_compile;
     const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
     const float dx = (float)atof(argv[6]), dy = (float)atof(argv[7]);
     std::vector<uint8_t> ia = read_raw(argv[1], (size_t)w * h), ib = read_raw(argv[2], (size_t)w * h);

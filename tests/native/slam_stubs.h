@@ -1,6 +1,6 @@
 // slam_stubs.h -- stand-ins for the reference's Frame / KeyFrame / MapPoint (include/Frame.h, KeyFrame.h, MapPoint.h of
 // kimwin2/ORB_SLAM2v2-1) carrying exactly the members that src/ORBmatcher.cc reads or writes, under the reference's names.
-// Test infrastructure: lets the reference's call lines (Tracking.cc:742-743, :907, :1112, LoopClosing.cc:249) compile verbatim
+// Test infrastructure: lets the reference's call lines (Tracking.cc:742-743, :907-910, :1028, :1336, LoopClosing.cc:275) compile verbatim
 // against include/ORBmatcher.h without the SLAM object graph (Map, ROS messages).
 #pragma once
 #include <map>

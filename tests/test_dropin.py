@@ -46,8 +46,8 @@ def _build_native(tmp_path, source, name, opencv_shaped=False):
 @pytest.mark.parametrize("opencv_shaped", [False, True], ids=["bundled_shim", "opencv_shaped_headers"])
 @pytest.mark.parametrize("source", ["dropin_test.cpp", "reference_api_test.cpp"])
 def test_headers_compile_in_both_modes(tmp_path, source, opencv_shaped):
-    """include/ORBextractor.h and include/ORBmatcher.h -- with the reference's call lines of Tracking.cc:742-743, :907, :1112,
-    :598 and LoopClosing.cc:249 written verbatim in reference_api_test.cpp -- compile and link with the bundled cv shim and in
+    """include/ORBextractor.h and include/ORBmatcher.h -- with the reference's call lines of Tracking.cc:742-743, :910, :1028,
+    :1336 and LoopClosing.cc:275 written verbatim in reference_api_test.cpp -- compile and link with the bundled cv shim and in
     the ORBX_USE_OPENCV branch."""
     _build_native(tmp_path, source, "t_" + source[:-4], opencv_shaped)
 
