@@ -4,7 +4,7 @@
 // they lie over the cv shim; KeyFrame / Frame / Map / ServerMapPoint / the boost archives are stand-ins (ref_shim/mappoint/MapPoint.h,
 // ref_shim/slam/slam_objects.h), namespace renamed to ORB_SLAM2_REFM.  This file builds a MapPoint through the reference's own
 // constructor, adds observations with the reference's AddObservation and calls the reference's ComputeDistinctiveDescriptors
-// (MapPoint.cc:252-312), UpdateNormalAndDepth (:331-383), Get{Min,Max}DistanceInvariance (:385-395) and PredictScale (:397-429).
+// (MapPoint.cc:252-312), UpdateNormalAndDepth (:340-383), Get{Min,Max}DistanceInvariance (:385-395) and PredictScale (:397-429).
 #include <opencv2/core/core.hpp>
 #include "MapPoint.h"
 #include "ORBmatcher.h"

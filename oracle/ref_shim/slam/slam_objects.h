@@ -79,7 +79,7 @@ public:
 #endif  // ORBX_REAL_MAPPOINT
 
 // the 64 x 48 bucket grid over the undistorted keypoints: Frame::AssignFeaturesToGrid / PosInGrid (Frame.cc:230-245, :397-407),
-// KeyFrame copies it (KeyFrame.cc:41-58)
+// KeyFrame copies it (KeyFrame.cc:31-57)
 struct FeatureGrid {
     float minX, minY, maxX, maxY, invW, invH;
     std::vector<size_t> cell[FRAME_GRID_COLS][FRAME_GRID_ROWS];
@@ -121,9 +121,9 @@ public:
                  mfLogScaleFactor(std::log(1.2f)), mnMinX(0), mnMinY(0), mnMaxX(0), mnMaxY(0) {}
     long unsigned int mnId, mnFrameId;
     bool bad;
-    bool isBad() { return bad; }                                                // KeyFrame.cc:563-567
-    void EraseMapPointMatch(const size_t& idx) { mvpMapPoints[idx] = static_cast<MapPoint*>(NULL); }          // KeyFrame.cc:213-217
-    void ReplaceMapPointMatch(const size_t& idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }                  // KeyFrame.cc:228-231
+    bool isBad() { return bad; }                                                // KeyFrame.cc:548-552
+    void EraseMapPointMatch(const size_t& idx) { mvpMapPoints[idx] = static_cast<MapPoint*>(NULL); }          // KeyFrame.cc:217-221
+    void ReplaceMapPointMatch(const size_t& idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }                  // KeyFrame.cc:231-234
     int N;
     float fx, fy, cx, cy, invfx, invfy, mbf, mb, mThDepth;
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
@@ -145,14 +145,14 @@ public:
     }
     MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
     void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }
-    cv::Mat GetRotation() { return Tcw.rowRange(0, 3).colRange(0, 3).clone(); }       // KeyFrame.cc:160-170
+    cv::Mat GetRotation() { return Tcw.rowRange(0, 3).colRange(0, 3).clone(); }       // KeyFrame.cc:111-121
     cv::Mat GetTranslation() { return Tcw.rowRange(0, 3).col(3).clone(); }
     cv::Mat GetCameraCenter() { return Ow.clone(); }
     bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }      // KeyFrame.cc:613-616
     std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r) const { return grid.query(mvKeysUn, x, y, r, false, -1, -1); }
 
     std::vector<MapPoint*> mvpMapPoints;
-    cv::Mat Tcw, Ow;           // 4 x 4 and 3 x 1 CV_32F; SetPose (KeyFrame.cc:129-146) computes Ow = -Rcw.t() * tcw
+    cv::Mat Tcw, Ow;           // 4 x 4 and 3 x 1 CV_32F; SetPose (KeyFrame.cc:70-84) computes Ow = -Rcw.t() * tcw
     FeatureGrid grid;
 };
 

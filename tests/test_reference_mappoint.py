@@ -72,7 +72,7 @@ def test_compute_distinctive_descriptors_is_the_reference():
 
 
 def test_normal_depth_and_predict_scale_of_the_stand_ins_are_the_reference():
-    """UpdateNormalAndDepth (MapPoint.cc:331-383), GetMin/MaxDistanceInvariance (:385-395), PredictScale (:397-429): what the stand-in
+    """UpdateNormalAndDepth (MapPoint.cc:340-383), GetMin/MaxDistanceInvariance (:385-395), PredictScale (:397-429): what the stand-in
     MapPoint of ref_shim/slam/slam_objects.h restates (0.8 f * min, 1.2 f * max, ceil(log(max / d) / logScaleFactor) clamped)."""
     L = _lib()
     rng = np.random.default_rng(22)
