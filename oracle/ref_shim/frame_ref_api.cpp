@@ -9,7 +9,7 @@
 // GetFeaturesInArea, ComputeStereoMatches, ComputeStereoFromRGBD, isInFrustum, ComputeBoW, UnprojectStereo -- is the reference's code.
 //
 // The stereo constructor (Frame.cc:61-117) calls ComputeStereoMatches() BEFORE it sets mb (:114), so the stock build reads an
-// uninitialised float as minZ (:510-512).  kind 1 below therefore builds the left side through the monocular constructor (which sets mb),
+// uninitialised float as minZ (:511-513).  kind 1 below therefore builds the left side through the monocular constructor (which sets mb),
 // extracts the right image with the second extractor exactly as ExtractORB(1, imRight) does (:247-253), and then calls the public
 // ComputeStereoMatches(): the same statements in the same order, with mb defined.
 #include <opencv2/core/core.hpp>
@@ -43,7 +43,7 @@ extern "C" {
 
 // kind: 0 = monocular constructor (Frame.cc:174-228), 1 = stereo (see the note above), 2 = RGB-D constructor (:119-171; depth: h x w floats).
 // K4 = (fx, fy, cx, cy); dist: 4 or 5 coefficients (k1 k2 p1 p2 [k3]); voc may be null.  The static "first frame" state is reset, so every
-// frame computes its own image bounds (Frame::mbInitialComputations, :93-110).
+// frame computes its own image bounds (Frame::mbInitialComputations, :97-112).
 reff_frame* reff_frame_create(int kind, const uint8_t* im, const uint8_t* im_right, const float* depth, int w, int h, int nfeatures, float scaleFactor,
                               int nlevels, int iniTh, int minTh, const float* K4, const float* dist, int ndist, float bf, float thDepth, reff_voc* voc)
 {

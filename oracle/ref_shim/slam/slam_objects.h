@@ -86,7 +86,7 @@ struct FeatureGrid {
     void build(const std::vector<cv::KeyPoint>& keysUn, float mnMinX, float mnMaxX, float mnMinY, float mnMaxY)
     {
         minX = mnMinX; maxX = mnMaxX; minY = mnMinY; maxY = mnMaxY;
-        invW = (float)FRAME_GRID_COLS / (maxX - minX);                          // Frame.cc:99-100
+        invW = (float)FRAME_GRID_COLS / (maxX - minX);                          // Frame.cc:101-102
         invH = (float)FRAME_GRID_ROWS / (maxY - minY);
         for (int i = 0; i < FRAME_GRID_COLS; i++) for (int j = 0; j < FRAME_GRID_ROWS; j++) cell[i][j].clear();
         for (size_t i = 0; i < keysUn.size(); i++) {

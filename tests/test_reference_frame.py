@@ -34,9 +34,9 @@ def test_compute_stereo_matches_is_the_reference(w, h, nf, fx, bf, seed):
     left, right = synth.stereo_rects(w, h, seed)[:2]
     F = RF.RefFrame("stereo", left, _K(w, h, fx, fx), np.zeros(4), bf=bf, im_right=right, nfeatures=nf)
     assert F.N > nf // 2 and len(F.keys_right) > nf // 2
-    assert F.mb == np.float32(np.float32(bf) / np.float32(fx))                                  # Frame.cc:224
+    assert F.mb == np.float32(np.float32(bf) / np.float32(fx))                                  # Frame.cc:225
     n, uR, dep = O.stereo_matches(F.keys, F.desc, F.keys_right, F.desc_right, F.pyramid(0), F.pyramid(1), F.sf, F.isf, bf,
-                                  float(np.float32(bf) / F.mb))                                 # minZ = mb, maxD = mbf / minZ (:510-512)
+                                  float(np.float32(bf) / F.mb))                                 # minZ = mb, maxD = mbf / minZ (:511-513)
     assert uR.tobytes() == F.u_right.tobytes() and dep.tobytes() == F.depth_out.tobytes()
     assert n == int((F.u_right >= 0).sum())
     assert n > 40                                                                               # not vacuous
@@ -89,7 +89,7 @@ def test_rgbd_frame_glue_is_the_reference(name, K4, dist):
     uR, dep = O.stereo_from_rgbd(F.keys, F.keys_un, depth, bf)
     assert uR.tobytes() == F.u_right.tobytes() and dep.tobytes() == F.depth_out.tobytes()
     assert 0 < int((dep > 0).sum()) < F.N
-    # grid scale (Frame.cc:156-157)
+    # grid scale (Frame.cc:155-156)
     assert F.grid_inv[0] == np.float32(64) / (F.bounds[1] - F.bounds[0]) and F.grid_inv[1] == np.float32(48) / (F.bounds[3] - F.bounds[2])
 
 
