@@ -34,7 +34,7 @@ public:
     ORBVocabulary(const ORBVocabulary&) = delete;
     ORBVocabulary& operator=(const ORBVocabulary&) = delete;
 
-    // Same text format and return convention as the reference (System.cc:68-76 checks the bool).
+    // Same text format and return convention as the reference (System.cc:79-92 checks the bool).
     bool loadFromTextFile(const std::string& filename)
     {
         std::ifstream f(filename.c_str());
